@@ -1,0 +1,621 @@
+// See tcp_transport.h.
+#include "tcp_transport.h"
+
+#include <arpa/inet.h>
+#include <errno.h>
+#include <fcntl.h>
+#include <netdb.h>
+#include <netinet/in.h>
+#include <netinet/tcp.h>
+#include <poll.h>
+#include <signal.h>
+#include <sys/socket.h>
+#include <unistd.h>
+
+#include <cstring>
+#include <stdexcept>
+#include <thread>
+
+#include "logging.h"
+
+namespace aar {
+namespace {
+
+using Clock = std::chrono::steady_clock;
+
+struct Writer {
+  std::string b;
+  template <class T>
+  void pod(T v) { b.append(reinterpret_cast<const char*>(&v), sizeof(T)); }
+  void str(const std::string& s) {
+    pod<uint32_t>((uint32_t)s.size());
+    b += s;
+  }
+  void floats(const std::vector<float>& v) {
+    pod<uint32_t>((uint32_t)v.size());
+    b.append(reinterpret_cast<const char*>(v.data()), v.size() * sizeof(float));
+  }
+  std::string frame(uint8_t type) {
+    std::string f;
+    uint32_t len = (uint32_t)b.size() + 1;
+    f.append(reinterpret_cast<const char*>(&len), 4);
+    f.push_back((char)type);
+    f += b;
+    return f;
+  }
+};
+
+struct Reader {
+  const std::string& b;
+  size_t i;
+  explicit Reader(const std::string& s, size_t start = 0) : b(s), i(start) {}
+  template <class T>
+  T pod() {
+    if (i + sizeof(T) > b.size()) throw std::runtime_error("wire: truncated frame");
+    T v;
+    std::memcpy(&v, b.data() + i, sizeof(T));
+    i += sizeof(T);
+    return v;
+  }
+  std::string str() {
+    uint32_t n = pod<uint32_t>();
+    if (i + n > b.size()) throw std::runtime_error("wire: truncated string");
+    std::string s = b.substr(i, n);
+    i += n;
+    return s;
+  }
+  std::vector<float> floats() {
+    uint32_t n = pod<uint32_t>();
+    if (i + (size_t)n * 4 > b.size()) throw std::runtime_error("wire: truncated vector");
+    std::vector<float> v(n);
+    std::memcpy(v.data(), b.data() + i, (size_t)n * 4);
+    i += (size_t)n * 4;
+    return v;
+  }
+};
+
+void setNonBlocking(int fd) {
+  int fl = fcntl(fd, F_GETFL, 0);
+  fcntl(fd, F_SETFL, fl | O_NONBLOCK);
+  int one = 1;
+  setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof one);
+}
+
+int listenOn(const std::string& host, int port, int* boundPort) {
+  int fd = socket(AF_INET, SOCK_STREAM, 0);
+  if (fd < 0) throw std::runtime_error("socket() failed");
+  int one = 1;
+  setsockopt(fd, SOL_SOCKET, SO_REUSEADDR, &one, sizeof one);
+  sockaddr_in a{};
+  a.sin_family = AF_INET;
+  a.sin_port = htons((uint16_t)port);
+  if (inet_pton(AF_INET, host.c_str(), &a.sin_addr) != 1) a.sin_addr.s_addr = htonl(INADDR_LOOPBACK);
+  if (bind(fd, (sockaddr*)&a, sizeof a) != 0) {
+    close(fd);
+    throw std::runtime_error("bind(" + host + ":" + std::to_string(port) + ") failed: " + strerror(errno));
+  }
+  if (listen(fd, 128) != 0) {
+    close(fd);
+    throw std::runtime_error("listen() failed");
+  }
+  socklen_t len = sizeof a;
+  getsockname(fd, (sockaddr*)&a, &len);
+  *boundPort = ntohs(a.sin_port);
+  setNonBlocking(fd);
+  return fd;
+}
+
+int connectTo(const std::string& host, int port, double timeoutSec) {
+  auto deadline = Clock::now() + std::chrono::duration<double>(timeoutSec);
+  for (;;) {
+    int fd = socket(AF_INET, SOCK_STREAM, 0);
+    if (fd < 0) throw std::runtime_error("socket() failed");
+    sockaddr_in a{};
+    a.sin_family = AF_INET;
+    a.sin_port = htons((uint16_t)port);
+    if (inet_pton(AF_INET, host.c_str(), &a.sin_addr) != 1) a.sin_addr.s_addr = htonl(INADDR_LOOPBACK);
+    if (connect(fd, (sockaddr*)&a, sizeof a) == 0) {
+      setNonBlocking(fd);
+      return fd;
+    }
+    close(fd);
+    if (Clock::now() > deadline) throw std::runtime_error("connect(" + host + ":" + std::to_string(port) + ") timed out: " + strerror(errno));
+    std::this_thread::sleep_for(std::chrono::milliseconds(50));
+  }
+}
+
+struct IgnoreSigpipe {
+  IgnoreSigpipe() { signal(SIGPIPE, SIG_IGN); }
+} ignoreSigpipe;
+
+}  // namespace
+
+class Connection {
+ public:
+  explicit Connection(int fd) : fd_(fd) {}
+  ~Connection() {
+    if (fd_ >= 0) close(fd_);
+  }
+  int fd() const { return fd_; }
+  bool open() const { return fd_ >= 0; }
+  bool wantsWrite() const { return !out_.empty(); }
+  void queue(const std::string& frame) {
+    out_ += frame;
+    flush();
+  }
+  // false when the peer closed or an error occurred
+  bool flush() {
+    while (!out_.empty()) {
+      ssize_t n = ::send(fd_, out_.data(), out_.size(), MSG_NOSIGNAL);
+      if (n > 0) {
+        out_.erase(0, (size_t)n);
+      } else if (n < 0 && (errno == EAGAIN || errno == EWOULDBLOCK)) {
+        return true;
+      } else if (n < 0 && errno == EINTR) {
+        continue;
+      } else {
+        return false;
+      }
+    }
+    return true;
+  }
+  bool readAvailable() {
+    char buf[65536];
+    for (;;) {
+      ssize_t n = ::recv(fd_, buf, sizeof buf, 0);
+      if (n > 0) {
+        in_.append(buf, (size_t)n);
+      } else if (n == 0) {
+        return false;
+      } else if (errno == EAGAIN || errno == EWOULDBLOCK) {
+        return true;
+      } else if (errno == EINTR) {
+        continue;
+      } else {
+        return false;
+      }
+    }
+  }
+  // Pops one complete frame body (type byte + payload).
+  bool next(std::string& body) {
+    if (in_.size() - pos_ < 4) {
+      compact();
+      return false;
+    }
+    uint32_t len;
+    std::memcpy(&len, in_.data() + pos_, 4);
+    if (in_.size() - pos_ - 4 < len) {
+      compact();
+      return false;
+    }
+    body.assign(in_, pos_ + 4, len);
+    pos_ += 4 + len;
+    return true;
+  }
+  // Blocking drain (used before close so queued frames are not lost).
+  void drain(double sec) {
+    auto deadline = Clock::now() + std::chrono::duration<double>(sec);
+    while (!out_.empty() && Clock::now() < deadline) {
+      pollfd p{fd_, POLLOUT, 0};
+      ::poll(&p, 1, 20);
+      if (!flush()) return;
+    }
+  }
+  Clock::time_point lastSeen = Clock::now();
+
+ private:
+  void compact() {
+    if (pos_ > (1u << 20) || pos_ == in_.size()) {
+      in_.erase(0, pos_);
+      pos_ = 0;
+    }
+  }
+  int fd_;
+  std::string in_, out_;
+  size_t pos_ = 0;
+};
+
+namespace wire {
+
+std::string encode(const Message& m, const std::map<int, Endpoint>* endpoints) {
+  Writer w;
+  switch (m.index()) {
+    case 0: {
+      const auto& i = std::get<InitWorkers>(m);
+      w.pod<int32_t>(i.destId);
+      w.pod<float>(i.thReduce);
+      w.pod<float>(i.thComplete);
+      w.pod<int32_t>(i.maxLag);
+      w.pod<int32_t>(i.dataSize);
+      w.pod<int32_t>(i.maxChunkSize);
+      w.pod<int32_t>(i.generation);
+      w.pod<uint32_t>((uint32_t)i.workers.size());
+      for (auto& kv : i.workers) {
+        w.pod<int32_t>(kv.first);
+        Endpoint e;
+        if (endpoints) {
+          auto it = endpoints->find(kv.first);
+          if (it != endpoints->end()) e = it->second;
+        }
+        w.str(e.host);
+        w.pod<int32_t>(e.port);
+      }
+      return w.frame(Init);
+    }
+    case 1:
+      w.pod<int32_t>(std::get<StartAllreduce>(m).round);
+      w.pod<int32_t>(std::get<StartAllreduce>(m).generation);
+      return w.frame(Start);
+    case 2: {
+      const auto& s = std::get<ScatterBlock>(m);
+      w.pod<int32_t>(s.srcId);
+      w.pod<int32_t>(s.destId);
+      w.pod<int32_t>(s.chunkId);
+      w.pod<int32_t>(s.round);
+      w.pod<int32_t>(s.generation);
+      w.floats(s.value);
+      return w.frame(Scatter);
+    }
+    case 3: {
+      const auto& r = std::get<ReduceBlock>(m);
+      w.pod<int32_t>(r.srcId);
+      w.pod<int32_t>(r.destId);
+      w.pod<int32_t>(r.chunkId);
+      w.pod<int32_t>(r.round);
+      w.pod<int32_t>(r.count);
+      w.pod<int32_t>(r.generation);
+      w.floats(r.value);
+      return w.frame(Reduce);
+    }
+    default: {
+      const auto& c = std::get<CompleteAllreduce>(m);
+      w.pod<int32_t>(c.srcId);
+      w.pod<int32_t>(c.round);
+      w.pod<int32_t>(c.generation);
+      return w.frame(Complete);
+    }
+  }
+}
+
+std::string encodeJoin(const std::string& role, const Endpoint& e) {
+  Writer w;
+  w.str(role);
+  w.str(e.host);
+  w.pod<int32_t>(e.port);
+  return w.frame(Join);
+}
+
+std::string encodeSimple(Type t, int32_t arg) {
+  Writer w;
+  w.pod<int32_t>(arg);
+  return w.frame(t);
+}
+
+}  // namespace wire
+
+namespace {
+
+// Decodes a frame body into a Message. Returns false for non-message frames (join/heartbeat/...).
+bool decode(const std::string& body, Message& out, std::map<int, Endpoint>* endpoints) {
+  if (body.empty()) return false;
+  Reader r(body, 1);
+  switch ((uint8_t)body[0]) {
+    case wire::Init: {
+      InitWorkers i;
+      i.destId = r.pod<int32_t>();
+      i.thReduce = r.pod<float>();
+      i.thComplete = r.pod<float>();
+      i.maxLag = r.pod<int32_t>();
+      i.dataSize = r.pod<int32_t>();
+      i.maxChunkSize = r.pod<int32_t>();
+      i.generation = r.pod<int32_t>();
+      uint32_t n = r.pod<uint32_t>();
+      if (endpoints) endpoints->clear();
+      for (uint32_t k = 0; k < n; ++k) {
+        int id = r.pod<int32_t>();
+        Endpoint e;
+        e.host = r.str();
+        e.port = r.pod<int32_t>();
+        i.workers[id] = id;  // on a worker node the address of peer `id` is its id
+        if (endpoints) (*endpoints)[id] = e;
+      }
+      i.master = WorkerNode::kMaster;
+      out = std::move(i);
+      return true;
+    }
+    case wire::Start:
+    {
+      StartAllreduce st;
+      st.round = r.pod<int32_t>();
+      st.generation = r.pod<int32_t>();
+      out = st;
+    }
+      return true;
+    case wire::Scatter: {
+      ScatterBlock s;
+      s.srcId = r.pod<int32_t>();
+      s.destId = r.pod<int32_t>();
+      s.chunkId = r.pod<int32_t>();
+      s.round = r.pod<int32_t>();
+      s.generation = r.pod<int32_t>();
+      s.value = r.floats();
+      out = std::move(s);
+      return true;
+    }
+    case wire::Reduce: {
+      ReduceBlock b;
+      b.srcId = r.pod<int32_t>();
+      b.destId = r.pod<int32_t>();
+      b.chunkId = r.pod<int32_t>();
+      b.round = r.pod<int32_t>();
+      b.count = r.pod<int32_t>();
+      b.generation = r.pod<int32_t>();
+      b.value = r.floats();
+      out = std::move(b);
+      return true;
+    }
+    case wire::Complete: {
+      CompleteAllreduce c;
+      c.srcId = r.pod<int32_t>();
+      c.round = r.pod<int32_t>();
+      c.generation = r.pod<int32_t>();
+      out = c;
+      return true;
+    }
+    default:
+      return false;
+  }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ MasterNode
+
+struct MasterNode::Member {
+  std::unique_ptr<Connection> conn;
+  std::string role;
+  Endpoint data;
+  bool joined = false;
+};
+
+MasterNode::MasterNode(MasterConfig cfg, const std::string& host, int port, double autoDownAfterMs)
+    : cfg_(cfg), autoDownAfterMs_(autoDownAfterMs) {
+  listenFd_ = listenOn(host, port, &port_);
+  master_ = std::make_unique<Master>(cfg_, this, 0);
+  AAR_INFO("master: listening on %s:%d (totalWorkers=%d dataSize=%d maxChunkSize=%d)", host.c_str(), port_, cfg.totalWorkers, cfg.dataSize,
+           cfg.maxChunkSize);
+}
+
+MasterNode::~MasterNode() {
+  for (auto& kv : members_)
+    if (kv.second->conn) kv.second->conn->drain(0.5);
+  if (listenFd_ >= 0) close(listenFd_);
+}
+
+void MasterNode::acceptAll() {
+  for (;;) {
+    int fd = accept(listenFd_, nullptr, nullptr);
+    if (fd < 0) return;
+    setNonBlocking(fd);
+    auto m = std::make_unique<Member>();
+    m->conn = std::make_unique<Connection>(fd);
+    members_[nextAddr_++] = std::move(m);
+  }
+}
+
+void MasterNode::dropMember(Address a, const char* why) {
+  auto it = members_.find(a);
+  if (it == members_.end()) return;
+  AAR_INFO("master: member %ld down (%s)", (long)a, why);
+  bool wasWorker = it->second->joined && it->second->role == "worker";
+  members_.erase(it);
+  if (wasWorker) master_->terminated(a);
+}
+
+void MasterNode::send(Address to, Message msg) {
+  auto it = members_.find(to);
+  if (it == members_.end()) return;  // dead letter
+  std::map<int, Endpoint> eps;
+  if (std::holds_alternative<InitWorkers>(msg)) {
+    for (auto& kv : std::get<InitWorkers>(msg).workers) {
+      auto mt = members_.find(kv.second);
+      if (mt != members_.end()) eps[kv.first] = mt->second->data;
+    }
+  }
+  it->second->conn->queue(wire::encode(msg, &eps));
+}
+
+int MasterNode::poll(int timeoutMs) {
+  std::vector<pollfd> fds;
+  std::vector<Address> addrs;
+  fds.push_back({listenFd_, POLLIN, 0});
+  for (auto& kv : members_) {
+    short ev = POLLIN;
+    if (kv.second->conn->wantsWrite()) ev |= POLLOUT;
+    fds.push_back({kv.second->conn->fd(), ev, 0});
+    addrs.push_back(kv.first);
+  }
+  int rc = ::poll(fds.data(), fds.size(), timeoutMs);
+  int handled = 0;
+  if (rc > 0) {
+    if (fds[0].revents & POLLIN) acceptAll();
+    for (size_t k = 1; k < fds.size(); ++k) {
+      Address a = addrs[k - 1];
+      auto it = members_.find(a);
+      if (it == members_.end()) continue;
+      Member& m = *it->second;
+      bool alive = true;
+      if (fds[k].revents & POLLOUT) alive = m.conn->flush();
+      if (alive && (fds[k].revents & (POLLIN | POLLHUP | POLLERR))) alive = m.conn->readAvailable();
+      std::string body;
+      while (m.conn->next(body)) {
+        ++handled;
+        m.conn->lastSeen = Clock::now();
+        uint8_t type = (uint8_t)body[0];
+        if (type == wire::Join) {
+          Reader r(body, 1);
+          m.role = r.str();
+          m.data.host = r.str();
+          m.data.port = r.pod<int32_t>();
+          m.joined = true;
+          master_->memberUp(a, m.role);
+        } else if (type == wire::Heartbeat) {
+          // lastSeen already refreshed
+        } else {
+          Message msg;
+          if (decode(body, msg, nullptr)) master_->receive(msg);
+        }
+        if (members_.find(a) == members_.end()) break;
+      }
+      if (!alive) dropMember(a, "connection closed");
+    }
+  }
+  // phi-accrual stand-in: a fixed silence window (application.conf:20 auto-down-unreachable-after)
+  auto now = Clock::now();
+  std::vector<Address> dead;
+  for (auto& kv : members_)
+    if (kv.second->joined && std::chrono::duration<double, std::milli>(now - kv.second->conn->lastSeen).count() > autoDownAfterMs_) dead.push_back(kv.first);
+  for (Address a : dead) dropMember(a, "unreachable");
+  return handled;
+}
+
+void MasterNode::broadcastShutdown() {
+  for (auto& kv : members_) {
+    kv.second->conn->queue(wire::encodeSimple(wire::Shutdown));
+    kv.second->conn->drain(1.0);
+  }
+}
+
+bool MasterNode::run(double timeoutSec) {
+  auto deadline = Clock::now() + std::chrono::duration<double>(timeoutSec);
+  while (!master_->finished() && Clock::now() < deadline) poll(50);
+  bool ok = master_->finished();
+  broadcastShutdown();
+  return ok;
+}
+
+// ------------------------------------------------------------------ WorkerNode
+
+WorkerNode::WorkerNode(const std::string& masterHost, int masterPort, const std::string& listenHost, int listenPort, double heartbeatMs,
+                       const std::string& role)
+    : heartbeatMs_(heartbeatMs), lastBeat_(Clock::now()) {
+  listenFd_ = listenOn(listenHost, listenPort, &listenPort_);
+  masterConn_ = std::make_unique<Connection>(connectTo(masterHost, masterPort, 30.0));
+  masterConn_->queue(wire::encodeJoin(role, Endpoint{listenHost, listenPort_}));
+}
+
+WorkerNode::~WorkerNode() {
+  if (masterConn_) masterConn_->drain(0.5);
+  for (auto& kv : outPeers_) kv.second->drain(0.5);
+  if (listenFd_ >= 0) close(listenFd_);
+}
+
+Connection* WorkerNode::peer(int id) {
+  auto it = outPeers_.find(id);
+  if (it != outPeers_.end()) return it->second.get();
+  auto ep = endpoints_.find(id);
+  if (ep == endpoints_.end()) return nullptr;
+  auto c = std::make_unique<Connection>(connectTo(ep->second.host, ep->second.port, 10.0));
+  Connection* raw = c.get();
+  outPeers_[id] = std::move(c);
+  return raw;
+}
+
+void WorkerNode::send(Address to, Message msg) {
+  if (to == kMaster) {
+    if (masterConn_) masterConn_->queue(wire::encode(msg));
+    return;
+  }
+  Connection* c = peer((int)to);
+  if (!c) return;  // dead letter
+  c->queue(wire::encode(msg));
+}
+
+void WorkerNode::dispatch(const std::string& body) {
+  uint8_t type = (uint8_t)body[0];
+  if (type == wire::Shutdown) {
+    shutdown_ = true;
+    return;
+  }
+  Message msg;
+  std::map<int, Endpoint> eps;
+  if (!decode(body, msg, &eps)) return;
+  if (std::holds_alternative<InitWorkers>(msg)) {
+    endpoints_ = eps;
+    outPeers_.clear();  // re-initialisation: peers may have changed
+  }
+  if (handler_) handler_(msg);
+}
+
+int WorkerNode::poll(int timeoutMs) {
+  std::vector<pollfd> fds;
+  fds.push_back({listenFd_, POLLIN, 0});
+  if (masterConn_) fds.push_back({masterConn_->fd(), (short)(POLLIN | (masterConn_->wantsWrite() ? POLLOUT : 0)), 0});
+  size_t inBase = fds.size();
+  for (auto& c : inPeers_) fds.push_back({c->fd(), POLLIN, 0});
+  size_t outBase = fds.size();
+  std::vector<int> outIds;
+  for (auto& kv : outPeers_) {
+    fds.push_back({kv.second->fd(), (short)(kv.second->wantsWrite() ? POLLOUT : 0), 0});
+    outIds.push_back(kv.first);
+  }
+  int rc = ::poll(fds.data(), fds.size(), timeoutMs);
+  int handled = 0;
+  std::string body;
+  if (rc > 0) {
+    if (fds[0].revents & POLLIN) {
+      for (;;) {
+        int fd = accept(listenFd_, nullptr, nullptr);
+        if (fd < 0) break;
+        setNonBlocking(fd);
+        inPeers_.push_back(std::make_unique<Connection>(fd));
+      }
+    }
+    if (masterConn_ && inBase == 2) {
+      bool alive = true;
+      if (fds[1].revents & POLLOUT) alive = masterConn_->flush();
+      if (alive && (fds[1].revents & (POLLIN | POLLHUP | POLLERR))) alive = masterConn_->readAvailable();
+      while (masterConn_->next(body)) {
+        ++handled;
+        dispatch(body);
+      }
+      if (!alive) {
+        AAR_WARN("worker: master link closed");
+        masterConn_.reset();
+        shutdown_ = true;
+      }
+    }
+    size_t nIn = outBase - inBase;
+    std::vector<size_t> deadIn;
+    for (size_t k = 0; k < nIn; ++k) {
+      if (!(fds[inBase + k].revents & (POLLIN | POLLHUP | POLLERR))) continue;
+      Connection& c = *inPeers_[k];
+      bool alive = c.readAvailable();
+      while (c.next(body)) {
+        ++handled;
+        dispatch(body);
+      }
+      if (!alive) deadIn.push_back(k);
+    }
+    for (auto it = deadIn.rbegin(); it != deadIn.rend(); ++it) inPeers_.erase(inPeers_.begin() + *it);
+    for (size_t k = 0; k < outIds.size(); ++k) {
+      if (!(fds[outBase + k].revents & (POLLOUT | POLLHUP | POLLERR))) continue;
+      auto it = outPeers_.find(outIds[k]);
+      if (it != outPeers_.end() && !it->second->flush()) outPeers_.erase(it);
+    }
+  }
+  auto now = Clock::now();
+  if (masterConn_ && std::chrono::duration<double, std::milli>(now - lastBeat_).count() >= heartbeatMs_) {
+    masterConn_->queue(wire::encodeSimple(wire::Heartbeat));
+    lastBeat_ = now;
+  }
+  return handled;
+}
+
+bool WorkerNode::run(double timeoutSec) {
+  auto deadline = Clock::now() + std::chrono::duration<double>(timeoutSec);
+  while (!shutdown_ && Clock::now() < deadline) poll(50);
+  return shutdown_;
+}
+
+}  // namespace aar

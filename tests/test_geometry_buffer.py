@@ -1,0 +1,74 @@
+"""Partitioning / threshold arithmetic (csrc/core/geometry.h) and the host ring (csrc/core/data_buffer.h).
+
+The reference has no direct DataBuffer tests; thresholds are the float32 values
+listed in SURVEY.md section 2.4.
+"""
+import numpy as np
+import pytest
+
+from akka_allreduce_b200 import _core as core
+
+
+@pytest.mark.parametrize(
+    "th,P,want",
+    [(0.9, 2, 1), (0.75, 4, 3), (0.7, 3, 2), (0.6, 2, 1), (0.75, 8, 6), (0.9, 8, 7), (1.0, 8, 8), (0.1, 1, 1), (0.8, 4, 3)],
+)
+def test_min_required_float32(th, P, want):
+    assert core.Geometry.min_required(th, P) == want
+
+
+@pytest.mark.parametrize(
+    "th,P,data,chunk,want",
+    [
+        (0.8, 2, 6, 2, 3),      # 0.8f * 2 * 2
+        (0.7, 3, 9, 1, 6),      # 0.7f * 3 * 3
+        (0.75, 3, 9, 2, 4),     # 0.75f * 3 * 2
+        (0.8, 4, 8, 2, 3),      # 0.8f * 4 * 1
+        (0.75, 8, 8 * 16, 1, 96),
+        (0.9, 8, 8 * 16, 1, 115),
+        (1.0, 2, 3, 2, 2),
+    ],
+)
+def test_min_chunks_required_float32(th, P, data, chunk, want):
+    assert core.Geometry(P, data, chunk).min_chunks_required(th) == want
+
+
+def test_partition_matches_reference_formulas():
+    g = core.Geometry(2, 10, 2)
+    assert g.step_size == 5
+    assert [(g.block_start(i), g.block_end(i)) for i in range(2)] == [(0, 5), (5, 10)]
+    assert [g.chunk_len(0, c) for c in range(g.num_chunks(0))] == [2, 2, 1]
+    assert g.total_chunks() == 6
+
+
+def test_uneven_and_empty_blocks_are_legal():
+    g = core.Geometry(4, 9, 2)  # reference: ArrayIndexOutOfBounds (B2)
+    assert [g.block_len(i) for i in range(4)] == [3, 3, 3, 0]
+    assert [g.num_chunks(i) for i in range(4)] == [2, 2, 2, 0]
+    assert g.total_chunks() == 6 and g.min_chunks_required(1.0) == 6  # B3: reachable at thComplete = 1
+    g = core.Geometry(8, 7, 4)
+    assert [g.block_len(i) for i in range(8)] == [1] * 7 + [0]
+    assert g.chunk_index(3, 0) == 3
+
+
+def test_appendix_b_config2_sizes():
+    g = core.Geometry(8, 16 * 1024 * 1024, 1024 * 1024)
+    assert g.max_block_len() == 2097152 and g.max_num_chunks() == 2 and g.total_chunks() == 16
+
+
+def test_ring_store_count_retire():
+    b = core.DataBuffer(4, 3, 2, 2, [2, 2, 2])  # rowLen 4, 3 peers, depth 2, chunk 2
+    assert b.store(0, 1, 0, [1.0, 2.0])
+    assert not b.store(0, 1, 0, [5.0, 6.0])  # duplicate (src, chunk): count unchanged, data refreshed
+    assert b.count_chunk(0, 0) == 1 and b.mask_chunk(0, 0) == 0b010
+    assert list(b.row(0, 1)[:2]) == [5.0, 6.0]
+    assert b.store(1, 0, 1, [9.0, 9.0], aux=3)
+    assert b.slot_of(1) == 1 and b.aux(1, 0, 1) == 3
+    assert b.count_round(0) == 1 and b.count_round(1) == 1
+    b.retire(0)
+    assert b.count_chunk(0, 0) == 0
+    # round 2 reuses slot 0; nothing of round 0 leaks into it
+    assert b.store(2, 2, 1, [7.0, 8.0])
+    assert b.mask_chunk(2, 0) == 0 and b.mask_chunk(2, 1) == 0b100
+    with pytest.raises(Exception):
+        b.store(2, 0, 1, [1.0, 2.0, 3.0])  # overflows the row

@@ -1,0 +1,154 @@
+"""TCP control/data transport, CLI mains (BASELINE.json config 1) and checkpoint / restore."""
+import subprocess
+import sys
+import threading
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from akka_allreduce_b200 import _core as core
+from akka_allreduce_b200.utils import build
+
+from harness import Harness, basic_source
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def _free_port():
+    import socket
+
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def test_tcp_cluster_in_threads_matches_golden_trace():
+    cfg = core.MasterConfig(total_workers=3, data_size=10, max_chunk_size=2, max_round=20, max_lag=1)
+    node = core.MasterNode(cfg, "127.0.0.1", 0)
+    outs = [[] for _ in range(3)]
+    workers, nodes = [], []
+    for i in range(3):
+        wn = core.WorkerNode("127.0.0.1", node.port)
+        w = core.Worker(lambda it: np.arange(10, dtype=np.float32) + np.float32(it),
+                        (lambda k: lambda data, count, it: outs[k].append((it, np.array(data), np.array(count))))(i), wn)
+        wn.attach(w)
+        workers.append(w)
+        nodes.append(wn)
+    threads = [threading.Thread(target=n.run, args=(30.0,)) for n in nodes]
+    for t in threads:
+        t.start()
+    assert node.run(30.0)
+    for t in threads:
+        t.join(35)
+    assert all(n.shutdown_requested for n in nodes)
+    assert sorted(w.id for w in workers) == [0, 1, 2]
+    for k in range(3):
+        assert [it for it, _, _ in outs[k]] == list(range(21))
+        for it, data, count in outs[k]:
+            np.testing.assert_array_equal(data, 3 * (np.arange(10, dtype=np.float32) + it))
+            assert (count == 3).all()
+
+
+def test_master_detects_a_dead_worker():
+    cfg = core.MasterConfig(total_workers=2, th_allreduce=1.0, data_size=4, max_chunk_size=2, max_round=1000000)
+    node = core.MasterNode(cfg, "127.0.0.1", 0)
+    a = core.WorkerNode("127.0.0.1", node.port)
+    b = core.WorkerNode("127.0.0.1", node.port)
+    for _ in range(20):
+        node.poll(20)
+    assert len(node.master().workers) == 2
+    del b  # closes its sockets -> Terminated at the master (death-watch, AllreduceMaster.scala:50-56,74)
+    import gc
+
+    gc.collect()
+    for _ in range(20):
+        node.poll(20)
+    assert len(node.master().workers) == 1 and node.master().metrics()["workers_terminated"] == 1
+    del a
+
+
+def test_cli_config1_master_and_two_workers():
+    """BASELINE.json config 1: master + 2 workers on localhost, dataSize=10, maxChunkSize=2, thresholds 1.0."""
+    build.build_cli()
+    port = _free_port()
+    common = ["--set", f"allreduce.transport.port={port}", "--set", "allreduce.loglevel=WARNING", "--timeout", "60"]
+    m = subprocess.Popen([str(ROOT / "bin/aar_master"), str(port), "2", "10", "2", "--set", "allreduce.th-reduce=1.0", "--set",
+                          "allreduce.th-complete=1.0", *common], stdout=subprocess.PIPE, text=True, cwd=ROOT)
+    ws = [subprocess.Popen([str(ROOT / "bin/aar_worker"), "0", "10", "--check", *common], stdout=subprocess.PIPE, text=True, cwd=ROOT)
+          for _ in range(2)]
+    mo, _ = m.communicate(timeout=90)
+    assert m.returncode == 0 and "finished=1 rounds_started=101" in mo
+    for w in ws:
+        wo, _ = w.communicate(timeout=90)
+        assert w.returncode == 0 and "rounds_flushed=101 mismatches=0" in wo
+
+
+def test_worker_checkpoint_round_trip(tmp_path):
+    # stop a worker mid-flight (round 0 half reduced, round 1 open), restore into a fresh one, finish identically
+    def script_first_half(h):
+        h.init(4, 0, 0.75, 0.75, 5, 4, 100)
+        h.start(0)
+        h.scatter([2], 1, 0, 0, 0)
+        h.scatter([4], 2, 0, 0, 0)
+        h.reduce([11], 1, 0, 0, 0, 3)
+        h.start(1)
+        h.scatter([3], 1, 0, 0, 1)
+        h.outbox.clear()
+
+    def script_second_half(h):
+        h.scatter([6], 3, 0, 0, 0)       # third arrival: reduce fires with 2+4+6
+        h.reduce([10], 2, 0, 0, 0, 3)
+        h.reduce([9], 3, 0, 0, 0, 3)     # completes round 0
+        return [(type(m).__name__, getattr(m, "round", None), list(getattr(m, "value", []))) for m in h.outbox]
+
+    a = Harness(basic_source(4))
+    script_first_half(a)
+    path = str(tmp_path / "w.ckpt")
+    core.save_worker_checkpoint(path, a.worker)
+    want = script_second_half(a)
+
+    b = Harness(basic_source(4))
+    core.load_worker_checkpoint(path, b.worker)
+    st = b.worker.state()
+    assert (st.id, st.round, st.max_round, st.max_scattered, st.max_lag) == (0, 0, 1, 1, 5)
+    assert st.th_reduce == pytest.approx(0.75) and st.data_size == 4 and st.max_chunk_size == 100
+    got = script_second_half(b)
+    assert got == want and any(n == "CompleteAllreduce" for n, _, _ in got)
+    np.testing.assert_array_equal(a.flushed[-1][1], b.flushed[-1][1])
+
+
+def test_master_checkpoint_round_trip(tmp_path):
+    sent = []
+    port = core.CallbackPort(lambda to, m: sent.append((to, m)))
+    cfg = core.MasterConfig(total_workers=2, max_round=10)
+    m = core.Master(cfg, port, 0)
+    m.member_up(5, "worker")
+    m.member_up(6, "worker")
+    m.receive(core.CompleteAllreduce(0, 0, 1))
+    m.receive(core.CompleteAllreduce(1, 0, 1))
+    m.receive(core.CompleteAllreduce(0, 1, 1))
+    path = str(tmp_path / "m.ckpt")
+    core.save_master_checkpoint(path, m)
+    m2 = core.Master(cfg, port, 0)
+    core.load_master_checkpoint(path, m2)
+    assert (m2.round, m2.quorum_round, m2.generation, m2.workers, m2.num_complete) == (1, 0, 1, {0: 5, 1: 6}, 1)
+    m2.receive(core.CompleteAllreduce(1, 1, 1))
+    assert m2.round == 2
+    with pytest.raises(Exception, match="differs"):
+        core.load_master_checkpoint(path, core.Master(core.MasterConfig(total_workers=3), port, 0))
+
+
+def test_ring_snapshot_round_trip(tmp_path):
+    s = core.RingSnapshot()
+    s.rank, s.P, s.L, s.data_size, s.max_chunk_size, s.round = 1, 2, 2, 8, 2, 7
+    s.scatter_ring = [1.0, 2.0]
+    s.reduce_ring = [3.0]
+    s.scatter_flags = [8, 8]
+    s.reduce_flags = [(8 << 32) | 2]
+    p = str(tmp_path / "r.ckpt")
+    core.save_ring_snapshot(p, s)
+    t = core.load_ring_snapshot(p)
+    assert (t.rank, t.P, t.L, t.round) == (1, 2, 2, 7) and t.reduce_flags == [(8 << 32) | 2] and t.scatter_ring == [1.0, 2.0]
