@@ -1,0 +1,149 @@
+"""One rank's handle on the device data plane: launches the round kernels on a CUDA stream, owns the L-deep
+ring of output / count buffers, the host doorbell (newest round announced by the master) and the host-visible
+completion word.
+
+This is the part of AllreduceWorker.scala:84-104 (StartAllreduce -> fetch -> scatter) and :253-268 (complete) that
+touches data, with the actor mailbox replaced by stream order: rounds of one rank run in order on its stream, ranks
+are decoupled from each other by the thresholds, the device-resident ring and the flow-control words.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Sequence
+
+import torch
+
+from .. import _core as core
+from ..ops import lib as L
+from .local_gpu import _TORCH2AAR
+
+# Measured crossover (profiles/): below this many bytes the one-hop one-shot kernel wins over two-shot.
+ONESHOT_MAX_BYTES = 256 * 1024
+
+
+class RoundEngine:
+    def __init__(self, rank: int, region_ptrs: Sequence[int], layout: L.AarLayout, *, th_reduce: float = 1.0, th_complete: float = 1.0,
+                 normalize: bool = False, exact_quorum: bool = False, timeout_ms: float = 0.0, device: int = 0, grid: int = 0,
+                 algo: str = "auto", mc_ptr: int = 0, keepalive=None):
+        self.lib = L.load()
+        self.rank, self.P = rank, layout.P
+        self.layout = layout
+        self.device = torch.device("cuda", device)
+        self.dtype = torch.float32 if layout.dtype == L.AAR_F32 else torch.bfloat16
+        self.grid = grid
+        self.keepalive = keepalive
+        self.geo = core.Geometry(layout.P, layout.dataSize, layout.maxChunk)
+        self.data_size = layout.dataSize
+        self.max_lag = layout.L - 1
+        self.mc_ptr = mc_ptr
+        self.algo = self._select(algo, th_reduce, th_complete)
+        with torch.cuda.device(self.device):
+            self.outputs = [torch.empty(self.data_size, dtype=self.dtype, device=self.device) for _ in range(layout.L)]
+            self.counts = [torch.zeros(layout.totalChunks, dtype=torch.int32, device=self.device) for _ in range(layout.L)]
+            host = C.POINTER(C.c_uint)()
+            dev = C.POINTER(C.c_uint)()
+            L.check(self.lib.aar_host_words_alloc(16, C.byref(host), C.byref(dev)), "aar_host_words_alloc")
+        self._host_words, self._dev_words = host, dev
+        p = L.AarRankParams()
+        p.rank = rank
+        p.minRequired = core.Geometry.min_required(th_reduce, layout.P)
+        p.minChunksRequired = self.geo.min_chunks_required(th_complete)
+        p.maxLag = self.max_lag
+        p.flags = (L.FLAG_NORMALIZE if normalize else 0) | (L.FLAG_EXACT_QUORUM if exact_quorum else 0)
+        p.timeoutNs = int(timeout_ms * 1e6)
+        dev_addr = C.cast(dev, C.c_void_p).value
+        p.doorbell = dev_addr            # word 0: newest round announced by the master
+        p.hostDone = dev_addr + 4        # word 1: rounds flushed (round + 1)
+        for j in range(layout.P):
+            p.region[j] = region_ptrs[j]
+        p.mcRegion = mc_ptr
+        self.params = p
+        self.base_flags = p.flags
+        self._lay = C.byref(self.layout)
+        self._pref = C.byref(self.params)
+        self.rounds_enqueued = 0
+        self.launches = 0
+
+    # ------------------------------------------------------------------ construction helpers
+    @classmethod
+    def single_process(cls, data_size: int, max_chunk: int, max_lag: int = 1, dtype: torch.dtype = torch.float32, device: int = 0, **kw):
+        """A world of one rank (N=1 runs and the smoke test): the region is a plain device allocation."""
+        lay = L.compute_layout(1, data_size, max_chunk, max_lag, _TORCH2AAR[dtype], ONESHOT_MAX_BYTES // (4 if dtype == torch.float32 else 2), False)
+        with torch.cuda.device(device):
+            region = torch.zeros(lay.regionBytes, dtype=torch.uint8, device=f"cuda:{device}")
+        return cls(0, [region.data_ptr()], lay, device=device, keepalive=region, **kw)
+
+    @classmethod
+    def from_symmetric(cls, symm, layout: L.AarLayout, **kw):
+        return cls(symm.rank, symm.ptrs, layout, device=symm.device, mc_ptr=symm.mc_ptr, keepalive=symm, **kw)
+
+    def _select(self, algo: str, th_reduce: float, th_complete: float) -> str:
+        lay = self.layout
+        nbytes = lay.dataSize * lay.elemSize
+        if algo == "auto":
+            if lay.oneshotOff and nbytes <= ONESHOT_MAX_BYTES and lay.P > 1:
+                return "oneshot"
+            if self.mc_ptr and lay.stageOff and th_reduce >= 1.0 and th_complete >= 1.0 and hasattr(self.lib, "aar_launch_nvls"):
+                return "nvls"
+            return "twoshot"
+        if algo == "oneshot" and not lay.oneshotOff:
+            raise ValueError("algo=oneshot needs a layout with one-shot buffers")
+        if algo == "nvls" and not (self.mc_ptr and lay.stageOff):
+            raise ValueError("algo=nvls needs a multicast mapping and the staging area")
+        return algo
+
+    # ------------------------------------------------------------------ rounds
+    def set_doorbell(self, newest_round: int) -> None:
+        """Host side of StartAllreduce: kernels that wait compare this with their round (catch-up when > maxLag behind)."""
+        self._host_words[0] = max(int(self._host_words[0]), newest_round) if newest_round >= 0 else 0
+
+    def rounds_flushed(self) -> int:
+        return int(self._host_words[1])
+
+    def enqueue_round(self, rnd: int, x: torch.Tensor, *, stream: torch.cuda.Stream | None = None, force: bool = False,
+                      skip_scatter: bool = False, out: torch.Tensor | None = None):
+        """Launch round `rnd` with input `x` on `stream`; returns (output, counts) tensors valid once the stream reaches
+        the end of the round (they are reused maxLag+1 rounds later)."""
+        if x.dtype != self.dtype or x.numel() != self.data_size or not x.is_contiguous() or x.device != self.device:
+            raise ValueError(f"input must be a contiguous {self.dtype} tensor of {self.data_size} elements on {self.device} "
+                             f"(AllreduceWorker.scala:174-176 rejects a size that differs from initialisation)")
+        slot = rnd % self.layout.L
+        output = self.outputs[slot] if out is None else out
+        p = self.params
+        p.round = rnd
+        p.input = x.data_ptr()
+        p.output = output.data_ptr()
+        p.outCounts = self.counts[slot].data_ptr()
+        p.flags = self.base_flags | (L.FLAG_FORCE if force else 0) | (L.FLAG_SKIP_SCATTER if skip_scatter else 0)
+        s = C.c_void_p((stream or torch.cuda.current_stream(self.device)).cuda_stream)
+        if self.algo == "twoshot":
+            L.check(self.lib.aar_launch_round_fused(self._pref, self._lay, self.grid, s), "aar_launch_round_fused")
+        elif self.algo == "oneshot":
+            L.check(self.lib.aar_launch_oneshot(self._pref, self._lay, 2, self.grid, s), "aar_launch_oneshot")
+        elif self.algo == "nvls":
+            L.check(self.lib.aar_launch_nvls(self._pref, self._lay, 3, self.grid, s), "aar_launch_nvls")
+        else:
+            raise ValueError(f"unknown algo {self.algo}")
+        self.launches += 1
+        self.rounds_enqueued = max(self.rounds_enqueued, rnd + 1)
+        return output, self.counts[slot]
+
+    def allreduce(self, x: torch.Tensor, rnd: int | None = None) -> torch.Tensor:
+        """Convenience: one round, result tensor (stream-ordered)."""
+        rnd = self.rounds_enqueued if rnd is None else rnd
+        out, _ = self.enqueue_round(rnd, x)
+        return out
+
+    def status(self) -> int:
+        """Device status bits (timeouts, dropped pushes) of this rank; synchronises."""
+        torch.cuda.synchronize(self.device)
+        t = torch.empty(2, dtype=torch.int32, device=self.device)
+        holder = type("H", (), {})()
+        holder.__cuda_array_interface__ = {"shape": (2,), "typestr": "<i4", "data": (self.params.region[self.rank] + self.layout.statusOff, False), "version": 3}
+        t.copy_(torch.as_tensor(holder, device=self.device))
+        return int(t[0].item())
+
+    def close(self) -> None:
+        if self._host_words:
+            self.lib.aar_host_words_free(self._host_words)
+            self._host_words = None

@@ -1,0 +1,637 @@
+// sm_100a kernels of the threshold allreduce: K1 scatter_push, K2 reduce_bcast, K3 gather_flush
+// (+ K6 ring_advance and K8 force_complete folded in), their single-launch fusion, K5 one-shot and the
+// single-device cluster emulation.  Reference steps replaced:
+//   S1/S2 fetch+scatter   AllreduceWorker.scala:171-209   -> phaseScatter
+//   S3/S4 store+threshold AllreduceWorker.scala:106-127, DataBuffer.scala:31-43 -> arrival flags + chunkDecision
+//   S5/S6 reduce+broadcast AllreduceWorker.scala:230-251  -> phaseReduceBcast
+//   S7/S8 store+round threshold AllreduceWorker.scala:129-150, DataBuffer.scala:69-75 -> gatherDecision
+//   S9/S10 complete+flush+up() AllreduceWorker.scala:180-192,253-268, DataBuffer.scala:63-67 -> phaseGather
+//   S11 catch-up          AllreduceWorker.scala:90-97     -> forcedByHost() inside every wait
+// No tensor-core work exists in this problem (one fp32 add per element per contributor); every phase is
+// NVLink- or HBM-bound, so the design effort goes into bytes moved, flags and overlap.
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "aar_device.cuh"
+#include "aar_host.h"
+
+using namespace aar_dev;
+
+namespace {
+
+struct Smem {
+  unsigned k1Known, k1Go;       // per-destination flow-control decisions cached by this CTA
+  int k2Chunk;                  // chunk whose contributor mask is cached
+  unsigned k2Mask;
+  int k3Leader;
+  int k3Count;
+  int scratch;
+};
+
+__device__ __forceinline__ char* regionOf(const AarRankParams& p, int r) { return reinterpret_cast<char*>(p.region[r]); }
+__device__ __forceinline__ uint32_t* statusWord(const AarRankParams& p, const AarLayout& l, int i) {
+  return reinterpret_cast<uint32_t*>(regionOf(p, p.rank) + l.statusOff) + i;
+}
+template <typename T>
+__device__ __forceinline__ bool geomVecOk(const AarLayout& l) {
+  constexpr int V = Elem<T>::kPerVec;
+  return (l.stepSize % V == 0) && (l.maxChunk % V == 0) && (l.blkStride % V == 0);
+}
+
+// ------------------------------------------------------------------------------------------------ K1
+// Flow control (replaces the unbounded actor mailbox): round R may overwrite slot R % L of peer `dest` only
+// after that peer retired round R - L.  One decision per (round, dest), shared by all CTAs through a CAS word.
+__device__ bool scatterDecision(const AarRankParams& p, const AarLayout& l, int dest, Smem& sm) {
+  if (!((sm.k1Known >> dest) & 1u)) {
+    if (threadIdx.x == 0) {
+      unsigned go = 1;
+      if (p.round >= l.L) {
+        char* my = regionOf(p, p.rank);
+        uint64_t* word = reinterpret_cast<uint64_t*>(my + l.k1DecOff) + dest;
+        const uint64_t epoch = (uint64_t)(p.round + 1);
+        uint64_t v = ld_acquire_gpu_u64(word);
+        if ((v >> 32) == epoch) {
+          go = (unsigned)(v & 1u);
+        } else {
+          const uint32_t need = (uint32_t)(p.round - l.L + 1);
+          const uint32_t* base = reinterpret_cast<const uint32_t*>(my + l.peerBaseOff) + dest;
+          Deadline dl(p.timeoutNs);
+          unsigned spins = 0;
+          for (;;) {
+            if (ld_acquire_sys_u32(base) >= need) break;
+            if (((++spins & 63u) == 0) && (forcedByHost(p) || dl.expired())) {
+              go = 0;  // the peer fell out of the window: its copy of this contribution is dropped
+              break;
+            }
+            __nanosleep(64);
+          }
+          __threadfence();
+          uint64_t old = atomicCAS(reinterpret_cast<unsigned long long*>(word), (unsigned long long)v,
+                                   (unsigned long long)((epoch << 32) | go));
+          if (old != v && (old >> 32) == epoch) go = (unsigned)(old & 1u);
+          if (!go) atomicOr(statusWord(p, l, 0), AAR_ST_PUSH_DROPPED);
+        }
+      }
+      sm.k1Known |= (1u << dest);
+      if (go) sm.k1Go |= (1u << dest);
+    }
+    __syncthreads();
+  }
+  return (sm.k1Go >> dest) & 1u;
+}
+
+template <typename T>
+__device__ void phaseScatter(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
+  if (p.flags & AAR_FLAG_SKIP_SCATTER) return;
+  const int P = l.P, C = l.C, Tm = l.tilesPerChunk;
+  const int slot = p.round % l.L;
+  const uint32_t epoch = (uint32_t)(p.round + 1);
+  char* my = regionOf(p, p.rank);
+  const bool vecOk = geomVecOk<T>(l) && (reinterpret_cast<uintptr_t>(p.input) % 16 == 0);
+  const long long total = (long long)C * P * Tm;
+  // chunk-major, then destination staggered from self (AllreduceWorker.scala:195-196), then tile
+  for (long long idx = cta; idx < total; idx += nctas) {
+    const int t = (int)(idx % Tm);
+    const int i = (int)((idx / Tm) % P);
+    const int c = (int)(idx / ((long long)Tm * P));
+    const int dest = (i + p.rank) % P;
+    const int clen = chunkLen(l, dest, c);
+    const int off = t * l.tileElems;
+    if (off >= clen) continue;
+    if (!scatterDecision(p, l, dest, sm)) continue;
+    const int n = min(l.tileElems, clen - off);
+    const T* src = reinterpret_cast<const T*>(p.input) + blockStart(l, dest) + (long long)c * l.maxChunk + off;
+    T* dst = reinterpret_cast<T*>(regionOf(p, dest) + l.scatterOff) + ((long long)slot * P + p.rank) * l.blkStride +
+             (long long)c * l.maxChunk + off;
+    copyTile<T, true, false>(dst, src, n, vecOk);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k1CtrOff) + dest * C + c;
+      const unsigned old = atomicAdd(ctr, 1u);
+      if (old + 1 == (unsigned)numTiles(l, clen)) {  // last tile of this "ScatterBlock": publish its arrival
+        atomicExch(ctr, 0u);
+        __threadfence_system();
+        uint32_t* flag = reinterpret_cast<uint32_t*>(regionOf(p, dest) + l.sflagOff) + ((long long)slot * C + c) * AAR_MAXP + p.rank;
+        st_release_sys_u32(flag, epoch);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ K2
+// Contributor set of one of my chunks: wait until at least minRequired sources have flagged it (or the host forces
+// the round), snapshot the arrived mask, and make that snapshot the single decision for all CTAs (exactly-once
+// firing, DataBuffer.scala:31-33 -- without the == overshoot bug B4).  Runs in warp 0.
+__device__ unsigned chunkDecision(const AarRankParams& p, const AarLayout& l, uint64_t* word, const uint32_t* flags) {
+  const int lane = threadIdx.x & 31;
+  const uint64_t epoch = (uint64_t)(p.round + 1);
+  uint64_t v = 0;
+  if (lane == 0) v = ld_acquire_gpu_u64(word);
+  v = __shfl_sync(0xffffffffu, v, 0);
+  if ((v >> 32) == epoch) return (unsigned)(v & 0xffffffffu);
+
+  Deadline dl(p.timeoutNs);
+  unsigned arrived = 0, spins = 0;
+  bool forced = false;
+  for (;;) {
+    uint32_t f = (lane < l.P) ? ld_acquire_sys_u32(flags + lane) : 0u;
+    arrived = __ballot_sync(0xffffffffu, lane < l.P && f == (uint32_t)epoch);
+    if (__popc(arrived) >= p.minRequired) break;
+    if ((spins++ & 15u) == 0) {
+      int stop = 0;
+      if (lane == 0) {
+        if (forcedByHost(p)) stop = 1;
+        else if (dl.expired()) stop = 2;
+      }
+      stop = __shfl_sync(0xffffffffu, stop, 0);
+      if (stop) {
+        if (stop == 2 && lane == 0) atomicOr(statusWord(p, l, 0), AAR_ST_TIMEOUT_REDUCE);
+        forced = true;
+        // one more look so the snapshot is as fresh as the decision
+        f = (lane < l.P) ? ld_acquire_sys_u32(flags + lane) : 0u;
+        arrived = __ballot_sync(0xffffffffu, lane < l.P && f == (uint32_t)epoch);
+        break;
+      }
+    }
+    __nanosleep(32);
+  }
+  if ((p.flags & AAR_FLAG_EXACT_QUORUM) && !forced) {
+    while (__popc(arrived) > p.minRequired) arrived &= ~(1u << (31 - __clz(arrived)));  // keep the lowest ids
+  }
+  unsigned mask = arrived;
+  if (lane == 0) {
+    __threadfence();
+    uint64_t old = atomicCAS(reinterpret_cast<unsigned long long*>(word), (unsigned long long)v,
+                             (unsigned long long)((epoch << 32) | mask));
+    if (old != v && (old >> 32) == epoch) mask = (unsigned)(old & 0xffffffffu);
+  }
+  return __shfl_sync(0xffffffffu, mask, 0);
+}
+
+// Ordered fp32 sum of the masked sources (peer-index order from 0.0f, AllreduceWorker.scala:245-249) and store of
+// the result into every peer's reduce ring while it is still in registers.
+// kBcast = true: result goes to every peer's reduce ring at element offset outElemOff (K2);
+// kBcast = false: result goes to the local pointer `localOut` (K5 one-shot).  `rowStride` = elements between sources.
+template <typename T, bool kBcast>
+__device__ __forceinline__ void reduceTile(const AarRankParams& p, const AarLayout& l, const T* ringChunk, long long rowStride,
+                                           long long outElemOff, T* localOut, int n, unsigned mask, float divisor, bool vecOk) {
+  constexpr int V = Elem<T>::kPerVec;
+  const int P = l.P;
+  const int nv = vecOk ? n / V : 0;
+  for (int base = threadIdx.x; base < nv; base += kThreads * kUnroll) {
+    float acc[kUnroll][V];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u)
+#pragma unroll
+      for (int k = 0; k < V; ++k) acc[u][k] = 0.f;
+    for (int src = 0; src < P; ++src) {
+      if (!((mask >> src) & 1u)) continue;
+      const uint4* sp = reinterpret_cast<const uint4*>(ringChunk + (long long)src * rowStride);
+      uint4 v[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int i = base + u * kThreads;
+        if (i < nv) v[u] = ld_ring(sp + i);
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int i = base + u * kThreads;
+        if (i < nv) {
+          float f[V];
+          Elem<T>::unpack(v[u], f);
+#pragma unroll
+          for (int k = 0; k < V; ++k) acc[u][k] += f[k];
+        }
+      }
+    }
+    uint4 outv[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      if (divisor != 1.f) {
+#pragma unroll
+        for (int k = 0; k < V; ++k) acc[u][k] = acc[u][k] / divisor;
+      }
+      outv[u] = Elem<T>::pack(acc[u]);
+    }
+    if (kBcast) {
+      for (int i2 = 0; i2 < P; ++i2) {
+        const int dest = (i2 + p.rank) % P;
+        uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<T*>(regionOf(p, dest) + l.reduceOff) + outElemOff);
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          const int i = base + u * kThreads;
+          if (i < nv) st_peer(op + i, outv[u]);
+        }
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int i = base + u * kThreads;
+        if (i < nv) st_stream(reinterpret_cast<uint4*>(localOut) + i, outv[u]);
+      }
+    }
+  }
+  for (int i = nv * V + threadIdx.x; i < n; i += kThreads) {
+    float a = 0.f;
+    for (int src = 0; src < P; ++src)
+      if ((mask >> src) & 1u) a += Elem<T>::toFloat(__ldcg(ringChunk + (long long)src * rowStride + i));
+    if (divisor != 1.f) a = a / divisor;
+    const T r = Elem<T>::fromFloat(a);
+    if (kBcast) {
+      for (int i2 = 0; i2 < P; ++i2) {
+        const int dest = (i2 + p.rank) % P;
+        (reinterpret_cast<T*>(regionOf(p, dest) + l.reduceOff) + outElemOff)[i] = r;
+      }
+    } else {
+      localOut[i] = r;
+    }
+  }
+}
+
+template <typename T>
+__device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
+  const int P = l.P, C = l.C, Tm = l.tilesPerChunk;
+  const int myChunks = numChunks(l, p.rank);
+  if (myChunks == 0) return;
+  const int slot = p.round % l.L;
+  const uint64_t epoch = (uint64_t)(p.round + 1);
+  char* my = regionOf(p, p.rank);
+  const bool vecOk = geomVecOk<T>(l);
+  const long long total = (long long)myChunks * Tm;
+  for (long long idx = cta; idx < total; idx += nctas) {
+    const int t = (int)(idx % Tm);
+    const int c = (int)(idx / Tm);
+    const int clen = chunkLen(l, p.rank, c);
+    const int off = t * l.tileElems;
+    if (off >= clen) continue;
+    if (sm.k2Chunk != c) {
+      __syncthreads();  // everybody has read the previous mask
+      if (threadIdx.x < 32) {
+        unsigned m = chunkDecision(p, l, reinterpret_cast<uint64_t*>(my + l.k2DecOff) + (long long)slot * C + c,
+                                   reinterpret_cast<const uint32_t*>(my + l.sflagOff) + ((long long)slot * C + c) * AAR_MAXP);
+        if (threadIdx.x == 0) {
+          sm.k2Mask = m;
+          sm.k2Chunk = c;
+        }
+      }
+      __syncthreads();
+    }
+    const unsigned mask = sm.k2Mask;
+    const int count = __popc(mask);
+    const float divisor = ((p.flags & AAR_FLAG_NORMALIZE) && count > 1) ? (float)count : 1.f;
+    const int n = min(l.tileElems, clen - off);
+    const T* ringChunk = reinterpret_cast<const T*>(my + l.scatterOff) + (long long)slot * P * l.blkStride + (long long)c * l.maxChunk + off;
+    const long long outElemOff = ((long long)slot * P + p.rank) * l.blkStride + (long long)c * l.maxChunk + off;
+    reduceTile<T, true>(p, l, ringChunk, l.blkStride, outElemOff, nullptr, n, mask, divisor, vecOk);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k2CtrOff) + c;
+      const unsigned old = atomicAdd(ctr, 1u);
+      if (old + 1 == (unsigned)numTiles(l, clen)) {  // last tile of this "ReduceBlock": tell every peer, count included
+        atomicExch(ctr, 0u);
+        __threadfence_system();
+        const uint64_t word = (epoch << 32) | (uint64_t)count;
+        for (int i2 = 0; i2 < P; ++i2) {
+          const int dest = (i2 + p.rank) % P;
+          uint64_t* flag = reinterpret_cast<uint64_t*>(regionOf(p, dest) + l.rflagOff) + ((long long)slot * P + p.rank) * C + c;
+          st_release_sys_u64(flag, word);
+        }
+      }
+    }
+  }
+}
+
+// K6 ring_advance: the last CTA retires the slot -- publish "round+1 rounds retired" to every peer (their flow
+// control) and to the host (CompleteAllreduce is posted from there).  No bulk zeroing: epochs make stale data
+// unreachable (the reference re-allocates and zero-fills the slot, DataBuffer.scala:63-67).
+__device__ void retireRound(const AarRankParams& p, const AarLayout& l, int nctas) {
+  char* my = regionOf(p, p.rank);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k3CtrOff);
+    const unsigned old = atomicAdd(ctr, 1u);
+    if (old + 1 == (unsigned)nctas) {
+      atomicExch(ctr, 0u);
+      __threadfence_system();
+      for (int i2 = 0; i2 < l.P; ++i2) {
+        const int dest = (i2 + p.rank) % l.P;
+        st_release_sys_u32(reinterpret_cast<uint32_t*>(regionOf(p, dest) + l.peerBaseOff) + p.rank, (uint32_t)(p.round + 1));
+      }
+      atomicAdd(statusWord(p, l, 1), 1u);  // rounds flushed
+      if (p.hostDone) st_release_sys_u32(p.hostDone, (uint32_t)(p.round + 1));
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ K3
+// One CTA becomes the leader of the round: it counts reduced-chunk arrivals against minChunksRequired
+// (DataBuffer.scala:69-75 with the true chunk total, B3), snapshots which chunks made it together with their
+// contributor counts (B5), and publishes the snapshot; every CTA then gathers from that one snapshot.
+template <typename T>
+__device__ void gatherDecision(const AarRankParams& p, const AarLayout& l, int slot, Smem& sm) {
+  char* my = regionOf(p, p.rank);
+  uint64_t* word = reinterpret_cast<uint64_t*>(my + l.k3DecOff) + slot;
+  const uint64_t epoch = (uint64_t)(p.round + 1);
+  const uint64_t busy = (epoch << 32) | 1u, done = (epoch << 32) | 2u;
+  if (threadIdx.x == 0) {
+    int leader = 0;
+    uint64_t v = ld_acquire_gpu_u64(word);
+    if (v != done && v != busy) {
+      uint64_t old = atomicCAS(reinterpret_cast<unsigned long long*>(word), (unsigned long long)v, (unsigned long long)busy);
+      leader = (old == v) ? 1 : 0;
+    }
+    sm.k3Leader = leader;
+  }
+  __syncthreads();
+  const int P = l.P, C = l.C;
+  int* counts = reinterpret_cast<int*>(my + l.countsOff) + (long long)slot * l.totalChunks;
+  if (sm.k3Leader) {
+    const uint64_t* flags = reinterpret_cast<const uint64_t*>(my + l.rflagOff) + (long long)slot * P * C;
+    Deadline dl(p.timeoutNs);
+    unsigned spins = 0;
+    for (;;) {
+      if (threadIdx.x == 0) sm.k3Count = 0;
+      __syncthreads();
+      int local = 0;
+      for (int i = threadIdx.x; i < P * C; i += kThreads) {
+        const int owner = i / C, c = i % C;
+        if (c < numChunks(l, owner) && (ld_acquire_sys_u64(flags + i) >> 32) == epoch) ++local;
+      }
+      if (local) atomicAdd(&sm.k3Count, local);
+      __syncthreads();
+      int stop = (sm.k3Count >= p.minChunksRequired) ? 1 : 0;
+      if (!stop && threadIdx.x == 0 && (spins++ & 7u) == 0) {
+        if (forcedByHost(p)) sm.scratch = 1;
+        else if (dl.expired()) {
+          sm.scratch = 1;
+          atomicOr(statusWord(p, l, 0), AAR_ST_TIMEOUT_GATHER);
+        }
+      }
+      __syncthreads();
+      if (stop || sm.scratch) break;
+      __nanosleep(32);
+    }
+    // snapshot (a superset of what was counted: anything that landed in between is welcome)
+    for (int i = threadIdx.x; i < P * C; i += kThreads) {
+      const int owner = i / C, c = i % C;
+      if (c >= numChunks(l, owner)) continue;
+      const uint64_t f = ld_acquire_sys_u64(flags + i);
+      const int cnt = ((f >> 32) == epoch) ? (int)(f & 0xffffffffu) : -1;
+      counts[i] = cnt;  // valid (owner, c) pairs are exactly the indices [0, totalChunks)
+      if (p.outCounts) p.outCounts[i] = cnt < 0 ? 0 : cnt;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      sm.scratch = 0;
+      __threadfence();
+      st_release_gpu_u64(word, done);
+    }
+  } else {
+    if (threadIdx.x == 0) {
+      while (ld_acquire_gpu_u64(word) != done) __nanosleep(64);
+    }
+  }
+  __syncthreads();
+}
+
+template <typename T>
+__device__ void phaseGather(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
+  const int P = l.P, C = l.C, Tm = l.tilesPerChunk;
+  const int slot = p.round % l.L;
+  char* my = regionOf(p, p.rank);
+  gatherDecision<T>(p, l, slot, sm);
+  const int* counts = reinterpret_cast<const int*>(my + l.countsOff) + (long long)slot * l.totalChunks;
+  const bool vecOk = geomVecOk<T>(l) && (reinterpret_cast<uintptr_t>(p.output) % 16 == 0);
+  const long long total = (long long)P * C * Tm;
+  for (long long idx = cta; idx < total; idx += nctas) {
+    const int t = (int)(idx % Tm);
+    const int c = (int)((idx / Tm) % C);
+    const int owner = (int)(idx / ((long long)Tm * C));
+    const int clen = chunkLen(l, owner, c);
+    const int off = t * l.tileElems;
+    if (off >= clen) continue;
+    const int n = min(l.tileElems, clen - off);
+    T* dst = reinterpret_cast<T*>(p.output) + blockStart(l, owner) + (long long)c * l.maxChunk + off;
+    const int cnt = __ldcg(counts + owner * C + c);
+    if (cnt >= 0) {
+      const T* src = reinterpret_cast<const T*>(my + l.reduceOff) + ((long long)slot * P + owner) * l.blkStride + (long long)c * l.maxChunk + off;
+      copyTile<T, false, true>(dst, src, n, vecOk);
+    } else {
+      zeroTile<T>(dst, n, vecOk);  // chunks whose ReduceBlock never arrived stay zero (AllreduceWorker.scala:183)
+    }
+  }
+  retireRound(p, l, nctas);
+}
+
+// ------------------------------------------------------------------------------------------------ K5 one-shot
+// Small messages are latency-bound: one hop instead of two.  Every rank pushes its whole vector into slot
+// [round % L][src] of every peer's one-shot buffer (+ one arrival flag per peer), then sums the arrived set locally.
+// thReduce decides how many sources to wait for; thComplete has nothing left to wait for.
+__device__ __forceinline__ long long oneshotStride(const AarLayout& l) {
+  const int V = 16 / l.elemSize;
+  return ((long long)l.dataSize + V - 1) / V * V;
+}
+
+template <typename T>
+__device__ void phaseOneshotPush(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
+  if (p.flags & AAR_FLAG_SKIP_SCATTER) return;
+  const int P = l.P;
+  const int slot = p.round % l.L;
+  const int Tn = numTiles(l, l.dataSize);
+  const long long stride = oneshotStride(l);
+  char* my = regionOf(p, p.rank);
+  const bool vecOk = reinterpret_cast<uintptr_t>(p.input) % 16 == 0;
+  for (long long idx = cta; idx < (long long)P * Tn; idx += nctas) {
+    const int t = (int)(idx % Tn);
+    const int dest = ((int)(idx / Tn) + p.rank) % P;
+    if (!scatterDecision(p, l, dest, sm)) continue;
+    const int off = t * l.tileElems;
+    const int n = min(l.tileElems, l.dataSize - off);
+    T* dst = reinterpret_cast<T*>(regionOf(p, dest) + l.oneshotOff) + ((long long)slot * P + p.rank) * stride + off;
+    copyTile<T, true, false>(dst, reinterpret_cast<const T*>(p.input) + off, n, vecOk);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k1CtrOff) + dest * l.C;
+      const unsigned old = atomicAdd(ctr, 1u);
+      if (old + 1 == (unsigned)Tn) {
+        atomicExch(ctr, 0u);
+        __threadfence_system();
+        st_release_sys_u32(reinterpret_cast<uint32_t*>(regionOf(p, dest) + l.oneshotFlagOff) + slot * AAR_MAXP + p.rank, (uint32_t)(p.round + 1));
+      }
+    }
+  }
+}
+
+template <typename T>
+__device__ void phaseOneshotReduce(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
+  const int P = l.P;
+  const int slot = p.round % l.L;
+  const int Tn = numTiles(l, l.dataSize);
+  const long long stride = oneshotStride(l);
+  char* my = regionOf(p, p.rank);
+  if (threadIdx.x < 32) {
+    unsigned m = chunkDecision(p, l, reinterpret_cast<uint64_t*>(my + l.k2DecOff) + (long long)slot * l.C,
+                               reinterpret_cast<const uint32_t*>(my + l.oneshotFlagOff) + slot * AAR_MAXP);
+    if (threadIdx.x == 0) sm.k2Mask = m;
+  }
+  __syncthreads();
+  const unsigned mask = sm.k2Mask;
+  const int count = __popc(mask);
+  const float divisor = ((p.flags & AAR_FLAG_NORMALIZE) && count > 1) ? (float)count : 1.f;
+  const bool vecOk = reinterpret_cast<uintptr_t>(p.output) % 16 == 0;
+  if (cta == 0 && p.outCounts)
+    for (int i = threadIdx.x; i < l.totalChunks; i += kThreads) p.outCounts[i] = count;
+  for (int t = cta; t < Tn; t += nctas) {
+    const int off = t * l.tileElems;
+    const int n = min(l.tileElems, l.dataSize - off);
+    const T* rows = reinterpret_cast<const T*>(my + l.oneshotOff) + (long long)slot * P * stride + off;
+    reduceTile<T, false>(p, l, rows, stride, 0, reinterpret_cast<T*>(p.output) + off, n, mask, divisor, vecOk);
+  }
+  retireRound(p, l, nctas);
+}
+
+__device__ __forceinline__ void initSmem(Smem& sm) {
+  if (threadIdx.x == 0) {
+    sm.k1Known = 0;
+    sm.k1Go = 0;
+    sm.k2Chunk = -1;
+    sm.k2Mask = 0;
+    sm.k3Leader = 0;
+    sm.k3Count = 0;
+    sm.scratch = 0;
+  }
+  __syncthreads();
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads, 1) scatterKernel(const AarRankParams p, const AarLayout l) {
+  __shared__ Smem sm;
+  initSmem(sm);
+  phaseScatter<T>(p, l, blockIdx.x, gridDim.x, sm);
+}
+template <typename T>
+__global__ void __launch_bounds__(kThreads, 1) reduceBcastKernel(const AarRankParams p, const AarLayout l) {
+  __shared__ Smem sm;
+  initSmem(sm);
+  phaseReduceBcast<T>(p, l, blockIdx.x, gridDim.x, sm);
+}
+template <typename T>
+__global__ void __launch_bounds__(kThreads, 1) gatherKernel(const AarRankParams p, const AarLayout l) {
+  __shared__ Smem sm;
+  initSmem(sm);
+  phaseGather<T>(p, l, blockIdx.x, gridDim.x, sm);
+}
+// One launch per round per rank: the three phases back to back; chunk flags let a CTA start reducing chunk c as soon
+// as its contributors landed while other CTAs are still pushing later chunks.
+template <typename T>
+__global__ void __launch_bounds__(kThreads, 1) roundFusedKernel(const AarRankParams p, const AarLayout l) {
+  __shared__ Smem sm;
+  initSmem(sm);
+  phaseScatter<T>(p, l, blockIdx.x, gridDim.x, sm);
+  phaseReduceBcast<T>(p, l, blockIdx.x, gridDim.x, sm);
+  phaseGather<T>(p, l, blockIdx.x, gridDim.x, sm);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads, 1) oneshotKernel(const AarRankParams p, const AarLayout l, int phase) {
+  __shared__ Smem sm;
+  initSmem(sm);
+  if (phase == 0 || phase == 2) phaseOneshotPush<T>(p, l, blockIdx.x, gridDim.x, sm);
+  if (phase == 1 || phase == 2) phaseOneshotReduce<T>(p, l, blockIdx.x, gridDim.x, sm);
+}
+
+__global__ void delayKernel(unsigned long long ns) {
+  const unsigned long long t0 = globaltimer_ns();
+  while (globaltimer_ns() - t0 < ns) __nanosleep(256);
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+template <typename K>
+int residentGrid(K kernel, int want) {
+  int dev = 0, sms = 0, perSm = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return -1;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kernel, kThreads, 0) != cudaSuccess) return -1;
+  int cap = sms * (perSm > 0 ? perSm : 1);
+  if (want <= 0) want = sms;
+  return want < cap ? want : cap;
+}
+
+template <typename K, typename... Extra>
+int launch(K kernel, const AarRankParams* p, const AarLayout* l, int grid, void* stream, const char* what, Extra... extra) {
+  if (!p || !l) return aar_host::fail(AAR_EINVAL, "%s: null params", what);
+  if (p->rank < 0 || p->rank >= l->P || l->P > AAR_MAXP) return aar_host::fail(AAR_EINVAL, "%s: bad rank %d for P=%d", what, p->rank, l->P);
+  // every CTA may wait on work that another CTA of the same grid still has to do: the grid must be co-resident
+  int g = residentGrid(kernel, grid);
+  if (g <= 0) return aar_host::fail(AAR_ECUDA, "%s: occupancy query failed: %s", what, cudaGetErrorString(cudaGetLastError()));
+  kernel<<<g, kThreads, 0, (cudaStream_t)stream>>>(*p, *l, extra...);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return aar_host::fail(AAR_ECUDA, "%s: launch failed: %s", what, cudaGetErrorString(e));
+  return AAR_OK;
+}
+
+#define AAR_DISPATCH(kernelT, what)                                                              \
+  do {                                                                                           \
+    if (lay->dtype == AAR_F32) return launch(kernelT<float>, p, lay, grid, stream, what);        \
+    if (lay->dtype == AAR_BF16) return launch(kernelT<__nv_bfloat16>, p, lay, grid, stream, what); \
+    return aar_host::fail(AAR_EINVAL, "%s: unknown dtype %d", what, lay->dtype);                 \
+  } while (0)
+
+}  // namespace
+
+extern "C" {
+
+__attribute__((visibility("default"))) int aar_launch_scatter(const AarRankParams* p, const AarLayout* lay, int grid, void* stream) {
+  AAR_DISPATCH(scatterKernel, "aar_launch_scatter");
+}
+__attribute__((visibility("default"))) int aar_launch_reduce_bcast(const AarRankParams* p, const AarLayout* lay, int grid, void* stream) {
+  AAR_DISPATCH(reduceBcastKernel, "aar_launch_reduce_bcast");
+}
+__attribute__((visibility("default"))) int aar_launch_gather(const AarRankParams* p, const AarLayout* lay, int grid, void* stream) {
+  AAR_DISPATCH(gatherKernel, "aar_launch_gather");
+}
+__attribute__((visibility("default"))) int aar_launch_round_fused(const AarRankParams* p, const AarLayout* lay, int grid, void* stream) {
+  AAR_DISPATCH(roundFusedKernel, "aar_launch_round_fused");
+}
+
+__attribute__((visibility("default"))) int aar_launch_oneshot(const AarRankParams* p, const AarLayout* lay, int phase, int grid, void* stream) {
+  if (!lay || lay->oneshotOff == 0) return aar_host::fail(AAR_EINVAL, "aar_launch_oneshot: layout has no one-shot buffers");
+  if (phase < 0 || phase > 2) return aar_host::fail(AAR_EINVAL, "aar_launch_oneshot: phase must be 0, 1 or 2");
+  if (lay->dtype == AAR_F32) return launch(oneshotKernel<float>, p, lay, grid, stream, "aar_launch_oneshot", phase);
+  if (lay->dtype == AAR_BF16) return launch(oneshotKernel<__nv_bfloat16>, p, lay, grid, stream, "aar_launch_oneshot", phase);
+  return aar_host::fail(AAR_EINVAL, "aar_launch_oneshot: unknown dtype %d", lay->dtype);
+}
+
+__attribute__((visibility("default"))) int aar_local_round(const AarRankParams* params, int nranks, const AarLayout* lay, unsigned skipMask,
+                                                           int grid, void* stream) {
+  if (!params || !lay || nranks != lay->P) return aar_host::fail(AAR_EINVAL, "aar_local_round: need one params entry per rank");
+  // Phase order matters on a single device: no kernel may wait for a later launch.
+  for (int r = 0; r < nranks; ++r) {
+    if ((skipMask >> r) & 1u) continue;
+    int rc = aar_launch_scatter(&params[r], lay, grid, stream);
+    if (rc) return rc;
+  }
+  for (int r = 0; r < nranks; ++r) {
+    int rc = aar_launch_reduce_bcast(&params[r], lay, grid, stream);
+    if (rc) return rc;
+  }
+  for (int r = 0; r < nranks; ++r) {
+    int rc = aar_launch_gather(&params[r], lay, grid, stream);
+    if (rc) return rc;
+  }
+  return AAR_OK;
+}
+
+__attribute__((visibility("default"))) int aar_launch_delay(unsigned long long ns, void* stream) {
+  delayKernel<<<1, 1, 0, (cudaStream_t)stream>>>(ns);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return aar_host::fail(AAR_ECUDA, "aar_launch_delay: %s", cudaGetErrorString(e));
+  return AAR_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,151 @@
+/* C ABI of the sm_100a data plane (libaar_cuda.so).
+ *
+ * The reference moves ScatterBlock / ReduceBlock actor messages over TCP
+ * (AllreduceWorker.scala:194-251).  Here the same steps are CUDA kernels that store straight into
+ * peer GPUs' ring slots over NVLink and publish arrival with release flags; see csrc/cuda/.
+ * Every function returns 0 on success or a negative AAR_E* code; aar_last_error() gives the text.
+ * `stream` arguments are cudaStream_t passed as void*.
+ */
+#ifndef AKKA_ALLREDUCE_B200_H
+#define AKKA_ALLREDUCE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AAR_MAXP 16 /* peers addressable by one round engine (one NVSwitch domain) */
+
+#define AAR_OK 0
+#define AAR_EINVAL -1
+#define AAR_ECUDA -2
+#define AAR_EUNSUPPORTED -3
+
+/* element types on the wire / in the rings (accumulation is always fp32) */
+#define AAR_F32 0
+#define AAR_BF16 1
+
+/* AarRankParams.flags */
+#define AAR_FLAG_NORMALIZE 1u   /* divide each reduced chunk by its contributor count */
+#define AAR_FLAG_EXACT_QUORUM 2u /* use exactly minRequired contributors (lowest ids), like the reference's == firing */
+#define AAR_FLAG_FORCE 4u       /* K8: do not wait, take whatever has arrived (catch-up, AllreduceWorker.scala:91-97) */
+#define AAR_FLAG_SKIP_SCATTER 8u /* fused kernel: this rank contributes nothing this round (fault injection) */
+
+/* bits of the device status word (AarLayout.statusOff, word 0) */
+#define AAR_ST_TIMEOUT_SCATTER 1u
+#define AAR_ST_TIMEOUT_REDUCE 2u
+#define AAR_ST_TIMEOUT_GATHER 4u
+#define AAR_ST_PUSH_DROPPED 8u
+
+/* Byte offsets of the sections of one rank's symmetric region; identical on every rank. */
+typedef struct AarLayout {
+  int P, L, C;               /* peers, ring depth (maxLag+1), max chunks per block */
+  int dataSize, maxChunk, stepSize, blkStride, totalChunks;
+  int elemSize, dtype;
+  int tileElems, tilesPerChunk;
+  uint64_t scatterOff;       /* T   [L][P(src)][blkStride]      written by peers (K1) */
+  uint64_t reduceOff;        /* T   [L][P(owner)][blkStride]    written by peers (K2); slot row == flushed vector */
+  uint64_t sflagOff;         /* u32 [L][C][AAR_MAXP]            epoch = round+1, written by src */
+  uint64_t rflagOff;         /* u64 [L][P(owner)][C]            epoch<<32 | contributor count, written by owner */
+  uint64_t peerBaseOff;      /* u32 [AAR_MAXP]                  rounds retired by each peer (flow control) */
+  uint64_t k1DecOff;         /* u64 [AAR_MAXP]                  local: per-destination go/skip decision */
+  uint64_t k1CtrOff;         /* u32 [P][C]                      local: last-CTA election, scatter */
+  uint64_t k2DecOff;         /* u64 [L][C]                      local: epoch<<32 | contributor mask */
+  uint64_t k2CtrOff;         /* u32 [C]                         local: last-CTA election, broadcast */
+  uint64_t k3DecOff;         /* u64 [L]                         local: epoch<<32 | state */
+  uint64_t k3CtrOff;         /* u32 [4]                         local: last-CTA election, retire */
+  uint64_t countsOff;        /* i32 [L][totalChunks]            local: per-chunk contributor count, -1 = missing */
+  uint64_t statusOff;        /* u32 [16]                        local: status bits, counters */
+  uint64_t oneshotOff;       /* T   [L][P(src)][dataSize] + u32 [L][AAR_MAXP] flags; 0 if not allocated */
+  uint64_t oneshotFlagOff;
+  uint64_t stageOff;         /* T   [2][dataSize] staging for the NVLS path; 0 if not allocated */
+  uint64_t barrierOff;       /* u32 [8] NVLS barrier counters */
+  uint64_t ctrlBytes;        /* first byte of the control area that must be zeroed at allocation */
+  uint64_t regionBytes;      /* total, rounded up to 2 MiB */
+} AarLayout;
+
+/* Per-rank launch parameters (passed to the kernels by value). */
+typedef struct AarRankParams {
+  int rank;
+  int round;                 /* absolute round; slot = round % L, epoch = round + 1 */
+  int minRequired;           /* floor(thReduce * P), >= 1 */
+  int minChunksRequired;     /* floor(thComplete * sum of chunks) */
+  int maxLag;
+  unsigned flags;
+  unsigned long long timeoutNs; /* liveness guard for every device-side wait; 0 = unbounded */
+  const void* input;         /* dataSize elements (this round's source data) */
+  void* output;              /* dataSize elements */
+  int* outCounts;            /* totalChunks ints (AllReduceOutput.count), may be NULL */
+  const int* doorbell;       /* host-mapped: newest round announced by the master, may be NULL */
+  unsigned* hostDone;        /* host-mapped: receives round+1 when the round is flushed, may be NULL */
+  void* region[AAR_MAXP];    /* every rank's region as mapped in this rank's address space */
+  void* mcRegion;            /* multicast mapping of the regions (NVLS), may be NULL */
+} AarRankParams;
+
+const char* aar_last_error(void);
+
+/* Geometry -> layout.  maxLag >= 0; dtype AAR_F32 | AAR_BF16; oneshotMaxElems = 0 disables the one-shot buffers;
+ * withStage != 0 adds the NVLS staging area. */
+int aar_layout_compute(int P, int dataSize, int maxChunkSize, int maxLag, int dtype, int oneshotMaxElems, int withStage, AarLayout* out);
+
+/* K1 scatter_push (AllreduceWorker.scala:194-209): copy my block j into peer j's scatter ring + arrival flags. */
+int aar_launch_scatter(const AarRankParams* p, const AarLayout* lay, int grid, void* stream);
+/* K2 reduce_bcast (AllreduceWorker.scala:106-127,230-251): wait for thReduce contributors per chunk, ordered fp32
+ * sum of exactly the arrived set, store to every peer's reduce ring + (epoch,count) flags. */
+int aar_launch_reduce_bcast(const AarRankParams* p, const AarLayout* lay, int grid, void* stream);
+/* K3 gather_flush (AllreduceWorker.scala:129-150,180-192,253-268 + DataBuffer.up :63-67): wait for thComplete chunks,
+ * copy the slot row to the caller's output (zeros for missing chunks), write counts, retire the slot. */
+int aar_launch_gather(const AarRankParams* p, const AarLayout* lay, int grid, void* stream);
+/* K1+K2+K3 in one launch (one kernel per round per rank; requires peers on other GPUs or an earlier launch). */
+int aar_launch_round_fused(const AarRankParams* p, const AarLayout* lay, int grid, void* stream);
+/* K5 one-shot: push the whole vector to every peer, then each rank sums the arrived set locally. Two phases so the
+ * single-GPU emulation can order them; phase = 0 push, 1 reduce, 2 both. */
+int aar_launch_oneshot(const AarRankParams* p, const AarLayout* lay, int phase, int grid, void* stream);
+/* K4 NVLS: multimem.ld_reduce over the staged inputs + multimem.st of the result (thresholds must be 1.0).
+ * phase = 0 stage+arrive, 1 reduce+broadcast, 2 gather, 3 all. */
+int aar_launch_nvls(const AarRankParams* p, const AarLayout* lay, int phase, int grid, void* stream);
+
+/* Single-device cluster emulation: P ranks' regions live on the current device; runs one full round for all
+ * ranks in phase order (all K1, all K2, all K3) on `stream`.  params[r] describes rank r.  skipMask bit r set =
+ * rank r does not scatter this round (missing contributor). */
+int aar_local_round(const AarRankParams* params, int nranks, const AarLayout* lay, unsigned skipMask, int grid, void* stream);
+
+/* Plain device allocation helpers for the emulation mode and tests (zero-filled). */
+int aar_region_alloc_local(size_t bytes, void** ptr);
+int aar_region_free_local(void* ptr);
+
+/* Symmetric memory over CUDA VMM (cuMemCreate + POSIX fd export/import) and multicast objects. */
+typedef struct AarVmm {
+  uint64_t handle;   /* CUmemGenericAllocationHandle */
+  void* ptr;         /* mapped address in this process */
+  size_t bytes;      /* rounded up to the allocation granularity */
+  int fd;            /* exportable POSIX fd (-1 for imports) */
+  int device;
+} AarVmm;
+int aar_vmm_granularity(int device, int multicast, int nDevices, size_t* out);
+int aar_vmm_create(int device, size_t bytes, AarVmm* out);               /* allocate + map + zero + export fd */
+int aar_vmm_import(int device, int fd, size_t bytes, AarVmm* out);        /* map a peer's allocation */
+int aar_vmm_release(AarVmm* v);
+int aar_mc_supported(int device);                                         /* 1 if multicast objects are available */
+int aar_mc_create(int nDevices, size_t bytes, uint64_t* mcHandle, int* fd); /* rank 0 */
+int aar_mc_import(int fd, uint64_t* mcHandle);                            /* other ranks */
+int aar_mc_add_device(uint64_t mcHandle, int device);
+int aar_mc_bind_and_map(uint64_t mcHandle, int device, const AarVmm* mem, size_t bytes, void** mcPtr);
+int aar_mc_release(uint64_t mcHandle, void* mcPtr, size_t bytes);
+/* Host-mapped words (doorbell / completion): pinned + device-visible. */
+int aar_host_words_alloc(size_t nWords, unsigned** hostPtr, unsigned** devPtr);
+int aar_host_words_free(unsigned* hostPtr);
+
+/* Device properties the selector needs. */
+int aar_device_sm_count(int device, int* out);
+int aar_enable_peer_access(int device, int peer);
+
+/* Spin kernel used by the straggler injector: busy-waits `ns` nanoseconds on `stream`. */
+int aar_launch_delay(unsigned long long ns, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

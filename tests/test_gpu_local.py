@@ -1,0 +1,223 @@
+"""GPU tests of the sm_100a kernels on ONE device (P emulated ranks, tests/README in local_gpu.py).
+
+Every result is compared bit-for-bit (torch.equal) with a plain PyTorch fp32 restatement of the reference's
+reduce / flush (AllreduceWorker.scala:240-251,180-192) over the contributor set the scenario defines.
+The scenarios mirror the reference spec's fault cases (missed scatter T9, missed reduce T11, cold catch-up
+T14, ring reuse T7/T12) on the device data plane.
+"""
+import pytest
+import torch
+
+from akka_allreduce_b200 import _core as core
+
+pytestmark = pytest.mark.gpu
+
+
+def make_inputs(P, n, dtype, seed, device="cuda:0"):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return [(torch.randn(n, generator=g) * 3).to(dtype).to(device) for _ in range(P)]
+
+
+def oracle(inputs, P, n, chunk, contributors, dtype, normalize=False, missing_owner_chunks=()):
+    """contributors: callable (owner, c) -> sorted list of source ranks summed for that chunk."""
+    geo = core.Geometry(P, n, chunk)
+    out = torch.zeros(n, dtype=dtype, device=inputs[0].device)
+    counts = []
+    for owner in range(P):
+        for c in range(geo.num_chunks(owner)):
+            s = geo.block_start(owner) + c * chunk
+            e = s + geo.chunk_len(owner, c)
+            if (owner, c) in missing_owner_chunks:
+                counts.append(0)
+                continue
+            srcs = contributors(owner, c)
+            acc = torch.zeros(e - s, dtype=torch.float32, device=out.device)
+            for src in srcs:  # peer-index order, from 0.0f
+                acc = acc + inputs[src][s:e].float()
+            if normalize and len(srcs) > 1:
+                acc = acc / float(len(srcs))
+            out[s:e] = acc.to(dtype)
+            counts.append(len(srcs))
+    return out, torch.tensor(counts, dtype=torch.int32, device=out.device)
+
+
+def cluster(*a, **kw):
+    from akka_allreduce_b200.parallel.local_gpu import LocalGpuCluster
+
+    return LocalGpuCluster(*a, **kw)
+
+
+@pytest.mark.parametrize(
+    "P,n,chunk",
+    [(1, 10, 2), (2, 10, 2), (3, 9, 2), (4, 9, 2), (8, 7, 4), (2, 3, 2), (5, 1003, 17), (4, 4096, 1024), (8, 1 << 20, 1 << 16), (8, (1 << 20) + 8, 40000)],
+)
+def test_full_rounds_fp32_bit_exact(P, n, chunk):
+    cl = cluster(P, n, chunk, max_lag=1)
+    for rnd in range(4):  # slots are reused twice
+        xs = make_inputs(P, n, torch.float32, 100 + rnd)
+        outs, counts = cl.run_round(rnd, xs)
+        want, wc = oracle(xs, P, n, chunk, lambda o, c: list(range(P)), torch.float32)
+        torch.cuda.synchronize()
+        for r in range(P):
+            assert torch.equal(outs[r], want), f"rank {r} round {rnd}"
+            assert torch.equal(counts[r], wc)
+            assert cl.status(r) == 0
+        assert cl.peer_base(0) == [rnd + 1] * P and cl.rounds_flushed(0) == rnd + 1
+
+
+@pytest.mark.parametrize("P,n,chunk", [(4, 4096, 512), (8, 1 << 19, 1 << 15), (3, 1001, 100)])
+def test_full_rounds_bf16_bit_exact(P, n, chunk):
+    cl = cluster(P, n, chunk, max_lag=2, dtype=torch.bfloat16)
+    for rnd in range(4):
+        xs = make_inputs(P, n, torch.bfloat16, 7 + rnd)
+        outs, counts = cl.run_round(rnd, xs)
+        want, wc = oracle(xs, P, n, chunk, lambda o, c: list(range(P)), torch.bfloat16)
+        torch.cuda.synchronize()
+        for r in range(P):
+            assert torch.equal(outs[r], want)
+            assert torch.equal(counts[r], wc)
+
+
+def test_missed_scatter_within_threshold_and_normalisation():
+    """T9 analogue: one rank never scatters; thReduce .75 of 4 -> the other three are summed, count 3 reaches the sink."""
+    P, n, chunk = 4, 8192, 1024
+    for normalize in (False, True):
+        cl = cluster(P, n, chunk, th_reduce=0.75, th_complete=0.75, normalize=normalize)
+        xs = make_inputs(P, n, torch.float32, 5)
+        outs, counts = cl.run_round(0, xs, skip=[2])
+        want, wc = oracle(xs, P, n, chunk, lambda o, c: [0, 1, 3], torch.float32, normalize=normalize)
+        torch.cuda.synchronize()
+        for r in range(P):
+            assert torch.equal(outs[r], want) and torch.equal(counts[r], wc)
+            assert cl.status(r) == 0
+        assert cl.contributor_mask(1, 0, 0) == 0b1011
+
+
+def test_exact_quorum_policy_uses_lowest_ids():
+    """quorum-policy = exact reproduces the reference's `==` firing: exactly minRequired contributors."""
+    P, n, chunk = 4, 2048, 256
+    cl = cluster(P, n, chunk, th_reduce=0.5, exact_quorum=True)
+    xs = make_inputs(P, n, torch.float32, 9)
+    outs, counts = cl.run_round(0, xs)
+    want, wc = oracle(xs, P, n, chunk, lambda o, c: [0, 1], torch.float32)
+    torch.cuda.synchronize()
+    assert torch.equal(outs[3], want) and torch.equal(counts[3], wc)
+
+
+def test_forced_round_with_no_arrivals_flushes_zeros():
+    """T14 analogue (cold catch-up): nothing arrived, the host forces the round: zeros with count 0."""
+    P, n, chunk = 4, 4096, 512
+    cl = cluster(P, n, chunk)
+    xs = make_inputs(P, n, torch.float32, 11)
+    for o in cl.outputs:
+        o.fill_(123.0)
+    outs, counts = cl.run_round(0, xs, skip=range(P), force=True)
+    torch.cuda.synchronize()
+    for r in range(P):
+        assert torch.count_nonzero(outs[r]) == 0 and torch.count_nonzero(counts[r]) == 0
+        assert cl.status(r) == 0  # forced by the host, not a timeout
+
+
+def test_missed_reduce_block_stays_zero():
+    """T11 analogue: owner 3 never broadcasts; thComplete .75 completes the round, its block is zero with count 0."""
+    P, n, chunk = 4, 4096, 512
+    cl = cluster(P, n, chunk, th_complete=0.75)
+    xs = make_inputs(P, n, torch.float32, 13)
+    cl.run_phases(0, xs, scatter=range(P), reduce=[0, 1, 2], gather=range(P))
+    geo = core.Geometry(P, n, chunk)
+    missing = {(3, c) for c in range(geo.num_chunks(3))}
+    want, wc = oracle(xs, P, n, chunk, lambda o, c: list(range(P)), torch.float32, missing_owner_chunks=missing)
+    torch.cuda.synchronize()
+    for r in range(P):
+        assert torch.equal(cl.outputs[r], want) and torch.equal(cl.counts[r], wc)
+
+
+def test_late_contributor_is_excluded_and_decision_fires_once():
+    """The chunk decision is taken once per (round, chunk): a source that lands after it is not half-included, and
+    re-running the reduce phase reproduces the same sum (AllreduceSpec.scala:375-385 semantics)."""
+    P, n, chunk = 4, 4096, 1024
+    cl = cluster(P, n, chunk, th_reduce=0.75, th_complete=1.0)
+    xs = make_inputs(P, n, torch.float32, 17)
+    cl.run_phases(0, xs, scatter=[0, 1, 2], reduce=range(P))
+    cl.run_phases(0, xs, scatter=[3])              # late
+    cl.run_phases(0, xs, reduce=range(P), gather=range(P))
+    want, wc = oracle(xs, P, n, chunk, lambda o, c: [0, 1, 2], torch.float32)
+    torch.cuda.synchronize()
+    for r in range(P):
+        assert torch.equal(cl.outputs[r], want) and torch.equal(cl.counts[r], wc)
+        assert cl.contributor_mask(r, 0, 0) == 0b0111
+
+
+def test_stale_slot_data_never_leaks_into_a_later_round():
+    """Ring reuse without zeroing: round 2 shares slot 0 with round 0; a rank that skips round 2 must not contribute
+    its round-0 data (epoch-tagged flags, replacing DataBuffer.up()'s re-zeroing, DataBuffer.scala:63-67)."""
+    P, n, chunk = 4, 4096, 512
+    cl = cluster(P, n, chunk, max_lag=1, th_reduce=0.5, th_complete=1.0)
+    for rnd in range(2):
+        cl.run_round(rnd, make_inputs(P, n, torch.float32, 20 + rnd))
+    xs = make_inputs(P, n, torch.float32, 22)
+    outs, counts = cl.run_round(2, xs, skip=[1])
+    want, wc = oracle(xs, P, n, chunk, lambda o, c: [0, 2, 3], torch.float32)
+    torch.cuda.synchronize()
+    assert torch.equal(outs[0], want) and torch.equal(counts[0], wc)
+
+
+def test_device_timeout_is_a_liveness_guard():
+    """thReduce 1.0 but one rank is silent and nobody forces the round: after spin-timeout the kernels proceed with
+    what they have and raise the status bit instead of hanging the stream."""
+    from akka_allreduce_b200.ops import lib as L
+
+    P, n, chunk = 4, 2048, 512
+    cl = cluster(P, n, chunk, timeout_ms=20.0)
+    xs = make_inputs(P, n, torch.float32, 31)
+    outs, counts = cl.run_round(0, xs, skip=[0])
+    want, wc = oracle(xs, P, n, chunk, lambda o, c: [1, 2, 3], torch.float32)
+    torch.cuda.synchronize()
+    assert torch.equal(outs[2], want) and torch.equal(counts[2], wc)
+    assert cl.status(2) & L.ST_TIMEOUT_REDUCE
+
+
+@pytest.mark.parametrize("P,n,dtype", [(2, 10, torch.float32), (8, 2048, torch.float32), (4, 50000, torch.bfloat16), (8, 65536, torch.float32)])
+def test_oneshot_bit_exact(P, n, dtype):
+    cl = cluster(P, n, max(1, n // P), max_lag=1, dtype=dtype, oneshot=True)
+    for rnd in range(3):
+        xs = make_inputs(P, n, dtype, 40 + rnd)
+        outs, counts = cl.run_oneshot(rnd, xs)
+        acc = torch.zeros(n, dtype=torch.float32, device="cuda:0")
+        for x in xs:
+            acc = acc + x.float()
+        torch.cuda.synchronize()
+        for r in range(P):
+            assert torch.equal(outs[r], acc.to(dtype))
+            assert int(counts[r].min()) == P and int(counts[r].max()) == P
+
+
+def test_oneshot_threshold():
+    P, n = 4, 4096
+    cl = cluster(P, n, n // P, th_reduce=0.75, oneshot=True)
+    xs = make_inputs(P, n, torch.float32, 50)
+    outs, counts = cl.run_oneshot(0, xs, skip=[1])
+    acc = (torch.zeros_like(acc) + xs[0]) + xs[2] + xs[3]
+    torch.cuda.synchronize()
+    assert torch.equal(outs[1], acc) and int(counts[1][0]) == 3
+
+
+def test_oracle_agrees_with_cpu_protocol_engine():
+    """The device data plane and the C++ message-passing engine (the CPU restatement of the reference) flush the
+    same vector for the same inputs."""
+    import numpy as np
+
+    P, n, chunk = 3, 1001, 100
+    xs = make_inputs(P, n, torch.float32, 60)
+    host = [x.cpu().numpy() for x in xs]
+    sinks = [[] for _ in range(P)]
+    cfg = core.MasterConfig(total_workers=P, data_size=n, max_chunk_size=chunk, max_round=0)
+    cpu = core.LocalCluster(cfg, P, lambda i: (lambda it: host[i]), lambda i: (lambda d, c, it: sinks[i].append((np.array(d), np.array(c)))))
+    cpu.join_all()
+    cpu.run()
+    cl = cluster(P, n, chunk)
+    outs, counts = cl.run_round(0, xs)
+    torch.cuda.synchronize()
+    for r in range(P):
+        np.testing.assert_array_equal(outs[r].cpu().numpy(), sinks[r][0][0])
+        np.testing.assert_array_equal(counts[r].cpu().numpy(), sinks[r][0][1])
