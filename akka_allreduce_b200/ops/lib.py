@@ -11,7 +11,7 @@ from pathlib import Path
 
 AAR_MAXP = 16
 AAR_F32, AAR_BF16 = 0, 1
-FLAG_NORMALIZE, FLAG_EXACT_QUORUM, FLAG_FORCE, FLAG_SKIP_SCATTER = 1, 2, 4, 8
+FLAG_NORMALIZE, FLAG_EXACT_QUORUM, FLAG_FORCE, FLAG_SKIP_SCATTER, FLAG_VIEW_OUTPUT = 1, 2, 4, 8, 16
 ST_TIMEOUT_SCATTER, ST_TIMEOUT_REDUCE, ST_TIMEOUT_GATHER, ST_PUSH_DROPPED = 1, 2, 4, 8
 
 

@@ -121,7 +121,7 @@ class RoundEngine:
         elif self.algo == "oneshot":
             L.check(self.lib.aar_launch_oneshot(self._pref, self._lay, 2, self.grid, s), "aar_launch_oneshot")
         elif self.algo == "nvls":
-            L.check(self.lib.aar_launch_nvls(self._pref, self._lay, 3, self.grid, s), "aar_launch_nvls")
+            L.check(self.lib.aar_launch_nvls(self._pref, self._lay, 7, self.grid, s), "aar_launch_nvls")
         else:
             raise ValueError(f"unknown algo {self.algo}")
         self.launches += 1

@@ -1,0 +1,198 @@
+"""AllreduceWorker: one per process (one per GPU on the device data plane).
+
+    worker = AllreduceWorker(data_source, data_sink, backend="cuda")
+    worker.run(master_host, master_port)
+
+Same contract as the reference actor (AllreduceWorker.scala:9-10): the worker pulls a `dataSize` buffer from
+`data_source(AllReduceInputRequest(round))` for every round, in order, exactly once, and pushes the reduced
+result to `data_sink(AllReduceOutput(data, count, round))`.
+
+backend="cpu"  : the C++ message-passing engine (csrc/core/worker.cpp) over TCP -- bit-compatible restatement of
+                 the reference, used for plumbing runs and as the oracle.
+backend="cuda" : control messages (InitWorkers / StartAllreduce / CompleteAllreduce) over the same TCP channel, data
+                 over NVLink by the sm_100a kernels.  Rounds of one worker run in order on its CUDA stream; a worker
+                 that falls more than maxLag rounds behind the master's newest round is forced through by the device
+                 doorbell (the catch-up loop of AllreduceWorker.scala:91-97 without a host round-trip).
+"""
+from __future__ import annotations
+
+import time
+from typing import Callable
+
+import numpy as np
+
+from . import _core as core
+from .api import AllReduceInput, AllReduceInputRequest, AllReduceOutput, DataSink, DataSource
+
+
+class AllreduceWorker:
+    def __init__(self, data_source: DataSource, data_sink: DataSink, backend: str = "cuda", *, device: int | None = None,
+                 dtype: str = "fp32", algo: str = "auto", normalize: bool = False, exact_quorum: bool = False,
+                 spin_timeout_ms: float = 0.0, grid: int = 0, session: str | None = None, want_multicast: bool = True,
+                 on_init: Callable[["AllreduceWorker"], None] | None = None):
+        if backend not in ("cpu", "cuda"):
+            raise ValueError("backend must be 'cpu' or 'cuda'")
+        self.data_source, self.data_sink, self.backend = data_source, data_sink, backend
+        self.device, self.dtype, self.algo = device, dtype, algo
+        self.normalize, self.exact_quorum, self.spin_timeout_ms, self.grid = normalize, exact_quorum, spin_timeout_ms, grid
+        self.session, self.want_multicast, self.on_init = session, want_multicast, on_init
+        self.node: core.WorkerNode | None = None
+        self.id = -1
+        self.generation = 0
+        # device data plane state
+        self.engine = None
+        self.symm = None
+        self.rdv = None
+        self.max_round = -1
+        self.max_scattered = -1
+        self.delivered = 0          # rounds handed to the sink (= reference `round` on this in-order data plane)
+        self.rounds_forced = 0
+        self._stream = None
+        self._inputs = {}           # round -> input tensor kept alive until the round is flushed
+        self._cpu_worker = None
+
+    # ------------------------------------------------------------------ lifecycle
+    def connect(self, master_host: str = "127.0.0.1", master_port: int = 2551, listen_port: int = 0, heartbeat_ms: float = 1000.0):
+        self.master_port = master_port
+        self.node = core.WorkerNode(master_host, master_port, "127.0.0.1", listen_port, heartbeat_ms)
+        if self.backend == "cpu":
+            def src(it):
+                d = self.data_source(AllReduceInputRequest(it)).data
+                return np.ascontiguousarray(np.asarray(d, dtype=np.float32))
+
+            def snk(data, count, it):
+                self.delivered += 1
+                self.data_sink(AllReduceOutput(data, count, it))
+
+            self._cpu_worker = core.Worker(src, snk, self.node)
+            self.node.attach(self._cpu_worker)
+        else:
+            self.node.set_handler(self._on_message)
+        return self
+
+    def run(self, master_host: str = "127.0.0.1", master_port: int = 2551, timeout_sec: float = 3600.0) -> bool:
+        """Join the master and serve until it says Shutdown (returns True) or the timeout expires."""
+        if self.node is None:
+            self.connect(master_host, master_port)
+        if self.backend == "cpu":
+            ok = self.node.run(timeout_sec)
+            self.id = self._cpu_worker.id
+            return ok
+        deadline = time.time() + timeout_sec
+        while not self.node.shutdown_requested and time.time() < deadline:
+            busy = self.engine is not None and self.delivered < self.max_scattered + 1
+            self.node.poll(0 if busy else 2)
+            self._deliver_flushed()
+        self._drain()
+        return self.node.shutdown_requested
+
+    def step(self, timeout_ms: int = 0) -> None:
+        """One iteration of the event loop (for callers that own the loop)."""
+        self.node.poll(timeout_ms)
+        if self.backend == "cuda":
+            self._deliver_flushed()
+
+    def close(self) -> None:
+        if self.engine is not None:
+            self.engine.close()
+            self.engine = None
+        if self.symm is not None:
+            self.symm.close()
+            self.symm = None
+        if self.rdv is not None:
+            self.rdv.close()
+            self.rdv = None
+
+    # ------------------------------------------------------------------ device data plane
+    def _on_message(self, msg) -> None:
+        if isinstance(msg, core.InitWorkers):
+            self._on_init(msg)
+        elif isinstance(msg, core.StartAllreduce):
+            if msg.generation in (0, self.generation):
+                self._on_start(msg.round)
+
+    def _on_init(self, m) -> None:
+        """AllreduceWorker.scala:37-82: (re)initialisation wipes all round state and allocates the rings -- here the
+        symmetric HBM region, mapped into every peer."""
+        import torch
+
+        from .ops import lib as L
+        from .parallel.engine import ONESHOT_MAX_BYTES, RoundEngine
+        from .parallel.symmetric import SymmetricMemory, UnixRendezvous
+
+        self.close()
+        self.id, self.generation = m.dest_id, m.generation
+        P = len(m.workers)
+        dev = self.device if self.device is not None else self.id % torch.cuda.device_count()
+        torch.cuda.set_device(dev)
+        dt = L.AAR_F32 if self.dtype == "fp32" else L.AAR_BF16
+        es = 4 if dt == L.AAR_F32 else 2
+        layout = L.compute_layout(P, m.data_size, m.max_chunk_size, m.max_lag, dt, ONESHOT_MAX_BYTES // es, self.want_multicast)
+        session = (self.session or f"w{self.master_port}") + f"_g{m.generation}"
+        self.rdv = UnixRendezvous(self.id, P, session)
+        self.symm = SymmetricMemory(self.rdv, layout.regionBytes, dev, want_multicast=self.want_multicast and P > 1)
+        self.engine = RoundEngine.from_symmetric(self.symm, layout, th_reduce=m.th_reduce, th_complete=m.th_complete,
+                                                 normalize=self.normalize, exact_quorum=self.exact_quorum,
+                                                 timeout_ms=self.spin_timeout_ms, grid=self.grid, algo=self.algo)
+        self._stream = torch.cuda.Stream(device=dev)
+        self.max_round = self.max_scattered = -1
+        self.delivered = 0
+        self._inputs.clear()
+        self.rdv.barrier()  # nobody launches before every peer has mapped every region
+        if self.on_init:
+            self.on_init(self)
+
+    def _on_start(self, rnd: int) -> None:
+        """AllreduceWorker.scala:84-104.  The catch-up loop is the doorbell: kernels of rounds that are now more than
+        maxLag behind stop waiting and complete with what has arrived.  Then every not-yet-scattered round is fetched and
+        launched, in order, exactly once."""
+        import torch
+
+        eng = self.engine
+        if eng is None:
+            return
+        self.max_round = max(self.max_round, rnd)
+        eng.set_doorbell(self.max_round)
+        L = eng.layout.L
+        while self.max_scattered < self.max_round:
+            r = self.max_scattered + 1
+            # the output / count buffers of round r - L must have reached the sink before round r reuses them
+            while self.delivered < r - L + 1:
+                self._deliver_flushed(block=True)
+            x = self.data_source(AllReduceInputRequest(r)).data
+            if x.numel() != eng.data_size:
+                raise ValueError(f"Input data size {x.numel()} is different from initialization time {eng.data_size}!")
+            # the source may have produced x on another stream: order our launch after it
+            self._stream.wait_stream(torch.cuda.current_stream(eng.device))
+            eng.enqueue_round(r, x, stream=self._stream)
+            self._inputs[r] = x
+            self.max_scattered = r
+
+    def _deliver_flushed(self, block: bool = False) -> None:
+        """AllreduceWorker.scala:253-268 (complete): sink, then CompleteAllreduce to the master, in round order."""
+        eng = self.engine
+        if eng is None:
+            return
+        while True:
+            flushed = eng.rounds_flushed()  # host-mapped word written by the last CTA of K3
+            progressed = False
+            while self.delivered < flushed:
+                r = self.delivered
+                slot = r % eng.layout.L
+                self._inputs.pop(r, None)
+                if self.max_round - r > eng.max_lag:
+                    self.rounds_forced += 1
+                self.data_sink(AllReduceOutput(eng.outputs[slot], eng.counts[slot], r))
+                self.node.send_complete(self.id, r, self.generation)
+                self.delivered += 1
+                progressed = True
+            if not block or progressed or self.delivered >= self.max_scattered + 1:
+                return
+            time.sleep(0)  # blocking mode: yield until the next round flushes
+
+    def _drain(self) -> None:
+        import torch
+
+        if self.engine is not None:
+            torch.cuda.synchronize(self.engine.device)
+            self._deliver_flushed()

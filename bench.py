@@ -1,0 +1,352 @@
+#!/usr/bin/env python
+"""Headline benchmark (BASELINE.json config 2): N workers on N B200s, dataSize = 16 Mi fp32 (64 MiB per worker per
+round), maxChunkSize = 1 Mi, thresholds = 1.0, maxLag = 1, synthetic data, compared with NCCL allreduce of the same
+buffers on the same box.
+
+    python bench.py --gpus 1 --steps 20 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
+
+Prints ONE JSON line (rank 0).  `value` is the whole-job aggregate: N x payload bytes x rounds/s, in GB/s (weak
+scaling: every GPU contributes a 64 MiB buffer every round); `busbw_GBps` (NCCL convention, algbw x 2(N-1)/N) and
+`rounds_per_sec` ride along, as does the NCCL measurement taken in the same process.  Device-timed with CUDA events
+on the launching stream, max over ranks.  `e2e` is the same workload through the public API (AllreduceMaster +
+AllreduceWorker with a data source that copies the step's input from pinned host memory and a sink that reads the
+step's contributor counts and a checksum slice back to the host).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="aar", choices=["aar", "reference", "nccl"])
+    ap.add_argument("--data-size", type=int, default=16 * 1024 * 1024)
+    ap.add_argument("--chunk", type=int, default=1024 * 1024)
+    ap.add_argument("--dtype", default="fp32", choices=["fp32", "bf16"])
+    ap.add_argument("--max-lag", type=int, default=1)
+    ap.add_argument("--algo", default="auto")
+    ap.add_argument("--grid", type=int, default=0)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-nccl", action="store_true")
+    ap.add_argument("--view", action="store_true", help="zero-copy output (sink reads the ring slot)")
+    return ap.parse_args()
+
+
+def reference_unavailable():
+    # The reference is a Scala/sbt/Akka project; it is not a Python distribution, so the offline pip install has
+    # nothing to build, and the box has no JVM, sbt or ivy cache (DESIGN.md "Reference arm").
+    print(json.dumps({"impl": "reference", "unavailable": "reference is a Scala/sbt Akka project: no setup.py/pyproject for pip, "
+                      "and no java/sbt/ivy cache on the box to run it (see DESIGN.md)"}))
+
+
+class ClockSampler:
+    """nvidia-smi sampling during the timed region (B200_PROFILING.md clocks line)."""
+
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index: int):
+        self.path = f"/tmp/aar_clocks_{os.getpid()}.csv"
+        self.proc = None
+        try:
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(gpu_index)],
+                                         stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self) -> dict:
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if not self.proc:
+            return out
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.f.close()
+        sm, mx, reasons = [], [], set()
+        try:
+            for line in open(self.path):
+                p = [x.strip() for x in line.split(",")]
+                if len(p) < 9:
+                    continue
+                try:
+                    sm.append(float(p[1]))
+                    mx.append(float(p[2]))
+                except ValueError:
+                    continue
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            out["sm_mhz"] = statistics.median(sm)
+            out["sm_max_mhz"] = max(mx)
+            out["samples"] = len(sm)
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        reference_unavailable()
+        return 0
+
+    import torch
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", str(rank)))
+    if world != a.gpus:
+        if a.gpus > 1 and world == 1:
+            print(f"bench.py --gpus {a.gpus} must be launched with torch.distributed.run (one process per GPU)", file=sys.stderr)
+            return 2
+        a.gpus = world
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    dtype = torch.float32 if a.dtype == "fp32" else torch.bfloat16
+    es = 4 if a.dtype == "fp32" else 2
+    nbytes = a.data_size * es
+    N, K, W = a.gpus, a.steps, a.warmup
+
+    from akka_allreduce_b200.ops import lib as L
+    from akka_allreduce_b200.parallel.engine import ONESHOT_MAX_BYTES, RoundEngine
+    from akka_allreduce_b200.parallel.symmetric import SymmetricMemory, UnixRendezvous
+
+    session = f"bench_{os.environ.get('MASTER_PORT', '0')}_{os.getppid() if world > 1 else os.getpid()}"
+    rdv = UnixRendezvous(rank, world, session + "_ctl")
+
+    def max_over_ranks(x: float) -> float:
+        import struct
+
+        return max(struct.unpack("d", b)[0] for b in rdv.all_gather_bytes(struct.pack("d", x)))
+
+    def global_sync():
+        torch.cuda.synchronize(dev)
+        rdv.barrier()
+
+    result = {}
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+
+    # synthetic inputs: rank r contributes (r + 1) * base + round-dependent offset; two buffers alternate so the
+    # working set (inputs + rings, > 300 MB per rank) stays far above the 126 MB L2
+    g = torch.Generator(device="cpu").manual_seed(1234)
+    base = torch.randn(a.data_size, generator=g).to(dtype)
+    xs = [(base * (rank + 1) + k).to(dev) for k in range(2)]
+    expect = [sum((base.to(torch.float32) * (r + 1) + k).to(dtype).to(torch.float32) for r in range(N)) for k in range(2)] if N <= 2 else None
+
+    # ---------------------------------------------------------------- device-timed rounds
+    if a.impl == "aar":
+        layout = L.compute_layout(N, a.data_size, a.chunk, a.max_lag, L.AAR_F32 if a.dtype == "fp32" else L.AAR_BF16, ONESHOT_MAX_BYTES // es, True)
+        if N == 1:
+            eng = RoundEngine.single_process(a.data_size, a.chunk, a.max_lag, dtype=dtype, device=local_rank, grid=a.grid,
+                                             algo="twoshot" if a.algo == "auto" else a.algo)
+            symm = None
+        else:
+            symm = SymmetricMemory(UnixRendezvous(rank, world, session + "_mem"), layout.regionBytes, local_rank, want_multicast=True)
+            eng = RoundEngine.from_symmetric(symm, layout, grid=a.grid, algo=a.algo)
+        if a.view:
+            eng.base_flags |= L.FLAG_VIEW_OUTPUT
+        global_sync()
+        rnd = 0
+        for _ in range(W):
+            eng.enqueue_round(rnd, xs[rnd % 2])
+            rnd += 1
+        global_sync()
+        launches0 = eng.launches
+        t0 = torch.cuda.Event(enable_timing=True)
+        t1 = torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for _ in range(K):
+            out, counts = eng.enqueue_round(rnd, xs[rnd % 2])
+            rnd += 1
+        t1.record()
+        global_sync()
+        ms = max_over_ranks(t0.elapsed_time(t1) / K)
+        launches = eng.launches - launches0
+        # correctness of the last timed round (outside the timed region)
+        last = (rnd - 1) % 2
+        want = None
+        if N == 1:
+            want = xs[last]
+        ok = True
+        if want is not None and not a.view:
+            ok = bool(torch.equal(out, want))
+        cmin, cmax = int(counts.min().item()), int(counts.max().item())
+        ok = ok and cmin == N and cmax == N
+        # cross-rank agreement + value check on a slice: every rank must hold the same sum
+        import struct
+
+        if not a.view:
+            head = out[:4096].to(torch.float64).sum().item()
+            heads = [struct.unpack("d", b)[0] for b in rdv.all_gather_bytes(struct.pack("d", head))]
+            ok = ok and all(h == heads[0] for h in heads)
+            ref = sum((base[:4096].to(torch.float32) * (r + 1) + last).to(dtype).to(torch.float32) for r in range(N))
+            ok = ok and abs(ref.to(torch.float64).sum().item() - head) <= 1e-3 * max(1.0, abs(head))
+        result.update({"algo": eng.algo, "status_bits": eng.status(), "verified": ok, "multicast": bool(symm and symm.has_multicast),
+                       "multicast_error": (symm.mc_error if symm else "")})
+        gpu_launches = launches * N
+    else:  # plain NCCL allreduce of the same buffers: the baseline named by BASELINE.json
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=dev)
+        bufs = [x.clone() for x in xs]
+        for i in range(W):
+            dist.all_reduce(bufs[i % 2])
+        global_sync()
+        t0 = torch.cuda.Event(enable_timing=True)
+        t1 = torch.cuda.Event(enable_timing=True)
+        t0.record()
+        for i in range(K):
+            dist.all_reduce(bufs[i % 2])
+        t1.record()
+        global_sync()
+        ms = max_over_ranks(t0.elapsed_time(t1) / K)
+        gpu_launches = 0
+        result.update({"algo": "nccl"})
+
+    rounds_per_sec = 1e3 / ms
+    algbw = nbytes / (ms * 1e-3) / 1e9
+    value = N * algbw
+    busbw = algbw * 2 * (N - 1) / N
+
+    # ---------------------------------------------------------------- NCCL on the same box, same buffers
+    nccl = None
+    if a.impl == "aar" and N > 1 and not a.no_nccl:
+        try:
+            import torch.distributed as dist
+
+            dist.init_process_group("nccl", device_id=dev)
+            bufs = [x.clone() for x in xs]
+            for i in range(W):
+                dist.all_reduce(bufs[i % 2])
+            global_sync()
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(K):
+                dist.all_reduce(bufs[i % 2])
+            e1.record()
+            global_sync()
+            nms = max_over_ranks(e0.elapsed_time(e1) / K)
+            nalg = nbytes / (nms * 1e-3) / 1e9
+            nccl = {"ms_per_step": nms, "algbw_GBps": nalg, "busbw_GBps": nalg * 2 * (N - 1) / N, "version": ".".join(map(str, torch.cuda.nccl.version()))}
+        except Exception as e:  # the comparison must never break the headline number
+            nccl = {"error": str(e)[:200]}
+
+    # ---------------------------------------------------------------- end to end through the public API
+    e2e = None
+    if a.impl == "aar" and not a.no_e2e:
+        try:
+            e2e = run_e2e(a, rank, world, local_rank, dtype, nbytes, rdv, max_over_ranks, global_sync)
+        except Exception as e:
+            e2e = {"error": f"{type(e).__name__}: {e}"[:300]}
+
+    clocks = sampler.stop() if sampler else None
+    if rank == 0:
+        line = {
+            "metric": "allreduce aggregate payload GB/s at dataSize=16Mi fp32 per worker (N x bytes x rounds/s); bus GB/s and rounds/sec alongside, vs NCCL",
+            "value": value, "unit": "GB/s", "n_gpus": N, "steps": K, "warmup": W, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
+            "impl": a.impl,
+            "config": {"model": "threshold allreduce, BASELINE.json config 2 (N workers, dataSize=16Mi, maxChunkSize=1Mi, thresholds=1.0, maxLag=1)",
+                       "global_batch": N * a.data_size, "seq_len": a.data_size, "parallelism": f"dp{N}", "data_size": a.data_size,
+                       "max_chunk_size": a.chunk, "max_lag": a.max_lag, "th_reduce": 1.0, "th_complete": 1.0,
+                       "l2_policy": "inputs+rings larger than L2 (2 x 64 MiB inputs alternate, 256 MiB rings per rank)", "view_output": a.view},
+            "rounds_per_sec": rounds_per_sec, "algbw_GBps": algbw, "busbw_GBps": busbw,
+            "gpu_launches": gpu_launches, "clocks": clocks, "nccl": nccl,
+            "vs_nccl": (nccl["ms_per_step"] / ms) if nccl and "ms_per_step" in nccl else None,
+            "e2e": e2e,
+        }
+        line.update(result)
+        print(json.dumps(line))
+    rdv.barrier()
+    return 0
+
+
+def run_e2e(a, rank, world, local_rank, dtype, nbytes, rdv, max_over_ranks, global_sync):
+    """The same rounds through AllreduceMaster + AllreduceWorker: per step the source copies the step's input from pinned
+    host memory to the device, the sink reads the contributor counts and a 4 KiB slice of the result back to the host."""
+    import torch
+
+    from akka_allreduce_b200 import AllreduceMaster, AllreduceWorker, AllReduceInput
+
+    N, K, W = a.gpus, a.steps, a.warmup
+    dev = torch.device("cuda", local_rank)
+    total = W + K
+    port = int(os.environ.get("MASTER_PORT", "29500")) + 101
+    master = None
+    if rank == 0:
+        master = AllreduceMaster(N, 1.0, 1.0, 1.0, a.max_lag, a.data_size, total - 1, a.chunk, pipeline_depth=a.max_lag, port=port)
+        master.start(600.0)
+    rdv.barrier()
+    pinned = [torch.randn(a.data_size).to(dtype).pin_memory() for _ in range(2)]
+    staging = [torch.empty(a.data_size, dtype=dtype, device=dev) for _ in range(a.max_lag + 2)]
+    host_counts = None
+    host_head = torch.empty(1024, dtype=dtype).pin_memory()
+    copy_stream = torch.cuda.Stream(device=dev)
+    marks = {}
+    bytes_in = nbytes
+    state = {"d2h": 0}
+
+    def source(req):
+        x = staging[req.iteration % len(staging)]
+        with torch.cuda.stream(copy_stream):
+            x.copy_(pinned[req.iteration % 2], non_blocking=True)
+        torch.cuda.current_stream(dev).wait_stream(copy_stream)
+        return AllReduceInput(x)
+
+    def sink(out):
+        nonlocal host_counts
+        if host_counts is None:
+            host_counts = torch.empty(out.count.numel(), dtype=torch.int32).pin_memory()
+        host_counts.copy_(out.count, non_blocking=True)
+        host_head.copy_(out.data[:1024], non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+        state["d2h"] = host_counts.numel() * 4 + host_head.numel() * host_head.element_size()
+        if int(host_counts.min()) != N:
+            raise RuntimeError(f"round {out.iteration}: contributor counts {host_counts.tolist()} != {N}")
+        if out.iteration == W - 1 or (W == 0 and out.iteration == 0):
+            marks["t0"] = time.perf_counter()
+        if out.iteration == total - 1:
+            marks["t1"] = time.perf_counter()
+
+    worker = AllreduceWorker(source, sink, backend="cuda", device=local_rank, dtype=a.dtype, algo=a.algo, grid=a.grid,
+                             session=f"e2e_{port}_{os.getppid() if world > 1 else os.getpid()}")
+    ok = worker.run("127.0.0.1", port, timeout_sec=600.0)
+    if master:
+        master.join(30)
+    worker.close()
+    global_sync()
+    if not ok or "t1" not in marks or "t0" not in marks:
+        return {"error": f"e2e did not finish (shutdown={ok}, delivered={worker.delivered})"}
+    steps = K if W > 0 else K - 1
+    sec = max_over_ranks(marks["t1"] - marks["t0"])
+    ms = sec * 1e3 / steps
+    return {"value": N * nbytes / (ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": ms, "rounds_per_sec": 1e3 / ms,
+            "h2d_bytes_per_step": bytes_in, "d2h_bytes_per_step": state["d2h"],
+            "path": "AllreduceMaster(pipeline_depth=maxLag) + AllreduceWorker(backend=cuda); source: pinned host -> device copy per round; "
+                    "sink: counts + 1024-element slice read back per round", "algo": worker.algo if not worker.engine else worker.engine.algo}
+
+
+if __name__ == "__main__":
+    sys.exit(main())

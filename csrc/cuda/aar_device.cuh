@@ -15,7 +15,8 @@
 namespace aar_dev {
 
 constexpr int kThreads = 512;
-constexpr int kUnroll = 4;  // 16-byte vectors in flight per thread per tile
+constexpr int kUnroll = 4;  // 16-byte vectors per thread per tile (tile = kThreads * kUnroll vectors = 32 KiB)
+constexpr int kCopyUnroll = 8;  // vectors in flight per thread in the copy loops (64 KiB per CTA)
 
 // ---------------------------------------------------------------- memory model helpers
 __device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t* p) {
@@ -61,6 +62,28 @@ __device__ __forceinline__ void st_peer(void* p, const uint4& v) {
   asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 __device__ __forceinline__ void st_stream(void* p, const uint4& v) { __stcs(reinterpret_cast<uint4*>(p), v); }
+
+// NVLS: one load returns the sum over every GPU bound to the multicast object (the reduction happens in the
+// NVSwitch), one store lands in every GPU's copy.  Accumulation of bf16 is in fp32 inside the switch.
+__device__ __forceinline__ uint4 multimem_ld_reduce_f32x4(const void* mc) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_x4(void* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 
 // ---------------------------------------------------------------- element traits
 template <typename T>
@@ -142,15 +165,15 @@ template <typename T, bool kRemoteDst, bool kRingSrc>
 __device__ __forceinline__ void copyTile(T* dst, const T* src, int n, bool vecOk) {
   constexpr int V = Elem<T>::kPerVec;
   const int nv = vecOk ? n / V : 0;
-  for (int base = threadIdx.x; base < nv; base += kThreads * kUnroll) {
-    uint4 v[kUnroll];
+  for (int base = threadIdx.x; base < nv; base += kThreads * kCopyUnroll) {
+    uint4 v[kCopyUnroll];
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
+    for (int u = 0; u < kCopyUnroll; ++u) {
       const int i = base + u * kThreads;
       if (i < nv) v[u] = kRingSrc ? ld_ring(reinterpret_cast<const uint4*>(src) + i) : ld_stream(reinterpret_cast<const uint4*>(src) + i);
     }
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
+    for (int u = 0; u < kCopyUnroll; ++u) {
       const int i = base + u * kThreads;
       if (i < nv) {
         if (kRemoteDst)

@@ -1,6 +1,6 @@
 // sm_100a kernels of the threshold allreduce: K1 scatter_push, K2 reduce_bcast, K3 gather_flush
-// (+ K6 ring_advance and K8 force_complete folded in), their single-launch fusion, K5 one-shot and the
-// single-device cluster emulation.  Reference steps replaced:
+// (+ K6 ring_advance and K8 force_complete folded in), their single-launch fusion, K4 NVLS, K5 one-shot and
+// the single-device cluster emulation.  Reference steps replaced:
 //   S1/S2 fetch+scatter   AllreduceWorker.scala:171-209   -> phaseScatter
 //   S3/S4 store+threshold AllreduceWorker.scala:106-127, DataBuffer.scala:31-43 -> arrival flags + chunkDecision
 //   S5/S6 reduce+broadcast AllreduceWorker.scala:230-251  -> phaseReduceBcast
@@ -9,6 +9,11 @@
 //   S11 catch-up          AllreduceWorker.scala:90-97     -> forcedByHost() inside every wait
 // No tensor-core work exists in this problem (one fp32 add per element per contributor); every phase is
 // NVLink- or HBM-bound, so the design effort goes into bytes moved, flags and overlap.
+//
+// Work decomposition: every (destination, chunk) "message" of the reference is cut into segments of whole
+// 32 KiB tiles so that a grid of one CTA per SM has about two segments per CTA; a CTA streams its segment
+// without synchronising, then pays ONE system-scope fence + one atomic, and the CTA that finishes a message
+// last publishes its arrival flag.
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -38,12 +43,34 @@ __device__ __forceinline__ bool geomVecOk(const AarLayout& l) {
   constexpr int V = Elem<T>::kPerVec;
   return (l.stepSize % V == 0) && (l.maxChunk % V == 0) && (l.blkStride % V == 0);
 }
+__device__ __forceinline__ long long paddedData(const AarLayout& l) {
+  const int V = 16 / l.elemSize;
+  return ((long long)l.dataSize + V - 1) / V * V;
+}
+
+// Segments per message so that `pairs` messages give about two units per CTA; whole tiles per segment.
+struct SegPlan {
+  int tilesPerSeg, segs;
+  __device__ SegPlan(const AarLayout& l, long long pairs, int nctas) {
+    const int Tm = l.tilesPerChunk;
+    long long want = (2LL * nctas + pairs - 1) / (pairs > 0 ? pairs : 1);
+    int S = (int)(want < 1 ? 1 : (want > Tm ? Tm : want));
+    tilesPerSeg = (Tm + S - 1) / S;
+    segs = (Tm + tilesPerSeg - 1) / tilesPerSeg;
+  }
+  __device__ int segElems(const AarLayout& l) const { return tilesPerSeg * l.tileElems; }
+  // segments of a message of `len` elements that are not empty
+  __device__ unsigned liveSegs(const AarLayout& l, int len) const { return (unsigned)((len + segElems(l) - 1) / segElems(l)); }
+};
 
 // ------------------------------------------------------------------------------------------------ K1
 // Flow control (replaces the unbounded actor mailbox): round R may overwrite slot R % L of peer `dest` only
 // after that peer retired round R - L.  One decision per (round, dest), shared by all CTAs through a CAS word.
 __device__ bool scatterDecision(const AarRankParams& p, const AarLayout& l, int dest, Smem& sm) {
   if (!((sm.k1Known >> dest) & 1u)) {
+    // Every thread must have evaluated the condition above before thread 0 changes k1Known: a warp that read the
+    // updated bit would skip this block and pair its next barrier with the one below.
+    __syncthreads();
     if (threadIdx.x == 0) {
       unsigned go = 1;
       if (p.round >= l.L) {
@@ -81,36 +108,47 @@ __device__ bool scatterDecision(const AarRankParams& p, const AarLayout& l, int 
   return (sm.k1Go >> dest) & 1u;
 }
 
-template <typename T>
+// kStage = false: K1 scatter_push -- block `dest` of my input goes into peer dest's scatter ring over NVLink.
+// kStage = true : NVLS variant -- the input is staged in MY region (the switch will pull it), only the flag travels.
+template <typename T, bool kStage>
 __device__ void phaseScatter(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
   if (p.flags & AAR_FLAG_SKIP_SCATTER) return;
-  const int P = l.P, C = l.C, Tm = l.tilesPerChunk;
+  const int P = l.P, C = l.C;
   const int slot = p.round % l.L;
   const uint32_t epoch = (uint32_t)(p.round + 1);
   char* my = regionOf(p, p.rank);
   const bool vecOk = geomVecOk<T>(l) && (reinterpret_cast<uintptr_t>(p.input) % 16 == 0);
-  const long long total = (long long)C * P * Tm;
-  // chunk-major, then destination staggered from self (AllreduceWorker.scala:195-196), then tile
+  const SegPlan plan(l, (long long)P * C, nctas);
+  const int S = plan.segs, segElems = plan.segElems(l);
+  T* stage = reinterpret_cast<T*>(my + l.stageOff) + (long long)slot * paddedData(l);
+  const bool inPlace = kStage && (reinterpret_cast<const T*>(p.input) == stage);  // the source wrote straight into the stage
+  const long long total = (long long)C * P * S;
+  // chunk-major, then destination staggered from self (AllreduceWorker.scala:195-196), then segment
   for (long long idx = cta; idx < total; idx += nctas) {
-    const int t = (int)(idx % Tm);
-    const int i = (int)((idx / Tm) % P);
-    const int c = (int)(idx / ((long long)Tm * P));
+    const int s = (int)(idx % S);
+    const int i = (int)((idx / S) % P);
+    const int c = (int)(idx / ((long long)S * P));
     const int dest = (i + p.rank) % P;
     const int clen = chunkLen(l, dest, c);
-    const int off = t * l.tileElems;
+    const int off = s * segElems;
     if (off >= clen) continue;
-    if (!scatterDecision(p, l, dest, sm)) continue;
-    const int n = min(l.tileElems, clen - off);
-    const T* src = reinterpret_cast<const T*>(p.input) + blockStart(l, dest) + (long long)c * l.maxChunk + off;
-    T* dst = reinterpret_cast<T*>(regionOf(p, dest) + l.scatterOff) + ((long long)slot * P + p.rank) * l.blkStride +
-             (long long)c * l.maxChunk + off;
-    copyTile<T, true, false>(dst, src, n, vecOk);
+    if (!kStage && !scatterDecision(p, l, dest, sm)) continue;
+    const int n = min(segElems, clen - off);
+    const long long inOff = blockStart(l, dest) + (long long)c * l.maxChunk + off;
+    const T* src = reinterpret_cast<const T*>(p.input) + inOff;
+    if (kStage) {
+      if (!inPlace) copyTile<T, false, false>(stage + inOff, src, n, vecOk);
+    } else {
+      T* dst = reinterpret_cast<T*>(regionOf(p, dest) + l.scatterOff) + ((long long)slot * P + p.rank) * l.blkStride +
+               (long long)c * l.maxChunk + off;
+      copyTile<T, true, false>(dst, src, n, vecOk);
+    }
     __syncthreads();
     if (threadIdx.x == 0) {
       __threadfence_system();
       unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k1CtrOff) + dest * C + c;
       const unsigned old = atomicAdd(ctr, 1u);
-      if (old + 1 == (unsigned)numTiles(l, clen)) {  // last tile of this "ScatterBlock": publish its arrival
+      if (old + 1 == plan.liveSegs(l, clen)) {  // last segment of this "ScatterBlock": publish its arrival
         atomicExch(ctr, 0u);
         __threadfence_system();
         uint32_t* flag = reinterpret_cast<uint32_t*>(regionOf(p, dest) + l.sflagOff) + ((long long)slot * C + c) * AAR_MAXP + p.rank;
@@ -124,7 +162,7 @@ __device__ void phaseScatter(const AarRankParams& p, const AarLayout& l, int cta
 // Contributor set of one of my chunks: wait until at least minRequired sources have flagged it (or the host forces
 // the round), snapshot the arrived mask, and make that snapshot the single decision for all CTAs (exactly-once
 // firing, DataBuffer.scala:31-33 -- without the == overshoot bug B4).  Runs in warp 0.
-__device__ unsigned chunkDecision(const AarRankParams& p, const AarLayout& l, uint64_t* word, const uint32_t* flags) {
+__device__ unsigned chunkDecision(const AarRankParams& p, const AarLayout& l, uint64_t* word, const uint32_t* flags, int minRequired) {
   const int lane = threadIdx.x & 31;
   const uint64_t epoch = (uint64_t)(p.round + 1);
   uint64_t v = 0;
@@ -138,7 +176,7 @@ __device__ unsigned chunkDecision(const AarRankParams& p, const AarLayout& l, ui
   for (;;) {
     uint32_t f = (lane < l.P) ? ld_acquire_sys_u32(flags + lane) : 0u;
     arrived = __ballot_sync(0xffffffffu, lane < l.P && f == (uint32_t)epoch);
-    if (__popc(arrived) >= p.minRequired) break;
+    if (__popc(arrived) >= minRequired) break;
     if ((spins++ & 15u) == 0) {
       int stop = 0;
       if (lane == 0) {
@@ -158,7 +196,7 @@ __device__ unsigned chunkDecision(const AarRankParams& p, const AarLayout& l, ui
     __nanosleep(32);
   }
   if ((p.flags & AAR_FLAG_EXACT_QUORUM) && !forced) {
-    while (__popc(arrived) > p.minRequired) arrived &= ~(1u << (31 - __clz(arrived)));  // keep the lowest ids
+    while (__popc(arrived) > minRequired) arrived &= ~(1u << (31 - __clz(arrived)));  // keep the lowest ids
   }
   unsigned mask = arrived;
   if (lane == 0) {
@@ -171,44 +209,54 @@ __device__ unsigned chunkDecision(const AarRankParams& p, const AarLayout& l, ui
 }
 
 // Ordered fp32 sum of the masked sources (peer-index order from 0.0f, AllreduceWorker.scala:245-249) and store of
-// the result into every peer's reduce ring while it is still in registers.
-// kBcast = true: result goes to every peer's reduce ring at element offset outElemOff (K2);
-// kBcast = false: result goes to the local pointer `localOut` (K5 one-shot).  `rowStride` = elements between sources.
-template <typename T, bool kBcast>
-__device__ __forceinline__ void reduceTile(const AarRankParams& p, const AarLayout& l, const T* ringChunk, long long rowStride,
-                                           long long outElemOff, T* localOut, int n, unsigned mask, float divisor, bool vecOk) {
+// the result while it is still in registers.
+//   kBcast = true : into every peer's reduce ring at element offset outElemOff (K2)
+//   kBcast = false: to the local pointer `localOut` (K5 one-shot)
+// PMAX bounds the source loop at compile time so all PMAX x U loads are issued before the first add
+// (memory-level parallelism: 16 outstanding 16-byte loads per thread).
+template <typename T, bool kBcast, int PMAX, int U>
+__device__ __forceinline__ void reduceSpanVec(const AarRankParams& p, const AarLayout& l, const T* rows, long long rowStride,
+                                              long long outElemOff, T* localOut, int nv, unsigned mask, float divisor) {
   constexpr int V = Elem<T>::kPerVec;
   const int P = l.P;
-  const int nv = vecOk ? n / V : 0;
-  for (int base = threadIdx.x; base < nv; base += kThreads * kUnroll) {
-    float acc[kUnroll][V];
+  for (int base = threadIdx.x; base < nv; base += kThreads * U) {
+    float acc[U][V];
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u)
+    for (int u = 0; u < U; ++u)
 #pragma unroll
       for (int k = 0; k < V; ++k) acc[u][k] = 0.f;
-    for (int src = 0; src < P; ++src) {
-      if (!((mask >> src) & 1u)) continue;
-      const uint4* sp = reinterpret_cast<const uint4*>(ringChunk + (long long)src * rowStride);
-      uint4 v[kUnroll];
+    // groups of PMAX sources: all loads of a group are in flight before its first add; order stays 0..P-1
+    for (int g = 0; g < P; g += PMAX) {
+      uint4 v[PMAX][U];
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        const int i = base + u * kThreads;
-        if (i < nv) v[u] = ld_ring(sp + i);
+      for (int s = 0; s < PMAX; ++s) {
+        const int src = g + s;
+        if (src < P && ((mask >> src) & 1u)) {
+          const uint4* sp = reinterpret_cast<const uint4*>(rows + (long long)src * rowStride);
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int i = base + u * kThreads;
+            if (i < nv) v[s][u] = ld_ring(sp + i);
+          }
+        }
       }
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        const int i = base + u * kThreads;
-        if (i < nv) {
-          float f[V];
-          Elem<T>::unpack(v[u], f);
+      for (int s = 0; s < PMAX; ++s) {
+        const int src = g + s;
+        if (src < P && ((mask >> src) & 1u)) {
 #pragma unroll
-          for (int k = 0; k < V; ++k) acc[u][k] += f[k];
+          for (int u = 0; u < U; ++u) {
+            float f[V];
+            Elem<T>::unpack(v[s][u], f);
+#pragma unroll
+            for (int k = 0; k < V; ++k) acc[u][k] += f[k];
+          }
         }
       }
     }
-    uint4 outv[kUnroll];
+    uint4 outv[U];
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
+    for (int u = 0; u < U; ++u) {
       if (divisor != 1.f) {
 #pragma unroll
         for (int k = 0; k < V; ++k) acc[u][k] = acc[u][k] / divisor;
@@ -220,23 +268,37 @@ __device__ __forceinline__ void reduceTile(const AarRankParams& p, const AarLayo
         const int dest = (i2 + p.rank) % P;
         uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<T*>(regionOf(p, dest) + l.reduceOff) + outElemOff);
 #pragma unroll
-        for (int u = 0; u < kUnroll; ++u) {
+        for (int u = 0; u < U; ++u) {
           const int i = base + u * kThreads;
           if (i < nv) st_peer(op + i, outv[u]);
         }
       }
     } else {
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
+      for (int u = 0; u < U; ++u) {
         const int i = base + u * kThreads;
         if (i < nv) st_stream(reinterpret_cast<uint4*>(localOut) + i, outv[u]);
       }
     }
   }
+}
+
+template <typename T, bool kBcast>
+__device__ __forceinline__ void reduceSpan(const AarRankParams& p, const AarLayout& l, const T* rows, long long rowStride,
+                                           long long outElemOff, T* localOut, int n, unsigned mask, float divisor, bool vecOk) {
+  constexpr int V = Elem<T>::kPerVec;
+  const int P = l.P;
+  const int nv = vecOk ? n / V : 0;
+  if (nv > 0) {
+    // 8 x 16-byte loads in flight per thread in every variant (64 KiB per CTA)
+    if (P <= 2) reduceSpanVec<T, kBcast, 2, 2>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
+    else if (P <= 4) reduceSpanVec<T, kBcast, 4, 2>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
+    else reduceSpanVec<T, kBcast, 8, 1>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
+  }
   for (int i = nv * V + threadIdx.x; i < n; i += kThreads) {
     float a = 0.f;
     for (int src = 0; src < P; ++src)
-      if ((mask >> src) & 1u) a += Elem<T>::toFloat(__ldcg(ringChunk + (long long)src * rowStride + i));
+      if ((mask >> src) & 1u) a += Elem<T>::toFloat(__ldcg(rows + (long long)src * rowStride + i));
     if (divisor != 1.f) a = a / divisor;
     const T r = Elem<T>::fromFloat(a);
     if (kBcast) {
@@ -250,27 +312,53 @@ __device__ __forceinline__ void reduceTile(const AarRankParams& p, const AarLayo
   }
 }
 
+// NVLS (K4): the NVSwitch sums the staged inputs of all ranks (multimem.ld_reduce) and replicates the result into
+// every rank's reduce ring (multimem.st).  Per direction each GPU moves about N(1 + 1/P) bytes instead of 2N(P-1)/P.
 template <typename T>
+__device__ __forceinline__ void nvlsSpan(const char* mcStage, char* mcOut, int nv) {
+  constexpr int U = 4;
+  for (int base = threadIdx.x; base < nv; base += kThreads * U) {
+    uint4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int i = base + u * kThreads;
+      if (i < nv) {
+        if (sizeof(T) == 4) v[u] = multimem_ld_reduce_f32x4(mcStage + (size_t)i * 16);
+        else v[u] = multimem_ld_reduce_bf16x8(mcStage + (size_t)i * 16);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int i = base + u * kThreads;
+      if (i < nv) multimem_st_x4(mcOut + (size_t)i * 16, v[u]);
+    }
+  }
+}
+
+template <typename T, bool kNvls>
 __device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
-  const int P = l.P, C = l.C, Tm = l.tilesPerChunk;
+  const int P = l.P, C = l.C;
   const int myChunks = numChunks(l, p.rank);
   if (myChunks == 0) return;
   const int slot = p.round % l.L;
   const uint64_t epoch = (uint64_t)(p.round + 1);
   char* my = regionOf(p, p.rank);
   const bool vecOk = geomVecOk<T>(l);
-  const long long total = (long long)myChunks * Tm;
+  const SegPlan plan(l, myChunks, nctas);
+  const int S = plan.segs, segElems = plan.segElems(l);
+  const long long total = (long long)myChunks * S;
   for (long long idx = cta; idx < total; idx += nctas) {
-    const int t = (int)(idx % Tm);
-    const int c = (int)(idx / Tm);
+    const int s = (int)(idx % S);
+    const int c = (int)(idx / S);
     const int clen = chunkLen(l, p.rank, c);
-    const int off = t * l.tileElems;
+    const int off = s * segElems;
     if (off >= clen) continue;
     if (sm.k2Chunk != c) {
       __syncthreads();  // everybody has read the previous mask
       if (threadIdx.x < 32) {
         unsigned m = chunkDecision(p, l, reinterpret_cast<uint64_t*>(my + l.k2DecOff) + (long long)slot * C + c,
-                                   reinterpret_cast<const uint32_t*>(my + l.sflagOff) + ((long long)slot * C + c) * AAR_MAXP);
+                                   reinterpret_cast<const uint32_t*>(my + l.sflagOff) + ((long long)slot * C + c) * AAR_MAXP,
+                                   kNvls ? P : p.minRequired);
         if (threadIdx.x == 0) {
           sm.k2Mask = m;
           sm.k2Chunk = c;
@@ -280,17 +368,25 @@ __device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int
     }
     const unsigned mask = sm.k2Mask;
     const int count = __popc(mask);
-    const float divisor = ((p.flags & AAR_FLAG_NORMALIZE) && count > 1) ? (float)count : 1.f;
-    const int n = min(l.tileElems, clen - off);
-    const T* ringChunk = reinterpret_cast<const T*>(my + l.scatterOff) + (long long)slot * P * l.blkStride + (long long)c * l.maxChunk + off;
+    const int n = min(segElems, clen - off);
     const long long outElemOff = ((long long)slot * P + p.rank) * l.blkStride + (long long)c * l.maxChunk + off;
-    reduceTile<T, true>(p, l, ringChunk, l.blkStride, outElemOff, nullptr, n, mask, divisor, vecOk);
+    if (kNvls) {
+      // the switch sums every bound GPU: only valid when all P contributed (the launcher enforces thresholds = 1)
+      const char* mcStage = reinterpret_cast<const char*>(p.mcRegion) + l.stageOff +
+                            ((long long)slot * paddedData(l) + blockStart(l, p.rank) + (long long)c * l.maxChunk + off) * sizeof(T);
+      char* mcOut = reinterpret_cast<char*>(p.mcRegion) + l.reduceOff + outElemOff * sizeof(T);
+      nvlsSpan<T>(mcStage, mcOut, n / Elem<T>::kPerVec);
+    } else {
+      const float divisor = ((p.flags & AAR_FLAG_NORMALIZE) && count > 1) ? (float)count : 1.f;
+      const T* rows = reinterpret_cast<const T*>(my + l.scatterOff) + (long long)slot * P * l.blkStride + (long long)c * l.maxChunk + off;
+      reduceSpan<T, true>(p, l, rows, l.blkStride, outElemOff, nullptr, n, mask, divisor, vecOk);
+    }
     __syncthreads();
     if (threadIdx.x == 0) {
       __threadfence_system();
       unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k2CtrOff) + c;
       const unsigned old = atomicAdd(ctr, 1u);
-      if (old + 1 == (unsigned)numTiles(l, clen)) {  // last tile of this "ReduceBlock": tell every peer, count included
+      if (old + 1 == plan.liveSegs(l, clen)) {  // last segment of this "ReduceBlock": tell every peer, count included
         atomicExch(ctr, 0u);
         __threadfence_system();
         const uint64_t word = (epoch << 32) | (uint64_t)count;
@@ -331,7 +427,6 @@ __device__ void retireRound(const AarRankParams& p, const AarLayout& l, int ncta
 // One CTA becomes the leader of the round: it counts reduced-chunk arrivals against minChunksRequired
 // (DataBuffer.scala:69-75 with the true chunk total, B3), snapshots which chunks made it together with their
 // contributor counts (B5), and publishes the snapshot; every CTA then gathers from that one snapshot.
-template <typename T>
 __device__ void gatherDecision(const AarRankParams& p, const AarLayout& l, int slot, Smem& sm) {
   char* my = regionOf(p, p.rank);
   uint64_t* word = reinterpret_cast<uint64_t*>(my + l.k3DecOff) + slot;
@@ -400,26 +495,35 @@ __device__ void gatherDecision(const AarRankParams& p, const AarLayout& l, int s
 
 template <typename T>
 __device__ void phaseGather(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
-  const int P = l.P, C = l.C, Tm = l.tilesPerChunk;
+  const int P = l.P, C = l.C;
   const int slot = p.round % l.L;
   char* my = regionOf(p, p.rank);
-  gatherDecision<T>(p, l, slot, sm);
+  gatherDecision(p, l, slot, sm);
   const int* counts = reinterpret_cast<const int*>(my + l.countsOff) + (long long)slot * l.totalChunks;
-  const bool vecOk = geomVecOk<T>(l) && (reinterpret_cast<uintptr_t>(p.output) % 16 == 0);
-  const long long total = (long long)P * C * Tm;
+  // AAR_FLAG_VIEW_OUTPUT: the caller consumes the ring slot itself ([P][blkStride] == the flushed vector when
+  // blkStride == stepSize), stream-ordered; only chunks that never arrived are touched (zero-filled in place).
+  const bool view = (p.flags & AAR_FLAG_VIEW_OUTPUT) != 0;
+  const bool vecOk = geomVecOk<T>(l) && (view || reinterpret_cast<uintptr_t>(p.output) % 16 == 0);
+  const SegPlan plan(l, (long long)P * C, nctas);
+  const int S = plan.segs, segElems = plan.segElems(l);
+  const long long total = (long long)P * C * S;
   for (long long idx = cta; idx < total; idx += nctas) {
-    const int t = (int)(idx % Tm);
-    const int c = (int)((idx / Tm) % C);
-    const int owner = (int)(idx / ((long long)Tm * C));
+    const int s = (int)(idx % S);
+    const int c = (int)((idx / S) % C);
+    const int owner = (int)(idx / ((long long)S * C));
     const int clen = chunkLen(l, owner, c);
-    const int off = t * l.tileElems;
+    const int off = s * segElems;
     if (off >= clen) continue;
-    const int n = min(l.tileElems, clen - off);
-    T* dst = reinterpret_cast<T*>(p.output) + blockStart(l, owner) + (long long)c * l.maxChunk + off;
+    const int n = min(segElems, clen - off);
     const int cnt = __ldcg(counts + owner * C + c);
+    T* ring = reinterpret_cast<T*>(my + l.reduceOff) + ((long long)slot * P + owner) * l.blkStride + (long long)c * l.maxChunk + off;
+    if (view) {
+      if (cnt < 0) zeroTile<T>(ring, n, vecOk);
+      continue;
+    }
+    T* dst = reinterpret_cast<T*>(p.output) + blockStart(l, owner) + (long long)c * l.maxChunk + off;
     if (cnt >= 0) {
-      const T* src = reinterpret_cast<const T*>(my + l.reduceOff) + ((long long)slot * P + owner) * l.blkStride + (long long)c * l.maxChunk + off;
-      copyTile<T, false, true>(dst, src, n, vecOk);
+      copyTile<T, false, true>(dst, ring, n, vecOk);
     } else {
       zeroTile<T>(dst, n, vecOk);  // chunks whose ReduceBlock never arrived stay zero (AllreduceWorker.scala:183)
     }
@@ -431,18 +535,13 @@ __device__ void phaseGather(const AarRankParams& p, const AarLayout& l, int cta,
 // Small messages are latency-bound: one hop instead of two.  Every rank pushes its whole vector into slot
 // [round % L][src] of every peer's one-shot buffer (+ one arrival flag per peer), then sums the arrived set locally.
 // thReduce decides how many sources to wait for; thComplete has nothing left to wait for.
-__device__ __forceinline__ long long oneshotStride(const AarLayout& l) {
-  const int V = 16 / l.elemSize;
-  return ((long long)l.dataSize + V - 1) / V * V;
-}
-
 template <typename T>
 __device__ void phaseOneshotPush(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
   if (p.flags & AAR_FLAG_SKIP_SCATTER) return;
   const int P = l.P;
   const int slot = p.round % l.L;
   const int Tn = numTiles(l, l.dataSize);
-  const long long stride = oneshotStride(l);
+  const long long stride = paddedData(l);
   char* my = regionOf(p, p.rank);
   const bool vecOk = reinterpret_cast<uintptr_t>(p.input) % 16 == 0;
   for (long long idx = cta; idx < (long long)P * Tn; idx += nctas) {
@@ -472,11 +571,11 @@ __device__ void phaseOneshotReduce(const AarRankParams& p, const AarLayout& l, i
   const int P = l.P;
   const int slot = p.round % l.L;
   const int Tn = numTiles(l, l.dataSize);
-  const long long stride = oneshotStride(l);
+  const long long stride = paddedData(l);
   char* my = regionOf(p, p.rank);
   if (threadIdx.x < 32) {
     unsigned m = chunkDecision(p, l, reinterpret_cast<uint64_t*>(my + l.k2DecOff) + (long long)slot * l.C,
-                               reinterpret_cast<const uint32_t*>(my + l.oneshotFlagOff) + slot * AAR_MAXP);
+                               reinterpret_cast<const uint32_t*>(my + l.oneshotFlagOff) + slot * AAR_MAXP, p.minRequired);
     if (threadIdx.x == 0) sm.k2Mask = m;
   }
   __syncthreads();
@@ -490,7 +589,7 @@ __device__ void phaseOneshotReduce(const AarRankParams& p, const AarLayout& l, i
     const int off = t * l.tileElems;
     const int n = min(l.tileElems, l.dataSize - off);
     const T* rows = reinterpret_cast<const T*>(my + l.oneshotOff) + (long long)slot * P * stride + off;
-    reduceTile<T, false>(p, l, rows, stride, 0, reinterpret_cast<T*>(p.output) + off, n, mask, divisor, vecOk);
+    reduceSpan<T, false>(p, l, rows, stride, 0, reinterpret_cast<T*>(p.output) + off, n, mask, divisor, vecOk);
   }
   retireRound(p, l, nctas);
 }
@@ -508,33 +607,16 @@ __device__ __forceinline__ void initSmem(Smem& sm) {
   __syncthreads();
 }
 
-template <typename T>
-__global__ void __launch_bounds__(kThreads, 1) scatterKernel(const AarRankParams p, const AarLayout l) {
+// phases: bit 0 = scatter, bit 1 = reduce+broadcast, bit 2 = gather.  7 = one launch per round per rank: the three
+// phases back to back; chunk flags let a CTA start reducing chunk c as soon as its contributors landed while other
+// CTAs are still pushing later chunks.
+template <typename T, bool kNvls>
+__global__ void __launch_bounds__(kThreads, 1) roundKernel(const AarRankParams p, const AarLayout l, int phases) {
   __shared__ Smem sm;
   initSmem(sm);
-  phaseScatter<T>(p, l, blockIdx.x, gridDim.x, sm);
-}
-template <typename T>
-__global__ void __launch_bounds__(kThreads, 1) reduceBcastKernel(const AarRankParams p, const AarLayout l) {
-  __shared__ Smem sm;
-  initSmem(sm);
-  phaseReduceBcast<T>(p, l, blockIdx.x, gridDim.x, sm);
-}
-template <typename T>
-__global__ void __launch_bounds__(kThreads, 1) gatherKernel(const AarRankParams p, const AarLayout l) {
-  __shared__ Smem sm;
-  initSmem(sm);
-  phaseGather<T>(p, l, blockIdx.x, gridDim.x, sm);
-}
-// One launch per round per rank: the three phases back to back; chunk flags let a CTA start reducing chunk c as soon
-// as its contributors landed while other CTAs are still pushing later chunks.
-template <typename T>
-__global__ void __launch_bounds__(kThreads, 1) roundFusedKernel(const AarRankParams p, const AarLayout l) {
-  __shared__ Smem sm;
-  initSmem(sm);
-  phaseScatter<T>(p, l, blockIdx.x, gridDim.x, sm);
-  phaseReduceBcast<T>(p, l, blockIdx.x, gridDim.x, sm);
-  phaseGather<T>(p, l, blockIdx.x, gridDim.x, sm);
+  if (phases & 1) phaseScatter<T, kNvls>(p, l, blockIdx.x, gridDim.x, sm);
+  if (phases & 2) phaseReduceBcast<T, kNvls>(p, l, blockIdx.x, gridDim.x, sm);
+  if (phases & 4) phaseGather<T>(p, l, blockIdx.x, gridDim.x, sm);
 }
 
 template <typename T>
@@ -562,44 +644,42 @@ int residentGrid(K kernel, int want) {
   return want < cap ? want : cap;
 }
 
-template <typename K, typename... Extra>
-int launch(K kernel, const AarRankParams* p, const AarLayout* l, int grid, void* stream, const char* what, Extra... extra) {
+template <typename K>
+int launch(K kernel, const AarRankParams* p, const AarLayout* l, int grid, void* stream, const char* what, int phases) {
   if (!p || !l) return aar_host::fail(AAR_EINVAL, "%s: null params", what);
   if (p->rank < 0 || p->rank >= l->P || l->P > AAR_MAXP) return aar_host::fail(AAR_EINVAL, "%s: bad rank %d for P=%d", what, p->rank, l->P);
   // every CTA may wait on work that another CTA of the same grid still has to do: the grid must be co-resident
   int g = residentGrid(kernel, grid);
   if (g <= 0) return aar_host::fail(AAR_ECUDA, "%s: occupancy query failed: %s", what, cudaGetErrorString(cudaGetLastError()));
-  kernel<<<g, kThreads, 0, (cudaStream_t)stream>>>(*p, *l, extra...);
+  kernel<<<g, kThreads, 0, (cudaStream_t)stream>>>(*p, *l, phases);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return aar_host::fail(AAR_ECUDA, "%s: launch failed: %s", what, cudaGetErrorString(e));
   return AAR_OK;
 }
 
-#define AAR_DISPATCH(kernelT, what)                                                              \
-  do {                                                                                           \
-    if (lay->dtype == AAR_F32) return launch(kernelT<float>, p, lay, grid, stream, what);        \
-    if (lay->dtype == AAR_BF16) return launch(kernelT<__nv_bfloat16>, p, lay, grid, stream, what); \
-    return aar_host::fail(AAR_EINVAL, "%s: unknown dtype %d", what, lay->dtype);                 \
-  } while (0)
+int launchRound(const AarRankParams* p, const AarLayout* lay, int grid, void* stream, const char* what, int phases) {
+  if (!lay) return aar_host::fail(AAR_EINVAL, "%s: null layout", what);
+  if (lay->dtype == AAR_F32) return launch(roundKernel<float, false>, p, lay, grid, stream, what, phases);
+  if (lay->dtype == AAR_BF16) return launch(roundKernel<__nv_bfloat16, false>, p, lay, grid, stream, what, phases);
+  return aar_host::fail(AAR_EINVAL, "%s: unknown dtype %d", what, lay->dtype);
+}
 
 }  // namespace
 
-extern "C" {
-
-__attribute__((visibility("default"))) int aar_launch_scatter(const AarRankParams* p, const AarLayout* lay, int grid, void* stream) {
-  AAR_DISPATCH(scatterKernel, "aar_launch_scatter");
+AAR_API int aar_launch_scatter(const AarRankParams* p, const AarLayout* lay, int grid, void* stream) {
+  return launchRound(p, lay, grid, stream, "aar_launch_scatter", 1);
 }
-__attribute__((visibility("default"))) int aar_launch_reduce_bcast(const AarRankParams* p, const AarLayout* lay, int grid, void* stream) {
-  AAR_DISPATCH(reduceBcastKernel, "aar_launch_reduce_bcast");
+AAR_API int aar_launch_reduce_bcast(const AarRankParams* p, const AarLayout* lay, int grid, void* stream) {
+  return launchRound(p, lay, grid, stream, "aar_launch_reduce_bcast", 2);
 }
-__attribute__((visibility("default"))) int aar_launch_gather(const AarRankParams* p, const AarLayout* lay, int grid, void* stream) {
-  AAR_DISPATCH(gatherKernel, "aar_launch_gather");
+AAR_API int aar_launch_gather(const AarRankParams* p, const AarLayout* lay, int grid, void* stream) {
+  return launchRound(p, lay, grid, stream, "aar_launch_gather", 4);
 }
-__attribute__((visibility("default"))) int aar_launch_round_fused(const AarRankParams* p, const AarLayout* lay, int grid, void* stream) {
-  AAR_DISPATCH(roundFusedKernel, "aar_launch_round_fused");
+AAR_API int aar_launch_round_fused(const AarRankParams* p, const AarLayout* lay, int grid, void* stream) {
+  return launchRound(p, lay, grid, stream, "aar_launch_round_fused", 7);
 }
 
-__attribute__((visibility("default"))) int aar_launch_oneshot(const AarRankParams* p, const AarLayout* lay, int phase, int grid, void* stream) {
+AAR_API int aar_launch_oneshot(const AarRankParams* p, const AarLayout* lay, int phase, int grid, void* stream) {
   if (!lay || lay->oneshotOff == 0) return aar_host::fail(AAR_EINVAL, "aar_launch_oneshot: layout has no one-shot buffers");
   if (phase < 0 || phase > 2) return aar_host::fail(AAR_EINVAL, "aar_launch_oneshot: phase must be 0, 1 or 2");
   if (lay->dtype == AAR_F32) return launch(oneshotKernel<float>, p, lay, grid, stream, "aar_launch_oneshot", phase);
@@ -607,8 +687,23 @@ __attribute__((visibility("default"))) int aar_launch_oneshot(const AarRankParam
   return aar_host::fail(AAR_EINVAL, "aar_launch_oneshot: unknown dtype %d", lay->dtype);
 }
 
-__attribute__((visibility("default"))) int aar_local_round(const AarRankParams* params, int nranks, const AarLayout* lay, unsigned skipMask,
-                                                           int grid, void* stream) {
+AAR_API int aar_launch_nvls(const AarRankParams* p, const AarLayout* lay, int phases, int grid, void* stream) {
+  const char* what = "aar_launch_nvls";
+  if (!p || !lay) return aar_host::fail(AAR_EINVAL, "%s: null params", what);
+  if (!p->mcRegion || lay->stageOff == 0) return aar_host::fail(AAR_EUNSUPPORTED, "%s: needs a multicast mapping and the staging area", what);
+  if (phases <= 0 || phases > 7) return aar_host::fail(AAR_EINVAL, "%s: phases is a bit mask 1..7", what);
+  const int V = 16 / lay->elemSize;
+  if (lay->stepSize % V || lay->maxChunk % V || lay->dataSize % V)
+    return aar_host::fail(AAR_EUNSUPPORTED, "%s: multimem needs 16-byte aligned blocks and chunks", what);
+  const int total = lay->totalChunks;
+  if (p->minRequired != lay->P || p->minChunksRequired != total || (p->flags & (AAR_FLAG_SKIP_SCATTER | AAR_FLAG_EXACT_QUORUM | AAR_FLAG_NORMALIZE)))
+    return aar_host::fail(AAR_EUNSUPPORTED, "%s: the switch sums every bound GPU, so thresholds must be 1.0 (use the P2P paths otherwise)", what);
+  if (lay->dtype == AAR_F32) return launch(roundKernel<float, true>, p, lay, grid, stream, what, phases);
+  if (lay->dtype == AAR_BF16) return launch(roundKernel<__nv_bfloat16, true>, p, lay, grid, stream, what, phases);
+  return aar_host::fail(AAR_EINVAL, "%s: unknown dtype %d", what, lay->dtype);
+}
+
+AAR_API int aar_local_round(const AarRankParams* params, int nranks, const AarLayout* lay, unsigned skipMask, int grid, void* stream) {
   if (!params || !lay || nranks != lay->P) return aar_host::fail(AAR_EINVAL, "aar_local_round: need one params entry per rank");
   // Phase order matters on a single device: no kernel may wait for a later launch.
   for (int r = 0; r < nranks; ++r) {
@@ -627,11 +722,9 @@ __attribute__((visibility("default"))) int aar_local_round(const AarRankParams* 
   return AAR_OK;
 }
 
-__attribute__((visibility("default"))) int aar_launch_delay(unsigned long long ns, void* stream) {
+AAR_API int aar_launch_delay(unsigned long long ns, void* stream) {
   delayKernel<<<1, 1, 0, (cudaStream_t)stream>>>(ns);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return aar_host::fail(AAR_ECUDA, "aar_launch_delay: %s", cudaGetErrorString(e));
   return AAR_OK;
 }
-
-}  // extern "C"

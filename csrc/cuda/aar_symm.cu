@@ -97,7 +97,7 @@ AAR_API int aar_layout_compute(int P, int dataSize, int maxChunkSize, int maxLag
   l.scatterOff = take(ring);
   l.reduceOff = take(ring);
   if (oneshotMaxElems > 0 && dataSize <= oneshotMaxElems) l.oneshotOff = take((uint64_t)l.L * P * alignUp(dataSize, V) * l.elemSize) + 0;
-  if (withStage) l.stageOff = take((uint64_t)2 * alignUp(dataSize, V) * l.elemSize);
+  if (withStage) l.stageOff = take((uint64_t)l.L * alignUp(dataSize, V) * l.elemSize);
   // offsets of 0 mean "absent" for the optional sections; the scatter ring legitimately sits at 0
   l.ctrlBytes = off;
   l.sflagOff = take((uint64_t)l.L * l.C * AAR_MAXP * 4);

@@ -32,6 +32,7 @@ extern "C" {
 #define AAR_FLAG_EXACT_QUORUM 2u /* use exactly minRequired contributors (lowest ids), like the reference's == firing */
 #define AAR_FLAG_FORCE 4u       /* K8: do not wait, take whatever has arrived (catch-up, AllreduceWorker.scala:91-97) */
 #define AAR_FLAG_SKIP_SCATTER 8u /* fused kernel: this rank contributes nothing this round (fault injection) */
+#define AAR_FLAG_VIEW_OUTPUT 16u /* K3 does not copy: the caller reads the reduce-ring slot itself, stream-ordered */
 
 /* bits of the device status word (AarLayout.statusOff, word 0) */
 #define AAR_ST_TIMEOUT_SCATTER 1u
@@ -60,7 +61,7 @@ typedef struct AarLayout {
   uint64_t statusOff;        /* u32 [16]                        local: status bits, counters */
   uint64_t oneshotOff;       /* T   [L][P(src)][dataSize] + u32 [L][AAR_MAXP] flags; 0 if not allocated */
   uint64_t oneshotFlagOff;
-  uint64_t stageOff;         /* T   [2][dataSize] staging for the NVLS path; 0 if not allocated */
+  uint64_t stageOff;         /* T   [L][dataSize] staging for the NVLS path; 0 if not allocated */
   uint64_t barrierOff;       /* u32 [8] NVLS barrier counters */
   uint64_t ctrlBytes;        /* first byte of the control area that must be zeroed at allocation */
   uint64_t regionBytes;      /* total, rounded up to 2 MiB */
@@ -104,8 +105,8 @@ int aar_launch_round_fused(const AarRankParams* p, const AarLayout* lay, int gri
  * single-GPU emulation can order them; phase = 0 push, 1 reduce, 2 both. */
 int aar_launch_oneshot(const AarRankParams* p, const AarLayout* lay, int phase, int grid, void* stream);
 /* K4 NVLS: multimem.ld_reduce over the staged inputs + multimem.st of the result (thresholds must be 1.0).
- * phase = 0 stage+arrive, 1 reduce+broadcast, 2 gather, 3 all. */
-int aar_launch_nvls(const AarRankParams* p, const AarLayout* lay, int phase, int grid, void* stream);
+ * phases is a bit mask: 1 stage + arrival flags, 2 in-switch reduce + multicast store, 4 gather; 7 = one launch. */
+int aar_launch_nvls(const AarRankParams* p, const AarLayout* lay, int phases, int grid, void* stream);
 
 /* Single-device cluster emulation: P ranks' regions live on the current device; runs one full round for all
  * ranks in phase order (all K1, all K2, all K3) on `stream`.  params[r] describes rank r.  skipMask bit r set =

@@ -1,0 +1,88 @@
+"""Public Python API on the CPU data plane (AllreduceMaster + AllreduceWorker(backend="cpu")) and the fd rendezvous."""
+import multiprocessing as mp
+import os
+import threading
+
+import numpy as np
+import pytest
+
+from akka_allreduce_b200 import AllreduceMaster, AllreduceWorker, AllReduceInput, AllReduceInputRequest, AllReduceOutput, load_settings
+
+
+def test_master_and_cpu_workers_through_the_public_api():
+    P, n, rounds = 3, 12, 6
+    master = AllreduceMaster(P, 1.0, 1.0, 1.0, max_lag=1, data_size=n, max_round=rounds - 1, max_chunk_size=3)
+    master.start(60)
+    got = [[] for _ in range(P)]
+
+    def make(i):
+        def source(req: AllReduceInputRequest) -> AllReduceInput:
+            return AllReduceInput(np.arange(n, dtype=np.float32) * (i + 1) + req.iteration)
+
+        def sink(out: AllReduceOutput) -> None:
+            got[i].append((out.iteration, np.array(out.data), np.array(out.count)))
+
+        return AllreduceWorker(source, sink, backend="cpu")
+
+    workers = [make(i) for i in range(P)]
+    threads = [threading.Thread(target=w.run, args=("127.0.0.1", master.port, 60)) for w in workers]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(90)
+    assert master.join(30)
+    ids = sorted(w.id for w in workers)
+    assert ids == [0, 1, 2]
+    # sources differ per worker: sum over workers of arange * (k+1) + it, whatever id each thread was given
+    for i in range(P):
+        assert [it for it, _, _ in got[i]] == list(range(rounds))
+        for it, data, count in got[i]:
+            np.testing.assert_array_equal(data, np.arange(n, dtype=np.float32) * 6 + 3 * it)
+            assert (count == P).all()
+    assert master.metrics()["rounds_started"] == rounds
+
+
+def test_load_settings_layers_overrides_over_the_shipped_file():
+    s = load_settings(overrides={"allreduce.total-workers": 8, "allreduce.data-size": 16777216, "allreduce.max-chunk-size": 1048576,
+                                 "allreduce.th-reduce": 1.0, "allreduce.th-complete": 1.0, "allreduce.dtype": "bf16"})
+    assert (s.master.total_workers, s.master.data_size, s.master.max_chunk_size) == (8, 16777216, 1048576)
+    assert s.master.max_lag == 1 and s.dtype == "bf16" and s.port == 2551
+
+
+def _rdv_proc(rank, world, session, q):
+    from akka_allreduce_b200.parallel.symmetric import UnixRendezvous
+
+    rdv = UnixRendezvous(rank, world, session, timeout=30)
+    r, w = os.pipe()
+    os.write(w, f"hello from {rank}".encode())
+    os.close(w)
+    fds = rdv.all_gather_fds(r)
+    texts = []
+    for k, fd in enumerate(fds):
+        if k == rank:
+            texts.append(None)
+            continue
+        texts.append(None)  # a pipe can be read once; only rank (k+1) % world reads rank k's pipe
+    reader_of = (rank - 1) % world
+    msg = os.read(fds[reader_of], 100).decode()
+    blobs = rdv.all_gather_bytes(bytes([rank]) * (rank + 1))
+    b = rdv.broadcast_fd(r if rank == 0 else None)
+    rdv.barrier()
+    q.put((rank, msg, [len(x) for x in blobs], b >= 0))
+    rdv.close()
+
+
+def test_unix_rendezvous_passes_fds_between_processes():
+    world = 3
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    session = f"test_{os.getpid()}"
+    procs = [ctx.Process(target=_rdv_proc, args=(r, world, session, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=60) for _ in range(world))
+    for p in procs:
+        p.join(30)
+    for rank, msg, lens, ok in res:
+        assert msg == f"hello from {(rank - 1) % world}"
+        assert lens == [1, 2, 3] and ok

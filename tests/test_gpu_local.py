@@ -35,7 +35,7 @@ def oracle(inputs, P, n, chunk, contributors, dtype, normalize=False, missing_ow
             for src in srcs:  # peer-index order, from 0.0f
                 acc = acc + inputs[src][s:e].float()
             if normalize and len(srcs) > 1:
-                acc = acc / float(len(srcs))
+                acc = torch.div(acc, torch.full_like(acc, float(len(srcs))))  # IEEE division (tensor / python scalar multiplies by 1/x)
             out[s:e] = acc.to(dtype)
             counts.append(len(srcs))
     return out, torch.tensor(counts, dtype=torch.int32, device=out.device)
@@ -197,7 +197,7 @@ def test_oneshot_threshold():
     cl = cluster(P, n, n // P, th_reduce=0.75, oneshot=True)
     xs = make_inputs(P, n, torch.float32, 50)
     outs, counts = cl.run_oneshot(0, xs, skip=[1])
-    acc = (torch.zeros_like(acc) + xs[0]) + xs[2] + xs[3]
+    acc = (torch.zeros_like(xs[0]) + xs[0]) + xs[2] + xs[3]
     torch.cuda.synchronize()
     assert torch.equal(outs[1], acc) and int(counts[1][0]) == 3
 
