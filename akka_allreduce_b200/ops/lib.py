@@ -11,7 +11,8 @@ from pathlib import Path
 
 AAR_MAXP = 16
 AAR_F32, AAR_BF16 = 0, 1
-FLAG_NORMALIZE, FLAG_EXACT_QUORUM, FLAG_FORCE, FLAG_SKIP_SCATTER, FLAG_VIEW_OUTPUT = 1, 2, 4, 8, 16
+FLAG_NORMALIZE, FLAG_EXACT_QUORUM, FLAG_FORCE, FLAG_SKIP_SCATTER, FLAG_VIEW_OUTPUT, FLAG_TRACE = 1, 2, 4, 8, 16, 32
+TRACE_CTAS, TRACE_MARKS = 512, 8
 ST_TIMEOUT_SCATTER, ST_TIMEOUT_REDUCE, ST_TIMEOUT_GATHER, ST_PUSH_DROPPED = 1, 2, 4, 8
 
 
@@ -25,7 +26,7 @@ class AarLayout(C.Structure):
         ("peerBaseOff", C.c_uint64), ("k1DecOff", C.c_uint64), ("k1CtrOff", C.c_uint64), ("k2DecOff", C.c_uint64),
         ("k2CtrOff", C.c_uint64), ("k3DecOff", C.c_uint64), ("k3CtrOff", C.c_uint64), ("countsOff", C.c_uint64),
         ("statusOff", C.c_uint64), ("oneshotOff", C.c_uint64), ("oneshotFlagOff", C.c_uint64), ("stageOff", C.c_uint64),
-        ("barrierOff", C.c_uint64), ("ctrlBytes", C.c_uint64), ("regionBytes", C.c_uint64),
+        ("barrierOff", C.c_uint64), ("traceOff", C.c_uint64), ("ctrlBytes", C.c_uint64), ("regionBytes", C.c_uint64),
     ]
 
 
@@ -74,6 +75,7 @@ def load():
         "aar_launch_reduce_bcast": [P(AarRankParams), P(AarLayout), C.c_int, C.c_void_p],
         "aar_launch_gather": [P(AarRankParams), P(AarLayout), C.c_int, C.c_void_p],
         "aar_launch_round_fused": [P(AarRankParams), P(AarLayout), C.c_int, C.c_void_p],
+        "aar_launch_round_pipelined": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_void_p],
         "aar_launch_oneshot": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_void_p],
         "aar_launch_nvls": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_void_p],
         "aar_local_round": [P(AarRankParams), C.c_int, P(AarLayout), C.c_uint, C.c_int, C.c_void_p],
@@ -94,6 +96,8 @@ def load():
         "aar_device_sm_count": [C.c_int, P(C.c_int)],
         "aar_enable_peer_access": [C.c_int, C.c_int],
         "aar_launch_delay": [C.c_ulonglong, C.c_void_p],
+        "aar_bench_all2all": [C.c_int, C.c_int, C.c_int, P(C.c_void_p), C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p],
+        "aar_bench_link": [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p],
     }
     for name, argtypes in sigs.items():
         fn = getattr(lib, name, None)

@@ -63,6 +63,9 @@ class RoundEngine:
         self._pref = C.byref(self.params)
         self.rounds_enqueued = 0
         self.launches = 0
+        # CTA role split of the pipelined kernels (measured on 8xB200, profiles/r1_phase_bench_*.txt)
+        self.split = 32 | (48 << 16)      # nPush | nReduce << 16; the rest gather
+        self.nvls_reduce_ctas = 16
 
     # ------------------------------------------------------------------ construction helpers
     @classmethod
@@ -83,9 +86,14 @@ class RoundEngine:
         if algo == "auto":
             if lay.oneshotOff and nbytes <= ONESHOT_MAX_BYTES and lay.P > 1:
                 return "oneshot"
-            if self.mc_ptr and lay.stageOff and th_reduce >= 1.0 and th_complete >= 1.0 and hasattr(self.lib, "aar_launch_nvls"):
+            # In-switch reduction moves N(1 + 1/P) bytes per direction against 2N(P-1)/P for two-shot P2P: it only pays
+            # from four GPUs up (at P = 2 it is 1.5N against N).  The switch sums every bound GPU, so thresholds must be 1.
+            V = 16 // lay.elemSize
+            aligned = lay.stepSize % V == 0 and lay.maxChunk % V == 0 and lay.dataSize % V == 0
+            if self.mc_ptr and lay.stageOff and lay.P >= 4 and aligned and th_reduce >= 1.0 and th_complete >= 1.0:
                 return "nvls"
-            return "twoshot"
+            # role-specialised CTAs overlap push / reduce / gather chunk by chunk; with one rank there is nothing to overlap
+            return "pipelined" if lay.P > 1 else "twoshot"
         if algo == "oneshot" and not lay.oneshotOff:
             raise ValueError("algo=oneshot needs a layout with one-shot buffers")
         if algo == "nvls" and not (self.mc_ptr and lay.stageOff):
@@ -118,10 +126,12 @@ class RoundEngine:
         s = C.c_void_p((stream or torch.cuda.current_stream(self.device)).cuda_stream)
         if self.algo == "twoshot":
             L.check(self.lib.aar_launch_round_fused(self._pref, self._lay, self.grid, s), "aar_launch_round_fused")
+        elif self.algo == "pipelined":
+            L.check(self.lib.aar_launch_round_pipelined(self._pref, self._lay, self.grid, self.split, s), "aar_launch_round_pipelined")
         elif self.algo == "oneshot":
             L.check(self.lib.aar_launch_oneshot(self._pref, self._lay, 2, self.grid, s), "aar_launch_oneshot")
         elif self.algo == "nvls":
-            L.check(self.lib.aar_launch_nvls(self._pref, self._lay, 7, self.grid, s), "aar_launch_nvls")
+            L.check(self.lib.aar_launch_nvls(self._pref, self._lay, 7 | (self.nvls_reduce_ctas << 8), self.grid, s), "aar_launch_nvls")
         else:
             raise ValueError(f"unknown algo {self.algo}")
         self.launches += 1

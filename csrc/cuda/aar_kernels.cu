@@ -32,11 +32,17 @@ struct Smem {
   int k3Leader;
   int k3Count;
   int scratch;
+  int gKey, gCnt;               // eager gather: (owner, chunk) whose flag this CTA has already seen, and its count
 };
 
 __device__ __forceinline__ char* regionOf(const AarRankParams& p, int r) { return reinterpret_cast<char*>(p.region[r]); }
 __device__ __forceinline__ uint32_t* statusWord(const AarRankParams& p, const AarLayout& l, int i) {
   return reinterpret_cast<uint32_t*>(regionOf(p, p.rank) + l.statusOff) + i;
+}
+// Tracing (the reference has none): per-CTA %globaltimer stamps at phase boundaries.
+__device__ __forceinline__ void traceMark(const AarRankParams& p, const AarLayout& l, int mark) {
+  if ((p.flags & AAR_FLAG_TRACE) && threadIdx.x == 0 && blockIdx.x < AAR_TRACE_CTAS)
+    reinterpret_cast<unsigned long long*>(regionOf(p, p.rank) + l.traceOff)[blockIdx.x * AAR_TRACE_MARKS + mark] = globaltimer_ns();
 }
 template <typename T>
 __device__ __forceinline__ bool geomVecOk(const AarLayout& l) {
@@ -123,10 +129,13 @@ __device__ void phaseScatter(const AarRankParams& p, const AarLayout& l, int cta
   T* stage = reinterpret_cast<T*>(my + l.stageOff) + (long long)slot * paddedData(l);
   const bool inPlace = kStage && (reinterpret_cast<const T*>(p.input) == stage);  // the source wrote straight into the stage
   const long long total = (long long)C * P * S;
-  // chunk-major, then destination staggered from self (AllreduceWorker.scala:195-196), then segment
+  // chunk-major, then segment, then destination staggered from self (AllreduceWorker.scala:195-196).  Consecutive
+  // units go to different peers so every CTA spreads its pushes over all NVLink destinations; when the grid size is a
+  // multiple of P a CTA would otherwise always draw the same destination, so each pass rotates by one.
+  const bool rotate = (nctas % P) == 0;
   for (long long idx = cta; idx < total; idx += nctas) {
-    const int s = (int)(idx % S);
-    const int i = (int)((idx / S) % P);
+    const int i = (int)((idx % P + (rotate ? idx / nctas : 0)) % P);
+    const int s = (int)((idx / P) % S);
     const int c = (int)(idx / ((long long)S * P));
     const int dest = (i + p.rank) % P;
     const int clen = chunkLen(l, dest, c);
@@ -155,6 +164,9 @@ __device__ void phaseScatter(const AarRankParams& p, const AarLayout& l, int cta
         st_release_sys_u32(flag, epoch);
       }
     }
+    // Nobody starts the next segment before the fence above has drained: the SM-wide write drain would otherwise
+    // wait for the new stores too and the arrival flag of an early chunk would only go out at the end of the phase.
+    __syncthreads();
   }
 }
 
@@ -171,13 +183,16 @@ __device__ unsigned chunkDecision(const AarRankParams& p, const AarLayout& l, ui
   if ((v >> 32) == epoch) return (unsigned)(v & 0xffffffffu);
 
   Deadline dl(p.timeoutNs);
-  unsigned arrived = 0, spins = 0;
+  unsigned arrived = 0, spins = 0, backoff = 32;
   bool forced = false;
+  // Poll with relaxed loads (one 64-byte line holds all P flags) and pay for the acquire once, after the quorum is
+  // seen.  The host doorbell lives across PCIe: look at it rarely (the AAR_FLAG_FORCE bit is checked up front).
   for (;;) {
-    uint32_t f = (lane < l.P) ? ld_acquire_sys_u32(flags + lane) : 0u;
+    uint32_t f = (lane < l.P) ? ld_relaxed_sys_u32(flags + lane) : 0u;
     arrived = __ballot_sync(0xffffffffu, lane < l.P && f == (uint32_t)epoch);
     if (__popc(arrived) >= minRequired) break;
-    if ((spins++ & 15u) == 0) {
+    const bool look = (p.flags & AAR_FLAG_FORCE) || ((++spins & 255u) == 0);
+    if (look) {
       int stop = 0;
       if (lane == 0) {
         if (forcedByHost(p)) stop = 1;
@@ -188,13 +203,15 @@ __device__ unsigned chunkDecision(const AarRankParams& p, const AarLayout& l, ui
         if (stop == 2 && lane == 0) atomicOr(statusWord(p, l, 0), AAR_ST_TIMEOUT_REDUCE);
         forced = true;
         // one more look so the snapshot is as fresh as the decision
-        f = (lane < l.P) ? ld_acquire_sys_u32(flags + lane) : 0u;
+        f = (lane < l.P) ? ld_relaxed_sys_u32(flags + lane) : 0u;
         arrived = __ballot_sync(0xffffffffu, lane < l.P && f == (uint32_t)epoch);
         break;
       }
     }
-    __nanosleep(32);
+    __nanosleep(backoff);
+    if (backoff < 512) backoff *= 2;
   }
+  __threadfence_system();  // acquire: the flagged sources' data is visible to everything after this point
   if ((p.flags & AAR_FLAG_EXACT_QUORUM) && !forced) {
     while (__popc(arrived) > minRequired) arrived &= ~(1u << (31 - __clz(arrived)));  // keep the lowest ids
   }
@@ -316,7 +333,7 @@ __device__ __forceinline__ void reduceSpan(const AarRankParams& p, const AarLayo
 // every rank's reduce ring (multimem.st).  Per direction each GPU moves about N(1 + 1/P) bytes instead of 2N(P-1)/P.
 template <typename T>
 __device__ __forceinline__ void nvlsSpan(const char* mcStage, char* mcOut, int nv) {
-  constexpr int U = 4;
+  constexpr int U = 8;
   for (int base = threadIdx.x; base < nv; base += kThreads * U) {
     uint4 v[U];
 #pragma unroll
@@ -360,6 +377,7 @@ __device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int
                                    reinterpret_cast<const uint32_t*>(my + l.sflagOff) + ((long long)slot * C + c) * AAR_MAXP,
                                    kNvls ? P : p.minRequired);
         if (threadIdx.x == 0) {
+          if (sm.k2Chunk < 0) traceMark(p, l, 2);
           sm.k2Mask = m;
           sm.k2Chunk = c;
         }
@@ -397,6 +415,7 @@ __device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int
         }
       }
     }
+    __syncthreads();  // see phaseScatter: let the fence drain before new stores are issued
   }
 }
 
@@ -447,19 +466,19 @@ __device__ void gatherDecision(const AarRankParams& p, const AarLayout& l, int s
   if (sm.k3Leader) {
     const uint64_t* flags = reinterpret_cast<const uint64_t*>(my + l.rflagOff) + (long long)slot * P * C;
     Deadline dl(p.timeoutNs);
-    unsigned spins = 0;
+    unsigned spins = 0, backoff = 32;
     for (;;) {
       if (threadIdx.x == 0) sm.k3Count = 0;
       __syncthreads();
       int local = 0;
       for (int i = threadIdx.x; i < P * C; i += kThreads) {
         const int owner = i / C, c = i % C;
-        if (c < numChunks(l, owner) && (ld_acquire_sys_u64(flags + i) >> 32) == epoch) ++local;
+        if (c < numChunks(l, owner) && (ld_relaxed_sys_u64(flags + i) >> 32) == epoch) ++local;
       }
       if (local) atomicAdd(&sm.k3Count, local);
       __syncthreads();
       int stop = (sm.k3Count >= p.minChunksRequired) ? 1 : 0;
-      if (!stop && threadIdx.x == 0 && (spins++ & 7u) == 0) {
+      if (!stop && threadIdx.x == 0 && ((p.flags & AAR_FLAG_FORCE) || (++spins & 127u) == 0)) {
         if (forcedByHost(p)) sm.scratch = 1;
         else if (dl.expired()) {
           sm.scratch = 1;
@@ -468,17 +487,20 @@ __device__ void gatherDecision(const AarRankParams& p, const AarLayout& l, int s
       }
       __syncthreads();
       if (stop || sm.scratch) break;
-      __nanosleep(32);
+      __nanosleep(backoff);
+      if (backoff < 512) backoff *= 2;
     }
+    __threadfence_system();  // acquire side of the rflag releases
     // snapshot (a superset of what was counted: anything that landed in between is welcome)
     for (int i = threadIdx.x; i < P * C; i += kThreads) {
       const int owner = i / C, c = i % C;
       if (c >= numChunks(l, owner)) continue;
-      const uint64_t f = ld_acquire_sys_u64(flags + i);
+      const uint64_t f = ld_relaxed_sys_u64(flags + i);
       const int cnt = ((f >> 32) == epoch) ? (int)(f & 0xffffffffu) : -1;
       counts[i] = cnt;  // valid (owner, c) pairs are exactly the indices [0, totalChunks)
       if (p.outCounts) p.outCounts[i] = cnt < 0 ? 0 : cnt;
     }
+    __threadfence_system();  // chunks that landed between the count and the snapshot
     __syncthreads();
     if (threadIdx.x == 0) {
       sm.scratch = 0;
@@ -487,18 +509,24 @@ __device__ void gatherDecision(const AarRankParams& p, const AarLayout& l, int s
     }
   } else {
     if (threadIdx.x == 0) {
-      while (ld_acquire_gpu_u64(word) != done) __nanosleep(64);
+      unsigned backoff = 64;
+      while (ld_acquire_gpu_u64(word) != done) {
+        __nanosleep(backoff);
+        if (backoff < 1024) backoff *= 2;
+      }
+      __threadfence_system();
     }
   }
   __syncthreads();
 }
 
 template <typename T>
-__device__ void phaseGather(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
+__device__ void phaseGatherBody(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
   const int P = l.P, C = l.C;
   const int slot = p.round % l.L;
   char* my = regionOf(p, p.rank);
   gatherDecision(p, l, slot, sm);
+  traceMark(p, l, 4);
   const int* counts = reinterpret_cast<const int*>(my + l.countsOff) + (long long)slot * l.totalChunks;
   // AAR_FLAG_VIEW_OUTPUT: the caller consumes the ring slot itself ([P][blkStride] == the flushed vector when
   // blkStride == stepSize), stream-ordered; only chunks that never arrived are touched (zero-filled in place).
@@ -528,7 +556,78 @@ __device__ void phaseGather(const AarRankParams& p, const AarLayout& l, int cta,
       zeroTile<T>(dst, n, vecOk);  // chunks whose ReduceBlock never arrived stay zero (AllreduceWorker.scala:183)
     }
   }
+}
+
+template <typename T>
+__device__ void phaseGather(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
+  phaseGatherBody<T>(p, l, cta, nctas, sm);
   retireRound(p, l, nctas);
+}
+
+// Eager gather (thComplete = 1.0 only): every chunk is required, so nothing has to be decided -- a CTA copies chunk
+// (owner, c) as soon as its ReduceBlock flag lands, while other chunks are still in flight.  A chunk that never shows
+// up (host-forced round, device timeout) is zero-filled like in phaseGather.
+template <typename T>
+__device__ void phaseGatherEager(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
+  const int P = l.P, C = l.C;
+  const int slot = p.round % l.L;
+  const uint64_t epoch = (uint64_t)(p.round + 1);
+  char* my = regionOf(p, p.rank);
+  const bool view = (p.flags & AAR_FLAG_VIEW_OUTPUT) != 0;
+  const bool vecOk = geomVecOk<T>(l) && (view || reinterpret_cast<uintptr_t>(p.output) % 16 == 0);
+  const SegPlan plan(l, (long long)P * C, nctas);
+  const int S = plan.segs, segElems = plan.segElems(l);
+  const long long total = (long long)P * C * S;
+  const uint64_t* flags = reinterpret_cast<const uint64_t*>(my + l.rflagOff) + (long long)slot * P * C;
+  // chunk-major (chunk c of every owner is reduced at about the same time), owners staggered from self
+  for (long long idx = cta; idx < total; idx += nctas) {
+    const int s = (int)(idx % S);
+    const int owner = ((int)((idx / S) % P) + p.rank) % P;
+    const int c = (int)(idx / ((long long)S * P));
+    const int clen = chunkLen(l, owner, c);
+    const int off = s * segElems;
+    if (off >= clen) continue;
+    const int key = owner * C + c;
+    if (sm.gKey != key) {
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        Deadline dl(p.timeoutNs);
+        unsigned spins = 0, backoff = 32;
+        int cnt = -1;
+        for (;;) {
+          const uint64_t f = ld_relaxed_sys_u64(flags + key);
+          if ((f >> 32) == epoch) {
+            cnt = (int)(f & 0xffffffffu);
+            break;
+          }
+          if ((p.flags & AAR_FLAG_FORCE) || ((++spins & 255u) == 0)) {
+            if (forcedByHost(p)) break;
+            if (dl.expired()) {
+              atomicOr(statusWord(p, l, 0), AAR_ST_TIMEOUT_GATHER);
+              break;
+            }
+          }
+          __nanosleep(backoff);
+          if (backoff < 512) backoff *= 2;
+        }
+        __threadfence_system();
+        sm.gKey = key;
+        sm.gCnt = cnt;
+        if (s == 0 && p.outCounts) p.outCounts[key] = cnt < 0 ? 0 : cnt;
+      }
+      __syncthreads();
+    }
+    const int cnt = sm.gCnt;
+    const int n = min(segElems, clen - off);
+    T* ring = reinterpret_cast<T*>(my + l.reduceOff) + ((long long)slot * P + owner) * l.blkStride + (long long)c * l.maxChunk + off;
+    if (view) {
+      if (cnt < 0) zeroTile<T>(ring, n, vecOk);
+      continue;
+    }
+    T* dst = reinterpret_cast<T*>(p.output) + blockStart(l, owner) + (long long)c * l.maxChunk + off;
+    if (cnt >= 0) copyTile<T, false, true>(dst, ring, n, vecOk);
+    else zeroTile<T>(dst, n, vecOk);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------ K5 one-shot
@@ -603,6 +702,8 @@ __device__ __forceinline__ void initSmem(Smem& sm) {
     sm.k3Leader = 0;
     sm.k3Count = 0;
     sm.scratch = 0;
+    sm.gKey = -1;
+    sm.gCnt = -1;
   }
   __syncthreads();
 }
@@ -614,9 +715,72 @@ template <typename T, bool kNvls>
 __global__ void __launch_bounds__(kThreads, 1) roundKernel(const AarRankParams p, const AarLayout l, int phases) {
   __shared__ Smem sm;
   initSmem(sm);
+  traceMark(p, l, 0);
   if (phases & 1) phaseScatter<T, kNvls>(p, l, blockIdx.x, gridDim.x, sm);
+  traceMark(p, l, 1);
   if (phases & 2) phaseReduceBcast<T, kNvls>(p, l, blockIdx.x, gridDim.x, sm);
+  traceMark(p, l, 3);
   if (phases & 4) phaseGather<T>(p, l, blockIdx.x, gridDim.x, sm);
+  traceMark(p, l, 5);
+}
+
+// Two-shot P2P, one launch per round, CTAs specialised by role so K1, K2 and K3 overlap chunk by chunk:
+//   CTAs [0, nPush)               K1 scatter_push
+//   CTAs [nPush, nPush+nReduce)   K2 reduce_bcast
+//   the rest                      K3 gather (eager per chunk when every chunk is required, else the round decision)
+template <typename T>
+__global__ void __launch_bounds__(kThreads, 1) p2pPipelinedKernel(const AarRankParams p, const AarLayout l, int split) {
+  __shared__ Smem sm;
+  initSmem(sm);
+  traceMark(p, l, 0);
+  const int nctas = gridDim.x;
+  const int nPush = split & 0xffff, nReduce = split >> 16;
+  const int b = blockIdx.x;
+  if (b < nPush) {
+    phaseScatter<T, false>(p, l, b, nPush, sm);
+    traceMark(p, l, 1);
+  } else if (b < nPush + nReduce) {
+    phaseReduceBcast<T, false>(p, l, b - nPush, nReduce, sm);
+    traceMark(p, l, 3);
+  } else {
+    const int cta = b - nPush - nReduce, n = nctas - nPush - nReduce;
+    if (p.minChunksRequired >= l.totalChunks && !(p.flags & AAR_FLAG_FORCE)) {
+      phaseGatherEager<T>(p, l, cta, n, sm);
+      traceMark(p, l, 4);
+    } else {
+      phaseGatherBody<T>(p, l, cta, n, sm);
+    }
+  }
+  retireRound(p, l, nctas);
+  traceMark(p, l, 5);
+}
+
+// K4, one launch per round, CTAs specialised by role so the three stages overlap chunk by chunk:
+//   CTAs [0, nReduce)      in-switch reduce + multicast store of my block (few CTAs saturate NVLS: measured
+//                          multimem throughput falls when more than ~32 CTAs issue it, profiles/r1_link_bench_8gpu.json)
+//   CTAs [nReduce, grid)   stage my input into the multicast-bound region (arrival flags per chunk), then copy every
+//                          reduced chunk to the caller's output as soon as its flag lands.
+template <typename T>
+__global__ void __launch_bounds__(kThreads, 1) nvlsPipelinedKernel(const AarRankParams p, const AarLayout l, int nReduce) {
+  __shared__ Smem sm;
+  initSmem(sm);
+  traceMark(p, l, 0);
+  const int nctas = gridDim.x;
+  if ((int)blockIdx.x < nReduce) {
+    traceMark(p, l, 1);
+    phaseReduceBcast<T, true>(p, l, blockIdx.x, nReduce, sm);
+    traceMark(p, l, 3);
+    traceMark(p, l, 4);
+  } else {
+    const int cta = blockIdx.x - nReduce, n = nctas - nReduce;
+    phaseScatter<T, true>(p, l, cta, n, sm);
+    traceMark(p, l, 1);
+    traceMark(p, l, 3);
+    phaseGatherEager<T>(p, l, cta, n, sm);
+    traceMark(p, l, 4);
+  }
+  retireRound(p, l, nctas);
+  traceMark(p, l, 5);
 }
 
 template <typename T>
@@ -679,6 +843,28 @@ AAR_API int aar_launch_round_fused(const AarRankParams* p, const AarLayout* lay,
   return launchRound(p, lay, grid, stream, "aar_launch_round_fused", 7);
 }
 
+// Role-specialised two-shot round.  split = nPush | nReduce << 16 (0 = heuristic); the remaining CTAs gather.
+AAR_API int aar_launch_round_pipelined(const AarRankParams* p, const AarLayout* lay, int grid, int split, void* stream) {
+  const char* what = "aar_launch_round_pipelined";
+  if (!p || !lay) return aar_host::fail(AAR_EINVAL, "%s: null params", what);
+  int dev = 0, sms = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  int g = grid > 0 ? grid : sms;
+  if (g < 3) g = 3;
+  int nPush = split & 0xffff, nReduce = split >> 16;
+  if (nPush <= 0 || nReduce <= 0 || nPush + nReduce >= g) {
+    nPush = g * 3 / 8;
+    nReduce = g * 3 / 8;
+  }
+  if (nPush < 1) nPush = 1;
+  if (nReduce < 1) nReduce = 1;
+  const int sp = nPush | (nReduce << 16);
+  if (lay->dtype == AAR_F32) return launch(p2pPipelinedKernel<float>, p, lay, g, stream, what, sp);
+  if (lay->dtype == AAR_BF16) return launch(p2pPipelinedKernel<__nv_bfloat16>, p, lay, g, stream, what, sp);
+  return aar_host::fail(AAR_EINVAL, "%s: unknown dtype %d", what, lay->dtype);
+}
+
 AAR_API int aar_launch_oneshot(const AarRankParams* p, const AarLayout* lay, int phase, int grid, void* stream) {
   if (!lay || lay->oneshotOff == 0) return aar_host::fail(AAR_EINVAL, "aar_launch_oneshot: layout has no one-shot buffers");
   if (phase < 0 || phase > 2) return aar_host::fail(AAR_EINVAL, "aar_launch_oneshot: phase must be 0, 1 or 2");
@@ -691,15 +877,29 @@ AAR_API int aar_launch_nvls(const AarRankParams* p, const AarLayout* lay, int ph
   const char* what = "aar_launch_nvls";
   if (!p || !lay) return aar_host::fail(AAR_EINVAL, "%s: null params", what);
   if (!p->mcRegion || lay->stageOff == 0) return aar_host::fail(AAR_EUNSUPPORTED, "%s: needs a multicast mapping and the staging area", what);
-  if (phases <= 0 || phases > 7) return aar_host::fail(AAR_EINVAL, "%s: phases is a bit mask 1..7", what);
+  if ((phases & 7) == 0) return aar_host::fail(AAR_EINVAL, "%s: phases is a bit mask 1..7 (| nReduceCtas << 8)", what);
   const int V = 16 / lay->elemSize;
   if (lay->stepSize % V || lay->maxChunk % V || lay->dataSize % V)
     return aar_host::fail(AAR_EUNSUPPORTED, "%s: multimem needs 16-byte aligned blocks and chunks", what);
   const int total = lay->totalChunks;
   if (p->minRequired != lay->P || p->minChunksRequired != total || (p->flags & (AAR_FLAG_SKIP_SCATTER | AAR_FLAG_EXACT_QUORUM | AAR_FLAG_NORMALIZE)))
     return aar_host::fail(AAR_EUNSUPPORTED, "%s: the switch sums every bound GPU, so thresholds must be 1.0 (use the P2P paths otherwise)", what);
-  if (lay->dtype == AAR_F32) return launch(roundKernel<float, true>, p, lay, grid, stream, what, phases);
-  if (lay->dtype == AAR_BF16) return launch(roundKernel<__nv_bfloat16, true>, p, lay, grid, stream, what, phases);
+  const int mask = phases & 7, nReduceArg = phases >> 8;
+  if (mask == 7) {
+    // one launch: role-specialised pipeline; needs at least one CTA of each role
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    int g = grid > 0 ? grid : sms;
+    if (g < 2) g = 2;
+    int nReduce = nReduceArg > 0 ? nReduceArg : 24;
+    if (nReduce > g / 2) nReduce = g / 2;
+    if (lay->dtype == AAR_F32) return launch(nvlsPipelinedKernel<float>, p, lay, g, stream, what, nReduce);
+    if (lay->dtype == AAR_BF16) return launch(nvlsPipelinedKernel<__nv_bfloat16>, p, lay, g, stream, what, nReduce);
+    return aar_host::fail(AAR_EINVAL, "%s: unknown dtype %d", what, lay->dtype);
+  }
+  if (lay->dtype == AAR_F32) return launch(roundKernel<float, true>, p, lay, grid, stream, what, mask);
+  if (lay->dtype == AAR_BF16) return launch(roundKernel<__nv_bfloat16, true>, p, lay, grid, stream, what, mask);
   return aar_host::fail(AAR_EINVAL, "%s: unknown dtype %d", what, lay->dtype);
 }
 

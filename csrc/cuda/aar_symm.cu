@@ -113,6 +113,7 @@ AAR_API int aar_layout_compute(int P, int dataSize, int maxChunkSize, int maxLag
   l.statusOff = take(16 * 4);
   l.oneshotFlagOff = take((uint64_t)l.L * AAR_MAXP * 4);
   l.barrierOff = take(8 * 4 * 16);
+  l.traceOff = take((uint64_t)AAR_TRACE_CTAS * AAR_TRACE_MARKS * 8);
   l.regionBytes = alignUp(off, 2ull << 20);
   *out = l;
   return AAR_OK;

@@ -33,6 +33,9 @@ extern "C" {
 #define AAR_FLAG_FORCE 4u       /* K8: do not wait, take whatever has arrived (catch-up, AllreduceWorker.scala:91-97) */
 #define AAR_FLAG_SKIP_SCATTER 8u /* fused kernel: this rank contributes nothing this round (fault injection) */
 #define AAR_FLAG_VIEW_OUTPUT 16u /* K3 does not copy: the caller reads the reduce-ring slot itself, stream-ordered */
+#define AAR_FLAG_TRACE 32u      /* every CTA stamps %globaltimer at its phase boundaries into the trace section */
+#define AAR_TRACE_CTAS 512
+#define AAR_TRACE_MARKS 8
 
 /* bits of the device status word (AarLayout.statusOff, word 0) */
 #define AAR_ST_TIMEOUT_SCATTER 1u
@@ -62,7 +65,8 @@ typedef struct AarLayout {
   uint64_t oneshotOff;       /* T   [L][P(src)][dataSize] + u32 [L][AAR_MAXP] flags; 0 if not allocated */
   uint64_t oneshotFlagOff;
   uint64_t stageOff;         /* T   [L][dataSize] staging for the NVLS path; 0 if not allocated */
-  uint64_t barrierOff;       /* u32 [8] NVLS barrier counters */
+  uint64_t barrierOff;       /* reserved */
+  uint64_t traceOff;         /* u64 [AAR_TRACE_CTAS][AAR_TRACE_MARKS] phase timestamps (AAR_FLAG_TRACE) */
   uint64_t ctrlBytes;        /* first byte of the control area that must be zeroed at allocation */
   uint64_t regionBytes;      /* total, rounded up to 2 MiB */
 } AarLayout;
@@ -101,6 +105,9 @@ int aar_launch_reduce_bcast(const AarRankParams* p, const AarLayout* lay, int gr
 int aar_launch_gather(const AarRankParams* p, const AarLayout* lay, int grid, void* stream);
 /* K1+K2+K3 in one launch (one kernel per round per rank; requires peers on other GPUs or an earlier launch). */
 int aar_launch_round_fused(const AarRankParams* p, const AarLayout* lay, int grid, void* stream);
+/* Same round with the CTAs specialised by role (push / reduce+broadcast / gather) so the phases overlap chunk by chunk.
+ * split = nPush | nReduce << 16, 0 = heuristic; the remaining CTAs gather. */
+int aar_launch_round_pipelined(const AarRankParams* p, const AarLayout* lay, int grid, int split, void* stream);
 /* K5 one-shot: push the whole vector to every peer, then each rank sums the arrived set locally. Two phases so the
  * single-GPU emulation can order them; phase = 0 push, 1 reduce, 2 both. */
 int aar_launch_oneshot(const AarRankParams* p, const AarLayout* lay, int phase, int grid, void* stream);
@@ -142,6 +149,14 @@ int aar_host_words_free(unsigned* hostPtr);
 /* Device properties the selector needs. */
 int aar_device_sm_count(int device, int* out);
 int aar_enable_peer_access(int device, int peer);
+
+/* Link micro-benchmark (roofline denominators): mode 0 multimem.ld_reduce, 1 multimem.st, 2 both, 3 peer load, 4 peer
+ * store, 5 local copy; buffers hold 2 * bytes; `iters` launches on `stream`, timed by the caller. */
+int aar_bench_link(int mode, int grid, int unroll, void* mc, void* peer, void* local, size_t bytes, int iters, void* stream);
+
+/* All-to-all variant: mode 0 each CTA stores to one peer, 1 each CTA stores to all peers, 2 each CTA loads from one
+ * peer, 3 like 0 with 32-byte stores.  Every peer buffer holds 2 * bytesPerPeer. */
+int aar_bench_all2all(int mode, int grid, int unroll, void** peers, int nPeers, void* local, size_t bytesPerPeer, int iters, void* stream);
 
 /* Spin kernel used by the straggler injector: busy-waits `ns` nanoseconds on `stream`. */
 int aar_launch_delay(unsigned long long ns, void* stream);
