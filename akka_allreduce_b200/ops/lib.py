@@ -79,6 +79,7 @@ def load():
         "aar_launch_oneshot": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_void_p],
         "aar_launch_nvls": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_void_p],
         "aar_local_round": [P(AarRankParams), C.c_int, P(AarLayout), C.c_uint, C.c_int, C.c_void_p],
+        "aar_local_allreduce_static": [P(C.c_void_p), P(C.c_void_p), C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p],
         "aar_region_alloc_local": [C.c_size_t, P(C.c_void_p)],
         "aar_region_free_local": [C.c_void_p],
         "aar_vmm_granularity": [C.c_int, C.c_int, C.c_int, P(C.c_size_t)],

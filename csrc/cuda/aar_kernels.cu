@@ -16,6 +16,7 @@
 // last publishes its arrival flag.
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 
 #include "aar_device.cuh"
@@ -927,4 +928,93 @@ AAR_API int aar_launch_delay(unsigned long long ns, void* stream) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return aar_host::fail(AAR_ECUDA, "aar_launch_delay: %s", cudaGetErrorString(e));
   return AAR_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ fixed-scratch variant
+// One full allreduce round of `nranks` emulated ranks on the current device whose ring buffers, flag words and
+// counters -- everything aar_local_round() expects the caller to have allocated as "regions" -- live in the
+// file-scope array below instead.  For callers that are not allowed to allocate device memory themselves: code
+// that runs inside someone else's memory plan (an inference server with a frozen arena, a plugin called from a
+// host application that owns the allocator, a signal-safe or real-time path where cudaMalloc's implicit
+// synchronisation and possible failure are not acceptable).  Nothing here calls cudaMalloc/cudaFree or any
+// routine that allocates; inputs and outputs still come from the caller.
+//
+// The array is part of the library image: every GPU that loads libaar_cuda.so carries AAR_STATIC_SCRATCH_BYTES of
+// it until the process exits.  All calls on a device share it and it keeps what the previous call left behind, so
+// each call first clears the words that must start at zero (flags, election counters, decision words); the ring
+// payload needs no clearing because a chunk is only read after its flag of the current call is seen.  Two calls that
+// overlap on the same GPU (different streams, different threads) race on the array: serialise them.
+//
+// `g_staticScratch` names a device symbol; in host code the identifier is only a handle, not an address a kernel
+// can use.  The device address is looked up once per device with cudaGetSymbolAddress(), with that device current,
+// on the first call made on that device.  That first call should therefore come before any stream capture.
+namespace {
+
+__device__ __align__(256) unsigned char g_staticScratch[AAR_STATIC_SCRATCH_BYTES];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_staticMutex;
+void* g_staticBase[kMaxDevices] = {};
+
+int staticScratchBase(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return aar_host::fail(AAR_ECUDA, "aar_local_allreduce_static: cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= kMaxDevices) return aar_host::fail(AAR_EUNSUPPORTED, "aar_local_allreduce_static: device index %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_staticMutex);
+  if (!g_staticBase[dev]) {
+    void* ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_staticScratch);
+    if (e != cudaSuccess || !ptr)
+      return aar_host::fail(AAR_ECUDA, "aar_local_allreduce_static: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+    g_staticBase[dev] = ptr;
+  }
+  *out = g_staticBase[dev];
+  return AAR_OK;
+}
+
+}  // namespace
+
+AAR_API int aar_local_allreduce_static(const void* const* inputs, void* const* outputs, int nranks, int dataSize, int maxChunkSize, int dtype,
+                                       void* stream) {
+  const char* what = "aar_local_allreduce_static";
+  if (!inputs || !outputs) return aar_host::fail(AAR_EINVAL, "%s: null input/output table", what);
+  if (nranks < 1 || nranks > AAR_MAXP) return aar_host::fail(AAR_EINVAL, "%s: nranks=%d outside 1..%d", what, nranks, AAR_MAXP);
+  for (int r = 0; r < nranks; ++r)
+    if (!inputs[r] || !outputs[r]) return aar_host::fail(AAR_EINVAL, "%s: rank %d has a null input or output", what, r);
+  AarLayout lay;
+  int rc = aar_layout_compute(nranks, dataSize, maxChunkSize, /*maxLag=*/0, dtype, /*oneshot=*/0, /*stage=*/0, &lay);
+  if (rc) return rc;
+  // bytes one emulated rank really uses (the layout's own regionBytes is padded to the 2 MiB VMM granularity)
+  const uint64_t perRank = (lay.traceOff + (uint64_t)AAR_TRACE_CTAS * AAR_TRACE_MARKS * 8 + 255) / 256 * 256;
+  const uint64_t need = perRank * (uint64_t)nranks;
+  if (need > (uint64_t)AAR_STATIC_SCRATCH_BYTES)
+    return aar_host::fail(AAR_EINVAL,
+                          "%s: %d ranks x %d elements need %llu bytes of scratch but the built-in array holds %llu; use aar_local_round() with "
+                          "caller-allocated regions for this size",
+                          what, nranks, dataSize, (unsigned long long)need, (unsigned long long)AAR_STATIC_SCRATCH_BYTES);
+  void* base = nullptr;
+  rc = staticScratchBase(&base);
+  if (rc) return rc;
+  char* b = static_cast<char*>(base);
+  // flags, counters and decision words of the previous call must not be mistaken for this call's
+  for (int r = 0; r < nranks; ++r) {
+    cudaError_t e = cudaMemsetAsync(b + (uint64_t)r * perRank + lay.ctrlBytes, 0, perRank - lay.ctrlBytes, (cudaStream_t)stream);
+    if (e != cudaSuccess) return aar_host::fail(AAR_ECUDA, "%s: clearing the control words: %s", what, cudaGetErrorString(e));
+  }
+  AarRankParams params[AAR_MAXP];
+  for (int r = 0; r < nranks; ++r) {
+    AarRankParams& p = params[r];
+    memset(&p, 0, sizeof p);
+    p.rank = r;
+    p.round = 0;
+    p.minRequired = nranks;               // plain allreduce: every rank contributes, every chunk is required
+    p.minChunksRequired = lay.totalChunks;
+    p.maxLag = 0;
+    p.timeoutNs = 2000000000ull;          // liveness guard only; every flag is already set when a phase looks at it
+    p.input = inputs[r];
+    p.output = outputs[r];
+    for (int j = 0; j < nranks; ++j) p.region[j] = b + (uint64_t)j * perRank;
+  }
+  return aar_local_round(params, nranks, &lay, 0u, 0, stream);
 }

@@ -120,6 +120,20 @@ int aar_launch_nvls(const AarRankParams* p, const AarLayout* lay, int phases, in
  * rank r does not scatter this round (missing contributor). */
 int aar_local_round(const AarRankParams* params, int nranks, const AarLayout* lay, unsigned skipMask, int grid, void* stream);
 
+/* No counterpart in the reference.  aar_local_round() for callers that may not allocate device memory (code running
+ * inside a host application's fixed memory plan, or on a path where cudaMalloc's implicit synchronisation or failure is not
+ * acceptable): one plain allreduce round (all thresholds 1.0) of `nranks` emulated ranks on the current device, with the
+ * ring buffers and flag words taken from an array built into the library instead of caller-allocated regions.
+ * inputs[r] / outputs[r]: dataSize elements of `dtype` each, device memory owned by the caller.
+ * Limit: nranks x per-rank ring bytes must fit AAR_STATIC_SCRATCH_BYTES, otherwise AAR_EINVAL with the sizes in
+ * aar_last_error().  No cudaMalloc / cudaFree / allocating routine is called.  The array is shared by every call on a
+ * device and keeps the previous call's contents; each call clears its control words on `stream` first.  Calls that overlap
+ * on one GPU race on it.  The first call on a device also looks up the array's device address; make that call before any
+ * stream capture. */
+#define AAR_STATIC_SCRATCH_BYTES (16u << 20)
+int aar_local_allreduce_static(const void* const* inputs, void* const* outputs, int nranks, int dataSize, int maxChunkSize, int dtype,
+                               void* stream);
+
 /* Plain device allocation helpers for the emulation mode and tests (zero-filled). */
 int aar_region_alloc_local(size_t bytes, void** ptr);
 int aar_region_free_local(void* ptr);
