@@ -24,7 +24,7 @@ ONESHOT_MAX_BYTES = 256 * 1024
 class RoundEngine:
     def __init__(self, rank: int, region_ptrs: Sequence[int], layout: L.AarLayout, *, th_reduce: float = 1.0, th_complete: float = 1.0,
                  normalize: bool = False, exact_quorum: bool = False, timeout_ms: float = 0.0, device: int = 0, grid: int = 0,
-                 algo: str = "auto", mc_ptr: int = 0, keepalive=None):
+                 algo: str = "auto", mc_ptr: int = 0, keepalive=None, overlap: bool | None = None):
         self.lib = L.load()
         self.rank, self.P = rank, layout.P
         self.layout = layout
@@ -66,6 +66,14 @@ class RoundEngine:
         # CTA role split of the pipelined kernels (measured on 8xB200, profiles/r1_phase_bench_*.txt)
         self.split = 32 | (48 << 16)      # nPush | nReduce << 16; the rest gather
         self.nvls_reduce_ctas = 16
+        self.nvls_stage_ctas = 48
+        # The maxLag window lets two consecutive rounds of one worker be in flight: they alternate between two internal
+        # streams, so the push of round r+1 starts on the SMs that round r's push CTAs have already left while round r is
+        # still reducing and gathering.  Needs two ring slots (maxLag >= 1) and peers to overlap with.
+        self.overlap = (layout.L >= 2 and layout.P > 1) if overlap is None else (overlap and layout.L >= 2)
+        with torch.cuda.device(self.device):
+            self._streams = [torch.cuda.Stream(device=self.device) for _ in range(2)] if self.overlap else []
+            self._events = [torch.cuda.Event() for _ in range(layout.L)]
 
     # ------------------------------------------------------------------ construction helpers
     @classmethod
@@ -90,8 +98,8 @@ class RoundEngine:
             # from four GPUs up (at P = 2 it is 1.5N against N).  The switch sums every bound GPU, so thresholds must be 1.
             V = 16 // lay.elemSize
             aligned = lay.stepSize % V == 0 and lay.maxChunk % V == 0 and lay.dataSize % V == 0
-            if self.mc_ptr and lay.stageOff and lay.P >= 4 and aligned and th_reduce >= 1.0 and th_complete >= 1.0:
-                return "nvls"
+            if self.mc_ptr and lay.stageOff and lay.P >= 8 and aligned and th_reduce >= 1.0 and th_complete >= 1.0:
+                return "nvls"  # measured: 222 us vs NCCL 277 us at 8 GPUs; at 4 GPUs the pipelined P2P kernel is faster (182 vs 205 us)
             # role-specialised CTAs overlap push / reduce / gather chunk by chunk; with one rank there is nothing to overlap
             return "pipelined" if lay.P > 1 else "twoshot"
         if algo == "oneshot" and not lay.oneshotOff:
@@ -109,9 +117,10 @@ class RoundEngine:
         return int(self._host_words[1])
 
     def enqueue_round(self, rnd: int, x: torch.Tensor, *, stream: torch.cuda.Stream | None = None, force: bool = False,
-                      skip_scatter: bool = False, out: torch.Tensor | None = None):
-        """Launch round `rnd` with input `x` on `stream`; returns (output, counts) tensors valid once the stream reaches
-        the end of the round (they are reused maxLag+1 rounds later)."""
+                      skip_scatter: bool = False, out: torch.Tensor | None = None, delay_ns: int = 0):
+        """Launch round `rnd` with input `x`; returns (output, counts) tensors that are valid after `wait_round(rnd)` (or once
+        the explicit `stream` reaches the end of the round) and are reused maxLag+1 rounds later.  `x` must stay alive
+        and unmodified until then."""
         if x.dtype != self.dtype or x.numel() != self.data_size or not x.is_contiguous() or x.device != self.device:
             raise ValueError(f"input must be a contiguous {self.dtype} tensor of {self.data_size} elements on {self.device} "
                              f"(AllreduceWorker.scala:174-176 rejects a size that differs from initialisation)")
@@ -123,7 +132,15 @@ class RoundEngine:
         p.output = output.data_ptr()
         p.outCounts = self.counts[slot].data_ptr()
         p.flags = self.base_flags | (L.FLAG_FORCE if force else 0) | (L.FLAG_SKIP_SCATTER if skip_scatter else 0)
-        s = C.c_void_p((stream or torch.cuda.current_stream(self.device)).cuda_stream)
+        cur = torch.cuda.current_stream(self.device)
+        if stream is None and self.overlap:
+            stream = self._streams[rnd % 2]
+            stream.wait_stream(cur)          # x was produced on the caller's stream
+            p.flags |= L.FLAG_OVERLAPPED
+        run_stream = stream or cur
+        s = C.c_void_p(run_stream.cuda_stream)
+        if delay_ns > 0:  # straggler injection: this rank's round starts late
+            L.check(self.lib.aar_launch_delay(int(delay_ns), s), "aar_launch_delay")
         if self.algo == "twoshot":
             L.check(self.lib.aar_launch_round_fused(self._pref, self._lay, self.grid, s), "aar_launch_round_fused")
         elif self.algo == "pipelined":
@@ -131,17 +148,28 @@ class RoundEngine:
         elif self.algo == "oneshot":
             L.check(self.lib.aar_launch_oneshot(self._pref, self._lay, 2, self.grid, s), "aar_launch_oneshot")
         elif self.algo == "nvls":
-            L.check(self.lib.aar_launch_nvls(self._pref, self._lay, 7 | (self.nvls_reduce_ctas << 8), self.grid, s), "aar_launch_nvls")
+            L.check(self.lib.aar_launch_nvls(self._pref, self._lay, 7 | (self.nvls_reduce_ctas << 8) | (self.nvls_stage_ctas << 16), self.grid, s), "aar_launch_nvls")
         else:
             raise ValueError(f"unknown algo {self.algo}")
+        self._events[slot].record(run_stream)
         self.launches += 1
         self.rounds_enqueued = max(self.rounds_enqueued, rnd + 1)
         return output, self.counts[slot]
+
+    def wait_round(self, rnd: int, stream: torch.cuda.Stream | None = None) -> None:
+        """Make `stream` (default: the current stream) wait for round `rnd`; call before consuming its output on a stream."""
+        (stream or torch.cuda.current_stream(self.device)).wait_event(self._events[rnd % self.layout.L])
+
+    def wait_all(self, stream: torch.cuda.Stream | None = None) -> None:
+        st = stream or torch.cuda.current_stream(self.device)
+        for ev in self._events:
+            st.wait_event(ev)
 
     def allreduce(self, x: torch.Tensor, rnd: int | None = None) -> torch.Tensor:
         """Convenience: one round, result tensor (stream-ordered)."""
         rnd = self.rounds_enqueued if rnd is None else rnd
         out, _ = self.enqueue_round(rnd, x)
+        self.wait_round(rnd)
         return out
 
     def status(self) -> int:

@@ -43,6 +43,9 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-nccl", action="store_true")
     ap.add_argument("--view", action="store_true", help="zero-copy output (sink reads the ring slot)")
+    ap.add_argument("--nvls-ctas", default="", help="nStage:nReduce for the NVLS kernel")
+    ap.add_argument("--split", default="", help="nPush:nReduce for the pipelined P2P kernel")
+    ap.add_argument("--no-overlap", action="store_true", help="one round in flight at a time (no use of the maxLag window)")
     return ap.parse_args()
 
 
@@ -152,7 +155,6 @@ def main():
     g = torch.Generator(device="cpu").manual_seed(1234)
     base = torch.randn(a.data_size, generator=g).to(dtype)
     xs = [(base * (rank + 1) + k).to(dev) for k in range(2)]
-    expect = [sum((base.to(torch.float32) * (r + 1) + k).to(dtype).to(torch.float32) for r in range(N)) for k in range(2)] if N <= 2 else None
 
     # ---------------------------------------------------------------- device-timed rounds
     if a.impl == "aar":
@@ -163,14 +165,20 @@ def main():
             symm = None
         else:
             symm = SymmetricMemory(UnixRendezvous(rank, world, session + "_mem"), layout.regionBytes, local_rank, want_multicast=True)
-            eng = RoundEngine.from_symmetric(symm, layout, grid=a.grid, algo=a.algo)
+            eng = RoundEngine.from_symmetric(symm, layout, grid=a.grid, algo=a.algo, overlap=False if a.no_overlap else None)
         if a.view:
             eng.base_flags |= L.FLAG_VIEW_OUTPUT
+        if a.nvls_ctas:
+            eng.nvls_stage_ctas, eng.nvls_reduce_ctas = (int(v) for v in a.nvls_ctas.split(":"))
+        if a.split:
+            ps, rs = (int(v) for v in a.split.split(":"))
+            eng.split = ps | (rs << 16)
         global_sync()
         rnd = 0
         for _ in range(W):
             eng.enqueue_round(rnd, xs[rnd % 2])
             rnd += 1
+        eng.wait_all()
         global_sync()
         launches0 = eng.launches
         t0 = torch.cuda.Event(enable_timing=True)
@@ -179,6 +187,7 @@ def main():
         for _ in range(K):
             out, counts = eng.enqueue_round(rnd, xs[rnd % 2])
             rnd += 1
+        eng.wait_all()   # the launching stream joins the round streams before the end event
         t1.record()
         global_sync()
         ms = max_over_ranks(t0.elapsed_time(t1) / K)
@@ -271,7 +280,7 @@ def main():
             "config": {"model": "threshold allreduce, BASELINE.json config 2 (N workers, dataSize=16Mi, maxChunkSize=1Mi, thresholds=1.0, maxLag=1)",
                        "global_batch": N * a.data_size, "seq_len": a.data_size, "parallelism": f"dp{N}", "data_size": a.data_size,
                        "max_chunk_size": a.chunk, "max_lag": a.max_lag, "th_reduce": 1.0, "th_complete": 1.0,
-                       "l2_policy": "inputs+rings larger than L2 (2 x 64 MiB inputs alternate, 256 MiB rings per rank)", "view_output": a.view},
+                       "l2_policy": "inputs+rings larger than L2 (2 x 64 MiB inputs alternate, 256 MiB rings per rank)", "view_output": a.view, "rounds_in_flight": 2 if (a.impl == "aar" and N > 1 and a.max_lag >= 1 and not a.no_overlap) else 1},
             "rounds_per_sec": rounds_per_sec, "algbw_GBps": algbw, "busbw_GBps": busbw,
             "gpu_launches": gpu_launches, "clocks": clocks, "nccl": nccl,
             "vs_nccl": (nccl["ms_per_step"] / ms) if nccl and "ms_per_step" in nccl else None,

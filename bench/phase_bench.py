@@ -58,7 +58,7 @@ def main():
         variants += ([("nvls", int(x)) for x in a.nreduce.split(",")] if symm.has_multicast else [])
         for algo, nred in variants:
             tag = algo if algo == "twoshot" else (f"nvls_r{nred}" if algo == "nvls" else f"pipe_{nred & 0xffff}_{nred >> 16}")
-            eng = RoundEngine.from_symmetric(symm, lay, grid=grid, algo="twoshot" if algo == "pipe" else algo)
+            eng = RoundEngine.from_symmetric(symm, lay, grid=grid, algo="twoshot" if algo == "pipe" else algo, overlap=False)
             if a.no_doorbell:
                 eng.params.doorbell = None
             launcher = lib.aar_launch_nvls if algo == "nvls" else None

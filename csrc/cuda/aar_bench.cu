@@ -10,7 +10,17 @@ using namespace aar_dev;
 
 namespace {
 
+__device__ __forceinline__ uint4 mm_ld_weak(const void* mc) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.weak.global.add.v4.f32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mm_st_weak(void* mc, const uint4& v) {
+  asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
 // mode 0: multimem.ld_reduce   1: multimem.st   2: ld_reduce + st   3: peer ld   4: peer st   5: local copy
+// mode 6: ld_reduce.weak + st.weak
 template <int U>
 __global__ void __launch_bounds__(512, 1) linkBench(int mode, char* mc, char* peer, char* local, size_t bytes, unsigned* sink) {
   const size_t nv = bytes / 16;
@@ -24,6 +34,7 @@ __global__ void __launch_bounds__(512, 1) linkBench(int mode, char* mc, char* pe
       const size_t i = base + (size_t)u * blockDim.x;
       if (i < hi) {
         if (mode == 0 || mode == 2) v[u] = multimem_ld_reduce_f32x4(mc + i * 16);
+        else if (mode == 6) v[u] = mm_ld_weak(mc + i * 16);
         else if (mode == 3) v[u] = __ldcg(reinterpret_cast<const uint4*>(peer) + i);
         else if (mode == 5) v[u] = __ldcs(reinterpret_cast<const uint4*>(local) + i);
         else v[u] = make_uint4((unsigned)i, 1, 2, 3);
@@ -34,6 +45,7 @@ __global__ void __launch_bounds__(512, 1) linkBench(int mode, char* mc, char* pe
       const size_t i = base + (size_t)u * blockDim.x;
       if (i < hi) {
         if (mode == 1 || mode == 2) multimem_st_x4(mc + bytes + i * 16, v[u]);
+        else if (mode == 6) mm_st_weak(mc + bytes + i * 16, v[u]);
         else if (mode == 4) st_peer(peer + bytes + i * 16, v[u]);
         else if (mode == 5) __stcs(reinterpret_cast<uint4*>(local + bytes) + i, v[u]);
         else acc ^= v[u].x ^ v[u].y ^ v[u].z ^ v[u].w;
@@ -139,12 +151,14 @@ AAR_API int aar_bench_all2all(int mode, int grid, int unroll, void** peers, int 
 
 // Runs `iters` launches on `stream`; the caller times them with events.  The buffers need 2 * bytes (read half, write half).
 AAR_API int aar_bench_link(int mode, int grid, int unroll, void* mc, void* peer, void* local, size_t bytes, int iters, void* stream) {
-  if (mode < 0 || mode > 5 || grid <= 0) return aar_host::fail(-1, "aar_bench_link: bad arguments");
-  if ((mode <= 2) && !mc) return aar_host::fail(-3, "aar_bench_link: multimem modes need the multicast mapping");
+  if (mode < 0 || mode > 6 || grid <= 0) return aar_host::fail(-1, "aar_bench_link: bad arguments");
+  if ((mode <= 2 || mode == 6) && !mc) return aar_host::fail(-3, "aar_bench_link: multimem modes need the multicast mapping");
   static unsigned* sink = nullptr;
   if (!sink) cudaMalloc(&sink, 4);
   for (int i = 0; i < iters; ++i) {
-    if (unroll >= 8)
+    if (unroll >= 16)
+      linkBench<16><<<grid, 512, 0, (cudaStream_t)stream>>>(mode, (char*)mc, (char*)peer, (char*)local, bytes, sink);
+    else if (unroll >= 8)
       linkBench<8><<<grid, 512, 0, (cudaStream_t)stream>>>(mode, (char*)mc, (char*)peer, (char*)local, bytes, sink);
     else if (unroll >= 4)
       linkBench<4><<<grid, 512, 0, (cudaStream_t)stream>>>(mode, (char*)mc, (char*)peer, (char*)local, bytes, sink);

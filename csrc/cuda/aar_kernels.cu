@@ -58,9 +58,11 @@ __device__ __forceinline__ long long paddedData(const AarLayout& l) {
 // Segments per message so that `pairs` messages give about two units per CTA; whole tiles per segment.
 struct SegPlan {
   int tilesPerSeg, segs;
-  __device__ SegPlan(const AarLayout& l, long long pairs, int nctas) {
+  // unitsPerCta = 2 balances well when segments are cheap to finish; = 1 gives every CTA exactly one segment and therefore
+  // one fence, so its memory pipeline never drains in the middle (used where the link latency is long: NVLS reduce).
+  __device__ SegPlan(const AarLayout& l, long long pairs, int nctas, int unitsPerCta = 2) {
     const int Tm = l.tilesPerChunk;
-    long long want = (2LL * nctas + pairs - 1) / (pairs > 0 ? pairs : 1);
+    long long want = ((long long)unitsPerCta * nctas + pairs - 1) / (pairs > 0 ? pairs : 1);
     int S = (int)(want < 1 ? 1 : (want > Tm ? Tm : want));
     tilesPerSeg = (Tm + S - 1) / S;
     segs = (Tm + tilesPerSeg - 1) / tilesPerSeg;
@@ -82,7 +84,7 @@ __device__ bool scatterDecision(const AarRankParams& p, const AarLayout& l, int 
       unsigned go = 1;
       if (p.round >= l.L) {
         char* my = regionOf(p, p.rank);
-        uint64_t* word = reinterpret_cast<uint64_t*>(my + l.k1DecOff) + dest;
+        uint64_t* word = reinterpret_cast<uint64_t*>(my + l.k1DecOff) + (p.round % l.L) * AAR_MAXP + dest;
         const uint64_t epoch = (uint64_t)(p.round + 1);
         uint64_t v = ld_acquire_gpu_u64(word);
         if ((v >> 32) == epoch) {
@@ -118,14 +120,14 @@ __device__ bool scatterDecision(const AarRankParams& p, const AarLayout& l, int 
 // kStage = false: K1 scatter_push -- block `dest` of my input goes into peer dest's scatter ring over NVLink.
 // kStage = true : NVLS variant -- the input is staged in MY region (the switch will pull it), only the flag travels.
 template <typename T, bool kStage>
-__device__ void phaseScatter(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
+__device__ void phaseScatter(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm, int unitsPerCta = 2) {
   if (p.flags & AAR_FLAG_SKIP_SCATTER) return;
   const int P = l.P, C = l.C;
   const int slot = p.round % l.L;
   const uint32_t epoch = (uint32_t)(p.round + 1);
   char* my = regionOf(p, p.rank);
   const bool vecOk = geomVecOk<T>(l) && (reinterpret_cast<uintptr_t>(p.input) % 16 == 0);
-  const SegPlan plan(l, (long long)P * C, nctas);
+  const SegPlan plan(l, (long long)P * C, nctas, unitsPerCta);
   const int S = plan.segs, segElems = plan.segElems(l);
   T* stage = reinterpret_cast<T*>(my + l.stageOff) + (long long)slot * paddedData(l);
   const bool inPlace = kStage && (reinterpret_cast<const T*>(p.input) == stage);  // the source wrote straight into the stage
@@ -156,7 +158,7 @@ __device__ void phaseScatter(const AarRankParams& p, const AarLayout& l, int cta
     __syncthreads();
     if (threadIdx.x == 0) {
       __threadfence_system();
-      unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k1CtrOff) + dest * C + c;
+      unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k1CtrOff) + ((long long)slot * P + dest) * C + c;
       const unsigned old = atomicAdd(ctr, 1u);
       if (old + 1 == plan.liveSegs(l, clen)) {  // last segment of this "ScatterBlock": publish its arrival
         atomicExch(ctr, 0u);
@@ -354,7 +356,7 @@ __device__ __forceinline__ void nvlsSpan(const char* mcStage, char* mcOut, int n
 }
 
 template <typename T, bool kNvls>
-__device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
+__device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm, int unitsPerCta = 2) {
   const int P = l.P, C = l.C;
   const int myChunks = numChunks(l, p.rank);
   if (myChunks == 0) return;
@@ -362,7 +364,7 @@ __device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int
   const uint64_t epoch = (uint64_t)(p.round + 1);
   char* my = regionOf(p, p.rank);
   const bool vecOk = geomVecOk<T>(l);
-  const SegPlan plan(l, myChunks, nctas);
+  const SegPlan plan(l, myChunks, nctas, kNvls ? 1 : unitsPerCta);
   const int S = plan.segs, segElems = plan.segElems(l);
   const long long total = (long long)myChunks * S;
   for (long long idx = cta; idx < total; idx += nctas) {
@@ -403,7 +405,7 @@ __device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int
     __syncthreads();
     if (threadIdx.x == 0) {
       __threadfence_system();
-      unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k2CtrOff) + c;
+      unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k2CtrOff) + (long long)slot * C + c;
       const unsigned old = atomicAdd(ctr, 1u);
       if (old + 1 == plan.liveSegs(l, clen)) {  // last segment of this "ReduceBlock": tell every peer, count included
         atomicExch(ctr, 0u);
@@ -428,16 +430,27 @@ __device__ void retireRound(const AarRankParams& p, const AarLayout& l, int ncta
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence_system();
-    unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k3CtrOff);
+    unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k3CtrOff) + (p.round % l.L);
     const unsigned old = atomicAdd(ctr, 1u);
     if (old + 1 == (unsigned)nctas) {
       atomicExch(ctr, 0u);
+      // Rounds of one rank may overlap on two streams (the maxLag window), but they retire in order: peers use
+      // peerBase as "every round below this is finished with its slot".  The older round's CTAs are resident and
+      // never wait for this one, so this spin ends.
+      if (p.flags & AAR_FLAG_OVERLAPPED) {
+        const uint32_t* flushed = statusWord(p, l, 1);
+        unsigned backoff = 64;
+        while (ld_relaxed_sys_u32(flushed) < (uint32_t)p.round) {
+          __nanosleep(backoff);
+          if (backoff < 1024) backoff *= 2;
+        }
+      }
       __threadfence_system();
       for (int i2 = 0; i2 < l.P; ++i2) {
         const int dest = (i2 + p.rank) % l.P;
         st_release_sys_u32(reinterpret_cast<uint32_t*>(regionOf(p, dest) + l.peerBaseOff) + p.rank, (uint32_t)(p.round + 1));
       }
-      atomicAdd(statusWord(p, l, 1), 1u);  // rounds flushed
+      atomicMax(statusWord(p, l, 1), (uint32_t)(p.round + 1));  // rounds flushed
       if (p.hostDone) st_release_sys_u32(p.hostDone, (uint32_t)(p.round + 1));
     }
   }
@@ -655,7 +668,7 @@ __device__ void phaseOneshotPush(const AarRankParams& p, const AarLayout& l, int
     __syncthreads();
     if (threadIdx.x == 0) {
       __threadfence_system();
-      unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k1CtrOff) + dest * l.C;
+      unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k1CtrOff) + ((long long)slot * P + dest) * l.C;
       const unsigned old = atomicAdd(ctr, 1u);
       if (old + 1 == (unsigned)Tn) {
         atomicExch(ctr, 0u);
@@ -738,10 +751,10 @@ __global__ void __launch_bounds__(kThreads, 1) p2pPipelinedKernel(const AarRankP
   const int nPush = split & 0xffff, nReduce = split >> 16;
   const int b = blockIdx.x;
   if (b < nPush) {
-    phaseScatter<T, false>(p, l, b, nPush, sm);
+    phaseScatter<T, false>(p, l, b, nPush, sm, 1);
     traceMark(p, l, 1);
   } else if (b < nPush + nReduce) {
-    phaseReduceBcast<T, false>(p, l, b - nPush, nReduce, sm);
+    phaseReduceBcast<T, false>(p, l, b - nPush, nReduce, sm, 1);
     traceMark(p, l, 3);
   } else {
     const int cta = b - nPush - nReduce, n = nctas - nPush - nReduce;
@@ -756,28 +769,29 @@ __global__ void __launch_bounds__(kThreads, 1) p2pPipelinedKernel(const AarRankP
   traceMark(p, l, 5);
 }
 
-// K4, one launch per round, CTAs specialised by role so the three stages overlap chunk by chunk:
-//   CTAs [0, nReduce)      in-switch reduce + multicast store of my block (few CTAs saturate NVLS: measured
-//                          multimem throughput falls when more than ~32 CTAs issue it, profiles/r1_link_bench_8gpu.json)
-//   CTAs [nReduce, grid)   stage my input into the multicast-bound region (arrival flags per chunk), then copy every
-//                          reduced chunk to the caller's output as soon as its flag lands.
+// K4, one launch per round, CTAs specialised by role so the stages overlap chunk by chunk -- and, because consecutive
+// rounds alternate between two streams, round by round: the stage CTAs sit first in block order and leave early, so
+// the next round's stage CTAs take their SMs while this round is still reducing and gathering.
+//   CTAs [0, nStage)                  copy my input into the multicast-bound staging area, arrival flags per chunk
+//   CTAs [nStage, nStage + nReduce)   in-switch reduce + multicast store of my block (few CTAs saturate NVLS: measured
+//                                     multimem throughput does not grow beyond ~8-16 CTAs, profiles/r1_link_bench_8gpu.json)
+//   the rest                          copy every reduced chunk to the caller's output as soon as its flag lands
 template <typename T>
-__global__ void __launch_bounds__(kThreads, 1) nvlsPipelinedKernel(const AarRankParams p, const AarLayout l, int nReduce) {
+__global__ void __launch_bounds__(kThreads, 1) nvlsPipelinedKernel(const AarRankParams p, const AarLayout l, int split) {
   __shared__ Smem sm;
   initSmem(sm);
   traceMark(p, l, 0);
   const int nctas = gridDim.x;
-  if ((int)blockIdx.x < nReduce) {
+  const int nStage = split & 0xffff, nReduce = split >> 16;
+  const int b = blockIdx.x;
+  if (b < nStage) {
+    phaseScatter<T, true>(p, l, b, nStage, sm, 1);
     traceMark(p, l, 1);
-    phaseReduceBcast<T, true>(p, l, blockIdx.x, nReduce, sm);
+  } else if (b < nStage + nReduce) {
+    phaseReduceBcast<T, true>(p, l, b - nStage, nReduce, sm);
     traceMark(p, l, 3);
-    traceMark(p, l, 4);
   } else {
-    const int cta = blockIdx.x - nReduce, n = nctas - nReduce;
-    phaseScatter<T, true>(p, l, cta, n, sm);
-    traceMark(p, l, 1);
-    traceMark(p, l, 3);
-    phaseGatherEager<T>(p, l, cta, n, sm);
+    phaseGatherEager<T>(p, l, b - nStage - nReduce, nctas - nStage - nReduce, sm);
     traceMark(p, l, 4);
   }
   retireRound(p, l, nctas);
@@ -892,11 +906,15 @@ AAR_API int aar_launch_nvls(const AarRankParams* p, const AarLayout* lay, int ph
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     int g = grid > 0 ? grid : sms;
-    if (g < 2) g = 2;
-    int nReduce = nReduceArg > 0 ? nReduceArg : 24;
-    if (nReduce > g / 2) nReduce = g / 2;
-    if (lay->dtype == AAR_F32) return launch(nvlsPipelinedKernel<float>, p, lay, g, stream, what, nReduce);
-    if (lay->dtype == AAR_BF16) return launch(nvlsPipelinedKernel<__nv_bfloat16>, p, lay, g, stream, what, nReduce);
+    if (g < 3) g = 3;
+    int nReduce = nReduceArg & 0xff, nStage = (nReduceArg >> 8) & 0xff;
+    if (nReduce <= 0) nReduce = 16;
+    if (nStage <= 0) nStage = g / 3;
+    if (nReduce > g / 3) nReduce = g / 3;
+    if (nStage + nReduce >= g) nStage = g - nReduce - 1;
+    const int sp = nStage | (nReduce << 16);
+    if (lay->dtype == AAR_F32) return launch(nvlsPipelinedKernel<float>, p, lay, g, stream, what, sp);
+    if (lay->dtype == AAR_BF16) return launch(nvlsPipelinedKernel<__nv_bfloat16>, p, lay, g, stream, what, sp);
     return aar_host::fail(AAR_EINVAL, "%s: unknown dtype %d", what, lay->dtype);
   }
   if (lay->dtype == AAR_F32) return launch(roundKernel<float, true>, p, lay, grid, stream, what, mask);

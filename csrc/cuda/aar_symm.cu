@@ -103,12 +103,12 @@ AAR_API int aar_layout_compute(int P, int dataSize, int maxChunkSize, int maxLag
   l.sflagOff = take((uint64_t)l.L * l.C * AAR_MAXP * 4);
   l.rflagOff = take((uint64_t)l.L * P * l.C * 8);
   l.peerBaseOff = take(AAR_MAXP * 4);
-  l.k1DecOff = take(AAR_MAXP * 8);
-  l.k1CtrOff = take((uint64_t)P * l.C * 4);
+  l.k1DecOff = take((uint64_t)l.L * AAR_MAXP * 8);
+  l.k1CtrOff = take((uint64_t)l.L * P * l.C * 4);
   l.k2DecOff = take((uint64_t)l.L * l.C * 8);
-  l.k2CtrOff = take((uint64_t)l.C * 4);
+  l.k2CtrOff = take((uint64_t)l.L * l.C * 4);
   l.k3DecOff = take((uint64_t)l.L * 8);
-  l.k3CtrOff = take(4 * 4);
+  l.k3CtrOff = take((uint64_t)l.L * 4);
   l.countsOff = take((uint64_t)l.L * (uint64_t)P * l.C * 4);
   l.statusOff = take(16 * 4);
   l.oneshotFlagOff = take((uint64_t)l.L * AAR_MAXP * 4);

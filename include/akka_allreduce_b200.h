@@ -33,6 +33,7 @@ extern "C" {
 #define AAR_FLAG_FORCE 4u       /* K8: do not wait, take whatever has arrived (catch-up, AllreduceWorker.scala:91-97) */
 #define AAR_FLAG_SKIP_SCATTER 8u /* fused kernel: this rank contributes nothing this round (fault injection) */
 #define AAR_FLAG_VIEW_OUTPUT 16u /* K3 does not copy: the caller reads the reduce-ring slot itself, stream-ordered */
+#define AAR_FLAG_OVERLAPPED 64u /* consecutive rounds of this rank run on different streams: retire strictly in order */
 #define AAR_FLAG_TRACE 32u      /* every CTA stamps %globaltimer at its phase boundaries into the trace section */
 #define AAR_TRACE_CTAS 512
 #define AAR_TRACE_MARKS 8
@@ -54,12 +55,12 @@ typedef struct AarLayout {
   uint64_t sflagOff;         /* u32 [L][C][AAR_MAXP]            epoch = round+1, written by src */
   uint64_t rflagOff;         /* u64 [L][P(owner)][C]            epoch<<32 | contributor count, written by owner */
   uint64_t peerBaseOff;      /* u32 [AAR_MAXP]                  rounds retired by each peer (flow control) */
-  uint64_t k1DecOff;         /* u64 [AAR_MAXP]                  local: per-destination go/skip decision */
-  uint64_t k1CtrOff;         /* u32 [P][C]                      local: last-CTA election, scatter */
+  uint64_t k1DecOff;         /* u64 [L][AAR_MAXP]               local: per-destination go/skip decision */
+  uint64_t k1CtrOff;         /* u32 [L][P][C]                   local: last-CTA election, scatter */
   uint64_t k2DecOff;         /* u64 [L][C]                      local: epoch<<32 | contributor mask */
-  uint64_t k2CtrOff;         /* u32 [C]                         local: last-CTA election, broadcast */
+  uint64_t k2CtrOff;         /* u32 [L][C]                      local: last-CTA election, broadcast */
   uint64_t k3DecOff;         /* u64 [L]                         local: epoch<<32 | state */
-  uint64_t k3CtrOff;         /* u32 [4]                         local: last-CTA election, retire */
+  uint64_t k3CtrOff;         /* u32 [L]                         local: last-CTA election, retire (per slot: rounds overlap) */
   uint64_t countsOff;        /* i32 [L][totalChunks]            local: per-chunk contributor count, -1 = missing */
   uint64_t statusOff;        /* u32 [16]                        local: status bits, counters */
   uint64_t oneshotOff;       /* T   [L][P(src)][dataSize] + u32 [L][AAR_MAXP] flags; 0 if not allocated */
@@ -112,7 +113,8 @@ int aar_launch_round_pipelined(const AarRankParams* p, const AarLayout* lay, int
  * single-GPU emulation can order them; phase = 0 push, 1 reduce, 2 both. */
 int aar_launch_oneshot(const AarRankParams* p, const AarLayout* lay, int phase, int grid, void* stream);
 /* K4 NVLS: multimem.ld_reduce over the staged inputs + multimem.st of the result (thresholds must be 1.0).
- * phases is a bit mask: 1 stage + arrival flags, 2 in-switch reduce + multicast store, 4 gather; 7 = one launch. */
+ * phases is a bit mask: 1 stage + arrival flags, 2 in-switch reduce + multicast store, 4 gather; 7 = one launch with the CTAs
+ * specialised by role (| nReduceCtas << 8 | nStageCtas << 16, 0 = defaults). */
 int aar_launch_nvls(const AarRankParams* p, const AarLayout* lay, int phases, int grid, void* stream);
 
 /* Single-device cluster emulation: P ranks' regions live on the current device; runs one full round for all

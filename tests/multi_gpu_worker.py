@@ -1,0 +1,159 @@
+"""Body of the multi-GPU tests (launched by tests/test_gpu_multi.py under torch.distributed.run, one process per GPU).
+
+Every check is bit-exact against a PyTorch fp32 restatement of the reference's ordered reduction over the contributor set
+(AllreduceWorker.scala:240-251): the inputs of all ranks are generated from a shared seed, so every rank can compute the
+oracle locally."""
+import os
+import struct
+import sys
+import threading
+from pathlib import Path
+
+import torch
+
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+from akka_allreduce_b200 import AllreduceMaster, AllreduceWorker, AllReduceInput  # noqa: E402
+from akka_allreduce_b200.ops import lib as L  # noqa: E402
+from akka_allreduce_b200.parallel.engine import ONESHOT_MAX_BYTES, RoundEngine  # noqa: E402
+from akka_allreduce_b200.parallel.symmetric import SymmetricMemory, UnixRendezvous  # noqa: E402
+
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+lr = int(os.environ.get("LOCAL_RANK", rank))
+torch.cuda.set_device(lr)
+dev = torch.device("cuda", lr)
+sess = f"mt_{os.environ.get('MASTER_PORT', '0')}_{os.getppid()}"
+rdv = UnixRendezvous(rank, world, sess + "_c")
+failures = []
+
+
+def inputs_for(n, dtype, seed):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return [(torch.randn(n, generator=g) * 3).to(dtype).to(dev) for _ in range(world)]
+
+
+def ordered_sum(xs, srcs, dtype, normalize=False):
+    acc = torch.zeros_like(xs[0], dtype=torch.float32)
+    for s in srcs:
+        acc = acc + xs[s].float()
+    if normalize and len(srcs) > 1:
+        acc = torch.div(acc, torch.full_like(acc, float(len(srcs))))
+    return acc.to(dtype)
+
+
+def check(name, cond):
+    ok = all(b == b"\1" for b in rdv.all_gather_bytes(b"\1" if cond else b"\0"))
+    if rank == 0:
+        print(("PASS " if ok else "FAIL ") + name, flush=True)
+    if not ok:
+        failures.append(name)
+
+
+k = [0]
+
+
+def engine_case(n, chunk, dtype, algo, rounds=5, th=1.0, normalize=False, overlap=None, max_lag=1):
+    code = L.AAR_F32 if dtype == torch.float32 else L.AAR_BF16
+    es = 4 if dtype == torch.float32 else 2
+    lay = L.compute_layout(world, n, chunk, max_lag, code, ONESHOT_MAX_BYTES // es, True)
+    k[0] += 1
+    symm = SymmetricMemory(UnixRendezvous(rank, world, f"{sess}_m{k[0]}"), lay.regionBytes, lr, want_multicast=True)
+    name = f"{algo} n={n} chunk={chunk} {str(dtype)[6:]} th={th} overlap={overlap} mc={symm.has_multicast}"
+    try:
+        eng = RoundEngine.from_symmetric(symm, lay, algo=algo, th_reduce=th, th_complete=th, normalize=normalize, overlap=overlap, timeout_ms=5000.0)
+    except ValueError as e:
+        if rank == 0:
+            print(f"SKIP {name}: {e}", flush=True)
+        symm.close()
+        return
+    good = True
+    keep = []
+    for r in range(rounds):
+        xs = inputs_for(n, dtype, 1000 + r)
+        keep.append(xs)
+        out, counts = eng.enqueue_round(r, xs[rank])
+        eng.wait_round(r)
+        torch.cuda.synchronize()
+        want = ordered_sum(xs, list(range(world)), dtype, normalize)
+        if algo == "nvls":  # the switch does not promise peer-index order: equal up to fp32 reassociation
+            good &= bool(torch.allclose(out.float(), want.float(), rtol=2e-5 if dtype == torch.float32 else 2e-2, atol=1e-4))
+        else:
+            good &= bool(torch.equal(out, want))
+        good &= int(counts.min()) == world and int(counts.max()) == world
+        rdv.barrier()
+    good &= eng.status() == 0
+    check(name + f" -> {eng.algo}", good)
+    eng.close()
+    symm.close()
+
+
+def threshold_case():
+    """One rank never scatters (AAR_FLAG_SKIP_SCATTER): with thReduce = thComplete = 0.5 the others' sum is flushed and the
+    counts say so; nobody hangs."""
+    n, chunk = 1 << 16, 1 << 12
+    lay = L.compute_layout(world, n, chunk, 1, L.AAR_F32, 0, False)
+    k[0] += 1
+    symm = SymmetricMemory(UnixRendezvous(rank, world, f"{sess}_m{k[0]}"), lay.regionBytes, lr, want_multicast=False)
+    eng = RoundEngine.from_symmetric(symm, lay, algo="twoshot", th_reduce=0.5, th_complete=0.5, timeout_ms=5000.0, overlap=False)
+    silent = world - 1
+    xs = inputs_for(n, torch.float32, 77)
+    out, counts = eng.enqueue_round(0, xs[rank], skip_scatter=(rank == silent))
+    torch.cuda.synchronize()
+    rdv.barrier()
+    cmin, cmax = int(counts.min()), int(counts.max())
+    # every reduced chunk has world-1 or world contributors depending on whether it was decided before the silent rank's (absent) data;
+    # since that rank never sends, exactly world-1 (or fewer chunks than total if its own block's owner was late)
+    ok = cmax <= world - 1 or world == 1
+    want = ordered_sum(xs, [r for r in range(world) if r != silent], torch.float32)
+    arrived = counts.repeat_interleave(chunk)[:n] > 0 if lay.totalChunks * chunk >= n else None
+    if arrived is not None:
+        ok &= bool(torch.equal(out[arrived], want[arrived])) and bool((out[~arrived] == 0).all())
+    check(f"threshold 0.5 with a silent rank (counts {cmin}..{cmax})", ok and eng.status() == 0)
+    eng.close()
+    symm.close()
+
+
+def api_case():
+    """AllreduceMaster + AllreduceWorker(backend=cuda) end to end, 12 rounds, pipelined master clock."""
+    n, chunk, rounds = 1 << 18, 1 << 14, 12
+    port = int(os.environ.get("MASTER_PORT", "29500")) + 57
+    master = None
+    if rank == 0:
+        master = AllreduceMaster(world, 1.0, 1.0, 1.0, 1, n, rounds - 1, chunk, pipeline_depth=1, port=port)
+        master.start(120)
+    rdv.barrier()
+    seen = []
+    good = [True]
+
+    def source(req):
+        return AllReduceInput(inputs_for(n, torch.float32, 5000 + req.iteration)[worker.id])
+
+    def sink(out):
+        xs = inputs_for(n, torch.float32, 5000 + out.iteration)
+        want = ordered_sum(xs, list(range(world)), torch.float32)
+        ok = bool(torch.equal(out.data, want)) if worker.engine.algo != "nvls" else bool(torch.allclose(out.data, want, rtol=2e-5, atol=1e-4))
+        good[0] &= ok and int(out.count.min()) == world
+        seen.append(out.iteration)
+
+    worker = AllreduceWorker(source, sink, backend="cuda", device=lr, session=f"{sess}_api")
+    ok = worker.run("127.0.0.1", port, timeout_sec=120)
+    if master:
+        master.join(30)
+    check("public API: master + cuda workers, rounds in order, sums exact", ok and good[0] and seen == list(range(rounds)))
+    worker.close()
+
+
+for dtype in (torch.float32, torch.bfloat16):
+    engine_case(1 << 20, 1 << 16, dtype, "twoshot", overlap=False)
+    engine_case(1 << 20, 1 << 16, dtype, "pipelined")
+    engine_case(1 << 20, 1 << 16, dtype, "nvls")
+    engine_case(8192, 1024, dtype, "oneshot")
+engine_case((1 << 20) + 8, 40000, torch.float32, "pipelined")      # unaligned blocks and chunks: scalar path
+engine_case(1003, 17, torch.float32, "twoshot", overlap=False)
+engine_case(1 << 20, 1 << 16, torch.float32, "auto", normalize=True)
+engine_case(1 << 22, 1 << 18, torch.float32, "auto", rounds=12, max_lag=3)
+threshold_case()
+api_case()
+rdv.barrier()
+if rank == 0:
+    print("MULTI-GPU RESULT:", "FAILED " + "; ".join(failures) if failures else "ALL PASSED", flush=True)
+sys.exit(1 if failures else 0)
