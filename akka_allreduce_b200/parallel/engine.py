@@ -65,7 +65,7 @@ class RoundEngine:
         self.launches = 0
         # CTA role split of the pipelined kernels (measured on 8xB200, profiles/r1_phase_bench_*.txt)
         self.split = 32 | (48 << 16)      # nPush | nReduce << 16; the rest gather
-        self.nvls_reduce_ctas = 16
+        self.nvls_reduce_ctas = 8        # 207.7 us with 8 vs 222 us with 16 reduce CTAs at 8 GPUs, 64 MiB
         self.nvls_stage_ctas = 48
         # The maxLag window lets two consecutive rounds of one worker be in flight: they alternate between two internal
         # streams, so the push of round r+1 starts on the SMs that round r's push CTAs have already left while round r is

@@ -54,10 +54,14 @@ symm = SymmetricMemory(UnixRendezvous(rank, world, sess + "_m"), lay.regionBytes
 
 def run_engine(th, delay_us, tag):
     eng = RoundEngine.from_symmetric(symm, lay, th_reduce=th, th_complete=th, timeout_ms=2000.0)
+    import time
     base = run_engine.next_round
+    tw = time.time()
     for r in range(base, base + a.warmup):
         eng.enqueue_round(r, xs[r % 2])
     eng.wait_all(); sync()
+    warm_s = time.time() - tw
+    st_warm = eng.status()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     cmin, cmax = 1 << 30, 0
@@ -70,7 +74,7 @@ def run_engine(th, delay_us, tag):
     sync()
     ms = gmax(e0.elapsed_time(e1) / a.rounds)
     cmin, cmax = int(counts.min()), int(counts.max())
-    res[tag] = {"ms_per_round": round(ms, 4), "rounds_per_sec": round(1e3 / ms, 1), "last_round_counts_min_max": [cmin, cmax], "status_bits": eng.status(), "algo": eng.algo}
+    res[tag] = {"ms_per_round": round(ms, 4), "rounds_per_sec": round(1e3 / ms, 1), "last_round_counts_min_max": [cmin, cmax], "status_bits": eng.status(), "status_after_warmup": st_warm, "warmup_wall_s": round(warm_s, 3), "algo": eng.algo}
     run_engine.next_round = first + a.rounds
     eng.close()
     # the region keeps its flags: continue with later round numbers so epochs stay monotone

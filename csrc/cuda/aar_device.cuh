@@ -152,10 +152,21 @@ struct Deadline {
   __device__ bool expired() const { return budget != 0 && globaltimer_ns() - start > budget; }
 };
 
-// True when the host (or the caller) demands completion with whatever has arrived:
-// AAR_FLAG_FORCE, or the master's newest round left this round outside the maxLag window.
-__device__ __forceinline__ bool forcedByHost(const AarRankParams& p) {
+// True when this round must complete with whatever has arrived (the catch-up of AllreduceWorker.scala:91-97):
+//   * AAR_FLAG_FORCE, or
+//   * the master's newest round (host doorbell) left this round outside the maxLag window, or
+//   * a peer is known to have FINISHED a round more than maxLag ahead of this one.  That is the device-side form of the
+//     reference's peer-ahead self-start (AllreduceWorker.scala:123-126): progress of the peers reaches a worker through
+//     the data plane (their retire words land in my region), not only through the master.
+__device__ __forceinline__ bool forcedByHost(const AarRankParams& p, const AarLayout& l) {
   if (p.flags & AAR_FLAG_FORCE) return true;
+  const uint32_t* base = reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(p.region[p.rank]) + l.peerBaseOff);
+  int newestDone = -1;
+  for (int j = 0; j < l.P; ++j) {
+    const int done = (int)ld_relaxed_sys_u32(base + j) - 1;  // newest round peer j has retired
+    newestDone = done > newestDone ? done : newestDone;
+  }
+  if (newestDone - p.round > p.maxLag) return true;
   if (p.doorbell) {
     int newest = (int)ld_relaxed_sys_u32(reinterpret_cast<const uint32_t*>(p.doorbell));
     if (newest - p.round > p.maxLag) return true;

@@ -96,7 +96,7 @@ __device__ bool scatterDecision(const AarRankParams& p, const AarLayout& l, int 
           unsigned spins = 0;
           for (;;) {
             if (ld_acquire_sys_u32(base) >= need) break;
-            if (((++spins & 63u) == 0) && (forcedByHost(p) || dl.expired())) {
+            if (((++spins & 63u) == 0) && (forcedByHost(p, l) || dl.expired())) {
               go = 0;  // the peer fell out of the window: its copy of this contribution is dropped
               break;
             }
@@ -194,11 +194,11 @@ __device__ unsigned chunkDecision(const AarRankParams& p, const AarLayout& l, ui
     uint32_t f = (lane < l.P) ? ld_relaxed_sys_u32(flags + lane) : 0u;
     arrived = __ballot_sync(0xffffffffu, lane < l.P && f == (uint32_t)epoch);
     if (__popc(arrived) >= minRequired) break;
-    const bool look = (p.flags & AAR_FLAG_FORCE) || ((++spins & 255u) == 0);
+    const bool look = (p.flags & AAR_FLAG_FORCE) || ((++spins & 31u) == 0);
     if (look) {
       int stop = 0;
       if (lane == 0) {
-        if (forcedByHost(p)) stop = 1;
+        if (forcedByHost(p, l)) stop = 1;
         else if (dl.expired()) stop = 2;
       }
       stop = __shfl_sync(0xffffffffu, stop, 0);
@@ -493,7 +493,7 @@ __device__ void gatherDecision(const AarRankParams& p, const AarLayout& l, int s
       __syncthreads();
       int stop = (sm.k3Count >= p.minChunksRequired) ? 1 : 0;
       if (!stop && threadIdx.x == 0 && ((p.flags & AAR_FLAG_FORCE) || (++spins & 127u) == 0)) {
-        if (forcedByHost(p)) sm.scratch = 1;
+        if (forcedByHost(p, l)) sm.scratch = 1;
         else if (dl.expired()) {
           sm.scratch = 1;
           atomicOr(statusWord(p, l, 0), AAR_ST_TIMEOUT_GATHER);
@@ -615,7 +615,7 @@ __device__ void phaseGatherEager(const AarRankParams& p, const AarLayout& l, int
             break;
           }
           if ((p.flags & AAR_FLAG_FORCE) || ((++spins & 255u) == 0)) {
-            if (forcedByHost(p)) break;
+            if (forcedByHost(p, l)) break;
             if (dl.expired()) {
               atomicOr(statusWord(p, l, 0), AAR_ST_TIMEOUT_GATHER);
               break;

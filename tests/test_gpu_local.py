@@ -177,6 +177,27 @@ def test_device_timeout_is_a_liveness_guard():
     assert cl.status(2) & L.ST_TIMEOUT_REDUCE
 
 
+def test_rank_outside_the_lag_window_forces_itself_through():
+    """Device-side catch-up (AllreduceWorker.scala:91-97 / :123-126): a rank that sees a peer has already FINISHED a round
+    more than maxLag ahead stops waiting for its quorum and completes with what it has -- here nothing -- instead of
+    sitting in its wait until the liveness timeout."""
+    import time
+
+    P, n, chunk = 4, 4096, 512
+    cl = cluster(P, n, chunk, max_lag=1, th_reduce=1.0, th_complete=1.0, timeout_ms=20000.0)
+    lay = cl.layout
+    xs = make_inputs(P, n, torch.float32, 90)
+    # peers 0..2 announce (through rank 3's copy of the retire words) that they finished rounds 0..4
+    cl._section(3, lay.peerBaseOff, 16 * 4, torch.int32)[:3] = 5
+    torch.cuda.synchronize()
+    t0 = time.time()
+    cl.run_phases(0, xs, reduce=[3], gather=[3])  # nobody scattered anything for round 0
+    torch.cuda.synchronize()
+    assert time.time() - t0 < 5.0, "the round waited for the timeout instead of forcing itself"
+    assert torch.count_nonzero(cl.outputs[3]) == 0 and torch.count_nonzero(cl.counts[3]) == 0
+    assert cl.status(3) == 0
+
+
 @pytest.mark.parametrize("P,n,dtype", [(2, 10, torch.float32), (8, 2048, torch.float32), (4, 50000, torch.bfloat16), (8, 65536, torch.float32)])
 def test_oneshot_bit_exact(P, n, dtype):
     cl = cluster(P, n, max(1, n // P), max_lag=1, dtype=dtype, oneshot=True)
