@@ -1,0 +1,130 @@
+"""Data-parallel gradient averaging through the worker source/sink contract, overlapped with backward.
+
+dataSize is fixed when a worker is initialised (AllreduceWorker.scala:174-176), so the flat gradient is cut into equal
+fixed-size buckets and every bucket gets its own round engine ("one round stream per bucket").
+Parameters' `.grad` tensors are views into the bucket buffers, so autograd accumulates straight into the memory the
+kernels read.  A post-accumulate-grad hook counts down each bucket; the moment a bucket is complete its source callback
+hands the buffer to the engine, which launches the round on its own streams while autograd keeps running.  The sink
+callback sees the averaged gradients (normalisation by the ACTUAL contributor count is fused into the reduce kernel) --
+written in place into the same bucket, so the optimizer needs no copy.
+"""
+from __future__ import annotations
+
+from typing import Callable
+
+import torch
+
+from ..api import AllReduceInput, AllReduceInputRequest, AllReduceOutput
+from ..ops import lib as L
+from .engine import RoundEngine
+from .symmetric import SymmetricMemory, UnixRendezvous
+
+
+class GradientBucket:
+    def __init__(self, index: int, numel: int, dtype: torch.dtype, device: torch.device):
+        self.index = index
+        self.buffer = torch.zeros(numel, dtype=dtype, device=device)
+        self.params: list[torch.nn.Parameter] = []
+        self.pending = 0
+        self.engine: RoundEngine | None = None
+        self.symm: SymmetricMemory | None = None
+
+    # the worker contract (DataWrapper.scala:3-7)
+    def data_source(self, req: AllReduceInputRequest) -> AllReduceInput:
+        return AllReduceInput(self.buffer)
+
+    def data_sink(self, out: AllReduceOutput) -> None:
+        self.last_counts = out.count
+
+
+class ThresholdDDP:
+    def __init__(self, module: torch.nn.Module, rank: int, world: int, device: int, *, bucket_mb: float = 32.0, max_chunk: int = 1 << 20,
+                 max_lag: int = 1, th_reduce: float = 1.0, th_complete: float = 1.0, session: str = "ddp", algo: str = "auto",
+                 sink: Callable[[int, AllReduceOutput], None] | None = None):
+        self.module, self.rank, self.world = module, rank, world
+        self.device = torch.device("cuda", device)
+        self.step = 0
+        self.user_sink = sink
+        params = [p for p in module.parameters() if p.requires_grad]
+        dtype = params[0].dtype
+        assert dtype in (torch.float32, torch.bfloat16) and all(p.dtype == dtype for p in params), "one gradient dtype (fp32 or bf16)"
+        es = params[0].element_size()
+        per_bucket = max(1, int(bucket_mb * (1 << 20)) // es)
+        # Reverse registration order ~ the order gradients become ready; pack greedily, pad every bucket to a size the
+        # 16-byte vector path likes (multiple of world * 64 elements).
+        self.buckets: list[GradientBucket] = []
+        cur: list[torch.nn.Parameter] = []
+        size = 0
+        groups = []
+        for p in reversed(params):
+            if size and size + p.numel() > per_bucket:
+                groups.append(cur)
+                cur, size = [], 0
+            cur.append(p)
+            size += p.numel()
+        if cur:
+            groups.append(cur)
+        align = world * 64
+        code = L.AAR_F32 if dtype == torch.float32 else L.AAR_BF16
+        for i, g in enumerate(groups):
+            n = sum(p.numel() for p in g)
+            n = (n + align - 1) // align * align
+            b = GradientBucket(i, n, dtype, self.device)
+            off = 0
+            for p in g:
+                p.grad = b.buffer[off:off + p.numel()].view_as(p)   # autograd accumulates in place from now on
+                off += p.numel()
+                b.params.append(p)
+                p.register_post_accumulate_grad_hook(self._make_hook(b))
+            chunk = max(1, min(max_chunk, (n + world - 1) // world))
+            if world > 1:
+                lay = L.compute_layout(world, n, chunk, max_lag, code, 0, True)
+                b.symm = SymmetricMemory(UnixRendezvous(rank, world, f"{session}_b{i}"), lay.regionBytes, device, want_multicast=True)
+                b.engine = RoundEngine.from_symmetric(b.symm, lay, th_reduce=th_reduce, th_complete=th_complete, normalize=True, algo=algo)
+            else:
+                b.engine = RoundEngine.single_process(n, chunk, max_lag, dtype=dtype, device=device, normalize=True)
+            self.buckets.append(b)
+        self._arm()
+
+    def _arm(self):
+        for b in self.buckets:
+            b.pending = len(b.params)
+
+    def _make_hook(self, b: GradientBucket):
+        def hook(_param):
+            b.pending -= 1
+            if b.pending == 0:
+                self._launch(b)
+        return hook
+
+    def _launch(self, b: GradientBucket):
+        x = b.data_source(AllReduceInputRequest(self.step)).data
+        # in place: every element range is pushed (read) before the chunk that overwrites it can have been reduced
+        out, counts = b.engine.enqueue_round(self.step, x, out=x)
+        b._out = (out, counts)
+
+    def finish(self) -> None:
+        """Call after backward(): the current stream waits for every bucket's round, sinks are invoked, hooks re-armed."""
+        for b in self.buckets:
+            if b.pending != 0:   # a parameter without gradient this step: launch what we have
+                self._launch(b)
+            b.engine.wait_round(self.step)
+            out = AllReduceOutput(b._out[0], b._out[1], self.step)
+            b.data_sink(out)
+            if self.user_sink:
+                self.user_sink(b.index, out)
+        self.step += 1
+        self._arm()
+
+    def zero_grad(self) -> None:
+        for b in self.buckets:
+            b.buffer.zero_()
+
+    def launches(self) -> int:
+        return sum(b.engine.launches for b in self.buckets)
+
+    def close(self) -> None:
+        for b in self.buckets:
+            b.engine.close()
+            if b.symm:
+                b.symm.close()

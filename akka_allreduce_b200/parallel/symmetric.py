@@ -175,6 +175,13 @@ class SymmetricMemory:
             os.close(fds[r])
             self.imports[r] = v
             self.ptrs[r] = v.ptr
+        # Load the kernel module now (the first launch of a process pays for lazy loading; ranks that differ by seconds
+        # there would look like stragglers to each other) and leave the constructor together.
+        import torch
+
+        with torch.cuda.device(device):
+            L.check(lib.aar_launch_delay(1, None), "aar_launch_delay")
+            torch.cuda.synchronize(device)
         rdv.barrier()
         self.mc_ptr = 0
         self.mc_handle = 0
