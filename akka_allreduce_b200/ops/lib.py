@@ -76,6 +76,7 @@ def load():
         "aar_launch_gather": [P(AarRankParams), P(AarLayout), C.c_int, C.c_void_p],
         "aar_launch_round_fused": [P(AarRankParams), P(AarLayout), C.c_int, C.c_void_p],
         "aar_launch_round_pipelined": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_void_p],
+        "aar_launch_persistent": [P(AarRankParams), P(AarLayout), C.c_void_p, C.c_int, C.c_int, C.c_void_p],
         "aar_launch_oneshot": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_void_p],
         "aar_launch_nvls": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_void_p],
         "aar_local_round": [P(AarRankParams), C.c_int, P(AarLayout), C.c_uint, C.c_int, C.c_void_p],

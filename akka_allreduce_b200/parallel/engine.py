@@ -185,3 +185,89 @@ class RoundEngine:
         if self._host_words:
             self.lib.aar_host_words_free(self._host_words)
             self._host_words = None
+
+
+class PersistentEngine:
+    """K7: a resident kernel per rank driven by a doorbell instead of one launch per round.
+
+    The host posts {round, input, output} into a ring in pinned memory (a few stores, ~1 us of Python) and the kernel
+    picks it up after one PCIe poll; completion comes back through the engine's host-mapped completion word.  Meant for
+    the latency-bound sizes, where a launch per round costs more than the round.  The inputs must already be complete
+    when a round is posted (the resident kernel cannot wait on a stream), and the kernel keeps `grid` SMs until stop().
+    While it runs, never synchronise the whole device (torch.cuda.synchronize / cudaDeviceSynchronize wait for the resident
+    kernel, which only ends at stop()); synchronise streams or use wait().  For the same reason every kernel that will be
+    launched while it runs must have been launched once before (CUDA loads modules lazily, and loading waits for an idle
+    device), or run with CUDA_MODULE_LOADING=EAGER.
+    """
+
+    DEPTH, WORDS, MAX_OUTSTANDING = 8, 16, 4
+
+    def __init__(self, eng: RoundEngine, algo: str = "oneshot", grid: int = 16):
+        if algo not in ("oneshot", "twoshot"):
+            raise ValueError("persistent algo must be 'oneshot' or 'twoshot'")
+        if algo == "oneshot" and not eng.layout.oneshotOff:
+            raise ValueError("the layout has no one-shot buffers")
+        self.eng, self.algo = eng, algo
+        lib = eng.lib
+        host = C.POINTER(C.c_uint)()
+        dev = C.POINTER(C.c_uint)()
+        with torch.cuda.device(eng.device):
+            L.check(lib.aar_host_words_alloc(self.DEPTH * self.WORDS, C.byref(host), C.byref(dev)), "aar_host_words_alloc")
+            self.stream = torch.cuda.Stream(device=eng.device)
+        self._ring, self._ring_dev = host, dev
+        self.posted = 0
+        self.first_round: int | None = None
+        p = L.AarRankParams.from_buffer_copy(eng.params)
+        p.flags = eng.base_flags
+        self._params = p
+        with torch.cuda.device(eng.device):
+            L.check(lib.aar_launch_persistent(C.byref(p), eng._lay, C.cast(dev, C.c_void_p), 1 if algo == "oneshot" else 0, grid,
+                                              C.c_void_p(self.stream.cuda_stream)), "aar_launch_persistent")
+        self.running = True
+
+    def _completed(self) -> int:
+        return 0 if self.first_round is None else max(0, self.eng.rounds_flushed() - self.first_round)
+
+    def post(self, rnd: int, x: torch.Tensor, out: torch.Tensor | None = None, flags: int = 0):
+        """Ring the doorbell for round `rnd` (rounds must be consecutive).  Returns (output, counts) tensors of the slot."""
+        eng = self.eng
+        if self.first_round is None:
+            self.first_round = rnd
+        elif rnd != self.first_round + self.posted:
+            raise ValueError("persistent rounds must be posted in consecutive order")
+        while self.posted - self._completed() >= self.MAX_OUTSTANDING:
+            pass  # the ring entry (and the output slot) of an unfinished round may not be reused
+        slot = rnd % eng.layout.L
+        output = eng.outputs[slot] if out is None else out
+        counts = eng.counts[slot]
+        r = self._ring
+        e = (self.posted % self.DEPTH) * self.WORDS
+        r[e + 1] = flags
+        r[e + 2] = rnd
+        r[e + 3] = 0
+        for k, ptr in ((4, x.data_ptr()), (6, output.data_ptr()), (8, counts.data_ptr())):
+            r[e + k] = ptr & 0xFFFFFFFF
+            r[e + k + 1] = ptr >> 32
+        r[e] = self.posted + 1  # the doorbell: written last (x86 keeps the store order)
+        self.posted += 1
+        eng.rounds_enqueued = max(eng.rounds_enqueued, rnd + 1)
+        return output, counts
+
+    def wait(self, rnd: int, timeout_s: float = 30.0) -> None:
+        import time
+
+        t0 = time.time()
+        while self.eng.rounds_flushed() < rnd + 1:
+            if time.time() - t0 > timeout_s:
+                raise TimeoutError(f"persistent engine: round {rnd} did not complete (flushed {self.eng.rounds_flushed()})")
+
+    def stop(self) -> None:
+        if not self.running:
+            return
+        e = (self.posted % self.DEPTH) * self.WORDS
+        self._ring[e + 3] = 1
+        self._ring[e] = self.posted + 1
+        self.posted += 1
+        self.stream.synchronize()
+        self.running = False
+        self.eng.lib.aar_host_words_free(self._ring)

@@ -41,11 +41,29 @@ def cuda_path() -> Path:
     return PKG / "libaar_cuda.so"
 
 
+def _digest(deps: list[Path]) -> str:
+    import hashlib
+
+    h = hashlib.sha1()
+    for d in sorted(set(deps)):
+        if d.exists():
+            h.update(str(d.relative_to(ROOT)).encode())
+            h.update(d.read_bytes())
+    return h.hexdigest()
+
+
 def _stale(out: Path, deps: list[Path]) -> bool:
+    """Stale = the output is missing or was built from different source CONTENT.  Modification times are useless here:
+    the tree is snapshotted onto fresh GPU boxes, where every file looks new and a time-based check would rebuild
+    everything on paid GPU time."""
     if not out.exists():
         return True
-    t = out.stat().st_mtime
-    return any(d.exists() and d.stat().st_mtime > t for d in deps)
+    stamp = out.with_name(out.name + ".srchash")
+    return (not stamp.exists()) or stamp.read_text().strip() != _digest(deps)
+
+
+def _stamp(out: Path, deps: list[Path]) -> None:
+    out.with_name(out.name + ".srchash").write_text(_digest(deps))
 
 
 def _run(cmd: list[str]) -> None:
@@ -69,7 +87,7 @@ def _compile_objects(srcs: list[Path], flags: list[str], tag: str, force: bool) 
     for src in srcs:
         obj = objdir / (src.stem + ".o")
         objs.append(obj)
-        if force or _stale(obj, [src] + hdrs):
+        if force or not obj.exists():
             jobs.append(["g++", *flags, "-c", src, "-o", obj])
     if jobs:
         with ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
@@ -85,8 +103,9 @@ def build_core(force: bool = False) -> Path:
     if force or _stale(out, srcs + _headers()):
         flags = ["-O2", "-g1", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-Wall", "-Wno-unused-function",
                  f"-I{pybind11.get_include()}", f"-I{sysconfig.get_paths()['include']}", f"-I{ROOT / 'include'}"]
-        objs = _compile_objects(srcs, flags, "core", force)
+        objs = _compile_objects(srcs, flags, "core", True)
         _run(["g++", "-shared", *objs, "-o", out, "-lpthread"])
+        _stamp(out, srcs + _headers())
     return out
 
 
@@ -110,6 +129,7 @@ def build_cuda(force: bool = False) -> Path | None:
                "-Xptxas", "-v", f"-I{ROOT / 'include'}", f"-I{CSRC}"]
         cmd += srcs + ["-o", out, "-lpthread", "-ldl"]
         _run(cmd)
+        _stamp(out, srcs + _headers())
     return out
 
 
@@ -124,8 +144,9 @@ def build_cli(force: bool = False) -> list[Path]:
             continue
         out = BIN / name
         if force or _stale(out, core_srcs + [src] + _headers()):
-            objs = _compile_objects(core_srcs + [src], flags, "cli", force)
+            objs = _compile_objects(core_srcs + [src], flags, "cli", True)
             _run(["g++", *objs, "-o", out, "-lpthread"])
+            _stamp(out, core_srcs + [src] + _headers())
         outs.append(out)
     return outs
 

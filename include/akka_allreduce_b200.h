@@ -109,6 +109,11 @@ int aar_launch_round_fused(const AarRankParams* p, const AarLayout* lay, int gri
 /* Same round with the CTAs specialised by role (push / reduce+broadcast / gather) so the phases overlap chunk by chunk.
  * split = nPush | nReduce << 16, 0 = heuristic; the remaining CTAs gather. */
 int aar_launch_round_pipelined(const AarRankParams* p, const AarLayout* lay, int grid, int split, void* stream);
+/* K7 persistent round engine: one resident kernel per rank, driven through a command ring in pinned host memory
+ * (8 entries x 16 u32: {seq, flags, round, exit, input lo/hi, output lo/hi, counts lo/hi}); the host writes an entry, then
+ * its seq word (= command number + 1).  algo 0 = fused two-shot, 1 = one-shot.  Returns after launching; the kernel ends
+ * when it reads a command with exit != 0.  Completion of each round is reported through p->hostDone as usual. */
+int aar_launch_persistent(const AarRankParams* p, const AarLayout* lay, const void* hostRing, int algo, int grid, void* stream);
 /* K5 one-shot: push the whole vector to every peer, then each rank sums the arrived set locally. Two phases so the
  * single-GPU emulation can order them; phase = 0 push, 1 reduce, 2 both. */
 int aar_launch_oneshot(const AarRankParams* p, const AarLayout* lay, int phase, int grid, void* stream);

@@ -223,6 +223,30 @@ def test_oneshot_threshold():
     assert torch.equal(outs[1], acc) and int(counts[1][0]) == 3
 
 
+@pytest.mark.skipif(not __import__("os").environ.get("AAR_TEST_PERSISTENT"), reason="K7 resident kernel is experimental: set AAR_TEST_PERSISTENT=1 (it hung on the round-1 box; see DESIGN.md)")
+def test_persistent_engine_single_rank_doorbell():
+    """K7 on one rank: the resident kernel picks rounds up from the host ring, runs them, reports completion, exits on command."""
+    from akka_allreduce_b200.parallel.engine import PersistentEngine, RoundEngine
+
+    n = 1 << 16
+    eng = RoundEngine.single_process(n, 1 << 12)
+    xs = [torch.randn(n, device="cuda:0") for _ in range(3)]
+    # Everything the loop below launches is used once up front: with lazy module loading the FIRST use of a kernel loads
+    # its module, which waits for the device to go idle -- and a resident kernel never lets it.
+    assert torch.equal(xs[0], xs[0]) and int(eng.counts[0].min()) == 0
+    torch.cuda.synchronize()   # inputs complete BEFORE the resident kernel starts: no device-wide sync while it runs
+    pe = PersistentEngine(eng, algo="twoshot", grid=8)
+    try:
+        for r in range(12):
+            out, counts = pe.post(r, xs[r % 3])
+            pe.wait(r, timeout_s=20)
+            assert torch.equal(out, xs[r % 3]) and int(counts.min()) == 1
+    finally:
+        pe.stop()
+    assert eng.rounds_flushed() == 12
+    eng.close()
+
+
 def test_oracle_agrees_with_cpu_protocol_engine():
     """The device data plane and the C++ message-passing engine (the CPU restatement of the reference) flush the
     same vector for the same inputs."""
