@@ -181,6 +181,53 @@ class RoundEngine:
         t.copy_(torch.as_tensor(holder, device=self.device))
         return int(t[0].item())
 
+    # ------------------------------------------------------------------ checkpoint of the device-resident ring
+    def _region_view(self, off: int, nbytes: int, dtype: torch.dtype) -> torch.Tensor:
+        holder = type("H", (), {})()
+        holder.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (self.params.region[self.rank] + off, False), "version": 3}
+        return torch.as_tensor(holder, device=self.device).view(dtype)
+
+    def snapshot(self) -> "core.RingSnapshot":
+        """Host copy of this rank's ring slots and flag words (layout of SURVEY.md section 5: temporalBuffer[L][P][block] +
+        arrival words per slot), to be written with `_core.save_ring_snapshot`.  Call with no round in flight."""
+        torch.cuda.synchronize(self.device)
+        lay = self.layout
+        ring_bytes = lay.L * lay.P * lay.blkStride * lay.elemSize
+        s = core.RingSnapshot()
+        s.rank, s.P, s.L, s.data_size, s.max_chunk_size = self.rank, lay.P, lay.L, lay.dataSize, lay.maxChunk
+        s.round = self.rounds_enqueued
+        to_f32 = (lambda t: t.float()) if self.dtype == torch.bfloat16 else (lambda t: t)
+        s.scatter_ring = to_f32(self._region_view(lay.scatterOff, ring_bytes, self.dtype)).cpu().tolist() if ring_bytes <= (64 << 20) else []
+        s.reduce_ring = to_f32(self._region_view(lay.reduceOff, ring_bytes, self.dtype)).cpu().tolist() if ring_bytes <= (64 << 20) else []
+        s.scatter_flags = [v & 0xFFFFFFFF for v in self._region_view(lay.sflagOff, lay.L * lay.C * L.AAR_MAXP * 4, torch.int32).cpu().tolist()]
+        s.reduce_flags = [v & 0xFFFFFFFFFFFFFFFF for v in self._region_view(lay.rflagOff, lay.L * lay.P * lay.C * 8, torch.int64).cpu().tolist()]
+        return s
+
+    def restore(self, s: "core.RingSnapshot") -> None:
+        """Inverse of snapshot(): the ring payload and the arrival words go back into this rank's region; round numbering
+        continues at s.round.  The geometry must match."""
+        lay = self.layout
+        if (s.P, s.L, s.data_size, s.max_chunk_size) != (lay.P, lay.L, lay.dataSize, lay.maxChunk):
+            raise ValueError("ring snapshot was taken with a different geometry")
+        ring_bytes = lay.L * lay.P * lay.blkStride * lay.elemSize
+        if s.scatter_ring:
+            self._region_view(lay.scatterOff, ring_bytes, self.dtype).copy_(torch.tensor(s.scatter_ring, dtype=torch.float32).to(self.dtype))
+            self._region_view(lay.reduceOff, ring_bytes, self.dtype).copy_(torch.tensor(s.reduce_ring, dtype=torch.float32).to(self.dtype))
+        self._region_view(lay.sflagOff, lay.L * lay.C * L.AAR_MAXP * 4, torch.int32).copy_(
+            torch.tensor([v - (1 << 32) if v >= (1 << 31) else v for v in s.scatter_flags], dtype=torch.int32))
+        self._region_view(lay.rflagOff, lay.L * lay.P * lay.C * 8, torch.int64).copy_(
+            torch.tensor([v - (1 << 64) if v >= (1 << 63) else v for v in s.reduce_flags], dtype=torch.int64))
+        self.rounds_enqueued = s.round
+        torch.cuda.synchronize(self.device)
+
+    def metrics(self) -> dict:
+        """Structured counters of this rank's data plane (the reference only has log lines)."""
+        st = self.status()
+        return {"algo": self.algo, "rounds_enqueued": self.rounds_enqueued, "rounds_flushed": self.rounds_flushed(), "launches": self.launches,
+                "timeout_scatter": bool(st & L.ST_TIMEOUT_SCATTER), "timeout_reduce": bool(st & L.ST_TIMEOUT_REDUCE),
+                "timeout_gather": bool(st & L.ST_TIMEOUT_GATHER), "push_dropped": bool(st & L.ST_PUSH_DROPPED),
+                "rounds_in_flight": 2 if self.overlap else 1, "multicast": bool(self.mc_ptr)}
+
     def close(self) -> None:
         if self._host_words:
             self.lib.aar_host_words_free(self._host_words)

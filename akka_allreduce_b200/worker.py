@@ -92,6 +92,18 @@ class AllreduceWorker:
         if self.backend == "cuda":
             self._deliver_flushed()
 
+    def metrics(self) -> dict:
+        """rounds/s, forced completions, lag and the data-plane counters (CPU backend: the C++ worker's counters)."""
+        if self.backend == "cpu":
+            return dict(self._cpu_worker.metrics()) if self._cpu_worker else {}
+        m = {"id": self.id, "generation": self.generation, "rounds_delivered": self.delivered, "rounds_forced": self.rounds_forced,
+             "max_round": self.max_round, "max_scattered": self.max_scattered, "lag": self.max_round - self.delivered + 1}
+        if self.engine is not None:
+            m.update(self.engine.metrics())
+        if getattr(self, "_t_first", None) is not None and self.delivered > 1:
+            m["rounds_per_sec"] = (self.delivered - 1) / max(1e-9, self._t_last - self._t_first)
+        return m
+
     def close(self) -> None:
         if self.engine is not None:
             self.engine.close()
@@ -137,6 +149,7 @@ class AllreduceWorker:
         self._stream = torch.cuda.Stream(device=dev)
         self.max_round = self.max_scattered = -1
         self.delivered = 0
+        self._t_first = None
         self._inputs.clear()
         self.rdv.barrier()  # nobody launches before every peer has mapped every region
         if self.on_init:
@@ -162,9 +175,9 @@ class AllreduceWorker:
             x = self.data_source(AllReduceInputRequest(r)).data
             if x.numel() != eng.data_size:
                 raise ValueError(f"Input data size {x.numel()} is different from initialization time {eng.data_size}!")
-            # the source may have produced x on another stream: order our launch after it
-            self._stream.wait_stream(torch.cuda.current_stream(eng.device))
-            eng.enqueue_round(r, x, stream=self._stream)
+            # The engine orders its launch after the current stream (where the source produced x) and, when the ring has
+            # two slots, alternates rounds between two internal streams so consecutive rounds overlap (the maxLag window).
+            eng.enqueue_round(r, x)
             self._inputs[r] = x
             self.max_scattered = r
 
@@ -185,6 +198,9 @@ class AllreduceWorker:
                 self.data_sink(AllReduceOutput(eng.outputs[slot], eng.counts[slot], r))
                 self.node.send_complete(self.id, r, self.generation)
                 self.delivered += 1
+                self._t_last = time.time()
+                if getattr(self, "_t_first", None) is None:
+                    self._t_first = self._t_last
                 progressed = True
             if not block or progressed or self.delivered >= self.max_scattered + 1:
                 return

@@ -247,6 +247,34 @@ def test_persistent_engine_single_rank_doorbell():
     eng.close()
 
 
+def test_device_ring_snapshot_restore(tmp_path):
+    """Checkpoint of the device-resident ring: flags and payload of a rank survive save -> load -> restore into a fresh
+    engine, which then continues the round numbering (the reference has no checkpointing)."""
+    from akka_allreduce_b200.parallel.engine import RoundEngine
+
+    n, chunk = 4096, 512
+    a = RoundEngine.single_process(n, chunk, max_lag=2)
+    xs = [torch.randn(n, device="cuda:0") for _ in range(3)]
+    for r in range(3):
+        a.enqueue_round(r, xs[r])
+    snap = a.snapshot()
+    path = str(tmp_path / "ring.ckpt")
+    core.save_ring_snapshot(path, snap)
+    back = core.load_ring_snapshot(path)
+    assert (back.P, back.L, back.data_size, back.round) == (1, 3, n, 3)
+    assert back.reduce_flags == snap.reduce_flags and back.scatter_flags == snap.scatter_flags and back.reduce_ring == snap.reduce_ring
+    # slot r holds round r's reduced vector, its flag carries epoch r+1 and one contributor
+    assert back.reduce_ring[:n] == xs[0].cpu().tolist() and back.reduce_flags[0] == (1 << 32) | 1
+    b = RoundEngine.single_process(n, chunk, max_lag=2)
+    b.restore(back)
+    assert b.snapshot().reduce_ring == snap.reduce_ring and b.rounds_enqueued == 3
+    out, counts = b.enqueue_round(3, xs[1])
+    torch.cuda.synchronize()
+    assert torch.equal(out, xs[1]) and b.metrics()["rounds_enqueued"] == 4
+    a.close()
+    b.close()
+
+
 def test_oracle_agrees_with_cpu_protocol_engine():
     """The device data plane and the C++ message-passing engine (the CPU restatement of the reference) flush the
     same vector for the same inputs."""
