@@ -217,6 +217,11 @@ class RoundEngine:
             torch.tensor([v - (1 << 32) if v >= (1 << 31) else v for v in s.scatter_flags], dtype=torch.int32))
         self._region_view(lay.rflagOff, lay.L * lay.P * lay.C * 8, torch.int64).copy_(
             torch.tensor([v - (1 << 64) if v >= (1 << 63) else v for v in s.reduce_flags], dtype=torch.int64))
+        # A snapshot is taken with no round in flight, so every peer had retired every round below s.round: restore the
+        # flow-control words accordingly (round s.round would otherwise wait for retirements that happened before the save).
+        self._region_view(lay.peerBaseOff, L.AAR_MAXP * 4, torch.int32)[: lay.P] = s.round
+        self._region_view(lay.statusOff, 8, torch.int32)[1] = s.round
+        self._host_words[1] = s.round
         self.rounds_enqueued = s.round
         torch.cuda.synchronize(self.device)
 

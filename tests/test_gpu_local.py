@@ -265,12 +265,12 @@ def test_device_ring_snapshot_restore(tmp_path):
     assert back.reduce_flags == snap.reduce_flags and back.scatter_flags == snap.scatter_flags and back.reduce_ring == snap.reduce_ring
     # slot r holds round r's reduced vector, its flag carries epoch r+1 and one contributor
     assert back.reduce_ring[:n] == xs[0].cpu().tolist() and back.reduce_flags[0] == (1 << 32) | 1
-    b = RoundEngine.single_process(n, chunk, max_lag=2)
+    b = RoundEngine.single_process(n, chunk, max_lag=2, timeout_ms=3000.0)  # device-side liveness guard: a bug fails, never hangs
     b.restore(back)
     assert b.snapshot().reduce_ring == snap.reduce_ring and b.rounds_enqueued == 3
     out, counts = b.enqueue_round(3, xs[1])
     torch.cuda.synchronize()
-    assert torch.equal(out, xs[1]) and b.metrics()["rounds_enqueued"] == 4
+    assert torch.equal(out, xs[1]) and b.metrics()["rounds_enqueued"] == 4 and b.status() == 0
     a.close()
     b.close()
 
