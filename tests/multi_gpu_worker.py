@@ -118,8 +118,10 @@ def persistent_case(algo, n, chunk):
 
 
 def threshold_case():
-    """One rank never scatters (AAR_FLAG_SKIP_SCATTER): with thReduce = thComplete = 0.5 the others' sum is flushed and the
-    counts say so; nobody hangs."""
+    """One rank never scatters (AAR_FLAG_SKIP_SCATTER): with thReduce = thComplete = 0.5 every chunk is reduced over whichever
+    quorum its owner saw first, the counts say how many, and nobody hangs.  The contributor set of a chunk is read back
+    from its owner's decision word (all regions are peer-mapped), so the flushed values can be checked bit for bit against
+    the ordered sum over exactly that set -- "bit-exact against a CPU reduction of the contributing set"."""
     n, chunk = 1 << 16, 1 << 12
     lay = L.compute_layout(world, n, chunk, 1, L.AAR_F32, 0, False)
     k[0] += 1
@@ -129,16 +131,28 @@ def threshold_case():
     xs = inputs_for(n, torch.float32, 77)
     out, counts = eng.enqueue_round(0, xs[rank], skip_scatter=(rank == silent))
     torch.cuda.synchronize()
-    rdv.barrier()
+    rdv.barrier()   # every owner has published its decisions
+    ok = True
+    geo_step, C = lay.stepSize, lay.C
     cmin, cmax = int(counts.min()), int(counts.max())
-    # every reduced chunk has world-1 or world contributors depending on whether it was decided before the silent rank's (absent) data;
-    # since that rank never sends, exactly world-1 (or fewer chunks than total if its own block's owner was late)
-    ok = cmax <= world - 1 or world == 1
-    want = ordered_sum(xs, [r for r in range(world) if r != silent], torch.float32)
-    arrived = counts.repeat_interleave(chunk)[:n] > 0 if lay.totalChunks * chunk >= n else None
-    if arrived is not None:
-        ok &= bool(torch.equal(out[arrived], want[arrived])) and bool((out[~arrived] == 0).all())
-    check(f"threshold 0.5 with a silent rank (counts {cmin}..{cmax})", ok and eng.status() == 0)
+    ok &= cmax <= world - 1 or world == 1
+    for owner in range(world):
+        for c in range(C):
+            s0 = owner * geo_step + c * chunk
+            e0 = min(s0 + chunk, (owner + 1) * geo_step, n)
+            if e0 <= s0:
+                continue
+            cnt = int(counts[owner * C + c])
+            got = out[s0:e0]
+            if cnt == 0:   # the chunk missed this rank's round decision (or was reduced over nobody): zero-filled
+                ok &= bool((got == 0).all())
+                continue
+            word = int(symm.tensor(owner, lay.k2DecOff + (0 * C + c) * 8, 8, torch.int64)[0].item())
+            mask = word & 0xFFFFFFFF
+            srcs = [r for r in range(world) if (mask >> r) & 1]
+            ok &= (word >> 32) == 1 and len(srcs) == cnt and silent not in srcs
+            ok &= bool(torch.equal(got, ordered_sum([x[s0:e0] for x in xs], srcs, torch.float32)))
+    check(f"threshold 0.5 with a silent rank: sums over the reported contributor sets (counts {cmin}..{cmax})", ok and eng.status() == 0)
     eng.close()
     symm.close()
 

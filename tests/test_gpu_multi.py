@@ -17,8 +17,7 @@ ROOT = Path(__file__).resolve().parents[1]
 
 @pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs at least two GPUs")
 def test_multi_gpu_suite():
-    n = min(torch.cuda.device_count(), 8)
-    n = 8 if n >= 8 else (4 if n >= 4 else 2)
+    n = 2   # the suite is size-independent; two real peers are enough for NVLink, VMM and multicast, and cheapest to run
     env = dict(os.environ)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
            "--master-port", "29631", str(ROOT / "tests" / "multi_gpu_worker.py")]
