@@ -196,9 +196,8 @@ engine_case((1 << 20) + 8, 40000, torch.float32, "pipelined")      # unaligned b
 engine_case(1003, 17, torch.float32, "twoshot", overlap=False)
 engine_case(1 << 20, 1 << 16, torch.float32, "auto", normalize=True)
 engine_case(1 << 22, 1 << 18, torch.float32, "auto", rounds=12, max_lag=3)
-if os.environ.get("AAR_TEST_PERSISTENT"):  # K7 is experimental: not part of the default suite
-    persistent_case("oneshot", 8192, 1024)
-    persistent_case("twoshot", 1 << 18, 1 << 14)
+persistent_case("oneshot", 8192, 1024)
+persistent_case("twoshot", 1 << 18, 1 << 14)
 threshold_case()
 api_case()
 rdv.barrier()

@@ -223,7 +223,6 @@ def test_oneshot_threshold():
     assert torch.equal(outs[1], acc) and int(counts[1][0]) == 3
 
 
-@pytest.mark.skipif(not __import__("os").environ.get("AAR_TEST_PERSISTENT"), reason="K7 resident kernel is experimental: set AAR_TEST_PERSISTENT=1 (it hung on the round-1 box; see DESIGN.md)")
 def test_persistent_engine_single_rank_doorbell():
     """K7 on one rank: the resident kernel picks rounds up from the host ring, runs them, reports completion, exits on command."""
     from akka_allreduce_b200.parallel.engine import PersistentEngine, RoundEngine
@@ -233,7 +232,8 @@ def test_persistent_engine_single_rank_doorbell():
     xs = [torch.randn(n, device="cuda:0") for _ in range(3)]
     # Everything the loop below launches is used once up front: with lazy module loading the FIRST use of a kernel loads
     # its module, which waits for the device to go idle -- and a resident kernel never lets it.
-    assert torch.equal(xs[0], xs[0]) and int(eng.counts[0].min()) == 0
+    # (two DIFFERENT tensors: torch.equal(t, t) short-circuits on identity and launches nothing)
+    assert not torch.equal(xs[0], xs[1]) and torch.equal(xs[0], xs[0].clone()) and int(eng.counts[0].min()) == 0
     torch.cuda.synchronize()   # inputs complete BEFORE the resident kernel starts: no device-wide sync while it runs
     pe = PersistentEngine(eng, algo="twoshot", grid=8)
     try:
