@@ -339,8 +339,10 @@ def run_e2e(a, rank, world, local_rank, dtype, nbytes, rdv, max_over_ranks, glob
         if out.iteration == total - 1:
             marks["t1"] = time.perf_counter()
 
+    info = {}
     worker = AllreduceWorker(source, sink, backend="cuda", device=local_rank, dtype=a.dtype, algo=a.algo, grid=a.grid,
-                             session=f"e2e_{port}_{os.getppid() if world > 1 else os.getpid()}")
+                             session=f"e2e_{port}_{os.getppid() if world > 1 else os.getpid()}",
+                             on_init=lambda w: info.update(algo=w.engine.algo, rounds_in_flight=2 if w.engine.overlap else 1))
     ok = worker.run("127.0.0.1", port, timeout_sec=600.0)
     if master:
         master.join(30)
@@ -354,7 +356,8 @@ def run_e2e(a, rank, world, local_rank, dtype, nbytes, rdv, max_over_ranks, glob
     return {"value": N * nbytes / (ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": ms, "rounds_per_sec": 1e3 / ms,
             "h2d_bytes_per_step": bytes_in, "d2h_bytes_per_step": state["d2h"],
             "path": "AllreduceMaster(pipeline_depth=maxLag) + AllreduceWorker(backend=cuda); source: pinned host -> device copy per round; "
-                    "sink: counts + 1024-element slice read back per round", "algo": worker.algo if not worker.engine else worker.engine.algo}
+                    "sink: counts + 1024-element slice read back per round", "algo": info.get("algo", a.algo),
+            "rounds_in_flight": info.get("rounds_in_flight", 1)}
 
 
 if __name__ == "__main__":
