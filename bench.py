@@ -111,7 +111,8 @@ class ClockSampler:
 def main():
     a = parse_args()
     if a.impl == "reference":
-        reference_unavailable()
+        if int(os.environ.get("RANK", "0")) == 0:   # one line per job, also when launched with one process per GPU
+            reference_unavailable()
         return 0
 
     import torch
