@@ -307,7 +307,7 @@ def run_e2e(a, rank, world, local_rank, dtype, nbytes, rdv, max_over_ranks, glob
     master = None
     if rank == 0:
         master = AllreduceMaster(N, 1.0, 1.0, 1.0, a.max_lag, a.data_size, total - 1, a.chunk, pipeline_depth=a.max_lag, port=port)
-        master.start(600.0)
+        master.start(120.0)
     rdv.barrier()
     pinned = [torch.randn(a.data_size).to(dtype).pin_memory() for _ in range(2)]
     staging = [torch.empty(a.data_size, dtype=dtype, device=dev) for _ in range(a.max_lag + 2)]
@@ -344,7 +344,7 @@ def run_e2e(a, rank, world, local_rank, dtype, nbytes, rdv, max_over_ranks, glob
     worker = AllreduceWorker(source, sink, backend="cuda", device=local_rank, dtype=a.dtype, algo=a.algo, grid=a.grid,
                              session=f"e2e_{port}_{os.getppid() if world > 1 else os.getpid()}",
                              on_init=lambda w: info.update(algo=w.engine.algo, rounds_in_flight=2 if w.engine.overlap else 1))
-    ok = worker.run("127.0.0.1", port, timeout_sec=600.0)
+    ok = worker.run("127.0.0.1", port, timeout_sec=120.0)
     if master:
         master.join(30)
     worker.close()
