@@ -160,6 +160,11 @@ class RoundEngine:
         """Make `stream` (default: the current stream) wait for round `rnd`; call before consuming its output on a stream."""
         (stream or torch.cuda.current_stream(self.device)).wait_event(self._events[rnd % self.layout.L])
 
+    def synchronize(self) -> None:
+        """Host waits until every launched round of this rank has finished."""
+        for ev in self._events:
+            ev.synchronize()
+
     def wait_all(self, stream: torch.cuda.Stream | None = None) -> None:
         st = stream or torch.cuda.current_stream(self.device)
         for ev in self._events:

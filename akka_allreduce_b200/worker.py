@@ -126,14 +126,26 @@ class AllreduceWorker:
     def _on_init(self, m) -> None:
         """AllreduceWorker.scala:37-82: (re)initialisation wipes all round state and allocates the rings -- here the
         symmetric HBM region, mapped into every peer."""
+        self.close()
+        self.id, self.generation = m.dest_id, m.generation
+        self.engine = self._make_engine(m)
+        self.max_round = self.max_scattered = -1
+        self.delivered = 0
+        self._t_first = None
+        self._inputs.clear()
+        if self.on_init:
+            self.on_init(self)
+
+    def _make_engine(self, m):
+        """Build this rank's data plane for the geometry in InitWorkers: symmetric region mapped into every peer + round
+        engine.  Kept separate from the bookkeeping so the host state machine can be tested against a fake data plane
+        (tests/test_device_worker_logic.py), the way the reference tests one worker against a fake cluster."""
         import torch
 
         from .ops import lib as L
         from .parallel.engine import ONESHOT_MAX_BYTES, RoundEngine
         from .parallel.symmetric import SymmetricMemory, UnixRendezvous
 
-        self.close()
-        self.id, self.generation = m.dest_id, m.generation
         P = len(m.workers)
         dev = self.device if self.device is not None else self.id % torch.cuda.device_count()
         torch.cuda.set_device(dev)
@@ -143,24 +155,16 @@ class AllreduceWorker:
         session = (self.session or f"w{self.master_port}") + f"_g{m.generation}"
         self.rdv = UnixRendezvous(self.id, P, session)
         self.symm = SymmetricMemory(self.rdv, layout.regionBytes, dev, want_multicast=self.want_multicast and P > 1)
-        self.engine = RoundEngine.from_symmetric(self.symm, layout, th_reduce=m.th_reduce, th_complete=m.th_complete,
-                                                 normalize=self.normalize, exact_quorum=self.exact_quorum,
-                                                 timeout_ms=self.spin_timeout_ms, grid=self.grid, algo=self.algo)
-        self._stream = torch.cuda.Stream(device=dev)
-        self.max_round = self.max_scattered = -1
-        self.delivered = 0
-        self._t_first = None
-        self._inputs.clear()
+        engine = RoundEngine.from_symmetric(self.symm, layout, th_reduce=m.th_reduce, th_complete=m.th_complete,
+                                            normalize=self.normalize, exact_quorum=self.exact_quorum,
+                                            timeout_ms=self.spin_timeout_ms, grid=self.grid, algo=self.algo)
         self.rdv.barrier()  # nobody launches before every peer has mapped every region
-        if self.on_init:
-            self.on_init(self)
+        return engine
 
     def _on_start(self, rnd: int) -> None:
         """AllreduceWorker.scala:84-104.  The catch-up loop is the doorbell: kernels of rounds that are now more than
         maxLag behind stop waiting and complete with what has arrived.  Then every not-yet-scattered round is fetched and
         launched, in order, exactly once."""
-        import torch
-
         eng = self.engine
         if eng is None:
             return
@@ -173,8 +177,9 @@ class AllreduceWorker:
             while self.delivered < r - L + 1:
                 self._deliver_flushed(block=True)
             x = self.data_source(AllReduceInputRequest(r)).data
-            if x.numel() != eng.data_size:
-                raise ValueError(f"Input data size {x.numel()} is different from initialization time {eng.data_size}!")
+            n = x.numel() if hasattr(x, "numel") else len(x)
+            if n != eng.data_size:
+                raise ValueError(f"Input data size {n} is different from initialization time {eng.data_size}!")
             # The engine orders its launch after the current stream (where the source produced x) and, when the ring has
             # two slots, alternates rounds between two internal streams so consecutive rounds overlap (the maxLag window).
             eng.enqueue_round(r, x)
@@ -207,8 +212,6 @@ class AllreduceWorker:
             time.sleep(0)  # blocking mode: yield until the next round flushes
 
     def _drain(self) -> None:
-        import torch
-
         if self.engine is not None:
-            torch.cuda.synchronize(self.engine.device)
+            self.engine.synchronize()
             self._deliver_flushed()

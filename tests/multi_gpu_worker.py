@@ -187,6 +187,13 @@ def api_case():
     worker.close()
 
 
+only = os.environ.get("AAR_MULTI_ONLY", "")
+if only == "api":   # quick check of the public API path alone
+    api_case()
+    rdv.barrier()
+    if rank == 0:
+        print("MULTI-GPU RESULT:", "FAILED " + "; ".join(failures) if failures else "ALL PASSED", flush=True)
+    sys.exit(1 if failures else 0)
 for dtype in (torch.float32, torch.bfloat16):
     engine_case(1 << 20, 1 << 16, dtype, "twoshot", overlap=False)
     engine_case(1 << 20, 1 << 16, dtype, "pipelined")

