@@ -127,6 +127,9 @@ def main():
         a.gpus = world
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    from akka_allreduce_b200.utils.affinity import bind_to_gpu_numa
+
+    numa = bind_to_gpu_numa(local_rank)   # pinned source buffers of the end-to-end run land next to this GPU's PCIe root
     dtype = torch.float32 if a.dtype == "fp32" else torch.bfloat16
     es = 4 if a.dtype == "fp32" else 2
     nbytes = a.data_size * es
@@ -283,7 +286,7 @@ def main():
                        "max_chunk_size": a.chunk, "max_lag": a.max_lag, "th_reduce": 1.0, "th_complete": 1.0,
                        "l2_policy": "inputs+rings larger than L2 (2 x 64 MiB inputs alternate, 256 MiB rings per rank)", "view_output": a.view, "rounds_in_flight": 2 if (a.impl == "aar" and N > 1 and a.max_lag >= 1 and not a.no_overlap) else 1},
             "rounds_per_sec": rounds_per_sec, "algbw_GBps": algbw, "busbw_GBps": busbw,
-            "gpu_launches": gpu_launches, "clocks": clocks, "nccl": nccl,
+            "gpu_launches": gpu_launches, "clocks": clocks, "numa_binding": numa, "nccl": nccl,
             "vs_nccl": (nccl["ms_per_step"] / ms) if nccl and "ms_per_step" in nccl else None,
             "e2e": e2e,
         }

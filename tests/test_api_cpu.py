@@ -86,3 +86,10 @@ def test_unix_rendezvous_passes_fds_between_processes():
     for rank, msg, lens, ok in res:
         assert msg == f"hello from {(rank - 1) % world}"
         assert lens == [1, 2, 3] and ok
+
+
+def test_numa_affinity_helper_is_best_effort():
+    from akka_allreduce_b200.utils import affinity
+
+    assert affinity._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert affinity.bind_to_gpu_numa(0) in ({},) or isinstance(affinity.bind_to_gpu_numa(0), dict)   # no GPU here: must not raise
