@@ -93,3 +93,32 @@ def test_numa_affinity_helper_is_best_effort():
 
     assert affinity._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
     assert affinity.bind_to_gpu_numa(0) in ({},) or isinstance(affinity.bind_to_gpu_numa(0), dict)   # no GPU here: must not raise
+
+
+def test_metrics_endpoint_serves_master_and_worker_counters():
+    import urllib.request
+
+    from akka_allreduce_b200.utils.metrics import MetricsServer, render_prometheus
+
+    master = AllreduceMaster(1, 1.0, 1.0, 1.0, max_lag=1, data_size=4, max_round=3, max_chunk_size=2)
+    master.start(30)
+    w = AllreduceWorker(lambda req: AllReduceInput(np.ones(4, dtype=np.float32)), lambda out: None, backend="cpu")
+    w.run("127.0.0.1", master.port, 30)
+    assert master.join(10)
+    srv = MetricsServer({"master": master.metrics, "worker": w.metrics}).start()
+    try:
+        text = urllib.request.urlopen(f"http://127.0.0.1:{srv.port}/metrics", timeout=5).read().decode()
+    finally:
+        srv.stop()
+    assert 'aar_rounds_started{role="master"} 4' in text
+    assert 'aar_rounds_completed{role="worker"} 4' in text
+    assert render_prometheus({"algo": "nvls", "push_dropped": False}, labels={"rank": "3"}) == \
+        'aar_algo_info{rank="3",value="nvls"} 1\naar_push_dropped{rank="3"} 0\n'
+
+
+def test_log_level_applies_to_both_runtimes():
+    from akka_allreduce_b200.utils import log
+
+    log.set_level("ERROR")
+    assert log.get_logger().level == 40
+    log.set_level("WARNING")

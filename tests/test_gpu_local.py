@@ -1,4 +1,4 @@
-"""GPU tests of the sm_100a kernels on ONE device (P emulated ranks, tests/README in local_gpu.py).
+"""GPU tests of the sm_100a kernels on ONE device (P emulated ranks, see akka_allreduce_b200/parallel/local_gpu.py).
 
 Every result is compared bit-for-bit (torch.equal) with a plain PyTorch fp32 restatement of the reference's
 reduce / flush (AllreduceWorker.scala:240-251,180-192) over the contributor set the scenario defines.
