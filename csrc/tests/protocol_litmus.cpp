@@ -1,0 +1,344 @@
+// Executable model of the DEVICE protocol (docs/PROTOCOL.md) on host threads, meant to be run under ThreadSanitizer.
+//
+// SURVEY.md section 5 asks for litmus tests of the flag protocol.  compute-sanitizer is closed on the build pool, so the
+// protocol -- not the GPU memory model -- is checked here: every "CTA" is a host thread, every rank's symmetric region is
+// a struct of plain float rings plus std::atomic flag / decision / election words, and the phases below follow
+// csrc/cuda/aar_kernels.cu step for step (same index math, same publish / observe / decide-once / last-finisher
+// structure, same flow control, two rounds of one rank in flight, in-order retirement).  The ring payload is deliberately
+// NON-atomic: if any path reads or overwrites it without a happens-before edge through the flags, TSAN reports a race.
+// Device fences + relaxed atomics are modelled by acquire/release on the atomic operations themselves (TSAN does not
+// model std::atomic_thread_fence); that yields the same happens-before edges.
+//
+// Checks per run: no TSAN report; every flushed vector equals the peer-index-ordered fp32 sum over exactly the
+// contributor set its owner decided (bit-exact); with thresholds = 1 that set is everybody; counts match; no deadlock.
+//
+//   protocol_litmus [seed] [P] [rounds] [thresholdPercent] [maxLag] [overlap 0|1] [ctasPerKernel] [bcastFlowControl 0|1]
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <mutex>
+#include <random>
+#include <thread>
+#include <vector>
+
+namespace {
+
+struct Barrier {  // kernel boundary / __syncthreads stand-in
+  explicit Barrier(int n) : n_(n) {}
+  void wait() {
+    std::unique_lock<std::mutex> g(m_);
+    int gen = gen_;
+    if (++count_ == n_) {
+      count_ = 0;
+      ++gen_;
+      cv_.notify_all();
+    } else {
+      cv_.wait(g, [&] { return gen != gen_; });
+    }
+  }
+  std::mutex m_;
+  std::condition_variable cv_;
+  int n_, count_ = 0, gen_ = 0;
+};
+
+struct Config {
+  int P = 4, L = 2, C = 3, S = 2;   // ranks, ring slots (maxLag+1), chunks per block, segments per message
+  int chunkLen = 8;                // elements per chunk (segment = chunkLen / S)
+  int G = 4;                       // CTAs per kernel
+  int rounds = 12;
+  int minRequired = 4, minChunks = 12;
+  bool overlap = true;
+  bool bcastFlowControl = true;    // K2 also waits for the destination to have retired the slot's previous tenant
+  unsigned seed = 1;
+  int blockLen() const { return C * chunkLen; }
+  int dataSize() const { return P * blockLen(); }
+};
+
+struct Region {
+  std::vector<float> scatter, reduce;                 // [L][P][blockLen]   plain memory on purpose
+  std::vector<std::atomic<uint32_t>> sflag;           // [L][C][P]
+  std::vector<std::atomic<uint64_t>> rflag;           // [L][P][C]
+  std::vector<std::atomic<uint32_t>> peerBase;        // [P]
+  std::vector<std::atomic<uint32_t>> k1Ctr;           // [L][P][C]
+  std::vector<std::atomic<uint64_t>> k2Dec;           // [L][C]
+  std::vector<std::atomic<uint32_t>> k2Ctr;           // [L][C]
+  std::vector<std::atomic<uint64_t>> k3Dec;           // [L]
+  std::vector<std::atomic<uint32_t>> k3Ctr;           // [L]
+  std::vector<int> counts;                            // [L][P*C]           plain, published through k3Dec
+  std::atomic<uint32_t> flushed{0};
+  std::vector<std::atomic<int>> consumed;             // [L] newest round whose output slot the host has consumed (-1 = none)
+  std::vector<std::vector<float>> output;             // [L][dataSize]      what the sink would see
+  std::vector<std::vector<int>> outCounts;            // [L][P*C]
+  explicit Region(const Config& c)
+      : scatter((size_t)c.L * c.P * c.blockLen()), reduce((size_t)c.L * c.P * c.blockLen()), sflag((size_t)c.L * c.C * c.P),
+        rflag((size_t)c.L * c.P * c.C), peerBase(c.P), k1Ctr((size_t)c.L * c.P * c.C), k2Dec((size_t)c.L * c.C), k2Ctr((size_t)c.L * c.C),
+        k3Dec(c.L), k3Ctr(c.L), counts((size_t)c.L * c.P * c.C), consumed(c.L), output(c.L, std::vector<float>(c.dataSize())),
+        outCounts(c.L, std::vector<int>(c.P * c.C)) {
+    for (auto& x : consumed) x.store(-1);
+  }
+};
+
+struct World {
+  Config cfg;
+  std::vector<Region*> region;
+  std::vector<std::vector<std::vector<float>>> input;  // [round][rank][dataSize]
+  std::atomic<long> failures{0};
+};
+
+float inputValue(int round, int rank, int i) { return (float)((round * 131 + rank * 17 + i * 7) % 1000) * 0.125f + (float)rank; }
+
+void jitter(std::mt19937& rng) {
+  unsigned v = rng() % 64;
+  if (v == 0) std::this_thread::sleep_for(std::chrono::microseconds(rng() % 200));
+  else if (v < 8) std::this_thread::yield();
+}
+
+// ---------------------------------------------------------------------------------------------- K1 scatter_push
+void phaseScatter(World& w, int rank, int round, int cta, int nctas, std::mt19937& rng) {
+  const Config& c = w.cfg;
+  const int slot = round % c.L;
+  const uint32_t epoch = (uint32_t)round + 1;
+  Region& my = *w.region[rank];
+  const int segLen = c.chunkLen / c.S;
+  const long total = (long)c.C * c.P * c.S;
+  for (long idx = cta; idx < total; idx += nctas) {
+    const int i = (int)(idx % c.P), s = (int)((idx / c.P) % c.S), ch = (int)(idx / ((long)c.S * c.P));
+    const int dest = (i + rank) % c.P;
+    Region& peer = *w.region[dest];
+    // flow control: the previous tenant of this slot at `dest` must be retired
+    if (round >= c.L)
+      while ((int)my.peerBase[dest].load(std::memory_order_acquire) < round - c.L + 1) std::this_thread::yield();
+    jitter(rng);
+    const float* src = w.input[round][rank].data() + dest * c.blockLen() + ch * c.chunkLen + s * segLen;
+    float* dst = peer.scatter.data() + ((size_t)(slot * c.P + rank) * c.blockLen()) + ch * c.chunkLen + s * segLen;
+    for (int k = 0; k < segLen; ++k) dst[k] = src[k];
+    std::atomic<uint32_t>& ctr = my.k1Ctr[(size_t)(slot * c.P + dest) * c.C + ch];
+    if (ctr.fetch_add(1, std::memory_order_acq_rel) + 1 == (uint32_t)c.S) {  // last segment: publish the ScatterBlock
+      ctr.store(0, std::memory_order_relaxed);
+      peer.sflag[(size_t)(slot * c.C + ch) * c.P + rank].store(epoch, std::memory_order_release);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- K2 reduce_bcast
+unsigned chunkDecision(World& w, int rank, int round, int ch, std::mt19937& rng) {
+  const Config& c = w.cfg;
+  const int slot = round % c.L;
+  const uint64_t epoch = (uint64_t)round + 1;
+  Region& my = *w.region[rank];
+  std::atomic<uint64_t>& word = my.k2Dec[(size_t)slot * c.C + ch];
+  uint64_t v = word.load(std::memory_order_acquire);
+  if ((v >> 32) == epoch) return (unsigned)v;
+  unsigned arrived = 0;
+  for (;;) {
+    arrived = 0;
+    for (int src = 0; src < c.P; ++src)
+      if (my.sflag[(size_t)(slot * c.C + ch) * c.P + src].load(std::memory_order_acquire) == (uint32_t)epoch) arrived |= 1u << src;
+    if (__builtin_popcount(arrived) >= c.minRequired) break;
+    jitter(rng);
+    std::this_thread::yield();
+  }
+  uint64_t want = (epoch << 32) | arrived;
+  if (!word.compare_exchange_strong(v, want, std::memory_order_acq_rel, std::memory_order_acquire)) {
+    if ((v >> 32) == epoch) return (unsigned)v;  // somebody else decided first: adopt
+    // word still belongs to an older round (cannot happen: only this round's CTAs write it now)
+    w.failures++;
+  }
+  return arrived;
+}
+
+void phaseReduce(World& w, int rank, int round, int cta, int nctas, std::mt19937& rng) {
+  const Config& c = w.cfg;
+  const int slot = round % c.L;
+  const uint64_t epoch = (uint64_t)round + 1;
+  Region& my = *w.region[rank];
+  const int segLen = c.chunkLen / c.S;
+  for (long idx = cta; idx < (long)c.C * c.S; idx += nctas) {
+    const int s = (int)(idx % c.S), ch = (int)(idx / c.S);
+    const unsigned mask = chunkDecision(w, rank, round, ch, rng);
+    const int count = __builtin_popcount(mask);
+    // Flow control for the broadcast.  With thresholds < 1 an owner can reduce round R over a quorum that does not contain
+    // a lagging peer and would then overwrite that peer's reduce-ring slot while it still gathers round R - L (found by
+    // this model: data race between the store below and copyChunk).  So the broadcast obeys the same rule as the scatter.
+    if (c.bcastFlowControl && round >= c.L)
+      for (int d = 0; d < c.P; ++d)
+        while ((int)my.peerBase[d].load(std::memory_order_acquire) < round - c.L + 1) std::this_thread::yield();
+    jitter(rng);
+    for (int k = 0; k < segLen; ++k) {
+      const int e = ch * c.chunkLen + s * segLen + k;
+      float acc = 0.f;
+      for (int src = 0; src < c.P; ++src)
+        if (mask >> src & 1) acc += my.scatter[(size_t)(slot * c.P + src) * c.blockLen() + e];
+      for (int i = 0; i < c.P; ++i) {
+        Region& peer = *w.region[(i + rank) % c.P];
+        peer.reduce[(size_t)(slot * c.P + rank) * c.blockLen() + e] = acc;
+      }
+    }
+    std::atomic<uint32_t>& ctr = my.k2Ctr[(size_t)slot * c.C + ch];
+    if (ctr.fetch_add(1, std::memory_order_acq_rel) + 1 == (uint32_t)c.S) {  // last segment: publish the ReduceBlock + count
+      ctr.store(0, std::memory_order_relaxed);
+      for (int i = 0; i < c.P; ++i)
+        w.region[(i + rank) % c.P]->rflag[(size_t)(slot * c.P + rank) * c.C + ch].store((epoch << 32) | (uint64_t)count, std::memory_order_release);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------- K3 gather_flush
+void copyChunk(World& w, int rank, int round, int owner, int ch, int s, int cnt) {
+  const Config& c = w.cfg;
+  const int slot = round % c.L, segLen = c.chunkLen / c.S;
+  Region& my = *w.region[rank];
+  for (int k = 0; k < segLen; ++k) {
+    const int e = ch * c.chunkLen + s * segLen + k;
+    my.output[slot][owner * c.blockLen() + e] = cnt >= 0 ? my.reduce[(size_t)(slot * c.P + owner) * c.blockLen() + e] : 0.f;
+  }
+}
+
+void phaseGather(World& w, int rank, int round, int cta, int nctas, std::mt19937& rng) {
+  const Config& c = w.cfg;
+  const int slot = round % c.L;
+  const uint64_t epoch = (uint64_t)round + 1;
+  Region& my = *w.region[rank];
+  const bool eager = c.minChunks >= c.P * c.C;
+  if (!eager) {  // one leader counts arrivals against the round threshold and publishes a snapshot
+    const uint64_t busy = (epoch << 32) | 1, done = (epoch << 32) | 2;
+    std::atomic<uint64_t>& word = my.k3Dec[slot];
+    uint64_t v = word.load(std::memory_order_acquire);
+    bool leader = false;
+    if (v != busy && v != done) leader = word.compare_exchange_strong(v, busy, std::memory_order_acq_rel, std::memory_order_acquire);
+    if (leader) {
+      for (;;) {
+        int n = 0;
+        for (int i = 0; i < c.P * c.C; ++i)
+          if ((my.rflag[(size_t)slot * c.P * c.C + i].load(std::memory_order_acquire) >> 32) == epoch) ++n;
+        if (n >= c.minChunks) break;
+        jitter(rng);
+        std::this_thread::yield();
+      }
+      for (int i = 0; i < c.P * c.C; ++i) {
+        const uint64_t f = my.rflag[(size_t)slot * c.P * c.C + i].load(std::memory_order_acquire);
+        const int cnt = (f >> 32) == epoch ? (int)(uint32_t)f : -1;
+        my.counts[(size_t)slot * c.P * c.C + i] = cnt;
+        my.outCounts[slot][i] = cnt < 0 ? 0 : cnt;
+      }
+      word.store(done, std::memory_order_release);
+    } else {
+      while (word.load(std::memory_order_acquire) != done) std::this_thread::yield();
+    }
+  }
+  for (long idx = cta; idx < (long)c.P * c.C * c.S; idx += nctas) {
+    const int s = (int)(idx % c.S), owner = ((int)((idx / c.S) % c.P) + rank) % c.P, ch = (int)(idx / ((long)c.S * c.P));
+    int cnt;
+    if (eager) {
+      uint64_t f;
+      while (((f = my.rflag[(size_t)(slot * c.P + owner) * c.C + ch].load(std::memory_order_acquire)) >> 32) != epoch) std::this_thread::yield();
+      cnt = (int)(uint32_t)f;
+      if (s == 0) my.outCounts[slot][owner * c.C + ch] = cnt;
+    } else {
+      cnt = my.counts[(size_t)slot * c.P * c.C + owner * c.C + ch];
+    }
+    jitter(rng);
+    copyChunk(w, rank, round, owner, ch, s, cnt);
+  }
+}
+
+// K6: last CTA of the kernel retires the slot; with two rounds in flight retirement stays in order
+void retire(World& w, int rank, int round, int nctas) {
+  const Config& c = w.cfg;
+  Region& my = *w.region[rank];
+  std::atomic<uint32_t>& ctr = my.k3Ctr[round % c.L];
+  if (ctr.fetch_add(1, std::memory_order_acq_rel) + 1 == (uint32_t)nctas) {
+    ctr.store(0, std::memory_order_relaxed);
+    while ((int)my.flushed.load(std::memory_order_acquire) < round) std::this_thread::yield();
+    for (int i = 0; i < c.P; ++i) w.region[(i + rank) % c.P]->peerBase[rank].store((uint32_t)round + 1, std::memory_order_release);
+    my.flushed.store((uint32_t)round + 1, std::memory_order_release);
+  }
+}
+
+// What the host does when the completion word moves: check the flushed vector against the oracle over the DECIDED masks.
+void verifyRound(World& w, int rank, int round) {
+  const Config& c = w.cfg;
+  const int slot = round % c.L;
+  Region& my = *w.region[rank];
+  for (int owner = 0; owner < c.P; ++owner)
+    for (int ch = 0; ch < c.C; ++ch) {
+      const int cnt = my.outCounts[slot][owner * c.C + ch];
+      const uint64_t dec = w.region[owner]->k2Dec[(size_t)slot * c.C + ch].load(std::memory_order_acquire);
+      for (int k = 0; k < c.chunkLen; ++k) {
+        const int e = owner * c.blockLen() + ch * c.chunkLen + k;
+        float want = 0.f;
+        if (cnt > 0) {
+          if ((dec >> 32) != (uint64_t)round + 1) {  // the owner has moved on and reused the word: cannot re-derive, skip
+            continue;
+          }
+          for (int src = 0; src < c.P; ++src)
+            if ((unsigned)dec >> src & 1) want += w.input[round][src][e];
+          if (__builtin_popcount((unsigned)dec) != cnt) w.failures++;
+        }
+        if (my.output[slot][e] != want) w.failures++;
+      }
+    }
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  World w;
+  Config& c = w.cfg;
+  c.seed = argc > 1 ? (unsigned)atoi(argv[1]) : 1;
+  c.P = argc > 2 ? atoi(argv[2]) : 4;
+  c.rounds = argc > 3 ? atoi(argv[3]) : 12;
+  const int thPct = argc > 4 ? atoi(argv[4]) : 100;
+  c.L = (argc > 5 ? atoi(argv[5]) : 1) + 1;
+  c.overlap = argc > 6 ? atoi(argv[6]) != 0 : true;
+  c.G = argc > 7 ? atoi(argv[7]) : 4;
+  c.bcastFlowControl = argc > 8 ? atoi(argv[8]) != 0 : true;
+  c.minRequired = std::max(1, (int)((float)thPct / 100.f * (float)c.P));
+  c.minChunks = std::max(1, (int)((float)thPct / 100.f * (float)(c.P * c.C)));
+  if (c.L < 2) c.overlap = false;
+  for (int r = 0; r < c.P; ++r) w.region.push_back(new Region(c));
+  w.input.assign(c.rounds, std::vector<std::vector<float>>(c.P, std::vector<float>(c.dataSize())));
+  for (int r = 0; r < c.rounds; ++r)
+    for (int k = 0; k < c.P; ++k)
+      for (int i = 0; i < c.dataSize(); ++i) w.input[r][k][i] = inputValue(r, k, i);
+
+  const int streams = c.overlap ? 2 : 1;
+  std::vector<std::thread> threads;
+  std::vector<Barrier*> barriers;
+  for (int rank = 0; rank < c.P; ++rank)
+    for (int st = 0; st < streams; ++st) {
+      Barrier* b = new Barrier(c.G);
+      barriers.push_back(b);
+      for (int cta = 0; cta < c.G; ++cta)
+        threads.emplace_back([&w, rank, st, cta, streams, b] {
+          const Config& cf = w.cfg;
+          std::mt19937 rng(cf.seed * 7919u + rank * 131u + st * 17u + cta);
+          for (int round = st; round < cf.rounds; round += streams) {  // kernels of one stream run one after another
+            // the worker launches round R only after the sink has consumed round R - L (same output / count buffers)
+            if (round >= cf.L)
+              while (w.region[rank]->consumed[round % cf.L].load(std::memory_order_acquire) != round - cf.L) std::this_thread::yield();
+            if (rank == (round % cf.P) && (rng() % 3 == 0)) std::this_thread::sleep_for(std::chrono::microseconds(300));  // straggler
+            phaseScatter(w, rank, round, cta, cf.G, rng);
+            phaseReduce(w, rank, round, cta, cf.G, rng);
+            phaseGather(w, rank, round, cta, cf.G, rng);
+            retire(w, rank, round, cf.G);
+            b->wait();  // kernel boundary: the stream's next kernel starts when every CTA of this one is done
+            if (cta == 0) {
+              // host side: wait for the completion word, then consume this round's output slot before it is reused
+              while ((int)w.region[rank]->flushed.load(std::memory_order_acquire) < round + 1) std::this_thread::yield();
+              verifyRound(w, rank, round);
+              w.region[rank]->consumed[round % cf.L].store(round, std::memory_order_release);
+            }
+            b->wait();
+          }
+        });
+    }
+  for (auto& t : threads) t.join();
+  long bad = w.failures.load();
+  printf("protocol_litmus seed=%u P=%d rounds=%d th=%d%% L=%d overlap=%d G=%d: failures=%ld\n", c.seed, c.P, c.rounds, thPct, c.L, (int)c.overlap,
+         c.G, bad);
+  return bad == 0 ? 0 : 1;
+}

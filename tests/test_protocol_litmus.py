@@ -1,0 +1,55 @@
+"""Device-protocol litmus under ThreadSanitizer (csrc/tests/protocol_litmus.cpp): the kernels' flag / decision / election /
+flow-control logic re-stated on host threads with a NON-atomic ring payload, so any missing happens-before edge is a
+reported data race.  Replaces the compute-sanitizer runs that are not possible on the build pool.
+
+What is pinned:
+  * thresholds = 1.0 -- the protocol exactly as the round-1 kernels implement it (no flow control on the broadcast) is
+    race-free, bit-exact and deadlock-free, with one or two rounds in flight, for several ring depths;
+  * thresholds < 1.0 -- race-free only when the reduce-broadcast obeys the same slot flow control as the scatter.  The
+    round-1 kernels do not do that yet: an owner whose quorum excludes a peer lagging by a whole ring can overwrite the slot
+    that peer is still gathering from (found by this model, see docs/PROTOCOL.md "Known limits").
+"""
+import shutil
+import subprocess
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+@pytest.fixture(scope="module")
+def litmus(tmp_path_factory):
+    if shutil.which("g++") is None:
+        pytest.skip("needs g++")
+    exe = tmp_path_factory.mktemp("litmus") / "protocol_litmus"
+    b = subprocess.run(["g++", "-std=c++17", "-O1", "-g", "-fsanitize=thread", "-fno-omit-frame-pointer",
+                        str(ROOT / "csrc/tests/protocol_litmus.cpp"), "-o", str(exe), "-lpthread"], capture_output=True, text=True, timeout=300)
+    if b.returncode != 0:
+        pytest.skip("ThreadSanitizer build not available: " + b.stderr[-300:])
+    return exe
+
+
+def run(exe, *args):
+    r = subprocess.run([str(exe), *map(str, args)], capture_output=True, text=True, timeout=280, env={"TSAN_OPTIONS": "exitcode=66"})
+    if "unexpected memory mapping" in r.stderr:
+        pytest.skip("ThreadSanitizer cannot run in this container")
+    return r
+
+
+# seed, P, rounds, threshold %, maxLag, overlap, CTAs per kernel
+FULL = [(1, 4, 10, 100, 1, 1, 3), (2, 4, 10, 100, 1, 0, 3), (4, 3, 8, 100, 2, 1, 2), (6, 2, 12, 100, 0, 0, 3), (9, 5, 6, 100, 3, 1, 2)]
+
+
+@pytest.mark.parametrize("cfg", FULL)
+def test_round1_protocol_is_race_free_at_full_thresholds(litmus, cfg):
+    r = run(litmus, *cfg, 0)   # 0 = broadcast without flow control, i.e. what the shipped kernels do
+    assert "WARNING: ThreadSanitizer" not in r.stderr, r.stderr[-3000:]
+    assert r.returncode == 0 and "failures=0" in r.stdout, r.stdout + r.stderr[-1000:]
+
+
+@pytest.mark.parametrize("cfg", [(3, 4, 12, 75, 3, 1, 2), (5, 4, 12, 75, 1, 1, 2), (7, 6, 6, 50, 2, 1, 2)])
+def test_partial_thresholds_are_race_free_with_broadcast_flow_control(litmus, cfg):
+    r = run(litmus, *cfg, 1)
+    assert "WARNING: ThreadSanitizer" not in r.stderr, r.stderr[-3000:]
+    assert r.returncode == 0 and "failures=0" in r.stdout, r.stdout + r.stderr[-1000:]
