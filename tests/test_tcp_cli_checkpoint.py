@@ -152,3 +152,32 @@ def test_ring_snapshot_round_trip(tmp_path):
     core.save_ring_snapshot(p, s)
     t = core.load_ring_snapshot(p)
     assert (t.rank, t.P, t.L, t.round) == (1, 2, 2, 7) and t.reduce_flags == [(8 << 32) | 2] and t.scatter_ring == [1.0, 2.0]
+
+
+def test_tcp_transport_carries_multi_megabyte_chunks():
+    """ScatterBlock / ReduceBlock frames of 4 MiB (maxChunkSize = 1 Mi floats, the size BASELINE.json config 2 names and that
+    Akka's 128 kB default frame limit could not carry): non-blocking sockets see partial reads and writes at this size."""
+    P, n, chunk = 3, 3 * (1 << 20), 1 << 20
+    cfg = core.MasterConfig(total_workers=P, data_size=n, max_chunk_size=chunk, max_round=2, max_lag=1)
+    node = core.MasterNode(cfg, "127.0.0.1", 0)
+    sums = [[] for _ in range(P)]
+    nodes, workers = [], []
+    base = np.arange(n, dtype=np.float32) % 1000
+    for i in range(P):
+        wn = core.WorkerNode("127.0.0.1", node.port)
+        w = core.Worker(lambda it: base + np.float32(it),
+                        (lambda k: lambda data, count, it: sums[k].append((it, float(np.array(data, copy=False)[::4099].sum()), int(np.min(count)))))(i), wn)
+        wn.attach(w)
+        nodes.append(wn)
+        workers.append(w)
+    threads = [threading.Thread(target=x.run, args=(120.0,)) for x in nodes]
+    for t in threads:
+        t.start()
+    assert node.run(120.0)
+    for t in threads:
+        t.join(130)
+    for k in range(P):
+        assert [it for it, _, _ in sums[k]] == [0, 1, 2]
+        for it, s, cmin in sums[k]:
+            assert cmin == P
+            assert s == float((P * (base + np.float32(it)))[::4099].sum())
