@@ -9,6 +9,7 @@ are decoupled from each other by the thresholds, the device-resident ring and th
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Sequence
 
 import torch
@@ -63,6 +64,7 @@ class RoundEngine:
         self._pref = C.byref(self.params)
         self.rounds_enqueued = 0
         self.launches = 0
+        self._nvtx = os.environ.get("AAR_NVTX", "0") not in ("", "0")   # one NVTX range per round launch (off by default)
         # CTA role split of the pipelined kernels (measured on 8xB200, profiles/r1_phase_bench_*.txt)
         self.split = 32 | (48 << 16)      # nPush | nReduce << 16; the rest gather
         self.nvls_reduce_ctas = 8        # 207.7 us with 8 vs 222 us with 16 reduce CTAs at 8 GPUs, 64 MiB
@@ -139,6 +141,8 @@ class RoundEngine:
             p.flags |= L.FLAG_OVERLAPPED
         run_stream = stream or cur
         s = C.c_void_p(run_stream.cuda_stream)
+        if self._nvtx:
+            torch.cuda.nvtx.range_push(f"aar.round{rnd}.{self.algo}.slot{slot}")
         if delay_ns > 0:  # straggler injection: this rank's round starts late
             L.check(self.lib.aar_launch_delay(int(delay_ns), s), "aar_launch_delay")
         if self.algo == "twoshot":
@@ -152,6 +156,8 @@ class RoundEngine:
         else:
             raise ValueError(f"unknown algo {self.algo}")
         self._events[slot].record(run_stream)
+        if self._nvtx:
+            torch.cuda.nvtx.range_pop()
         self.launches += 1
         self.rounds_enqueued = max(self.rounds_enqueued, rnd + 1)
         return output, self.counts[slot]

@@ -47,6 +47,7 @@ class AllreduceWorker:
         self.max_scattered = -1
         self.delivered = 0          # rounds handed to the sink (= reference `round` on this in-order data plane)
         self.rounds_forced = 0
+        self.lag_hist: dict[int, int] = {}   # (master's newest round - round) at the moment a round reached the sink
         self._stream = None
         self._inputs = {}           # round -> input tensor kept alive until the round is flushed
         self._cpu_worker = None
@@ -100,8 +101,12 @@ class AllreduceWorker:
              "max_round": self.max_round, "max_scattered": self.max_scattered, "lag": self.max_round - self.delivered + 1}
         if self.engine is not None:
             m.update(self.engine.metrics())
+        m["lag_hist"] = dict(sorted(self.lag_hist.items()))
         if getattr(self, "_t_first", None) is not None and self.delivered > 1:
-            m["rounds_per_sec"] = (self.delivered - 1) / max(1e-9, self._t_last - self._t_first)
+            m["rounds_per_sec"] = rps = (self.delivered - 1) / max(1e-9, self._t_last - self._t_first)
+            lay = getattr(self.engine, "layout", None)
+            if lay is not None and getattr(lay, "P", 0) > 1:  # NCCL's bus-bandwidth convention: algbw * 2(P-1)/P
+                m["bus_gbps"] = rps * lay.dataSize * lay.elemSize * 2 * (lay.P - 1) / lay.P / 1e9
         return m
 
     def close(self) -> None:
@@ -131,6 +136,7 @@ class AllreduceWorker:
         self.engine = self._make_engine(m)
         self.max_round = self.max_scattered = -1
         self.delivered = 0
+        self.lag_hist = {}
         self._t_first = None
         self._inputs.clear()
         if self.on_init:
@@ -198,7 +204,9 @@ class AllreduceWorker:
                 r = self.delivered
                 slot = r % eng.layout.L
                 self._inputs.pop(r, None)
-                if self.max_round - r > eng.max_lag:
+                lag = self.max_round - r
+                self.lag_hist[lag] = self.lag_hist.get(lag, 0) + 1
+                if lag > eng.max_lag:
                     self.rounds_forced += 1
                 self.data_sink(AllReduceOutput(eng.outputs[slot], eng.counts[slot], r))
                 self.node.send_complete(self.id, r, self.generation)

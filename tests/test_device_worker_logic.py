@@ -135,6 +135,8 @@ def test_rounds_are_fetched_launched_and_sunk_in_order(max_lag, depth):
             assert cnt == world
         m = w.metrics()
         assert m["rounds_delivered"] == rounds and m["rounds_forced"] == 0 and m["max_scattered"] == rounds - 1
+        # lag histogram: every delivered round is counted once, and nothing was delivered from outside the window
+        assert sum(m["lag_hist"].values()) == rounds and max(m["lag_hist"]) <= max(max_lag, depth)
     assert master.metrics()["completions_counted"] == world * rounds
 
 
