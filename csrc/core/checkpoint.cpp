@@ -33,8 +33,12 @@ struct Out {
 
 struct In {
   std::ifstream f;
+  uint64_t size = 0;
   In(const std::string& path, uint32_t kind) : f(path, std::ios::binary) {
     if (!f) throw std::runtime_error("checkpoint: cannot read " + path);
+    f.seekg(0, std::ios::end);
+    size = (uint64_t)f.tellg();
+    f.seekg(0, std::ios::beg);
     char m[8];
     f.read(m, 8);
     if (!f || std::memcmp(m, kMagic, 8) != 0) throw std::runtime_error("checkpoint: bad magic in " + path);
@@ -50,7 +54,9 @@ struct In {
   template <class T>
   std::vector<T> vec() {
     uint64_t n = pod<uint64_t>();
-    if (n > (1ull << 34)) throw std::runtime_error("checkpoint: implausible vector length");
+    // a length that the rest of the file cannot hold is corruption: refuse before allocating for it
+    uint64_t here = (uint64_t)f.tellg();
+    if (n > (size - here) / sizeof(T)) throw std::runtime_error("checkpoint: vector length exceeds the file");
     std::vector<T> v(n);
     if (n) f.read(reinterpret_cast<char*>(v.data()), sizeof(T) * n);
     if (!f) throw std::runtime_error("checkpoint: truncated file");
@@ -85,7 +91,8 @@ void readBuffer(In& in, DataBuffer& b) {
   auto arrived = in.vec<uint8_t>();
   auto aux = in.vec<int>();
   auto data = in.vec<float>();
-  if (slotRound.size() != b.rawSlotRound().size() || arrived.size() != b.rawArrived().size() || data.size() != b.rawData().size())
+  if (slotRound.size() != b.rawSlotRound().size() || arrived.size() != b.rawArrived().size() || aux.size() != b.rawAux().size() ||
+      data.size() != b.rawData().size())
     throw std::runtime_error("checkpoint: ring payload mismatch");
   b.rawSlotRound() = std::move(slotRound);
   b.rawArrived() = std::move(arrived);
@@ -142,6 +149,11 @@ void loadWorkerCheckpoint(const std::string& path, Worker& w) {
   std::map<int, Address> peers;
   for (size_t i = 0; i + 1 < flat.size(); i += 2) peers[(int)flat[i]] = flat[i + 1];
   Address master = in.pod<int64_t>();
+  // The rings follow in the file: L x P x block floats each.  Fields that imply rings larger than the file are corrupt;
+  // refuse before restore() allocates for them.
+  if (s.maxLag < 0 || s.dataSize < 0 || s.maxChunkSize <= 0 || s.numPeers <= 0 || (size_t)s.numPeers != peers.size() ||
+      (uint64_t)(s.maxLag + 1) * (uint64_t)s.dataSize * sizeof(float) > in.size)
+    throw std::runtime_error("checkpoint: worker fields are inconsistent with the file");
   w.restore(s, peers, master);
   readBuffer(in, w.scatterBuffer());
   readBuffer(in, w.reduceBuffer());

@@ -23,6 +23,12 @@ namespace {
 
 using Clock = std::chrono::steady_clock;
 
+// Malformed bytes from the network.  Its own type so that the poll loops can drop the offending link without swallowing
+// errors raised by the message handlers (e.g. the input-size check of AllreduceWorker.scala:174-176).
+struct WireError : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+
 struct Writer {
   std::string b;
   template <class T>
@@ -51,7 +57,7 @@ struct Reader {
   explicit Reader(const std::string& s, size_t start = 0) : b(s), i(start) {}
   template <class T>
   T pod() {
-    if (i + sizeof(T) > b.size()) throw std::runtime_error("wire: truncated frame");
+    if (i + sizeof(T) > b.size()) throw WireError("wire: truncated frame");
     T v;
     std::memcpy(&v, b.data() + i, sizeof(T));
     i += sizeof(T);
@@ -59,14 +65,14 @@ struct Reader {
   }
   std::string str() {
     uint32_t n = pod<uint32_t>();
-    if (i + n > b.size()) throw std::runtime_error("wire: truncated string");
+    if (i + n > b.size()) throw WireError("wire: truncated string");
     std::string s = b.substr(i, n);
     i += n;
     return s;
   }
   std::vector<float> floats() {
     uint32_t n = pod<uint32_t>();
-    if (i + (size_t)n * 4 > b.size()) throw std::runtime_error("wire: truncated vector");
+    if (i + (size_t)n * 4 > b.size()) throw WireError("wire: truncated vector");
     std::vector<float> v(n);
     std::memcpy(v.data(), b.data() + i, (size_t)n * 4);
     i += (size_t)n * 4;
@@ -138,17 +144,24 @@ class Connection {
   }
   int fd() const { return fd_; }
   bool open() const { return fd_ >= 0; }
-  bool wantsWrite() const { return !out_.empty(); }
+  bool wantsWrite() const { return outPos_ < out_.size(); }
   void queue(const std::string& frame) {
+    if (outPos_ == out_.size()) {
+      out_.clear();
+      outPos_ = 0;
+    } else if (outPos_ > (4u << 20)) {  // reclaim the sent prefix now and then, never once per send()
+      out_.erase(0, outPos_);
+      outPos_ = 0;
+    }
     out_ += frame;
     flush();
   }
   // false when the peer closed or an error occurred
   bool flush() {
-    while (!out_.empty()) {
-      ssize_t n = ::send(fd_, out_.data(), out_.size(), MSG_NOSIGNAL);
+    while (outPos_ < out_.size()) {
+      ssize_t n = ::send(fd_, out_.data() + outPos_, out_.size() - outPos_, MSG_NOSIGNAL);
       if (n > 0) {
-        out_.erase(0, (size_t)n);
+        outPos_ += (size_t)n;
       } else if (n < 0 && (errno == EAGAIN || errno == EWOULDBLOCK)) {
         return true;
       } else if (n < 0 && errno == EINTR) {
@@ -157,6 +170,8 @@ class Connection {
         return false;
       }
     }
+    out_.clear();
+    outPos_ = 0;
     return true;
   }
   bool readAvailable() {
@@ -184,6 +199,7 @@ class Connection {
     }
     uint32_t len;
     std::memcpy(&len, in_.data() + pos_, 4);
+    if (len == 0 || len > kMaxFrameBytes) throw WireError("wire: frame length " + std::to_string(len) + " out of range");
     if (in_.size() - pos_ - 4 < len) {
       compact();
       return false;
@@ -195,7 +211,7 @@ class Connection {
   // Blocking drain (used before close so queued frames are not lost).
   void drain(double sec) {
     auto deadline = Clock::now() + std::chrono::duration<double>(sec);
-    while (!out_.empty() && Clock::now() < deadline) {
+    while (wantsWrite() && Clock::now() < deadline) {
       pollfd p{fd_, POLLOUT, 0};
       ::poll(&p, 1, 20);
       if (!flush()) return;
@@ -210,9 +226,11 @@ class Connection {
       pos_ = 0;
     }
   }
+  // One chunk of floats plus a header; nothing legitimate is larger, and a garbage length must not make us buffer 4 GB.
+  static constexpr uint32_t kMaxFrameBytes = (1u << 30) + 64;
   int fd_;
   std::string in_, out_;
-  size_t pos_ = 0;
+  size_t pos_ = 0, outPos_ = 0;
 };
 
 namespace wire {
@@ -448,24 +466,30 @@ int MasterNode::poll(int timeoutMs) {
       if (fds[k].revents & POLLOUT) alive = m.conn->flush();
       if (alive && (fds[k].revents & (POLLIN | POLLHUP | POLLERR))) alive = m.conn->readAvailable();
       std::string body;
-      while (m.conn->next(body)) {
-        ++handled;
-        m.conn->lastSeen = Clock::now();
-        uint8_t type = (uint8_t)body[0];
-        if (type == wire::Join) {
-          Reader r(body, 1);
-          m.role = r.str();
-          m.data.host = r.str();
-          m.data.port = r.pod<int32_t>();
-          m.joined = true;
-          master_->memberUp(a, m.role);
-        } else if (type == wire::Heartbeat) {
-          // lastSeen already refreshed
-        } else {
-          Message msg;
-          if (decode(body, msg, nullptr)) master_->receive(msg);
+      try {  // a peer that speaks garbage is disconnected; it must not take the coordinator down
+        while (m.conn->next(body)) {
+          ++handled;
+          m.conn->lastSeen = Clock::now();
+          uint8_t type = (uint8_t)body[0];
+          if (type == wire::Join) {
+            Reader r(body, 1);
+            m.role = r.str();
+            m.data.host = r.str();
+            m.data.port = r.pod<int32_t>();
+            m.joined = true;
+            master_->memberUp(a, m.role);
+          } else if (type == wire::Heartbeat) {
+            // lastSeen already refreshed
+          } else {
+            Message msg;
+            if (decode(body, msg, nullptr)) master_->receive(msg);
+          }
+          if (members_.find(a) == members_.end()) break;
         }
-        if (members_.find(a) == members_.end()) break;
+      } catch (const WireError& e) {
+        AAR_WARN("master: protocol error from member %ld: %s", (long)a, e.what());
+        dropMember(a, "protocol error");
+        continue;
       }
       if (!alive) dropMember(a, "connection closed");
     }
@@ -515,10 +539,18 @@ Connection* WorkerNode::peer(int id) {
   if (it != outPeers_.end()) return it->second.get();
   auto ep = endpoints_.find(id);
   if (ep == endpoints_.end()) return nullptr;
-  auto c = std::make_unique<Connection>(connectTo(ep->second.host, ep->second.port, 10.0));
-  Connection* raw = c.get();
-  outPeers_[id] = std::move(c);
-  return raw;
+  try {
+    auto c = std::make_unique<Connection>(connectTo(ep->second.host, ep->second.port, 10.0));
+    Connection* raw = c.get();
+    outPeers_[id] = std::move(c);
+    return raw;
+  } catch (const std::runtime_error& e) {
+    // A peer that cannot be reached is a dead letter box, as with Akka (the thresholds absorb its absence); forget the
+    // endpoint so that later sends do not pay the connect timeout again.  The next InitWorkers brings a fresh table.
+    AAR_WARN("worker: peer %d unreachable (%s); its messages are dropped", id, e.what());
+    endpoints_.erase(ep);
+    return nullptr;
+  }
 }
 
 void WorkerNode::send(Address to, Message msg) {
@@ -591,9 +623,14 @@ int WorkerNode::poll(int timeoutMs) {
       if (!(fds[inBase + k].revents & (POLLIN | POLLHUP | POLLERR))) continue;
       Connection& c = *inPeers_[k];
       bool alive = c.readAvailable();
-      while (c.next(body)) {
-        ++handled;
-        dispatch(body);
+      try {
+        while (c.next(body)) {
+          ++handled;
+          dispatch(body);
+        }
+      } catch (const WireError& e) {
+        AAR_WARN("worker: protocol error on a peer link: %s", e.what());
+        alive = false;
       }
       if (!alive) deadIn.push_back(k);
     }

