@@ -12,6 +12,7 @@ from pathlib import Path
 AAR_MAXP = 16
 AAR_F32, AAR_BF16 = 0, 1
 FLAG_NORMALIZE, FLAG_EXACT_QUORUM, FLAG_FORCE, FLAG_SKIP_SCATTER, FLAG_VIEW_OUTPUT, FLAG_TRACE, FLAG_OVERLAPPED = 1, 2, 4, 8, 16, 32, 64
+FLAG_BCAST_FC = 128  # opt-in (AAR_BCAST_FC=1): reduce-broadcast obeys the slot flow control at thresholds < 1
 TRACE_CTAS, TRACE_MARKS = 512, 8
 ST_TIMEOUT_SCATTER, ST_TIMEOUT_REDUCE, ST_TIMEOUT_GATHER, ST_PUSH_DROPPED = 1, 2, 4, 8
 

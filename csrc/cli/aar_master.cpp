@@ -16,6 +16,12 @@ using namespace aar;
 int main(int argc, char** argv) {
   try {
     CliArgs args = parseCli(argc, argv);
+    if (args.help) {
+      puts("usage: aar_master [port=2551] [totalWorkers=2] [dataSize=totalWorkers*5] [maxChunkSize=2]\n"
+           "                  [--conf application.conf] [--set allreduce.th-reduce=1.0]... [--timeout seconds]\n"
+           "Thresholds, maxLag and maxRound come from the allreduce { } block of the config file.");
+      return 0;
+    }
     Config conf = loadLayered(args, "master");
     // reference defaults when there is no file at all
     Config defaults = Config::parseString(

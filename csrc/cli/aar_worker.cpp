@@ -25,6 +25,12 @@ int main(int argc, char** argv) {
         rest.push_back(argv[i]);
     }
     CliArgs args = parseCli((int)rest.size(), rest.data());
+    if (args.help) {
+      puts("usage: aar_worker [port=2553] [dataSize=10] [--conf application.conf] [--set k=v]... [--timeout seconds] [--check]\n"
+           "CPU data plane, source data[i] = i + iteration.  The master is found at allreduce.transport.{hostname,port}.\n"
+           "GPU workers: python -m akka_allreduce_b200.cli.worker");
+      return 0;
+    }
     Config conf = loadLayered(args, "worker");
     AllreduceSettings s = AllreduceSettings::fromConfig(conf);
     Logger::instance().setLevel(Logger::parse(s.loglevel));

@@ -11,6 +11,7 @@
 namespace aar {
 
 struct CliArgs {
+  bool help = false;
   std::vector<std::string> positional;
   std::string conf;
   std::vector<std::string> overrides;  // --set path=value
@@ -21,7 +22,9 @@ inline CliArgs parseCli(int argc, char** argv) {
   CliArgs a;
   for (int i = 1; i < argc; ++i) {
     std::string s = argv[i];
-    if (s == "--conf" && i + 1 < argc) {
+    if (s == "--help" || s == "-h") {
+      a.help = true;
+    } else if (s == "--conf" && i + 1 < argc) {
       a.conf = argv[++i];
     } else if (s == "--set" && i + 1 < argc) {
       a.overrides.push_back(argv[++i]);

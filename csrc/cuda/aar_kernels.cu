@@ -234,9 +234,12 @@ __device__ unsigned chunkDecision(const AarRankParams& p, const AarLayout& l, ui
 //   kBcast = false: to the local pointer `localOut` (K5 one-shot)
 // PMAX bounds the source loop at compile time so all PMAX x U loads are issued before the first add
 // (memory-level parallelism: 16 outstanding 16-byte loads per thread).
-template <typename T, bool kBcast, int PMAX, int U>
+// kFC = true (AAR_FLAG_BCAST_FC): destinations whose bit in destMask is clear are skipped (their reduce-ring slot is
+// not ours to write yet, see bcastDestMask).  A separate instantiation so that the default path compiles unchanged.
+template <typename T, bool kBcast, int PMAX, int U, bool kFC = false>
 __device__ __forceinline__ void reduceSpanVec(const AarRankParams& p, const AarLayout& l, const T* rows, long long rowStride,
-                                              long long outElemOff, T* localOut, int nv, unsigned mask, float divisor) {
+                                              long long outElemOff, T* localOut, int nv, unsigned mask, float divisor,
+                                              unsigned destMask = 0xffffffffu) {
   constexpr int V = Elem<T>::kPerVec;
   const int P = l.P;
   for (int base = threadIdx.x; base < nv; base += kThreads * U) {
@@ -286,6 +289,7 @@ __device__ __forceinline__ void reduceSpanVec(const AarRankParams& p, const AarL
     if (kBcast) {
       for (int i2 = 0; i2 < P; ++i2) {
         const int dest = (i2 + p.rank) % P;
+        if (kFC && !((destMask >> dest) & 1u)) continue;
         uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<T*>(regionOf(p, dest) + l.reduceOff) + outElemOff);
 #pragma unroll
         for (int u = 0; u < U; ++u) {
@@ -303,17 +307,24 @@ __device__ __forceinline__ void reduceSpanVec(const AarRankParams& p, const AarL
   }
 }
 
-template <typename T, bool kBcast>
+template <typename T, bool kBcast, bool kFC = false>
 __device__ __forceinline__ void reduceSpan(const AarRankParams& p, const AarLayout& l, const T* rows, long long rowStride,
-                                           long long outElemOff, T* localOut, int n, unsigned mask, float divisor, bool vecOk) {
+                                           long long outElemOff, T* localOut, int n, unsigned mask, float divisor, bool vecOk,
+                                           unsigned destMask = 0xffffffffu) {
   constexpr int V = Elem<T>::kPerVec;
   const int P = l.P;
   const int nv = vecOk ? n / V : 0;
   if (nv > 0) {
     // 8 x 16-byte loads in flight per thread in every variant (64 KiB per CTA)
-    if (P <= 2) reduceSpanVec<T, kBcast, 2, 2>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
-    else if (P <= 4) reduceSpanVec<T, kBcast, 4, 2>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
-    else reduceSpanVec<T, kBcast, 8, 1>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
+    if (kFC) {
+      if (P <= 2) reduceSpanVec<T, kBcast, 2, 2, true>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor, destMask);
+      else if (P <= 4) reduceSpanVec<T, kBcast, 4, 2, true>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor, destMask);
+      else reduceSpanVec<T, kBcast, 8, 1, true>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor, destMask);
+    } else {
+      if (P <= 2) reduceSpanVec<T, kBcast, 2, 2>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
+      else if (P <= 4) reduceSpanVec<T, kBcast, 4, 2>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
+      else reduceSpanVec<T, kBcast, 8, 1>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
+    }
   }
   for (int i = nv * V + threadIdx.x; i < n; i += kThreads) {
     float a = 0.f;
@@ -324,6 +335,7 @@ __device__ __forceinline__ void reduceSpan(const AarRankParams& p, const AarLayo
     if (kBcast) {
       for (int i2 = 0; i2 < P; ++i2) {
         const int dest = (i2 + p.rank) % P;
+        if (kFC && !((destMask >> dest) & 1u)) continue;
         (reinterpret_cast<T*>(regionOf(p, dest) + l.reduceOff) + outElemOff)[i] = r;
       }
     } else {
@@ -355,7 +367,22 @@ __device__ __forceinline__ void nvlsSpan(const char* mcStage, char* mcOut, int n
   }
 }
 
-template <typename T, bool kNvls>
+// Slot flow control for the broadcast (thresholds < 1 only; found by csrc/tests/protocol_litmus.cpp).  With a partial
+// quorum the owner can finish reducing round R while a peer that was not in the quorum is still gathering round R - L
+// from the very reduce-ring slot the broadcast of round R writes.  The scatter already knows the answer: its per-
+// destination decision "peer retired round R - L, go" (or "peer fell out of the window, drop").  The broadcast adopts
+// that decision -- it waits for it like a push CTA would and skips the destinations that were dropped.  peerBase is
+// monotone, so a "go" seen by any CTA stays true.  Called by all threads of the CTA.
+__device__ unsigned bcastDestMask(const AarRankParams& p, const AarLayout& l, Smem& sm) {
+  unsigned m = 0;
+  for (int i2 = 0; i2 < l.P; ++i2) {
+    const int dest = (i2 + p.rank) % l.P;
+    if (dest == p.rank || scatterDecision(p, l, dest, sm)) m |= 1u << dest;
+  }
+  return m;
+}
+
+template <typename T, bool kNvls, bool kFC = false>
 __device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm, int unitsPerCta = 2) {
   const int P = l.P, C = l.C;
   const int myChunks = numChunks(l, p.rank);
@@ -367,6 +394,8 @@ __device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int
   const SegPlan plan(l, myChunks, nctas, kNvls ? 1 : unitsPerCta);
   const int S = plan.segs, segElems = plan.segElems(l);
   const long long total = (long long)myChunks * S;
+  unsigned destMask = 0xffffffffu;
+  if (kFC && !kNvls && cta < total) destMask = bcastDestMask(p, l, sm);
   for (long long idx = cta; idx < total; idx += nctas) {
     const int s = (int)(idx % S);
     const int c = (int)(idx / S);
@@ -400,7 +429,8 @@ __device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int
     } else {
       const float divisor = ((p.flags & AAR_FLAG_NORMALIZE) && count > 1) ? (float)count : 1.f;
       const T* rows = reinterpret_cast<const T*>(my + l.scatterOff) + (long long)slot * P * l.blkStride + (long long)c * l.maxChunk + off;
-      reduceSpan<T, true>(p, l, rows, l.blkStride, outElemOff, nullptr, n, mask, divisor, vecOk);
+      if (kFC) reduceSpan<T, true, true>(p, l, rows, l.blkStride, outElemOff, nullptr, n, mask, divisor, vecOk, destMask);
+      else reduceSpan<T, true>(p, l, rows, l.blkStride, outElemOff, nullptr, n, mask, divisor, vecOk);
     }
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -413,6 +443,7 @@ __device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int
         const uint64_t word = (epoch << 32) | (uint64_t)count;
         for (int i2 = 0; i2 < P; ++i2) {
           const int dest = (i2 + p.rank) % P;
+          if (kFC && !((destMask >> dest) & 1u)) continue;  // no data was written there: no flag either
           uint64_t* flag = reinterpret_cast<uint64_t*>(regionOf(p, dest) + l.rflagOff) + ((long long)slot * P + p.rank) * C + c;
           st_release_sys_u64(flag, word);
         }
@@ -725,14 +756,14 @@ __device__ __forceinline__ void initSmem(Smem& sm) {
 // phases: bit 0 = scatter, bit 1 = reduce+broadcast, bit 2 = gather.  7 = one launch per round per rank: the three
 // phases back to back; chunk flags let a CTA start reducing chunk c as soon as its contributors landed while other
 // CTAs are still pushing later chunks.
-template <typename T, bool kNvls>
+template <typename T, bool kNvls, bool kFC = false>
 __global__ void __launch_bounds__(kThreads, 1) roundKernel(const AarRankParams p, const AarLayout l, int phases) {
   __shared__ Smem sm;
   initSmem(sm);
   traceMark(p, l, 0);
   if (phases & 1) phaseScatter<T, kNvls>(p, l, blockIdx.x, gridDim.x, sm);
   traceMark(p, l, 1);
-  if (phases & 2) phaseReduceBcast<T, kNvls>(p, l, blockIdx.x, gridDim.x, sm);
+  if (phases & 2) phaseReduceBcast<T, kNvls, kFC>(p, l, blockIdx.x, gridDim.x, sm);
   traceMark(p, l, 3);
   if (phases & 4) phaseGather<T>(p, l, blockIdx.x, gridDim.x, sm);
   traceMark(p, l, 5);
@@ -742,7 +773,7 @@ __global__ void __launch_bounds__(kThreads, 1) roundKernel(const AarRankParams p
 //   CTAs [0, nPush)               K1 scatter_push
 //   CTAs [nPush, nPush+nReduce)   K2 reduce_bcast
 //   the rest                      K3 gather (eager per chunk when every chunk is required, else the round decision)
-template <typename T>
+template <typename T, bool kFC = false>
 __global__ void __launch_bounds__(kThreads, 1) p2pPipelinedKernel(const AarRankParams p, const AarLayout l, int split) {
   __shared__ Smem sm;
   initSmem(sm);
@@ -754,7 +785,7 @@ __global__ void __launch_bounds__(kThreads, 1) p2pPipelinedKernel(const AarRankP
     phaseScatter<T, false>(p, l, b, nPush, sm, 1);
     traceMark(p, l, 1);
   } else if (b < nPush + nReduce) {
-    phaseReduceBcast<T, false>(p, l, b - nPush, nReduce, sm, 1);
+    phaseReduceBcast<T, false, kFC>(p, l, b - nPush, nReduce, sm, 1);
     traceMark(p, l, 3);
   } else {
     const int cta = b - nPush - nReduce, n = nctas - nPush - nReduce;
@@ -900,6 +931,10 @@ int launch(K kernel, const AarRankParams* p, const AarLayout* l, int grid, void*
 
 int launchRound(const AarRankParams* p, const AarLayout* lay, int grid, void* stream, const char* what, int phases) {
   if (!lay) return aar_host::fail(AAR_EINVAL, "%s: null layout", what);
+  if (p && (p->flags & AAR_FLAG_BCAST_FC) && (phases & 2)) {  // opt-in: broadcast obeys the slot flow control
+    if (lay->dtype == AAR_F32) return launch(roundKernel<float, false, true>, p, lay, grid, stream, what, phases);
+    if (lay->dtype == AAR_BF16) return launch(roundKernel<__nv_bfloat16, false, true>, p, lay, grid, stream, what, phases);
+  }
   if (lay->dtype == AAR_F32) return launch(roundKernel<float, false>, p, lay, grid, stream, what, phases);
   if (lay->dtype == AAR_BF16) return launch(roundKernel<__nv_bfloat16, false>, p, lay, grid, stream, what, phases);
   return aar_host::fail(AAR_EINVAL, "%s: unknown dtype %d", what, lay->dtype);
@@ -937,6 +972,10 @@ AAR_API int aar_launch_round_pipelined(const AarRankParams* p, const AarLayout* 
   if (nPush < 1) nPush = 1;
   if (nReduce < 1) nReduce = 1;
   const int sp = nPush | (nReduce << 16);
+  if (p->flags & AAR_FLAG_BCAST_FC) {
+    if (lay->dtype == AAR_F32) return launch(p2pPipelinedKernel<float, true>, p, lay, g, stream, what, sp);
+    if (lay->dtype == AAR_BF16) return launch(p2pPipelinedKernel<__nv_bfloat16, true>, p, lay, g, stream, what, sp);
+  }
   if (lay->dtype == AAR_F32) return launch(p2pPipelinedKernel<float>, p, lay, g, stream, what, sp);
   if (lay->dtype == AAR_BF16) return launch(p2pPipelinedKernel<__nv_bfloat16>, p, lay, g, stream, what, sp);
   return aar_host::fail(AAR_EINVAL, "%s: unknown dtype %d", what, lay->dtype);

@@ -34,6 +34,8 @@ extern "C" {
 #define AAR_FLAG_SKIP_SCATTER 8u /* fused kernel: this rank contributes nothing this round (fault injection) */
 #define AAR_FLAG_VIEW_OUTPUT 16u /* K3 does not copy: the caller reads the reduce-ring slot itself, stream-ordered */
 #define AAR_FLAG_OVERLAPPED 64u /* consecutive rounds of this rank run on different streams: retire strictly in order */
+#define AAR_FLAG_BCAST_FC 128u  /* thresholds < 1: the reduce-broadcast adopts the scatter's per-destination slot flow control
+                                   (docs/PROTOCOL.md "Known limits"); opt-in until verified on hardware */
 #define AAR_FLAG_TRACE 32u      /* every CTA stamps %globaltimer at its phase boundaries into the trace section */
 #define AAR_TRACE_CTAS 512
 #define AAR_TRACE_MARKS 8

@@ -1,0 +1,72 @@
+"""GPU tests of code paths that are built but have NOT yet run on hardware (written after the round's GPU budget was spent).
+
+They are skipped unless AAR_EXPERIMENTAL=1, so that an unverified path can never turn the regular GPU suite red; the first GPU
+session of the next round runs them (`AAR_EXPERIMENTAL=1 python -m pytest tests/test_gpu_experimental.py -m gpu`), and whatever
+passes moves into the regular files.
+
+Currently: AAR_FLAG_BCAST_FC -- the reduce-broadcast adopts the scatter's per-destination slot flow control at thresholds < 1
+(docs/PROTOCOL.md "Known limits"; model: csrc/tests/protocol_litmus.cpp).
+"""
+import os
+
+import pytest
+import torch
+
+from test_gpu_local import cluster, make_inputs, oracle
+
+pytestmark = [pytest.mark.gpu,
+              pytest.mark.skipif(os.environ.get("AAR_EXPERIMENTAL", "0") in ("", "0"), reason="unverified paths: set AAR_EXPERIMENTAL=1")]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_bcast_flow_control_matches_the_default_path_when_nobody_lags(dtype):
+    """Same rounds, same inputs, with and without the flag: identical outputs, counts and masks over two ring revolutions."""
+    P, n, chunk = 4, 8192, 1024
+    a = cluster(P, n, chunk, max_lag=1, th_reduce=0.75, th_complete=0.75, dtype=dtype)
+    b = cluster(P, n, chunk, max_lag=1, th_reduce=0.75, th_complete=0.75, dtype=dtype, bcast_fc=True)
+    for rnd in range(5):
+        xs = make_inputs(P, n, dtype, 40 + rnd)
+        skip = [rnd % P] if rnd % 2 else []
+        oa, ca = a.run_round(rnd, xs, skip=skip)
+        ob, cb = b.run_round(rnd, xs, skip=skip)
+        torch.cuda.synchronize()
+        for r in range(P):
+            assert torch.equal(oa[r], ob[r]) and torch.equal(ca[r], cb[r])
+            assert b.status(r) == 0
+
+
+def test_bcast_flow_control_full_rounds_bit_exact():
+    P, n, chunk = 8, (1 << 18) + 8, 40000
+    cl = cluster(P, n, chunk, max_lag=1, th_reduce=0.9, th_complete=0.9, bcast_fc=True)
+    for rnd in range(4):
+        xs = make_inputs(P, n, torch.float32, 300 + rnd)
+        outs, counts = cl.run_round(rnd, xs)
+        want, wc = oracle(xs, P, n, chunk, lambda o, c: list(range(P)), torch.float32)
+        torch.cuda.synchronize()
+        for r in range(P):
+            assert torch.equal(outs[r], want) and torch.equal(counts[r], wc)
+
+
+def test_bcast_skips_a_destination_that_fell_out_of_the_window():
+    """Rank 3 stops taking part (never retires anything).  After L rounds its slots are still occupied: the scatter drops the
+    pushes to it (AAR_ST_PUSH_DROPPED) and, with the flag, the broadcast leaves its reduce ring alone as well: the rflag words
+    of rank 3 for the dropped round keep their old epoch."""
+    from akka_allreduce_b200.ops import lib as L
+
+    P, n, chunk = 4, 4096, 512
+    cl = cluster(P, n, chunk, max_lag=1, th_reduce=0.75, th_complete=0.75, timeout_ms=50.0, bcast_fc=True)
+    live = [0, 1, 2]
+    lay = cl.layout
+    for rnd in range(4):
+        xs = make_inputs(P, n, torch.float32, 500 + rnd)
+        cl.run_phases(rnd, xs, scatter=live, reduce=live, gather=live)
+        torch.cuda.synchronize()
+    flags3 = cl._section(3, lay.rflagOff, lay.L * lay.P * lay.C * 8, torch.int64).view(lay.L, lay.P, lay.C)
+    epochs = (flags3 >> 32).tolist()
+    # rounds 0 and 1 fit the ring (nothing to wait for); rounds 2 and 3 would overwrite slots rank 3 never retired
+    assert max(max(row) for slot in epochs for row in slot) <= 2, epochs
+    assert all(cl.status(r) & L.ST_PUSH_DROPPED for r in live)
+    # the live ranks still complete every round among themselves
+    want, _ = oracle(xs, P, n, chunk, lambda o, c: live, torch.float32, missing_owner_chunks=[(3, c) for c in range(2)])
+    for r in live:
+        assert torch.equal(cl.outputs[r], want)
