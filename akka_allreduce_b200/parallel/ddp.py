@@ -20,6 +20,29 @@ from .engine import RoundEngine
 from .symmetric import SymmetricMemory, UnixRendezvous
 
 
+def plan_buckets(sizes: list[int], per_bucket: int, align: int) -> list[tuple[list[int], int]]:
+    """Greedy packing of parameters (given in the order their gradients become ready) into buckets of at most `per_bucket`
+    elements -- a single larger parameter gets a bucket of its own -- each padded to a multiple of `align` elements.
+    Returns [(indices into sizes, padded bucket length)].  Pure function: the fixed-dataSize contract of the worker
+    (AllreduceWorker.scala:174-176) makes the plan part of the initialisation, so it is tested on its own."""
+    groups: list[list[int]] = []
+    cur: list[int] = []
+    size = 0
+    for i, n in enumerate(sizes):
+        if size and size + n > per_bucket:
+            groups.append(cur)
+            cur, size = [], 0
+        cur.append(i)
+        size += n
+    if cur:
+        groups.append(cur)
+    out = []
+    for g in groups:
+        n = sum(sizes[i] for i in g)
+        out.append((g, (n + align - 1) // align * align))
+    return out
+
+
 class GradientBucket:
     def __init__(self, index: int, numel: int, dtype: torch.dtype, device: torch.device):
         self.index = index
@@ -53,22 +76,10 @@ class ThresholdDDP:
         # Reverse registration order ~ the order gradients become ready; pack greedily, pad every bucket to a size the
         # 16-byte vector path likes (multiple of world * 64 elements).
         self.buckets: list[GradientBucket] = []
-        cur: list[torch.nn.Parameter] = []
-        size = 0
-        groups = []
-        for p in reversed(params):
-            if size and size + p.numel() > per_bucket:
-                groups.append(cur)
-                cur, size = [], 0
-            cur.append(p)
-            size += p.numel()
-        if cur:
-            groups.append(cur)
-        align = world * 64
+        ordered = list(reversed(params))
         code = L.AAR_F32 if dtype == torch.float32 else L.AAR_BF16
-        for i, g in enumerate(groups):
-            n = sum(p.numel() for p in g)
-            n = (n + align - 1) // align * align
+        for i, (idx, n) in enumerate(plan_buckets([p.numel() for p in ordered], per_bucket, world * 64)):
+            g = [ordered[k] for k in idx]
             b = GradientBucket(i, n, dtype, self.device)
             off = 0
             for p in g:
