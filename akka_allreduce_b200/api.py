@@ -16,6 +16,10 @@ from typing import Any, Callable
 @dataclass
 class AllReduceInputRequest:
     iteration: int
+    # Device plane, optional (AllreduceWorker(zero_copy_input=True) on the in-switch path): a CUDA tensor of dataSize elements
+    # inside the engine's staging area.  A source that writes its data there and returns that same tensor as
+    # AllReduceInput.data saves one device-side copy; any other tensor is still accepted.  None everywhere else.
+    buffer: Any = None
 
 
 @dataclass

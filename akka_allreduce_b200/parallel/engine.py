@@ -166,6 +166,23 @@ class RoundEngine:
         self.rounds_enqueued = max(self.rounds_enqueued, rnd + 1)
         return output, self.counts[slot]
 
+    def stage_input(self, rnd: int, stream: torch.cuda.Stream | None = None) -> torch.Tensor | None:
+        """Zero-copy input for the in-switch path: the slot of this rank's multicast-bound staging area that round `rnd` will
+        reduce from.  A source that writes its data here (H2D copy, the producing kernel's output, ...) and then passes the
+        SAME tensor to `enqueue_round(rnd, x)` saves the kernel's 1x read + 1x write staging pass (the stage role then only
+        publishes the arrival flags).  Returns None when the engine has no staging area (P2P paths copy from anywhere).
+        The slot was last read by the peers' reduce of round rnd - L; every owner had finished that before this rank's round
+        rnd - L could retire, so ordering after that round's event is enough: `stream` (default: current) is made to wait."""
+        lay = self.layout
+        if self.algo != "nvls" or not lay.stageOff:
+            return None
+        if rnd >= lay.L:
+            (stream or torch.cuda.current_stream(self.device)).wait_event(self._events[rnd % lay.L])
+        V = 16 // lay.elemSize
+        padded = (lay.dataSize + V - 1) // V * V
+        off = lay.stageOff + (rnd % lay.L) * padded * lay.elemSize
+        return self._region_view(off, lay.dataSize * lay.elemSize, self.dtype)
+
     def wait_round(self, rnd: int, stream: torch.cuda.Stream | None = None) -> None:
         """Make `stream` (default: the current stream) wait for round `rnd`; call before consuming its output on a stream."""
         (stream or torch.cuda.current_stream(self.device)).wait_event(self._events[rnd % self.layout.L])

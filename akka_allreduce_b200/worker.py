@@ -29,13 +29,14 @@ class AllreduceWorker:
     def __init__(self, data_source: DataSource, data_sink: DataSink, backend: str = "cuda", *, device: int | None = None,
                  dtype: str = "fp32", algo: str = "auto", normalize: bool = False, exact_quorum: bool = False,
                  spin_timeout_ms: float = 0.0, grid: int = 0, session: str | None = None, want_multicast: bool = True,
-                 on_init: Callable[["AllreduceWorker"], None] | None = None):
+                 zero_copy_input: bool = False, on_init: Callable[["AllreduceWorker"], None] | None = None):
         if backend not in ("cpu", "cuda"):
             raise ValueError("backend must be 'cpu' or 'cuda'")
         self.data_source, self.data_sink, self.backend = data_source, data_sink, backend
         self.device, self.dtype, self.algo = device, dtype, algo
         self.normalize, self.exact_quorum, self.spin_timeout_ms, self.grid = normalize, exact_quorum, spin_timeout_ms, grid
         self.session, self.want_multicast, self.on_init = session, want_multicast, on_init
+        self.zero_copy_input = zero_copy_input
         self.node: core.WorkerNode | None = None
         self.id = -1
         self.generation = 0
@@ -182,7 +183,10 @@ class AllreduceWorker:
             # the output / count buffers of round r - L must have reached the sink before round r reuses them
             while self.delivered < r - L + 1:
                 self._deliver_flushed(block=True)
-            x = self.data_source(AllReduceInputRequest(r)).data
+            req = AllReduceInputRequest(r)
+            if self.zero_copy_input and hasattr(eng, "stage_input"):
+                req.buffer = eng.stage_input(r)   # None unless the in-switch path is active
+            x = self.data_source(req).data
             n = x.numel() if hasattr(x, "numel") else len(x)
             if n != eng.data_size:
                 raise ValueError(f"Input data size {n} is different from initialization time {eng.data_size}!")

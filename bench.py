@@ -43,6 +43,8 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-nccl", action="store_true")
     ap.add_argument("--view", action="store_true", help="zero-copy output (sink reads the ring slot)")
+    ap.add_argument("--stage-input", action="store_true", help="zero-copy input on the in-switch path: the inputs live in the engine's "
+                    "multicast-bound staging slots (RoundEngine.stage_input); not the default, reported in config")
     ap.add_argument("--nvls-ctas", default="", help="nStage:nReduce for the NVLS kernel")
     ap.add_argument("--split", default="", help="nPush:nReduce for the pipelined P2P kernel")
     ap.add_argument("--no-overlap", action="store_true", help="one round in flight at a time (no use of the maxLag window)")
@@ -177,6 +179,10 @@ def main():
         if a.split:
             ps, rs = (int(v) for v in a.split.split(":"))
             eng.split = ps | (rs << 16)
+        staged = False
+        if a.stage_input and a.max_lag == 1 and eng.stage_input(0) is not None:   # slot of round r is r % 2 = index of its input
+            xs = [eng.stage_input(k).copy_(xs[k]) for k in range(2)]
+            staged = True
         global_sync()
         rnd = 0
         for _ in range(W):
@@ -284,7 +290,7 @@ def main():
             "config": {"model": "threshold allreduce, BASELINE.json config 2 (N workers, dataSize=16Mi, maxChunkSize=1Mi, thresholds=1.0, maxLag=1)",
                        "global_batch": N * a.data_size, "seq_len": a.data_size, "parallelism": f"dp{N}", "data_size": a.data_size,
                        "max_chunk_size": a.chunk, "max_lag": a.max_lag, "th_reduce": 1.0, "th_complete": 1.0,
-                       "l2_policy": "inputs+rings larger than L2 (2 x 64 MiB inputs alternate, 256 MiB rings per rank)", "view_output": a.view, "rounds_in_flight": 2 if (a.impl == "aar" and N > 1 and a.max_lag >= 1 and not a.no_overlap) else 1},
+                       "l2_policy": "inputs+rings larger than L2 (2 x 64 MiB inputs alternate, 256 MiB rings per rank)", "view_output": a.view, "stage_input": bool(a.impl == "aar" and a.stage_input), "rounds_in_flight": 2 if (a.impl == "aar" and N > 1 and a.max_lag >= 1 and not a.no_overlap) else 1},
             "rounds_per_sec": rounds_per_sec, "algbw_GBps": algbw, "busbw_GBps": busbw,
             "gpu_launches": gpu_launches, "clocks": clocks, "numa_binding": numa, "nccl": nccl,
             "vs_nccl": (nccl["ms_per_step"] / ms) if nccl and "ms_per_step" in nccl else None,

@@ -157,3 +157,57 @@ def test_input_size_mismatch_is_rejected_like_the_reference():
     w = FakeWorker(fabric, lambda req: AllReduceInput(np.zeros(5, dtype=np.float32)), lambda out: None)
     with pytest.raises(Exception, match="different from initialization"):
         w.run("127.0.0.1", master.port, 10)
+
+
+def test_zero_copy_input_offers_the_engines_buffer_to_the_source():
+    """AllreduceWorker(zero_copy_input=True): the request carries the engine's staging buffer for that round; a source that fills
+    and returns it is enqueued as is; without the option the request carries no buffer."""
+    world, n, rounds = 2, 8, 6
+    fabric = Fabric(world, n)
+    master = AllreduceMaster(world, 1.0, 1.0, 1.0, 1, n, rounds - 1, 4, pipeline_depth=1)
+    master.start(60)
+    seen = [[], []]
+    sunk = [[], []]
+
+    class StagedEngine(FakeEngine):
+        def __init__(self, *a):
+            super().__init__(*a)
+            self.stage = [np.zeros(n, dtype=np.float32) for _ in range(self.layout.L)]
+            self.identical = []
+
+        def stage_input(self, rnd):
+            return self.stage[rnd % self.layout.L]
+
+        def enqueue_round(self, rnd, x):
+            self.identical.append(x is self.stage[rnd % self.layout.L])
+            super().enqueue_round(rnd, x)
+
+    class W(FakeWorker):
+        def _make_engine(self, m):
+            return StagedEngine(self.fabric, m.dest_id, m.data_size, m.max_lag)
+
+    workers = []
+    for i, zc in enumerate((True, False)):
+        def source(req, i=i):
+            seen[i].append(req.buffer is not None)
+            data = np.full(n, float(i + 1) + req.iteration, dtype=np.float32)
+            if req.buffer is not None:
+                req.buffer[:] = data
+                return AllReduceInput(req.buffer)
+            return AllReduceInput(data)
+
+        workers.append(W(fabric, source, lambda out, i=i: sunk[i].append(float(out.data[0])), zero_copy_input=zc))
+    engines = []
+    for w in workers:
+        w.on_init = lambda ww: engines.append(ww.engine)
+    threads = [threading.Thread(target=w.run, args=("127.0.0.1", master.port, 60)) for w in workers]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(90)
+    assert master.join(30)
+    assert seen[0] == [True] * rounds and seen[1] == [False] * rounds
+    by_rank = {e.rank: e for e in engines}
+    zc_rank = workers[0].id
+    assert all(by_rank[zc_rank].identical) and not any(by_rank[1 - zc_rank].identical)
+    assert sunk[0] == sunk[1] == [3.0 + 2 * r for r in range(rounds)]
