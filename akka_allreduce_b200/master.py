@@ -26,10 +26,20 @@ def load_settings(conf: str | Path | None = None, overrides: dict | None = None,
 class AllreduceMaster:
     def __init__(self, total_workers: int, th_allreduce: float = 1.0, th_reduce: float = 1.0, th_complete: float = 1.0, max_lag: int = 1,
                  data_size: int = 10, max_round: int = 100, max_chunk_size: int = 2, *, pipeline_depth: int = 0, host: str = "127.0.0.1",
-                 port: int = 0, auto_down_after_ms: float = 10000.0):
+                 port: int = 0, auto_down_after_ms: float = 10000.0, start_round: int = 0, checkpoint: str | Path | None = None,
+                 checkpoint_every: int = 100, resume: bool = False):
+        """checkpoint: file the coordinator state is written to every `checkpoint_every` quorum rounds and when run() ends
+        (replaced atomically).  resume=True continues the round numbering of that file if it exists: the first admission starts
+        at the first round that had not reached its quorum (the reference always restarts at 0).  start_round sets that round
+        by hand."""
         self.config = core.MasterConfig(total_workers, th_allreduce, th_reduce, th_complete, max_lag, data_size, max_round, max_chunk_size,
-                                        pipeline_depth)
+                                        pipeline_depth, start_round)
         self.node = core.MasterNode(self.config, host, port, auto_down_after_ms)
+        self.start_round = start_round
+        if checkpoint is not None:
+            if resume and Path(checkpoint).exists():
+                self.start_round = core.resume_master_from_checkpoint(str(checkpoint), self.node.master())
+            self.node.set_checkpoint(str(checkpoint), checkpoint_every)
         self.host = host
         self._thread: threading.Thread | None = None
         self.finished = False

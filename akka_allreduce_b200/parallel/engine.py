@@ -235,6 +235,17 @@ class RoundEngine:
         s.reduce_flags = [v & 0xFFFFFFFFFFFFFFFF for v in self._region_view(lay.rflagOff, lay.L * lay.P * lay.C * 8, torch.int64).cpu().tolist()]
         return s
 
+    def start_at(self, rnd: int) -> None:
+        """Begin the round numbering at `rnd` on a fresh engine (a master that resumed from a checkpoint): every rank counts as
+        having retired all earlier rounds, so the slot flow control of round `rnd` has nothing to wait for.  Every rank calls
+        this on its own region before the first launch (the worker does, between mapping the regions and its first round)."""
+        lay = self.layout
+        self._region_view(lay.peerBaseOff, L.AAR_MAXP * 4, torch.int32)[: lay.P] = rnd
+        self._region_view(lay.statusOff, 8, torch.int32)[1] = rnd
+        self._host_words[1] = rnd
+        self.rounds_enqueued = rnd
+        torch.cuda.synchronize(self.device)
+
     def restore(self, s: "core.RingSnapshot") -> None:
         """Inverse of snapshot(): the ring payload and the arrival words go back into this rank's region; round numbering
         continues at s.round.  The geometry must match."""

@@ -103,8 +103,9 @@ class AllreduceWorker:
         if self.engine is not None:
             m.update(self.engine.metrics())
         m["lag_hist"] = dict(sorted(self.lag_hist.items()))
-        if getattr(self, "_t_first", None) is not None and self.delivered > 1:
-            m["rounds_per_sec"] = rps = (self.delivered - 1) / max(1e-9, self._t_last - self._t_first)
+        done = self.delivered - getattr(self, "start_round", 0)
+        if getattr(self, "_t_first", None) is not None and done > 1:
+            m["rounds_per_sec"] = rps = (done - 1) / max(1e-9, self._t_last - self._t_first)
             lay = getattr(self.engine, "layout", None)
             if lay is not None and getattr(lay, "P", 0) > 1:  # NCCL's bus-bandwidth convention: algbw * 2(P-1)/P
                 m["bus_gbps"] = rps * lay.dataSize * lay.elemSize * 2 * (lay.P - 1) / lay.P / 1e9
@@ -135,8 +136,14 @@ class AllreduceWorker:
         self.close()
         self.id, self.generation = m.dest_id, m.generation
         self.engine = self._make_engine(m)
-        self.max_round = self.max_scattered = -1
-        self.delivered = 0
+        # a resumed master continues its round numbering (InitWorkers.start_round; 0 in the reference): earlier rounds count as
+        # retired everywhere, which is what the device-side flow control has to be told as well
+        start = getattr(m, "start_round", 0)
+        if start > 0:
+            self.engine.start_at(start)
+        self.max_round = self.max_scattered = start - 1
+        self.delivered = start
+        self.start_round = start
         self.lag_hist = {}
         self._t_first = None
         self._inputs.clear()

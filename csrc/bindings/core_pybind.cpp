@@ -77,8 +77,9 @@ PYBIND11_MODULE(_core, m) {
 
   py::class_<InitWorkers>(m, "InitWorkers")
       .def(py::init([](std::map<int, Address> workers, Address master, int destId, float thReduce, float thComplete, int maxLag,
-                       int dataSize, int maxChunkSize, int generation) {
+                       int dataSize, int maxChunkSize, int generation, int startRound) {
              InitWorkers i;
+             i.startRound = startRound;
              i.workers = std::move(workers);
              i.master = master;
              i.destId = destId;
@@ -91,7 +92,7 @@ PYBIND11_MODULE(_core, m) {
              return i;
            }),
            py::arg("workers"), py::arg("master"), py::arg("dest_id"), py::arg("th_reduce"), py::arg("th_complete"), py::arg("max_lag"),
-           py::arg("data_size"), py::arg("max_chunk_size"), py::arg("generation") = 0)
+           py::arg("data_size"), py::arg("max_chunk_size"), py::arg("generation") = 0, py::arg("start_round") = 0)
       .def_readwrite("workers", &InitWorkers::workers)
       .def_readwrite("master", &InitWorkers::master)
       .def_readwrite("dest_id", &InitWorkers::destId)
@@ -100,7 +101,8 @@ PYBIND11_MODULE(_core, m) {
       .def_readwrite("max_lag", &InitWorkers::maxLag)
       .def_readwrite("data_size", &InitWorkers::dataSize)
       .def_readwrite("max_chunk_size", &InitWorkers::maxChunkSize)
-      .def_readwrite("generation", &InitWorkers::generation);
+      .def_readwrite("generation", &InitWorkers::generation)
+      .def_readwrite("start_round", &InitWorkers::startRound);
 
   py::class_<StartAllreduce>(m, "StartAllreduce")
       .def(py::init([](int round, int generation) { return StartAllreduce{round, generation}; }), py::arg("round"), py::arg("generation") = 0)
@@ -212,8 +214,9 @@ PYBIND11_MODULE(_core, m) {
 
   py::class_<MasterConfig>(m, "MasterConfig")
       .def(py::init([](int totalWorkers, float thAllreduce, float thReduce, float thComplete, int maxLag, int dataSize, int maxRound,
-                       int maxChunkSize, int pipelineDepth) {
+                       int maxChunkSize, int pipelineDepth, int startRound) {
              MasterConfig c;
+             c.startRound = startRound;
              c.totalWorkers = totalWorkers;
              c.thAllreduce = thAllreduce;
              c.thReduce = thReduce;
@@ -227,7 +230,7 @@ PYBIND11_MODULE(_core, m) {
            }),
            py::arg("total_workers") = 2, py::arg("th_allreduce") = 1.f, py::arg("th_reduce") = 1.f, py::arg("th_complete") = 1.f,
            py::arg("max_lag") = 1, py::arg("data_size") = 10, py::arg("max_round") = 100, py::arg("max_chunk_size") = 2,
-           py::arg("pipeline_depth") = 0)
+           py::arg("pipeline_depth") = 0, py::arg("start_round") = 0)
       .def_readwrite("total_workers", &MasterConfig::totalWorkers)
       .def_readwrite("th_allreduce", &MasterConfig::thAllreduce)
       .def_readwrite("th_reduce", &MasterConfig::thReduce)
@@ -236,7 +239,8 @@ PYBIND11_MODULE(_core, m) {
       .def_readwrite("data_size", &MasterConfig::dataSize)
       .def_readwrite("max_round", &MasterConfig::maxRound)
       .def_readwrite("max_chunk_size", &MasterConfig::maxChunkSize)
-      .def_readwrite("pipeline_depth", &MasterConfig::pipelineDepth);
+      .def_readwrite("pipeline_depth", &MasterConfig::pipelineDepth)
+      .def_readwrite("start_round", &MasterConfig::startRound);
 
   py::class_<Master>(m, "Master")
       .def(py::init<MasterConfig, WorkerPort*, Address>(), py::arg("config"), py::arg("port"), py::arg("self_address") = kNoAddress,
@@ -330,6 +334,7 @@ PYBIND11_MODULE(_core, m) {
   m.def("load_worker_checkpoint", &loadWorkerCheckpoint);
   m.def("save_master_checkpoint", &saveMasterCheckpoint);
   m.def("load_master_checkpoint", &loadMasterCheckpoint);
+  m.def("resume_master_from_checkpoint", &resumeMasterFromCheckpoint);
 
   py::class_<RingSnapshot>(m, "RingSnapshot")
       .def(py::init<>())
@@ -353,7 +358,9 @@ PYBIND11_MODULE(_core, m) {
       .def("master", &MasterNode::master, py::return_value_policy::reference_internal)
       .def("poll", &MasterNode::poll, py::arg("timeout_ms") = 0, py::call_guard<py::gil_scoped_release>())
       .def("run", &MasterNode::run, py::arg("timeout_sec") = 60.0, py::call_guard<py::gil_scoped_release>())
-      .def("broadcast_shutdown", &MasterNode::broadcastShutdown, py::call_guard<py::gil_scoped_release>());
+      .def("broadcast_shutdown", &MasterNode::broadcastShutdown, py::call_guard<py::gil_scoped_release>())
+      .def("set_checkpoint", &MasterNode::setCheckpoint, py::arg("path"), py::arg("every_rounds") = 100)
+      .def("checkpoint_now", &MasterNode::checkpointNow);
 
   py::class_<WorkerNode, WorkerPort>(m, "WorkerNode")
       .def(py::init<const std::string&, int, const std::string&, int, double, const std::string&>(), py::arg("master_host"),

@@ -2,12 +2,14 @@
 //
 //   aar_master [port=2551] [totalWorkers=2] [dataSize=totalWorkers*5] [maxChunkSize=2]
 //              [--conf application.conf] [--set allreduce.th-reduce=1.0]... [--timeout seconds]
+//              [--checkpoint file [--checkpoint-every rounds] [--resume]]
 //
 // Same positional arguments as `sbt "runMain sample.cluster.allreduce.AllreduceMaster ..."`
 // (AllreduceMaster.scala:101-138, README.md:3).  The thresholds / maxLag / maxRound the reference
 // hard-codes at :105-109 come from the `allreduce { }` block of the config file, with the same defaults.
 #include <cstdio>
 
+#include "../core/checkpoint.h"
 #include "../core/tcp_transport.h"
 #include "cli_common.h"
 
@@ -19,6 +21,7 @@ int main(int argc, char** argv) {
     if (args.help) {
       puts("usage: aar_master [port=2551] [totalWorkers=2] [dataSize=totalWorkers*5] [maxChunkSize=2]\n"
            "                  [--conf application.conf] [--set allreduce.th-reduce=1.0]... [--timeout seconds]\n"
+           "                  [--checkpoint file [--checkpoint-every rounds=100] [--resume]]\n"
            "Thresholds, maxLag and maxRound come from the allreduce { } block of the config file.");
       return 0;
     }
@@ -37,6 +40,18 @@ int main(int argc, char** argv) {
     AAR_INFO("-------\n Port = %d \n Number of Workers = %d \n Message Size = %d \n Max Chunk Size = %d", s.port, s.master.totalWorkers,
              s.master.dataSize, s.master.maxChunkSize);
     MasterNode node(s.master, s.hostname, s.port, s.autoDownAfterMs);
+    if (!args.checkpoint.empty()) {
+      bool exists = false;
+      if (FILE* f = fopen(args.checkpoint.c_str(), "rb")) {
+        fclose(f);
+        exists = true;
+      }
+      if (args.resume && exists) {
+        int start = resumeMasterFromCheckpoint(args.checkpoint, node.master());
+        printf("master: resuming at round %d from %s\n", start, args.checkpoint.c_str());
+      }
+      node.setCheckpoint(args.checkpoint, args.checkpointEvery);
+    }
     bool ok = node.run(args.timeoutSec);
     auto m = node.master().metrics().asMap();
     printf("master: finished=%d rounds_started=%.0f rounds_per_sec=%.1f\n", ok ? 1 : 0, m["rounds_started"], m["rounds_per_sec"]);

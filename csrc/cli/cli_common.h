@@ -16,6 +16,9 @@ struct CliArgs {
   std::string conf;
   std::vector<std::string> overrides;  // --set path=value
   double timeoutSec = 3600;
+  std::string checkpoint;  // master only: state file, replaced atomically every `checkpointEvery` quorum rounds and at exit
+  int checkpointEvery = 100;
+  bool resume = false;     // master only: continue the round numbering of `checkpoint` if the file exists
 };
 
 inline CliArgs parseCli(int argc, char** argv) {
@@ -28,6 +31,12 @@ inline CliArgs parseCli(int argc, char** argv) {
       a.conf = argv[++i];
     } else if (s == "--set" && i + 1 < argc) {
       a.overrides.push_back(argv[++i]);
+    } else if (s == "--checkpoint" && i + 1 < argc) {
+      a.checkpoint = argv[++i];
+    } else if (s == "--checkpoint-every" && i + 1 < argc) {
+      a.checkpointEvery = atoi(argv[++i]);
+    } else if (s == "--resume") {
+      a.resume = true;
     } else if (s == "--timeout" && i + 1 < argc) {
       a.timeoutSec = atof(argv[++i]);
     } else {

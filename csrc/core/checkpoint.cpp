@@ -189,6 +189,15 @@ void saveMasterCheckpoint(const std::string& path, const Master& m) {
   o.done();
 }
 
+int resumeMasterFromCheckpoint(const std::string& path, Master& m) {
+  Master scratch(m.config(), nullptr);
+  loadMasterCheckpoint(path, scratch);  // validates the geometry against m's configuration
+  if (m.started()) throw std::runtime_error("checkpoint: resume must happen before the first admission");
+  int start = scratch.quorumRound() + 1;
+  m.resumeAt(start, scratch.generation());
+  return start;
+}
+
 void loadMasterCheckpoint(const std::string& path, Master& m) {
   In in(path, 2);
   MasterConfig c;

@@ -25,6 +25,11 @@ void loadWorkerCheckpoint(const std::string& path, Worker& w);
 
 void saveMasterCheckpoint(const std::string& path, const Master& m);
 void loadMasterCheckpoint(const std::string& path, Master& m);
+// Restart after the coordinator process died: the saved worker addresses are gone with it, so instead of restoring the
+// member table a NEW master continues the round numbering -- the first admission starts at the first round that had not
+// reached its completion quorum, with a generation above the saved one.  Rounds in flight at the save are run again
+// (workers hold no state across a restart; the data source is asked for those iterations again).  Returns that round.
+int resumeMasterFromCheckpoint(const std::string& path, Master& m);
 
 // Device-ring snapshot used by the CUDA engine (host copies of the ring slots and flag words).
 struct RingSnapshot {

@@ -33,8 +33,8 @@ void Master::maybeAdmit() {
   int need = (int)((float)cfg_.totalWorkers * cfg_.thAllreduce);
   if ((int)workers_.size() >= std::max(1, need)) {
     initWorkers();
-    round_ = -1;
-    quorumRound_ = -1;
+    round_ = cfg_.startRound - 1;
+    quorumRound_ = cfg_.startRound - 1;
     completes_.clear();
     completedBy_.clear();
     advance();
@@ -61,6 +61,7 @@ void Master::initWorkers() {
     m.dataSize = cfg_.dataSize;
     m.maxChunkSize = cfg_.maxChunkSize;
     m.generation = generation_;
+    m.startRound = cfg_.startRound;
     port_->send(kv.second, std::move(m));
   }
 }

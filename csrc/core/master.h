@@ -34,6 +34,7 @@ struct MasterConfig {
   int maxRound = 100;
   int maxChunkSize = 2;
   int pipelineDepth = 0;
+  int startRound = 0;  // resume: rounds below this are taken as done; an admission (re)starts here instead of at 0
 };
 
 class Master {
@@ -60,6 +61,11 @@ class Master {
   // checkpoint
   void restore(int round, int quorumRound, int generation, const std::map<int, Address>& workers, const std::map<int, int>& completes);
   const std::map<int, int>& completes() const { return completes_; }
+  // Continue another coordinator's numbering (checkpoint.h, resumeMasterFromCheckpoint): before the first admission only.
+  void resumeAt(int startRound, int generation) {
+    cfg_.startRound = startRound;
+    generation_ = generation;
+  }
 
  private:
   void initWorkers();

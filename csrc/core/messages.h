@@ -27,6 +27,7 @@ struct InitWorkers {
   int dataSize = 0;
   int maxChunkSize = 1024;
   int generation = 0;  // (re)admission epoch; the reference has none (B7)
+  int startRound = 0;  // first round of this incarnation: 0 like the reference, > 0 when the master resumed from a checkpoint
 };
 
 struct StartAllreduce {

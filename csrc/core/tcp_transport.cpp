@@ -12,10 +12,12 @@
 #include <sys/socket.h>
 #include <unistd.h>
 
+#include <cstdio>
 #include <cstring>
 #include <stdexcept>
 #include <thread>
 
+#include "checkpoint.h"
 #include "logging.h"
 
 namespace aar {
@@ -247,6 +249,7 @@ std::string encode(const Message& m, const std::map<int, Endpoint>* endpoints) {
       w.pod<int32_t>(i.dataSize);
       w.pod<int32_t>(i.maxChunkSize);
       w.pod<int32_t>(i.generation);
+      w.pod<int32_t>(i.startRound);
       w.pod<uint32_t>((uint32_t)i.workers.size());
       for (auto& kv : i.workers) {
         w.pod<int32_t>(kv.first);
@@ -327,6 +330,7 @@ bool decode(const std::string& body, Message& out, std::map<int, Endpoint>* endp
       i.dataSize = r.pod<int32_t>();
       i.maxChunkSize = r.pod<int32_t>();
       i.generation = r.pod<int32_t>();
+      i.startRound = r.pod<int32_t>();
       uint32_t n = r.pod<uint32_t>();
       if (endpoints) endpoints->clear();
       for (uint32_t k = 0; k < n; ++k) {
@@ -510,10 +514,28 @@ void MasterNode::broadcastShutdown() {
   }
 }
 
+void MasterNode::setCheckpoint(const std::string& path, int everyRounds) {
+  ckptPath_ = path;
+  ckptEvery_ = everyRounds < 1 ? 1 : everyRounds;
+  ckptLast_ = master_->quorumRound();
+}
+
+void MasterNode::checkpointNow() {
+  if (ckptPath_.empty()) return;
+  const std::string tmp = ckptPath_ + ".tmp";
+  saveMasterCheckpoint(tmp, *master_);
+  if (std::rename(tmp.c_str(), ckptPath_.c_str()) != 0) throw std::runtime_error("checkpoint: cannot replace " + ckptPath_);
+  ckptLast_ = master_->quorumRound();
+}
+
 bool MasterNode::run(double timeoutSec) {
   auto deadline = Clock::now() + std::chrono::duration<double>(timeoutSec);
-  while (!master_->finished() && Clock::now() < deadline) poll(50);
+  while (!master_->finished() && Clock::now() < deadline) {
+    poll(50);
+    if (!ckptPath_.empty() && master_->quorumRound() >= ckptLast_ + ckptEvery_) checkpointNow();
+  }
   bool ok = master_->finished();
+  if (master_->started()) checkpointNow();
   broadcastShutdown();
   return ok;
 }

@@ -47,6 +47,10 @@ class MasterNode : public WorkerPort {
   // Run until every round reached its quorum (then broadcast Shutdown) or `timeoutSec` elapsed. Returns finished().
   bool run(double timeoutSec);
   void broadcastShutdown();
+  // Write the coordinator's state (checkpoint.h, master section) to `path` whenever the quorum clock has advanced by at
+  // least `everyRounds` since the last save, and once more when run() ends.  The file is replaced atomically.
+  void setCheckpoint(const std::string& path, int everyRounds = 100);
+  void checkpointNow();
   void send(Address to, Message msg) override;
 
  private:
@@ -59,6 +63,8 @@ class MasterNode : public WorkerPort {
   std::unique_ptr<Master> master_;
   std::map<Address, std::unique_ptr<Member>> members_;
   Address nextAddr_ = 1;
+  std::string ckptPath_;
+  int ckptEvery_ = 100, ckptLast_ = -1;
 };
 
 // Worker side: joins the master, listens for peers, routes inbound messages to `handler`.

@@ -51,9 +51,10 @@ void Worker::onInit(const InitWorkers& m) {
   thComplete_ = m.thComplete;
   maxLag_ = m.maxLag;
   generation_ = m.generation;
-  round_ = 0;
-  maxRound_ = -1;
-  maxScattered_ = -1;
+  if (m.startRound < 0) throw std::invalid_argument("InitWorkers: startRound must be >= 0");
+  round_ = m.startRound;  // 0 in the reference; a resumed master continues its round numbering
+  maxRound_ = m.startRound - 1;
+  maxScattered_ = m.startRound - 1;
   completed_.clear();
   geo_ = Geometry((int)peers_.size(), m.dataSize, m.maxChunkSize);
   for (int i = 0; i < geo_.P; ++i)

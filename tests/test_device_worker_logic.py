@@ -66,6 +66,10 @@ class FakeEngine:
     def set_doorbell(self, r):
         self.doorbell = max(self.doorbell, r)
 
+    def start_at(self, rnd):
+        self._flushed = rnd
+        self.started_at = rnd
+
     def rounds_flushed(self):
         if self.fabric.delay_s:
             time.sleep(self.fabric.delay_s)
@@ -95,9 +99,9 @@ class FakeWorker(AllreduceWorker):
         return FakeEngine(self.fabric, m.dest_id, m.data_size, m.max_lag)
 
 
-def run_cluster(world, n, rounds, max_lag, pipeline_depth, quorum=None, th=1.0):
+def run_cluster(world, n, rounds, max_lag, pipeline_depth, quorum=None, th=1.0, **master_kw):
     fabric = Fabric(world, n, quorum)
-    master = AllreduceMaster(world, th, 1.0, 1.0, max_lag, n, rounds - 1, 4, pipeline_depth=pipeline_depth)
+    master = AllreduceMaster(world, th, 1.0, 1.0, max_lag, n, rounds - 1, 4, pipeline_depth=pipeline_depth, **master_kw)
     master.start(60)
     log = [SimpleNamespace(fetched=[], sunk=[], data=[]) for _ in range(world)]
     workers = []
@@ -211,3 +215,20 @@ def test_zero_copy_input_offers_the_engines_buffer_to_the_source():
     zc_rank = workers[0].id
     assert all(by_rank[zc_rank].identical) and not any(by_rank[1 - zc_rank].identical)
     assert sunk[0] == sunk[1] == [3.0 + 2 * r for r in range(rounds)]
+
+
+def test_resumed_master_makes_the_device_plane_continue_at_its_round(tmp_path):
+    """AllreduceMaster(checkpoint=..., resume=True): a second coordinator continues the numbering of the first; the device-plane
+    worker tells its engine (start_at), fetches and sinks exactly the remaining rounds, and its counters start there."""
+    world, n = 2, 8
+    ck = tmp_path / "m.ckpt"
+    master, workers, log = run_cluster(world, n, 10, 1, 1, checkpoint=ck, checkpoint_every=3)
+    assert ck.exists() and all(lg.sunk == list(range(10)) for lg in log)
+    master, workers, log = run_cluster(world, n, 25, 1, 1, checkpoint=ck, resume=True)
+    assert master.start_round == 10
+    for w, lg in zip(workers, log):
+        assert lg.fetched == list(range(10, 25)) and lg.sunk == list(range(10, 25))
+        for it, (data, cnt) in zip(lg.sunk, lg.data):
+            np.testing.assert_array_equal(data, np.arange(n, dtype=np.float32) * 3 + 2 * it)
+        m = w.metrics()
+        assert m["rounds_delivered"] == 25 and m["rounds_forced"] == 0 and sum(m["lag_hist"].values()) == 15

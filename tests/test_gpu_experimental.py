@@ -70,3 +70,21 @@ def test_bcast_skips_a_destination_that_fell_out_of_the_window():
     want, _ = oracle(xs, P, n, chunk, lambda o, c: live, torch.float32, missing_owner_chunks=[(3, c) for c in range(2)])
     for r in live:
         assert torch.equal(cl.outputs[r], want)
+
+
+def test_engine_start_at_continues_the_round_numbering():
+    """RoundEngine.start_at (resume from a master checkpoint): a fresh engine begins at round 7 -- flow-control words say every
+    earlier round is retired -- and runs rounds 7..12 bit-exactly (slots reused three times)."""
+    from akka_allreduce_b200.parallel.engine import RoundEngine
+
+    n = 1 << 16
+    eng = RoundEngine.single_process(n, 1 << 12, max_lag=1, timeout_ms=2000.0)
+    eng.start_at(7)
+    for rnd in range(7, 13):
+        x = make_inputs(1, n, torch.float32, 700 + rnd)[0]
+        out, counts = eng.enqueue_round(rnd, x)
+        eng.wait_round(rnd)
+        torch.cuda.synchronize()
+        assert torch.equal(out, x) and int(counts.min()) == 1
+    assert eng.rounds_flushed() == 13 and eng.status() == 0
+    eng.close()

@@ -228,3 +228,31 @@ def test_cpu_baseline_runs():
     sec, checksum, msgs = core.cpu_baseline_seconds(cfg(total_workers=2, max_round=100), 2)
     assert sec > 0 and msgs == 101 * 28 + 2
     assert checksum == float(sum(2 * (i + 100) for i in range(10)))
+
+
+def test_start_round_continues_the_numbering_instead_of_restarting_at_zero():
+    """Resume support (not in the reference, which always restarts at round 0): MasterConfig.start_round travels in InitWorkers,
+    workers fetch / flush exactly the rounds start..maxRound, thresholds and the ring work on absolute round numbers."""
+    sinks = [[], [], []]
+    cl = make_cluster(3, sinks, data_size=9, max_chunk_size=2, max_round=12, max_lag=2, start_round=7)
+    cl.join_all()
+    cl.run()
+    for s in sinks:
+        assert [it for it, _, _ in s] == list(range(7, 13))
+        for it, data, count in s:
+            np.testing.assert_array_equal(data, 3 * (np.arange(9, dtype=np.float32) + it))
+    # partial thresholds: same round numbering, every element is the sum of `count` contributors
+    sinks = [[], [], []]
+    cl = make_cluster(3, sinks, data_size=9, max_chunk_size=2, max_round=12, max_lag=2, start_round=7, th_reduce=0.7, th_complete=0.7)
+    cl.join_all()
+    cl.run()
+    for s in sinks:
+        assert sorted(it for it, _, _ in s) == list(range(7, 13))
+
+
+def test_start_round_beyond_max_round_finishes_immediately():
+    sinks = [[], []]
+    cl = make_cluster(2, sinks, max_round=5, start_round=6)
+    cl.join_all()
+    cl.run()
+    assert cl.master().finished and sinks == [[], []]

@@ -223,3 +223,39 @@ def test_master_survives_garbage_and_oversized_frames():
         except (ConnectionResetError, socket.timeout):
             pass
         s.close()
+
+
+def test_cli_master_checkpoints_and_a_restarted_master_resumes(tmp_path):
+    """aar_master --checkpoint f: state saved while running and at exit; a NEW master process started with --resume continues at
+    the first round without quorum (31) instead of 0; the workers' --check verifies the data of exactly the resumed rounds."""
+    build.build_cli()
+    ck = tmp_path / "master.ckpt"
+
+    def run(max_round, resume):
+        port = _free_port()
+        common = ["--set", f"allreduce.transport.port={port}", "--set", "allreduce.loglevel=WARNING", "--timeout", "60"]
+        extra = ["--checkpoint", str(ck), "--checkpoint-every", "7"] + (["--resume"] if resume else [])
+        m = subprocess.Popen([str(ROOT / "bin/aar_master"), str(port), "2", "10", "2", "--set", "allreduce.th-reduce=1.0", "--set",
+                              "allreduce.th-complete=1.0", "--set", f"allreduce.max-round={max_round}", *extra, *common],
+                             stdout=subprocess.PIPE, text=True, cwd=ROOT)
+        ws = [subprocess.Popen([str(ROOT / "bin/aar_worker"), "0", "10", "--check", *common], stdout=subprocess.PIPE, text=True, cwd=ROOT)
+              for _ in range(2)]
+        mo, _ = m.communicate(timeout=90)
+        wos = [w.communicate(timeout=90)[0] for w in ws]
+        assert m.returncode == 0 and all(w.returncode == 0 for w in ws), (mo, wos)
+        return mo, wos
+
+    mo, wos = run(30, resume=False)
+    assert "rounds_started=31" in mo and all("rounds_flushed=31 mismatches=0" in w for w in wos)
+    assert ck.exists()
+    m2 = core.Master(core.MasterConfig(total_workers=2, data_size=10, max_chunk_size=2, max_lag=1), core.CallbackPort(lambda to, m: None), 0)
+    assert core.resume_master_from_checkpoint(str(ck), m2) == 31
+
+    mo, wos = run(60, resume=True)
+    assert "resuming at round 31" in mo and "rounds_started=30" in mo
+    assert all("rounds_flushed=30 mismatches=0" in w for w in wos)
+    m3 = core.Master(core.MasterConfig(total_workers=2, data_size=10, max_chunk_size=2, max_lag=1), core.CallbackPort(lambda to, m: None), 0)
+    assert core.resume_master_from_checkpoint(str(ck), m3) == 61
+    with pytest.raises(Exception, match="differs"):
+        core.resume_master_from_checkpoint(str(ck), core.Master(core.MasterConfig(total_workers=3, data_size=10, max_chunk_size=2),
+                                                                 core.CallbackPort(lambda to, m: None), 0))
