@@ -1,0 +1,35 @@
+#!/bin/bash
+# First GPU calls of the next round, in order, each one gpurun call.  Everything here was written after round 1's GPU budget
+# was spent and has NOT run on hardware yet.  Outputs go to gpurun_out/ (scratch); copy what is worth keeping into profiles/.
+#
+#   gpurun --timeout 900 -- 'bash bench/next_round_gpu_plan.sh one'            # 1 GPU
+#   gpurun --gpus 2 --timeout 900 -- 'bash bench/next_round_gpu_plan.sh two'   # 2 GPUs
+#   gpurun --gpus 8 --timeout 1200 -- 'bash bench/next_round_gpu_plan.sh eight'
+set -u
+cd "$(dirname "$0")/.."
+mkdir -p gpurun_out
+TR() { n=$1; port=$2; shift 2; python -m torch.distributed.run --nnodes=1 --nproc-per-node "$n" --master-addr 127.0.0.1 --master-port "$port" "$@"; }
+
+case "${1:-one}" in
+one)
+  # 1. the regular suite must still be green, then the unverified paths (flow-controlled broadcast, engine.start_at)
+  timeout 600 python -m pytest tests -x -q -m gpu 2>&1 | tail -5 | tee gpurun_out/r2_gpu_suite.txt
+  AAR_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_gpu_experimental.py -q -m gpu 2>&1 | tail -15 | tee gpurun_out/r2_experimental.txt
+  timeout 300 python bench.py --steps 30 --warmup 5 | tee gpurun_out/r2_bench_n1.json
+  ;;
+two)
+  # 2. real peers: regular multi-GPU suite, then the same suite with the flow-controlled broadcast switched on
+  timeout 600 python -m pytest tests/test_gpu_multi.py -x -q -m gpu 2>&1 | tail -5 | tee gpurun_out/r2_multi.txt
+  AAR_BCAST_FC=1 timeout 600 python -m pytest tests/test_gpu_multi.py -x -q -m gpu 2>&1 | tail -5 | tee gpurun_out/r2_multi_fc.txt
+  ;;
+eight)
+  # 3. does the flow control cost anything in straggler mode?  then the knobs that were added blind
+  TR 8 29611 bench/straggler_bench.py 2>&1 | grep "^{" | tee gpurun_out/r2_straggler_default.json
+  AAR_BCAST_FC=1 TR 8 29612 bench/straggler_bench.py 2>&1 | grep "^{" | tee gpurun_out/r2_straggler_fc.json
+  TR 8 29613 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8.json
+  TR 8 29614 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e --stage-input 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8_stage_input.json
+  for ctas in 48:4 48:6 48:8 32:8 64:8; do
+    TR 8 29615 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e --no-nccl --nvls-ctas $ctas 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8_ctas_${ctas/:/_}.json
+  done
+  ;;
+esac
