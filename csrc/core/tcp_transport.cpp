@@ -21,6 +21,14 @@
 #include "logging.h"
 
 namespace aar {
+
+// One frame body (type byte + payload) as it sits in a connection's receive buffer; valid until the connection is read
+// or asked for the next frame again.
+struct Frame {
+  const char* data = nullptr;
+  size_t size = 0;
+};
+
 namespace {
 
 using Clock = std::chrono::steady_clock;
@@ -32,7 +40,7 @@ struct WireError : std::runtime_error {
 };
 
 struct Writer {
-  std::string b;
+  std::string b = std::string(5, '\0');  // u32 length + type byte, filled in by frame()
   template <class T>
   void pod(T v) { b.append(reinterpret_cast<const char*>(&v), sizeof(T)); }
   void str(const std::string& s) {
@@ -40,44 +48,44 @@ struct Writer {
     b += s;
   }
   void floats(const std::vector<float>& v) {
+    b.reserve(b.size() + 4 + v.size() * sizeof(float));
     pod<uint32_t>((uint32_t)v.size());
     b.append(reinterpret_cast<const char*>(v.data()), v.size() * sizeof(float));
   }
   std::string frame(uint8_t type) {
-    std::string f;
-    uint32_t len = (uint32_t)b.size() + 1;
-    f.append(reinterpret_cast<const char*>(&len), 4);
-    f.push_back((char)type);
-    f += b;
-    return f;
+    uint32_t len = (uint32_t)b.size() - 4;  // type byte + payload
+    std::memcpy(&b[0], &len, 4);
+    b[4] = (char)type;
+    return std::move(b);
   }
 };
 
 struct Reader {
-  const std::string& b;
-  size_t i;
-  explicit Reader(const std::string& s, size_t start = 0) : b(s), i(start) {}
+  const char* b;
+  size_t n, i;
+  explicit Reader(const Frame& f, size_t start = 0) : b(f.data), n(f.size), i(start) {}
   template <class T>
   T pod() {
-    if (i + sizeof(T) > b.size()) throw WireError("wire: truncated frame");
+    if (i + sizeof(T) > n) throw WireError("wire: truncated frame");
     T v;
-    std::memcpy(&v, b.data() + i, sizeof(T));
+    std::memcpy(&v, b + i, sizeof(T));
     i += sizeof(T);
     return v;
   }
   std::string str() {
-    uint32_t n = pod<uint32_t>();
-    if (i + n > b.size()) throw WireError("wire: truncated string");
-    std::string s = b.substr(i, n);
-    i += n;
+    uint32_t len = pod<uint32_t>();
+    if (i + len > n) throw WireError("wire: truncated string");
+    std::string s(b + i, len);
+    i += len;
     return s;
   }
   std::vector<float> floats() {
-    uint32_t n = pod<uint32_t>();
-    if (i + (size_t)n * 4 > b.size()) throw WireError("wire: truncated vector");
-    std::vector<float> v(n);
-    std::memcpy(v.data(), b.data() + i, (size_t)n * 4);
-    i += (size_t)n * 4;
+    uint32_t len = pod<uint32_t>();
+    if (i + (size_t)len * 4 > n) throw WireError("wire: truncated vector");
+    const float* p = reinterpret_cast<const float*>(b + i);  // memcpy below: the payload need not be aligned
+    std::vector<float> v(len);
+    std::memcpy(v.data(), p, (size_t)len * 4);
+    i += (size_t)len * 4;
     return v;
   }
 };
@@ -147,15 +155,17 @@ class Connection {
   int fd() const { return fd_; }
   bool open() const { return fd_ >= 0; }
   bool wantsWrite() const { return outPos_ < out_.size(); }
-  void queue(const std::string& frame) {
-    if (outPos_ == out_.size()) {
-      out_.clear();
+  void queue(std::string frame) {
+    if (outPos_ == out_.size()) {  // nothing pending: adopt the frame's buffer instead of copying it
+      out_ = std::move(frame);
       outPos_ = 0;
-    } else if (outPos_ > (4u << 20)) {  // reclaim the sent prefix now and then, never once per send()
-      out_.erase(0, outPos_);
-      outPos_ = 0;
+    } else {
+      if (outPos_ > (4u << 20)) {  // reclaim the sent prefix now and then, never once per send()
+        out_.erase(0, outPos_);
+        outPos_ = 0;
+      }
+      out_ += frame;
     }
-    out_ += frame;
     flush();
   }
   // false when the peer closed or an error occurred
@@ -177,11 +187,22 @@ class Connection {
     return true;
   }
   bool readAvailable() {
-    char buf[65536];
+    size_t got = 0;
     for (;;) {
-      ssize_t n = ::recv(fd_, buf, sizeof buf, 0);
+      if (got >= (32u << 20)) return true;  // let the frames be consumed; poll() is level-triggered and comes back
+      // receive straight into the frame buffer (no bounce buffer, no zero-fill): keep at least 64 KiB of room, and once a
+      // frame header is known, room for the whole frame
+      size_t want = 65536;
+      if (len_ - pos_ >= 4) {
+        uint32_t flen;
+        std::memcpy(&flen, in_.get() + pos_, 4);
+        if (flen <= kMaxFrameBytes && (size_t)flen + 4 > len_ - pos_) want = std::max(want, (size_t)flen + 4 - (len_ - pos_));
+      }
+      reserve(want);
+      ssize_t n = ::recv(fd_, in_.get() + len_, cap_ - len_, 0);
       if (n > 0) {
-        in_.append(buf, (size_t)n);
+        len_ += (size_t)n;
+        got += (size_t)n;
       } else if (n == 0) {
         return false;
       } else if (errno == EAGAIN || errno == EWOULDBLOCK) {
@@ -193,21 +214,19 @@ class Connection {
       }
     }
   }
-  // Pops one complete frame body (type byte + payload).
-  bool next(std::string& body) {
-    if (in_.size() - pos_ < 4) {
-      compact();
+  // Pops one complete frame body (type byte + payload) as a view into the receive buffer.
+  bool next(Frame& body) {
+    if (len_ - pos_ < 4) {
+      if (pos_ == len_) pos_ = len_ = 0;
       return false;
     }
     uint32_t len;
-    std::memcpy(&len, in_.data() + pos_, 4);
+    std::memcpy(&len, in_.get() + pos_, 4);
     if (len == 0 || len > kMaxFrameBytes) throw WireError("wire: frame length " + std::to_string(len) + " out of range");
-    if (in_.size() - pos_ - 4 < len) {
-      compact();
-      return false;
-    }
-    body.assign(in_, pos_ + 4, len);
-    pos_ += 4 + len;
+    if (len_ - pos_ - 4 < len) return false;
+    body.data = in_.get() + pos_ + 4;
+    body.size = len;
+    pos_ += 4 + (size_t)len;
     return true;
   }
   // Blocking drain (used before close so queued frames are not lost).
@@ -222,17 +241,30 @@ class Connection {
   Clock::time_point lastSeen = Clock::now();
 
  private:
-  void compact() {
-    if (pos_ > (1u << 20) || pos_ == in_.size()) {
-      in_.erase(0, pos_);
-      pos_ = 0;
+  // Make room for `want` more bytes behind len_: slide the unread tail to the front when that is enough (it is at most one
+  // partial frame), otherwise grow geometrically.
+  void reserve(size_t want) {
+    if (cap_ - len_ >= want) return;
+    const size_t live = len_ - pos_;
+    if (pos_ > 0 && cap_ - live >= want) {
+      std::memmove(in_.get(), in_.get() + pos_, live);
+    } else {
+      size_t ncap = std::max(cap_ * 2, live + want);
+      std::unique_ptr<char[]> nb(new char[ncap]);
+      if (live) std::memcpy(nb.get(), in_.get() + pos_, live);
+      in_ = std::move(nb);
+      cap_ = ncap;
     }
+    pos_ = 0;
+    len_ = live;
   }
   // One chunk of floats plus a header; nothing legitimate is larger, and a garbage length must not make us buffer 4 GB.
   static constexpr uint32_t kMaxFrameBytes = (1u << 30) + 64;
   int fd_;
-  std::string in_, out_;
-  size_t pos_ = 0, outPos_ = 0;
+  std::unique_ptr<char[]> in_;  // receive buffer: [pos_, len_) is unread, capacity cap_
+  size_t cap_ = 0, len_ = 0, pos_ = 0;
+  std::string out_;
+  size_t outPos_ = 0;
 };
 
 namespace wire {
@@ -317,10 +349,10 @@ std::string encodeSimple(Type t, int32_t arg) {
 namespace {
 
 // Decodes a frame body into a Message. Returns false for non-message frames (join/heartbeat/...).
-bool decode(const std::string& body, Message& out, std::map<int, Endpoint>* endpoints) {
-  if (body.empty()) return false;
+bool decode(const Frame& body, Message& out, std::map<int, Endpoint>* endpoints) {
+  if (body.size == 0) return false;
   Reader r(body, 1);
-  switch ((uint8_t)body[0]) {
+  switch ((uint8_t)body.data[0]) {
     case wire::Init: {
       InitWorkers i;
       i.destId = r.pod<int32_t>();
@@ -469,12 +501,12 @@ int MasterNode::poll(int timeoutMs) {
       bool alive = true;
       if (fds[k].revents & POLLOUT) alive = m.conn->flush();
       if (alive && (fds[k].revents & (POLLIN | POLLHUP | POLLERR))) alive = m.conn->readAvailable();
-      std::string body;
+      Frame body;
       try {  // a peer that speaks garbage is disconnected; it must not take the coordinator down
         while (m.conn->next(body)) {
           ++handled;
           m.conn->lastSeen = Clock::now();
-          uint8_t type = (uint8_t)body[0];
+          uint8_t type = (uint8_t)body.data[0];
           if (type == wire::Join) {
             Reader r(body, 1);
             m.role = r.str();
@@ -585,8 +617,8 @@ void WorkerNode::send(Address to, Message msg) {
   c->queue(wire::encode(msg));
 }
 
-void WorkerNode::dispatch(const std::string& body) {
-  uint8_t type = (uint8_t)body[0];
+void WorkerNode::dispatch(const Frame& body) {
+  uint8_t type = (uint8_t)body.data[0];
   if (type == wire::Shutdown) {
     shutdown_ = true;
     return;
@@ -615,7 +647,7 @@ int WorkerNode::poll(int timeoutMs) {
   }
   int rc = ::poll(fds.data(), fds.size(), timeoutMs);
   int handled = 0;
-  std::string body;
+  Frame body;
   if (rc > 0) {
     if (fds[0].revents & POLLIN) {
       for (;;) {

@@ -34,6 +34,7 @@ std::string encodeSimple(Type t, int32_t arg = 0);
 }  // namespace wire
 
 class Connection;  // non-blocking framed socket
+struct Frame;      // view of one received frame
 
 // Master side: accepts members, feeds a Master, forwards its sends.
 class MasterNode : public WorkerPort {
@@ -85,7 +86,7 @@ class WorkerNode : public WorkerPort {
   void send(Address to, Message msg) override;  // to = worker id, or kMaster
 
  private:
-  void dispatch(const std::string& frame);
+  void dispatch(const Frame& frame);
   Connection* peer(int id);
   Handler handler_;
   std::unique_ptr<Connection> masterConn_;
