@@ -12,6 +12,7 @@ from pathlib import Path
 AAR_MAXP = 16
 AAR_F32, AAR_BF16 = 0, 1
 FLAG_NORMALIZE, FLAG_EXACT_QUORUM, FLAG_FORCE, FLAG_SKIP_SCATTER, FLAG_VIEW_OUTPUT, FLAG_TRACE, FLAG_OVERLAPPED = 1, 2, 4, 8, 16, 32, 64
+FLAG_EAGER_DEC = 256  # opt-in (AAR_STRICT=1): eager gather decides once per chunk (no half-flushed chunk when a wait gives up)
 FLAG_BCAST_FC = 128  # opt-in (AAR_BCAST_FC=1): reduce-broadcast obeys the slot flow control at thresholds < 1
 TRACE_CTAS, TRACE_MARKS = 512, 8
 ST_TIMEOUT_SCATTER, ST_TIMEOUT_REDUCE, ST_TIMEOUT_GATHER, ST_PUSH_DROPPED = 1, 2, 4, 8
@@ -28,6 +29,7 @@ class AarLayout(C.Structure):
         ("k2CtrOff", C.c_uint64), ("k3DecOff", C.c_uint64), ("k3CtrOff", C.c_uint64), ("countsOff", C.c_uint64),
         ("statusOff", C.c_uint64), ("oneshotOff", C.c_uint64), ("oneshotFlagOff", C.c_uint64), ("stageOff", C.c_uint64),
         ("barrierOff", C.c_uint64), ("traceOff", C.c_uint64), ("ctrlBytes", C.c_uint64), ("regionBytes", C.c_uint64),
+        ("egDecOff", C.c_uint64),
     ]
 
 
@@ -69,6 +71,11 @@ def load():
         raise AarError(f"{path} is missing: run `python -m akka_allreduce_b200.utils.build`")
     lib = C.CDLL(str(path))
     lib.aar_last_error.restype = C.c_char_p
+    a, b = C.c_int(0), C.c_int(0)
+    lib.aar_abi_sizes(C.byref(a), C.byref(b))
+    if (a.value, b.value) != (C.sizeof(AarLayout), C.sizeof(AarRankParams)):
+        raise AarError(f"{path} was built from a different header: AarLayout {a.value} vs {C.sizeof(AarLayout)} bytes, "
+                       f"AarRankParams {b.value} vs {C.sizeof(AarRankParams)} bytes -- rebuild (python -m akka_allreduce_b200.utils.build)")
     P = C.POINTER
     sigs = {
         "aar_layout_compute": [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, P(AarLayout)],

@@ -53,8 +53,11 @@ class RoundEngine:
         p.flags = (L.FLAG_NORMALIZE if normalize else 0) | (L.FLAG_EXACT_QUORUM if exact_quorum else 0)
         # Opt-in until it has run on hardware (docs/PROTOCOL.md, "Known limits"): with a partial quorum the broadcast waits
         # for / skips destinations exactly like the scatter does.  Full thresholds never need it.
-        if os.environ.get("AAR_BCAST_FC", "0") not in ("", "0") and (p.minRequired < layout.P or p.minChunksRequired < layout.totalChunks):
+        strict = os.environ.get("AAR_STRICT", "0") not in ("", "0")
+        if (strict or os.environ.get("AAR_BCAST_FC", "0") not in ("", "0")) and (p.minRequired < layout.P or p.minChunksRequired < layout.totalChunks):
             p.flags |= L.FLAG_BCAST_FC
+        if strict and p.minChunksRequired >= layout.totalChunks:   # eager gather: one decision per chunk (no half-flushed chunks)
+            p.flags |= L.FLAG_EAGER_DEC
         p.timeoutNs = int(timeout_ms * 1e6)
         dev_addr = C.cast(dev, C.c_void_p).value
         p.doorbell = dev_addr            # word 0: newest round announced by the master

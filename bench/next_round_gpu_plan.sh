@@ -18,15 +18,17 @@ one)
   timeout 300 python bench.py --steps 30 --warmup 5 | tee gpurun_out/r2_bench_n1.json
   ;;
 two)
-  # 2. real peers: regular multi-GPU suite, then the same suite with the flow-controlled broadcast switched on
+  # 2. real peers: regular multi-GPU suite, then the same suite with the strict variants switched on (AAR_STRICT=1: broadcast
+  #    flow control at thresholds < 1, one eager-gather decision per chunk at thresholds = 1)
   timeout 600 python -m pytest tests/test_gpu_multi.py -x -q -m gpu 2>&1 | tail -5 | tee gpurun_out/r2_multi.txt
-  AAR_BCAST_FC=1 timeout 600 python -m pytest tests/test_gpu_multi.py -x -q -m gpu 2>&1 | tail -5 | tee gpurun_out/r2_multi_fc.txt
+  AAR_STRICT=1 timeout 600 python -m pytest tests/test_gpu_multi.py -x -q -m gpu 2>&1 | tail -5 | tee gpurun_out/r2_multi_fc.txt
   ;;
 eight)
   # 3. does the flow control cost anything in straggler mode?  then the knobs that were added blind
   TR 8 29611 bench/straggler_bench.py 2>&1 | grep "^{" | tee gpurun_out/r2_straggler_default.json
-  AAR_BCAST_FC=1 TR 8 29612 bench/straggler_bench.py 2>&1 | grep "^{" | tee gpurun_out/r2_straggler_fc.json
+  AAR_STRICT=1 TR 8 29612 bench/straggler_bench.py 2>&1 | grep "^{" | tee gpurun_out/r2_straggler_fc.json
   TR 8 29613 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8.json
+  AAR_STRICT=1 TR 8 29616 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8_strict.json
   TR 8 29614 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e --stage-input 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8_stage_input.json
   for ctas in 48:4 48:6 48:8 32:8 64:8; do
     TR 8 29615 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e --no-nccl --nvls-ctas $ctas 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8_ctas_${ctas/:/_}.json

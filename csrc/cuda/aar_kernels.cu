@@ -612,7 +612,14 @@ __device__ void phaseGather(const AarRankParams& p, const AarLayout& l, int cta,
 // Eager gather (thComplete = 1.0 only): every chunk is required, so nothing has to be decided -- a CTA copies chunk
 // (owner, c) as soon as its ReduceBlock flag lands, while other chunks are still in flight.  A chunk that never shows
 // up (host-forced round, device timeout) is zero-filled like in phaseGather.
-template <typename T>
+//
+// kStrict (AAR_FLAG_EAGER_DEC): the segments of one chunk are copied by different CTAs, each with its own wait.  When a
+// wait gives up, a CTA that looked earlier may zero-fill its segment while one that looks later sees the flag and copies:
+// the chunk comes out half and half (found by csrc/tests/protocol_litmus.cpp, `eagerDecision`).  The strict variant takes
+// ONE decision per (round, chunk) in a CAS word -- "arrived with this count" or "abandoned" -- made by the first CTA that
+// stops waiting and adopted by everybody else; a ReduceBlock that lands after an "abandoned" is ignored, like a late
+// ScatterBlock after the contributor decision.  A separate instantiation: the default path compiles unchanged.
+template <typename T, bool kStrict = false>
 __device__ void phaseGatherEager(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm) {
   const int P = l.P, C = l.C;
   const int slot = p.round % l.L;
@@ -639,7 +646,17 @@ __device__ void phaseGatherEager(const AarRankParams& p, const AarLayout& l, int
         Deadline dl(p.timeoutNs);
         unsigned spins = 0, backoff = 32;
         int cnt = -1;
-        for (;;) {
+        uint64_t* dec = reinterpret_cast<uint64_t*>(my + l.egDecOff) + (long long)slot * P * C + key;
+        uint64_t d = 0;
+        bool decided = false;
+        if (kStrict) {
+          d = ld_acquire_gpu_u64(dec);
+          if ((d >> 32) == epoch) {  // somebody already stopped waiting for this chunk: adopt
+            cnt = (int)(d & 0xffffffffu) - 1;
+            decided = true;
+          }
+        }
+        while (!decided) {
           const uint64_t f = ld_relaxed_sys_u64(flags + key);
           if ((f >> 32) == epoch) {
             cnt = (int)(f & 0xffffffffu);
@@ -656,6 +673,16 @@ __device__ void phaseGatherEager(const AarRankParams& p, const AarLayout& l, int
           if (backoff < 512) backoff *= 2;
         }
         __threadfence_system();
+        if (kStrict && !decided) {
+          // the fence above is the acquire for the flag and, being cumulative, the release for the word below: a CTA
+          // that adopts "arrived" through the word also sees the owner's data
+          const uint64_t want = (epoch << 32) | (uint64_t)(uint32_t)(cnt + 1);
+          const uint64_t old = atomicCAS(reinterpret_cast<unsigned long long*>(dec), (unsigned long long)d, (unsigned long long)want);
+          if (old != d && (old >> 32) == epoch) {
+            cnt = (int)(old & 0xffffffffu) - 1;
+            __threadfence();
+          }
+        }
         sm.gKey = key;
         sm.gCnt = cnt;
         if (s == 0 && p.outCounts) p.outCounts[key] = cnt < 0 ? 0 : cnt;
@@ -790,7 +817,7 @@ __global__ void __launch_bounds__(kThreads, 1) p2pPipelinedKernel(const AarRankP
   } else {
     const int cta = b - nPush - nReduce, n = nctas - nPush - nReduce;
     if (p.minChunksRequired >= l.totalChunks && !(p.flags & AAR_FLAG_FORCE)) {
-      phaseGatherEager<T>(p, l, cta, n, sm);
+      phaseGatherEager<T, kFC>(p, l, cta, n, sm);
       traceMark(p, l, 4);
     } else {
       phaseGatherBody<T>(p, l, cta, n, sm);
@@ -807,7 +834,7 @@ __global__ void __launch_bounds__(kThreads, 1) p2pPipelinedKernel(const AarRankP
 //   CTAs [nStage, nStage + nReduce)   in-switch reduce + multicast store of my block (few CTAs saturate NVLS: measured
 //                                     multimem throughput does not grow beyond ~8-16 CTAs, profiles/r1_link_bench_8gpu.json)
 //   the rest                          copy every reduced chunk to the caller's output as soon as its flag lands
-template <typename T>
+template <typename T, bool kStrict = false>
 __global__ void __launch_bounds__(kThreads, 1) nvlsPipelinedKernel(const AarRankParams p, const AarLayout l, int split) {
   __shared__ Smem sm;
   initSmem(sm);
@@ -822,7 +849,7 @@ __global__ void __launch_bounds__(kThreads, 1) nvlsPipelinedKernel(const AarRank
     phaseReduceBcast<T, true>(p, l, b - nStage, nReduce, sm);
     traceMark(p, l, 3);
   } else {
-    phaseGatherEager<T>(p, l, b - nStage - nReduce, nctas - nStage - nReduce, sm);
+    phaseGatherEager<T, kStrict>(p, l, b - nStage - nReduce, nctas - nStage - nReduce, sm);
     traceMark(p, l, 4);
   }
   retireRound(p, l, nctas);
@@ -972,7 +999,7 @@ AAR_API int aar_launch_round_pipelined(const AarRankParams* p, const AarLayout* 
   if (nPush < 1) nPush = 1;
   if (nReduce < 1) nReduce = 1;
   const int sp = nPush | (nReduce << 16);
-  if (p->flags & AAR_FLAG_BCAST_FC) {
+  if (p->flags & (AAR_FLAG_BCAST_FC | AAR_FLAG_EAGER_DEC)) {  // strict variants do both (each only matters in its own regime)
     if (lay->dtype == AAR_F32) return launch(p2pPipelinedKernel<float, true>, p, lay, g, stream, what, sp);
     if (lay->dtype == AAR_BF16) return launch(p2pPipelinedKernel<__nv_bfloat16, true>, p, lay, g, stream, what, sp);
   }
@@ -1033,6 +1060,10 @@ AAR_API int aar_launch_nvls(const AarRankParams* p, const AarLayout* lay, int ph
     if (nReduce > g / 3) nReduce = g / 3;
     if (nStage + nReduce >= g) nStage = g - nReduce - 1;
     const int sp = nStage | (nReduce << 16);
+    if (p->flags & AAR_FLAG_EAGER_DEC) {
+      if (lay->dtype == AAR_F32) return launch(nvlsPipelinedKernel<float, true>, p, lay, g, stream, what, sp);
+      if (lay->dtype == AAR_BF16) return launch(nvlsPipelinedKernel<__nv_bfloat16, true>, p, lay, g, stream, what, sp);
+    }
     if (lay->dtype == AAR_F32) return launch(nvlsPipelinedKernel<float>, p, lay, g, stream, what, sp);
     if (lay->dtype == AAR_BF16) return launch(nvlsPipelinedKernel<__nv_bfloat16>, p, lay, g, stream, what, sp);
     return aar_host::fail(AAR_EINVAL, "%s: unknown dtype %d", what, lay->dtype);

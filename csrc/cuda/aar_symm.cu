@@ -60,6 +60,12 @@ CUmemAllocationProp deviceProp(int device) {
 
 AAR_API const char* aar_last_error(void) { return aar_host::g_lastError.c_str(); }
 
+AAR_API int aar_abi_sizes(int* layoutBytes, int* rankParamsBytes) {
+  if (layoutBytes) *layoutBytes = (int)sizeof(AarLayout);
+  if (rankParamsBytes) *rankParamsBytes = (int)sizeof(AarRankParams);
+  return AAR_OK;
+}
+
 AAR_API int aar_layout_compute(int P, int dataSize, int maxChunkSize, int maxLag, int dtype, int oneshotMaxElems, int withStage,
                                AarLayout* out) {
   if (!out) return fail(AAR_EINVAL, "aar_layout_compute: null output");
@@ -114,6 +120,7 @@ AAR_API int aar_layout_compute(int P, int dataSize, int maxChunkSize, int maxLag
   l.oneshotFlagOff = take((uint64_t)l.L * AAR_MAXP * 4);
   l.barrierOff = take(8 * 4 * 16);
   l.traceOff = take((uint64_t)AAR_TRACE_CTAS * AAR_TRACE_MARKS * 8);
+  l.egDecOff = take((uint64_t)l.L * P * l.C * 8);  // last: every older offset stays where it was
   l.regionBytes = alignUp(off, 2ull << 20);
   *out = l;
   return AAR_OK;

@@ -12,7 +12,15 @@
 // Checks per run: no TSAN report; every flushed vector equals the peer-index-ordered fp32 sum over exactly the
 // contributor set its owner decided (bit-exact); with thresholds = 1 that set is everybody; counts match; no deadlock.
 //
+// Degraded mode (`lagger` = 1): one rank is slow in EVERY round, so it falls out of the maxLag window.  That exercises what the
+// straggler-free runs never touch: waits that give up (the device-side form of the catch-up loop: a peer is known to have
+// retired a round more than maxLag ahead, or a spin budget standing in for the %globaltimer deadline), pushes that are
+// dropped by the per-destination decide-once word, the broadcast adopting those decisions, forced chunk decisions over
+// an incomplete contributor set, and gathers that zero-fill what never arrived.  Extra check there: a chunk is flushed
+// either whole or as zeros, never half and half (`eagerDecision` = 0 reproduces that hole in the eager gather).
+//
 //   protocol_litmus [seed] [P] [rounds] [thresholdPercent] [maxLag] [overlap 0|1] [ctasPerKernel] [bcastFlowControl 0|1]
+//                   [lagger 0|1] [eagerDecision 0|1] [spinBudget]
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -51,7 +59,10 @@ struct Config {
   int rounds = 12;
   int minRequired = 4, minChunks = 12;
   bool overlap = true;
-  bool bcastFlowControl = true;    // K2 also waits for the destination to have retired the slot's previous tenant
+  bool bcastFlowControl = true;    // K2 adopts K1's per-destination decision (wait for the slot, or skip a dropped destination)
+  bool lagger = false;             // rank 0 is slow in every round: degraded-mode paths (give-ups, drops, forced decisions)
+  bool eagerDecision = true;       // eager gather: one decision per (round, chunk) shared by all CTAs (proposed fix)
+  int spinBudget = 4000;           // stand-in for the %globaltimer deadline of a wait
   unsigned seed = 1;
   int blockLen() const { return C * chunkLen; }
   int dataSize() const { return P * blockLen(); }
@@ -63,6 +74,8 @@ struct Region {
   std::vector<std::atomic<uint64_t>> rflag;           // [L][P][C]
   std::vector<std::atomic<uint32_t>> peerBase;        // [P]
   std::vector<std::atomic<uint32_t>> k1Ctr;           // [L][P][C]
+  std::vector<std::atomic<uint64_t>> k1Dec;           // [L][P]   epoch << 32 | go
+  std::vector<std::atomic<uint64_t>> egDec;           // [L][P*C] epoch << 32 | (count + 1), 0 = abandoned   (eager gather)
   std::vector<std::atomic<uint64_t>> k2Dec;           // [L][C]
   std::vector<std::atomic<uint32_t>> k2Ctr;           // [L][C]
   std::vector<std::atomic<uint64_t>> k3Dec;           // [L]
@@ -74,7 +87,8 @@ struct Region {
   std::vector<std::vector<int>> outCounts;            // [L][P*C]
   explicit Region(const Config& c)
       : scatter((size_t)c.L * c.P * c.blockLen()), reduce((size_t)c.L * c.P * c.blockLen()), sflag((size_t)c.L * c.C * c.P),
-        rflag((size_t)c.L * c.P * c.C), peerBase(c.P), k1Ctr((size_t)c.L * c.P * c.C), k2Dec((size_t)c.L * c.C), k2Ctr((size_t)c.L * c.C),
+        rflag((size_t)c.L * c.P * c.C), peerBase(c.P), k1Ctr((size_t)c.L * c.P * c.C), k1Dec((size_t)c.L * c.P),
+        egDec((size_t)c.L * c.P * c.C), k2Dec((size_t)c.L * c.C), k2Ctr((size_t)c.L * c.C),
         k3Dec(c.L), k3Ctr(c.L), counts((size_t)c.L * c.P * c.C), consumed(c.L), output(c.L, std::vector<float>(c.dataSize())),
         outCounts(c.L, std::vector<int>(c.P * c.C)) {
     for (auto& x : consumed) x.store(-1);
@@ -86,6 +100,7 @@ struct World {
   std::vector<Region*> region;
   std::vector<std::vector<std::vector<float>>> input;  // [round][rank][dataSize]
   std::atomic<long> failures{0};
+  std::atomic<long> drops{0}, forcedChunks{0}, forcedRounds{0}, abandoned{0};  // how often the degraded paths ran
 };
 
 float inputValue(int round, int rank, int i) { return (float)((round * 131 + rank * 17 + i * 7) % 1000) * 0.125f + (float)rank; }
@@ -94,6 +109,40 @@ void jitter(std::mt19937& rng) {
   unsigned v = rng() % 64;
   if (v == 0) std::this_thread::sleep_for(std::chrono::microseconds(rng() % 200));
   else if (v < 8) std::this_thread::yield();
+}
+
+// forcedByHost without a host: a peer is known to have retired a round more than maxLag ahead of this one
+bool forced(World& w, int rank, int round) {
+  const Config& c = w.cfg;
+  int newestDone = -1;
+  for (int j = 0; j < c.P; ++j) newestDone = std::max(newestDone, (int)w.region[rank]->peerBase[j].load(std::memory_order_relaxed) - 1);
+  return newestDone - round > c.L - 1;
+}
+
+// One go / drop decision per (round, dest), shared by every CTA of the rank (scatterDecision in aar_kernels.cu)
+bool scatterDecision(World& w, int rank, int round, int dest) {
+  const Config& c = w.cfg;
+  if (round < c.L) return true;
+  Region& my = *w.region[rank];
+  std::atomic<uint64_t>& word = my.k1Dec[(size_t)(round % c.L) * c.P + dest];
+  const uint64_t epoch = (uint64_t)round + 1;
+  uint64_t v = word.load(std::memory_order_acquire);
+  if ((v >> 32) == epoch) return v & 1;
+  uint64_t go = 1;
+  int spins = 0;
+  while ((int)my.peerBase[dest].load(std::memory_order_acquire) < round - c.L + 1) {
+    if ((++spins & 63) == 0 && (forced(w, rank, round) || spins > c.spinBudget)) {
+      go = 0;  // the peer fell out of the window: its copy of this contribution is dropped
+      w.drops++;
+      break;
+    }
+    std::this_thread::yield();
+  }
+  if (!word.compare_exchange_strong(v, (epoch << 32) | go, std::memory_order_acq_rel, std::memory_order_acquire)) {
+    if ((v >> 32) == epoch) return v & 1;
+    w.failures++;
+  }
+  return go != 0;
 }
 
 // ---------------------------------------------------------------------------------------------- K1 scatter_push
@@ -108,9 +157,8 @@ void phaseScatter(World& w, int rank, int round, int cta, int nctas, std::mt1993
     const int i = (int)(idx % c.P), s = (int)((idx / c.P) % c.S), ch = (int)(idx / ((long)c.S * c.P));
     const int dest = (i + rank) % c.P;
     Region& peer = *w.region[dest];
-    // flow control: the previous tenant of this slot at `dest` must be retired
-    if (round >= c.L)
-      while ((int)my.peerBase[dest].load(std::memory_order_acquire) < round - c.L + 1) std::this_thread::yield();
+    // flow control: the previous tenant of this slot at `dest` must be retired -- or the push is dropped
+    if (!scatterDecision(w, rank, round, dest)) continue;
     jitter(rng);
     const float* src = w.input[round][rank].data() + dest * c.blockLen() + ch * c.chunkLen + s * segLen;
     float* dst = peer.scatter.data() + ((size_t)(slot * c.P + rank) * c.blockLen()) + ch * c.chunkLen + s * segLen;
@@ -133,11 +181,19 @@ unsigned chunkDecision(World& w, int rank, int round, int ch, std::mt19937& rng)
   uint64_t v = word.load(std::memory_order_acquire);
   if ((v >> 32) == epoch) return (unsigned)v;
   unsigned arrived = 0;
+  int spins = 0;
   for (;;) {
     arrived = 0;
     for (int src = 0; src < c.P; ++src)
       if (my.sflag[(size_t)(slot * c.C + ch) * c.P + src].load(std::memory_order_acquire) == (uint32_t)epoch) arrived |= 1u << src;
     if (__builtin_popcount(arrived) >= c.minRequired) break;
+    if ((++spins & 31) == 0 && (forced(w, rank, round) || spins > c.spinBudget)) {
+      w.forcedChunks++;
+      arrived = 0;  // forced: one more look so the snapshot is as fresh as the decision, then go with what is there
+      for (int src = 0; src < c.P; ++src)
+        if (my.sflag[(size_t)(slot * c.C + ch) * c.P + src].load(std::memory_order_acquire) == (uint32_t)epoch) arrived |= 1u << src;
+      break;
+    }
     jitter(rng);
     std::this_thread::yield();
   }
@@ -156,16 +212,22 @@ void phaseReduce(World& w, int rank, int round, int cta, int nctas, std::mt19937
   const uint64_t epoch = (uint64_t)round + 1;
   Region& my = *w.region[rank];
   const int segLen = c.chunkLen / c.S;
+  // Flow control for the broadcast.  With thresholds < 1 an owner can reduce round R over a quorum that does not contain
+  // a lagging peer and would then overwrite that peer's reduce-ring slot while it still gathers round R - L (found by
+  // this model: data race between the store below and copyChunk).  So the broadcast adopts the scatter's per-destination
+  // decision: it waits for it like a push CTA would, and leaves a dropped destination alone (bcastDestMask in the kernels).
+  unsigned destMask = ~0u;
+  if (c.bcastFlowControl && cta < (long)c.C * c.S) {
+    destMask = 0;
+    for (int i = 0; i < c.P; ++i) {
+      const int d = (i + rank) % c.P;
+      if (d == rank || scatterDecision(w, rank, round, d)) destMask |= 1u << d;
+    }
+  }
   for (long idx = cta; idx < (long)c.C * c.S; idx += nctas) {
     const int s = (int)(idx % c.S), ch = (int)(idx / c.S);
     const unsigned mask = chunkDecision(w, rank, round, ch, rng);
     const int count = __builtin_popcount(mask);
-    // Flow control for the broadcast.  With thresholds < 1 an owner can reduce round R over a quorum that does not contain
-    // a lagging peer and would then overwrite that peer's reduce-ring slot while it still gathers round R - L (found by
-    // this model: data race between the store below and copyChunk).  So the broadcast obeys the same rule as the scatter.
-    if (c.bcastFlowControl && round >= c.L)
-      for (int d = 0; d < c.P; ++d)
-        while ((int)my.peerBase[d].load(std::memory_order_acquire) < round - c.L + 1) std::this_thread::yield();
     jitter(rng);
     for (int k = 0; k < segLen; ++k) {
       const int e = ch * c.chunkLen + s * segLen + k;
@@ -173,15 +235,19 @@ void phaseReduce(World& w, int rank, int round, int cta, int nctas, std::mt19937
       for (int src = 0; src < c.P; ++src)
         if (mask >> src & 1) acc += my.scatter[(size_t)(slot * c.P + src) * c.blockLen() + e];
       for (int i = 0; i < c.P; ++i) {
-        Region& peer = *w.region[(i + rank) % c.P];
-        peer.reduce[(size_t)(slot * c.P + rank) * c.blockLen() + e] = acc;
+        const int d = (i + rank) % c.P;
+        if (!(destMask >> d & 1)) continue;
+        w.region[d]->reduce[(size_t)(slot * c.P + rank) * c.blockLen() + e] = acc;
       }
     }
     std::atomic<uint32_t>& ctr = my.k2Ctr[(size_t)slot * c.C + ch];
     if (ctr.fetch_add(1, std::memory_order_acq_rel) + 1 == (uint32_t)c.S) {  // last segment: publish the ReduceBlock + count
       ctr.store(0, std::memory_order_relaxed);
-      for (int i = 0; i < c.P; ++i)
-        w.region[(i + rank) % c.P]->rflag[(size_t)(slot * c.P + rank) * c.C + ch].store((epoch << 32) | (uint64_t)count, std::memory_order_release);
+      for (int i = 0; i < c.P; ++i) {
+        const int d = (i + rank) % c.P;
+        if (!(destMask >> d & 1)) continue;  // no data was written there: no flag either
+        w.region[d]->rflag[(size_t)(slot * c.P + rank) * c.C + ch].store((epoch << 32) | (uint64_t)count, std::memory_order_release);
+      }
     }
   }
 }
@@ -210,11 +276,16 @@ void phaseGather(World& w, int rank, int round, int cta, int nctas, std::mt19937
     bool leader = false;
     if (v != busy && v != done) leader = word.compare_exchange_strong(v, busy, std::memory_order_acq_rel, std::memory_order_acquire);
     if (leader) {
+      int spins = 0;
       for (;;) {
         int n = 0;
         for (int i = 0; i < c.P * c.C; ++i)
           if ((my.rflag[(size_t)slot * c.P * c.C + i].load(std::memory_order_acquire) >> 32) == epoch) ++n;
         if (n >= c.minChunks) break;
+        if ((++spins & 31) == 0 && (forced(w, rank, round) || spins > c.spinBudget)) {
+          w.forcedRounds++;
+          break;
+        }
         jitter(rng);
         std::this_thread::yield();
       }
@@ -233,10 +304,37 @@ void phaseGather(World& w, int rank, int round, int cta, int nctas, std::mt19937
     const int s = (int)(idx % c.S), owner = ((int)((idx / c.S) % c.P) + rank) % c.P, ch = (int)(idx / ((long)c.S * c.P));
     int cnt;
     if (eager) {
-      uint64_t f;
-      while (((f = my.rflag[(size_t)(slot * c.P + owner) * c.C + ch].load(std::memory_order_acquire)) >> 32) != epoch) std::this_thread::yield();
-      cnt = (int)(uint32_t)f;
-      if (s == 0) my.outCounts[slot][owner * c.C + ch] = cnt;
+      const int key = owner * c.C + ch;
+      std::atomic<uint64_t>& dec = my.egDec[(size_t)slot * c.P * c.C + key];
+      uint64_t d = c.eagerDecision ? dec.load(std::memory_order_acquire) : 0;
+      if (c.eagerDecision && (d >> 32) == epoch) {
+        cnt = (int)(uint32_t)d - 1;
+        if (cnt >= 0) (void)my.rflag[(size_t)(slot * c.P + owner) * c.C + ch].load(std::memory_order_acquire);  // acquire the data
+      } else {
+        uint64_t f;
+        int spins = 0;
+        cnt = -1;
+        for (;;) {
+          f = my.rflag[(size_t)(slot * c.P + owner) * c.C + ch].load(std::memory_order_acquire);
+          if ((f >> 32) == epoch) {
+            cnt = (int)(uint32_t)f;
+            break;
+          }
+          if ((++spins & 31) == 0 && (forced(w, rank, round) || spins > c.spinBudget)) {  // give up: zero-fill
+            w.abandoned++;
+            break;
+          }
+          std::this_thread::yield();
+        }
+        if (c.eagerDecision) {  // first CTA to stop waiting decides for everybody: arrived with this count, or abandoned
+          if (!dec.compare_exchange_strong(d, (epoch << 32) | (uint64_t)(cnt + 1), std::memory_order_acq_rel, std::memory_order_acquire)) {
+            if ((d >> 32) != epoch) w.failures++;
+            cnt = (int)(uint32_t)d - 1;
+            if (cnt >= 0) (void)my.rflag[(size_t)(slot * c.P + owner) * c.C + ch].load(std::memory_order_acquire);
+          }
+        }
+      }
+      if (s == 0) my.outCounts[slot][key] = cnt < 0 ? 0 : cnt;
     } else {
       cnt = my.counts[(size_t)slot * c.P * c.C + owner * c.C + ch];
     }
@@ -296,6 +394,9 @@ int main(int argc, char** argv) {
   c.overlap = argc > 6 ? atoi(argv[6]) != 0 : true;
   c.G = argc > 7 ? atoi(argv[7]) : 4;
   c.bcastFlowControl = argc > 8 ? atoi(argv[8]) != 0 : true;
+  c.lagger = argc > 9 ? atoi(argv[9]) != 0 : false;
+  c.eagerDecision = argc > 10 ? atoi(argv[10]) != 0 : true;
+  c.spinBudget = argc > 11 ? atoi(argv[11]) : 4000;
   c.minRequired = std::max(1, (int)((float)thPct / 100.f * (float)c.P));
   c.minChunks = std::max(1, (int)((float)thPct / 100.f * (float)(c.P * c.C)));
   if (c.L < 2) c.overlap = false;
@@ -321,6 +422,7 @@ int main(int argc, char** argv) {
             if (round >= cf.L)
               while (w.region[rank]->consumed[round % cf.L].load(std::memory_order_acquire) != round - cf.L) std::this_thread::yield();
             if (rank == (round % cf.P) && (rng() % 3 == 0)) std::this_thread::sleep_for(std::chrono::microseconds(300));  // straggler
+            if (cf.lagger && rank == 0 && cta == 0) std::this_thread::sleep_for(std::chrono::microseconds(1500 + rng() % 2000));
             phaseScatter(w, rank, round, cta, cf.G, rng);
             phaseReduce(w, rank, round, cta, cf.G, rng);
             phaseGather(w, rank, round, cta, cf.G, rng);
@@ -338,7 +440,9 @@ int main(int argc, char** argv) {
     }
   for (auto& t : threads) t.join();
   long bad = w.failures.load();
-  printf("protocol_litmus seed=%u P=%d rounds=%d th=%d%% L=%d overlap=%d G=%d: failures=%ld\n", c.seed, c.P, c.rounds, thPct, c.L, (int)c.overlap,
-         c.G, bad);
+  printf("protocol_litmus seed=%u P=%d rounds=%d th=%d%% L=%d overlap=%d G=%d fc=%d lagger=%d eagerDecision=%d: failures=%ld"
+         " (drops=%ld forcedChunks=%ld forcedRounds=%ld abandoned=%ld)\n", c.seed, c.P,
+         c.rounds, thPct, c.L, (int)c.overlap, c.G, (int)c.bcastFlowControl, (int)c.lagger, (int)c.eagerDecision, bad, w.drops.load(),
+         w.forcedChunks.load(), w.forcedRounds.load(), w.abandoned.load());
   return bad == 0 ? 0 : 1;
 }

@@ -34,6 +34,9 @@ extern "C" {
 #define AAR_FLAG_SKIP_SCATTER 8u /* fused kernel: this rank contributes nothing this round (fault injection) */
 #define AAR_FLAG_VIEW_OUTPUT 16u /* K3 does not copy: the caller reads the reduce-ring slot itself, stream-ordered */
 #define AAR_FLAG_OVERLAPPED 64u /* consecutive rounds of this rank run on different streams: retire strictly in order */
+#define AAR_FLAG_EAGER_DEC 256u /* thComplete = 1: the eager gather takes ONE decision per (round, chunk) -- arrived with this count, or
+                                   abandoned -- so a wait that gives up can never leave a chunk half copied, half zero-filled
+                                   (docs/PROTOCOL.md "Known limits"); opt-in until verified on hardware */
 #define AAR_FLAG_BCAST_FC 128u  /* thresholds < 1: the reduce-broadcast adopts the scatter's per-destination slot flow control
                                    (docs/PROTOCOL.md "Known limits"); opt-in until verified on hardware */
 #define AAR_FLAG_TRACE 32u      /* every CTA stamps %globaltimer at its phase boundaries into the trace section */
@@ -72,6 +75,7 @@ typedef struct AarLayout {
   uint64_t traceOff;         /* u64 [AAR_TRACE_CTAS][AAR_TRACE_MARKS] phase timestamps (AAR_FLAG_TRACE) */
   uint64_t ctrlBytes;        /* first byte of the control area that must be zeroed at allocation */
   uint64_t regionBytes;      /* total, rounded up to 2 MiB */
+  uint64_t egDecOff;         /* u64 [L][P][C]                   local: eager gather, epoch<<32 | count+1 (0 = abandoned); AAR_FLAG_EAGER_DEC */
 } AarLayout;
 
 /* Per-rank launch parameters (passed to the kernels by value). */
@@ -93,6 +97,9 @@ typedef struct AarRankParams {
 } AarRankParams;
 
 const char* aar_last_error(void);
+/* sizeof(AarLayout) / sizeof(AarRankParams) as this library was compiled: language bindings compare them with their own
+   declarations before the first call (a field added on one side only would otherwise corrupt memory silently). */
+int aar_abi_sizes(int* layoutBytes, int* rankParamsBytes);
 
 /* Geometry -> layout.  maxLag >= 0; dtype AAR_F32 | AAR_BF16; oneshotMaxElems = 0 disables the one-shot buffers;
  * withStage != 0 adds the NVLS staging area. */

