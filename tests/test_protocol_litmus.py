@@ -11,8 +11,9 @@ What is pinned:
   * degraded mode -- one rank slow in every round plus tiny wait budgets, so pushes are dropped, chunk and round decisions are
     forced over incomplete sets and the gather gives up on chunks: race-free, bit-exact over the decided sets, and every chunk
     flushed whole or as zeros, PROVIDED the broadcast adopts the scatter's per-destination decision (AAR_FLAG_BCAST_FC, as
-    written in aar_kernels.cu) and the eager gather decides once per chunk (not in the kernels yet: second hole found by this
-    model, `eagerDecision` = 0 reproduces half-flushed chunks at thresholds = 1 when a wait gives up).
+    written in aar_kernels.cu) and the eager gather decides once per chunk (AAR_FLAG_EAGER_DEC; second hole found by this model,
+    `eagerDecision` = 0 reproduces half-flushed chunks at thresholds = 1 when a wait gives up).  Both fixes are opt-in kernel
+    variants until they have run on hardware (AAR_STRICT=1).
 """
 import shutil
 import subprocess
