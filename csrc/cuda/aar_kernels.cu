@@ -420,7 +420,14 @@ __device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int
     const int count = __popc(mask);
     const int n = min(segElems, clen - off);
     const long long outElemOff = ((long long)slot * P + p.rank) * l.blkStride + (long long)c * l.maxChunk + off;
-    if (kNvls) {
+    // Strict NVLS: a decision that was forced over an incomplete set cannot be honoured by the switch (it would add the
+    // absent ranks' stale staging slots to the sum while `count` says they are not in it).  Such a chunk is not published
+    // at all: every rank's gather gives up on it and flushes zeros with count 0 -- "never arrived" -- instead of a sum
+    // that does not match its count.
+    const bool nvlsIncomplete = kNvls && kFC && count != P;
+    if (nvlsIncomplete) {
+      // nothing to move
+    } else if (kNvls) {
       // the switch sums every bound GPU: only valid when all P contributed (the launcher enforces thresholds = 1)
       const char* mcStage = reinterpret_cast<const char*>(p.mcRegion) + l.stageOff +
                             ((long long)slot * paddedData(l) + blockStart(l, p.rank) + (long long)c * l.maxChunk + off) * sizeof(T);
@@ -441,7 +448,7 @@ __device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int
         atomicExch(ctr, 0u);
         __threadfence_system();
         const uint64_t word = (epoch << 32) | (uint64_t)count;
-        for (int i2 = 0; i2 < P; ++i2) {
+        for (int i2 = 0; i2 < (nvlsIncomplete ? 0 : P); ++i2) {
           const int dest = (i2 + p.rank) % P;
           if (kFC && !((destMask >> dest) & 1u)) continue;  // no data was written there: no flag either
           uint64_t* flag = reinterpret_cast<uint64_t*>(regionOf(p, dest) + l.rflagOff) + ((long long)slot * P + p.rank) * C + c;
@@ -846,7 +853,7 @@ __global__ void __launch_bounds__(kThreads, 1) nvlsPipelinedKernel(const AarRank
     phaseScatter<T, true>(p, l, b, nStage, sm, 1);
     traceMark(p, l, 1);
   } else if (b < nStage + nReduce) {
-    phaseReduceBcast<T, true>(p, l, b - nStage, nReduce, sm);
+    phaseReduceBcast<T, true, kStrict>(p, l, b - nStage, nReduce, sm);
     traceMark(p, l, 3);
   } else {
     phaseGatherEager<T, kStrict>(p, l, b - nStage - nReduce, nctas - nStage - nReduce, sm);
