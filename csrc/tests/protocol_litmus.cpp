@@ -62,7 +62,7 @@ struct Config {
   bool bcastFlowControl = true;    // K2 adopts K1's per-destination decision (wait for the slot, or skip a dropped destination)
   bool lagger = false;             // rank 0 is slow in every round: degraded-mode paths (give-ups, drops, forced decisions)
   bool eagerDecision = true;       // eager gather: one decision per (round, chunk) shared by all CTAs (proposed fix)
-  int spinBudget = 4000;           // stand-in for the %globaltimer deadline of a wait
+  int spinBudget = 1 << 30;        // stand-in for the %globaltimer deadline of a wait (default: timeoutNs = 0, unbounded)
   unsigned seed = 1;
   int blockLen() const { return C * chunkLen; }
   int dataSize() const { return P * blockLen(); }
@@ -396,7 +396,7 @@ int main(int argc, char** argv) {
   c.bcastFlowControl = argc > 8 ? atoi(argv[8]) != 0 : true;
   c.lagger = argc > 9 ? atoi(argv[9]) != 0 : false;
   c.eagerDecision = argc > 10 ? atoi(argv[10]) != 0 : true;
-  c.spinBudget = argc > 11 ? atoi(argv[11]) : 4000;
+  c.spinBudget = argc > 11 ? atoi(argv[11]) : (1 << 30);
   c.minRequired = std::max(1, (int)((float)thPct / 100.f * (float)c.P));
   c.minChunks = std::max(1, (int)((float)thPct / 100.f * (float)(c.P * c.C)));
   if (c.L < 2) c.overlap = false;
