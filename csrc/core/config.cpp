@@ -124,7 +124,11 @@ struct Parser {
         get();
         break;
       }
+      const size_t before = i;
       val.list.push_back(scalar(true));
+      // scalar() stops in front of '}' (the end of an enclosing object) without consuming it: inside a list that is a
+      // stray brace, and looping on it would append empty elements until memory runs out
+      if (i == before) fail(std::string("unexpected '") + peek() + "' in list");
     }
     return val;
   }
