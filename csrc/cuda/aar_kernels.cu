@@ -1162,7 +1162,8 @@ AAR_API int aar_local_allreduce_static(const void* const* inputs, void* const* o
   int rc = aar_layout_compute(nranks, dataSize, maxChunkSize, /*maxLag=*/0, dtype, /*oneshot=*/0, /*stage=*/0, &lay);
   if (rc) return rc;
   // bytes one emulated rank really uses (the layout's own regionBytes is padded to the 2 MiB VMM granularity)
-  const uint64_t perRank = (lay.traceOff + (uint64_t)AAR_TRACE_CTAS * AAR_TRACE_MARKS * 8 + 255) / 256 * 256;
+  // = end of the last layout section (the eager-gather decision words, appended after the trace marks)
+  const uint64_t perRank = (lay.egDecOff + (uint64_t)lay.L * lay.P * lay.C * 8 + 255) / 256 * 256;
   const uint64_t need = perRank * (uint64_t)nranks;
   if (need > (uint64_t)AAR_STATIC_SCRATCH_BYTES)
     return aar_host::fail(AAR_EINVAL,
