@@ -63,7 +63,9 @@ class GradientBucket:
 class ThresholdDDP:
     def __init__(self, module: torch.nn.Module, rank: int, world: int, device: int, *, bucket_mb: float = 32.0, max_chunk: int = 1 << 20,
                  max_lag: int = 1, th_reduce: float = 1.0, th_complete: float = 1.0, session: str = "ddp", algo: str = "auto",
-                 sink: Callable[[int, AllReduceOutput], None] | None = None):
+                 sink: Callable[[int, AllReduceOutput], None] | None = None, comm_ctas: int = 0):
+        """comm_ctas: SM budget of the gradient allreduce (CTAs per launch, one CTA occupies one SM); 0 = all SMs.  A bucket's
+        round runs while backward is still producing the next bucket, so every SM it holds is taken from the GEMMs."""
         self.module, self.rank, self.world = module, rank, world
         self.device = torch.device("cuda", device)
         self.step = 0
@@ -91,9 +93,10 @@ class ThresholdDDP:
             if world > 1:
                 lay = L.compute_layout(world, n, chunk, max_lag, code, 0, True)
                 b.symm = SymmetricMemory(UnixRendezvous(rank, world, f"{session}_b{i}"), lay.regionBytes, device, want_multicast=True)
-                b.engine = RoundEngine.from_symmetric(b.symm, lay, th_reduce=th_reduce, th_complete=th_complete, normalize=True, algo=algo)
+                b.engine = RoundEngine.from_symmetric(b.symm, lay, th_reduce=th_reduce, th_complete=th_complete, normalize=True, algo=algo,
+                                                      grid=comm_ctas)
             else:
-                b.engine = RoundEngine.single_process(n, chunk, max_lag, dtype=dtype, device=device, normalize=True)
+                b.engine = RoundEngine.single_process(n, chunk, max_lag, dtype=dtype, device=device, normalize=True, grid=comm_ctas)
             self.buckets.append(b)
         self._arm()
 

@@ -19,7 +19,8 @@ from ..ops import lib as L
 from .local_gpu import _TORCH2AAR
 
 # Measured crossover (profiles/): below this many bytes the one-hop one-shot kernel wins over two-shot.
-ONESHOT_MAX_BYTES = 256 * 1024
+# AAR_ONESHOT_MAX_BYTES overrides it (crossover sweeps; every rank must use the same value, it sizes the layout).
+ONESHOT_MAX_BYTES = int(os.environ.get("AAR_ONESHOT_MAX_BYTES", 256 * 1024))
 
 
 class RoundEngine:

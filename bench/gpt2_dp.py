@@ -24,6 +24,8 @@ ap.add_argument("--steps", type=int, default=10)
 ap.add_argument("--warmup", type=int, default=3)
 ap.add_argument("--bucket-mb", type=float, default=32.0)
 ap.add_argument("--layers", type=int, default=12)
+ap.add_argument("--comm-ctas", type=int, default=0, help="SM budget of the gradient allreduce kernels (0 = all SMs)")
+ap.add_argument("--algo", default="auto")
 a = ap.parse_args()
 rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 lr = int(os.environ.get("LOCAL_RANK", rank))
@@ -57,7 +59,7 @@ def run(impl):
     opt = torch.optim.AdamW(model.parameters(), lr=1e-4, fused=True)
     ddp = None
     if impl == "aar":
-        ddp = ThresholdDDP(model, rank, world, lr, bucket_mb=a.bucket_mb, session=sess + "_" + impl)
+        ddp = ThresholdDDP(model, rank, world, lr, bucket_mb=a.bucket_mb, session=sess + "_" + impl, comm_ctas=a.comm_ctas, algo=a.algo)
         buckets = ddp.buckets
     else:
         import torch.distributed as dist

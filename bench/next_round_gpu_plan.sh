@@ -35,3 +35,7 @@ eight)
   done
   ;;
 esac
+# Further sweeps once the above is green (each is one call; N = 8 unless noted):
+#   TR 8 P bench/sweep.py --sizes 1048576,2097152,4194304 --algos auto,pipelined,nvls --grid 32      (and 16, 64): fewer CTAs, less sync
+#   AAR_ONESHOT_MAX_BYTES=4194304 TR 8 P bench/sweep.py --sizes 262144,524288,1048576,2097152 --algos oneshot,nvls   one-shot crossover
+#   TR 4 P bench/gpt2_dp.py --comm-ctas 32   (and 16, 48, 64; --algo pipelined)                      SM budget for the DDP buckets

@@ -22,6 +22,7 @@ ap.add_argument("--sizes", default="4096,16384,65536,262144,1048576,4194304,1677
 ap.add_argument("--chunks", default="1048576", help="maxChunkSize values (elements)")
 ap.add_argument("--algos", default="auto,oneshot,twoshot,pipelined,nvls")
 ap.add_argument("--dtype", default="fp32")
+ap.add_argument("--grid", type=int, default=0, help="CTAs per launch (0 = one per SM)")
 a = ap.parse_args()
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 lr = int(os.environ.get("LOCAL_RANK", rank))
@@ -77,7 +78,7 @@ for nbytes in [int(s) for s in a.sizes.split(",")]:
         symm = SymmetricMemory(UnixRendezvous(rank, world, f"{sess}_m{k}"), lay.regionBytes, lr, want_multicast=True)
         for algo in a.algos.split(","):
             try:
-                eng = RoundEngine.from_symmetric(symm, lay, algo=algo, timeout_ms=5000.0)
+                eng = RoundEngine.from_symmetric(symm, lay, algo=algo, timeout_ms=5000.0, grid=a.grid)
             except ValueError:
                 continue
             try:
