@@ -12,6 +12,7 @@ from pathlib import Path
 AAR_MAXP = 16
 AAR_F32, AAR_BF16 = 0, 1
 FLAG_NORMALIZE, FLAG_EXACT_QUORUM, FLAG_FORCE, FLAG_SKIP_SCATTER, FLAG_VIEW_OUTPUT, FLAG_TRACE, FLAG_OVERLAPPED = 1, 2, 4, 8, 16, 32, 64
+FLAG_ELIDE_LATE = 512  # opt-in (AAR_ELIDE_LATE=1): a rank a whole round late skips work nobody will read; implies FLAG_BCAST_FC
 FLAG_EAGER_DEC = 256  # opt-in (AAR_STRICT=1): eager gather decides once per chunk (no half-flushed chunk when a wait gives up)
 FLAG_BCAST_FC = 128  # opt-in (AAR_BCAST_FC=1): reduce-broadcast obeys the slot flow control at thresholds < 1
 TRACE_CTAS, TRACE_MARKS = 512, 8

@@ -57,6 +57,8 @@ class RoundEngine:
         strict = os.environ.get("AAR_STRICT", "0") not in ("", "0")
         if (strict or os.environ.get("AAR_BCAST_FC", "0") not in ("", "0")) and (p.minRequired < layout.P or p.minChunksRequired < layout.totalChunks):
             p.flags |= L.FLAG_BCAST_FC
+        if os.environ.get("AAR_ELIDE_LATE", "0") not in ("", "0") and (p.minRequired < layout.P or p.minChunksRequired < layout.totalChunks):
+            p.flags |= L.FLAG_ELIDE_LATE | L.FLAG_BCAST_FC   # lives in the strict kernel variants
         if strict and p.minChunksRequired >= layout.totalChunks:   # eager gather: one decision per chunk (no half-flushed chunks)
             p.flags |= L.FLAG_EAGER_DEC
         p.timeoutNs = int(timeout_ms * 1e6)

@@ -23,7 +23,8 @@ _TORCH2AAR = {torch.float32: L.AAR_F32, torch.bfloat16: L.AAR_BF16}
 class LocalGpuCluster:
     def __init__(self, P: int, data_size: int, max_chunk: int, max_lag: int = 1, th_reduce: float = 1.0, th_complete: float = 1.0,
                  dtype: torch.dtype = torch.float32, normalize: bool = False, exact_quorum: bool = False, timeout_ms: float = 2000.0,
-                 device: str | torch.device = "cuda:0", grid: int = 0, oneshot: bool = False, bcast_fc: bool = False, eager_dec: bool = False):
+                 device: str | torch.device = "cuda:0", grid: int = 0, oneshot: bool = False, bcast_fc: bool = False, eager_dec: bool = False,
+                 elide_late: bool = False):
         self.lib = L.load()
         self.P, self.data_size, self.max_chunk, self.max_lag = P, data_size, max_chunk, max_lag
         self.dtype = dtype
@@ -32,7 +33,7 @@ class LocalGpuCluster:
         self.geo = core.Geometry(P, data_size, max_chunk)
         self.min_required = core.Geometry.min_required(th_reduce, P)
         self.min_chunks_required = self.geo.min_chunks_required(th_complete)
-        self.base_flags = (L.FLAG_NORMALIZE if normalize else 0) | (L.FLAG_EXACT_QUORUM if exact_quorum else 0) | (L.FLAG_BCAST_FC if bcast_fc else 0) | (L.FLAG_EAGER_DEC if eager_dec else 0)
+        self.base_flags = (L.FLAG_NORMALIZE if normalize else 0) | (L.FLAG_EXACT_QUORUM if exact_quorum else 0) | (L.FLAG_BCAST_FC if bcast_fc else 0) | (L.FLAG_EAGER_DEC if eager_dec else 0) | ((L.FLAG_ELIDE_LATE | L.FLAG_BCAST_FC) if elide_late else 0)
         self.timeout_ns = int(timeout_ms * 1e6)
         self.layout = L.compute_layout(P, data_size, max_chunk, max_lag, _TORCH2AAR[dtype], data_size if oneshot else 0, False)
         with torch.cuda.device(self.device):

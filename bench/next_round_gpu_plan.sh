@@ -27,6 +27,7 @@ eight)
   # 3. does the flow control cost anything in straggler mode?  then the knobs that were added blind
   TR 8 29611 bench/straggler_bench.py 2>&1 | grep "^{" | tee gpurun_out/r2_straggler_default.json
   AAR_STRICT=1 TR 8 29612 bench/straggler_bench.py 2>&1 | grep "^{" | tee gpurun_out/r2_straggler_fc.json
+  AAR_ELIDE_LATE=1 TR 8 29617 bench/straggler_bench.py 2>&1 | grep "^{" | tee gpurun_out/r2_straggler_elide.json
   TR 8 29613 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8.json
   AAR_STRICT=1 TR 8 29616 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8_strict.json
   TR 8 29614 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e --stage-input 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8_stage_input.json

@@ -119,9 +119,30 @@ __device__ bool scatterDecision(const AarRankParams& p, const AarLayout& l, int 
 
 // kStage = false: K1 scatter_push -- block `dest` of my input goes into peer dest's scatter ring over NVLink.
 // kStage = true : NVLS variant -- the input is staged in MY region (the switch will pull it), only the flag travels.
-template <typename T, bool kStage>
+//
+// kElide (AAR_FLAG_ELIDE_LATE, strict variants): a rank that starts a round after some peer has already RETIRED it is a
+// whole round late.  With thresholds < 1 most owners have then decided their chunks without it, and a copy nobody will
+// read only keeps the rank late.  Such a rank looks at the owner's decision word (one remote load per message segment)
+// and skips the copy when the decision excludes it.  Skipped segments still take part in the last-finisher election --
+// the counter must be back at zero when the slot is reused -- but taint the message (upper half of the counter), and a
+// tainted message is never flagged.  Modelled in csrc/tests/protocol_litmus.cpp (`elide`).
+template <typename T, bool kStage, bool kElide = false>
 __device__ void phaseScatter(const AarRankParams& p, const AarLayout& l, int cta, int nctas, Smem& sm, int unitsPerCta = 2) {
   if (p.flags & AAR_FLAG_SKIP_SCATTER) return;
+  const bool elide = kElide && !kStage && (p.flags & AAR_FLAG_ELIDE_LATE);
+  // shared words of the elision live here, not in Smem: only the strict instantiations carry them, the default kernels'
+  // shared layout and code stay exactly as measured
+  __shared__ int k1Late;   // some peer has already retired this round
+  __shared__ int k1Skip;   // current unit: its owner has decided the chunk without this rank
+  if (elide) {
+    if (threadIdx.x == 0) {
+      const uint32_t* base = reinterpret_cast<const uint32_t*>(regionOf(p, p.rank) + l.peerBaseOff);
+      int late = 0;
+      for (int j = 0; j < l.P; ++j) late |= ((int)ld_relaxed_sys_u32(base + j) > p.round) ? 1 : 0;
+      k1Late = late;
+    }
+    __syncthreads();
+  }
   const int P = l.P, C = l.C;
   const int slot = p.round % l.L;
   const uint32_t epoch = (uint32_t)(p.round + 1);
@@ -148,7 +169,18 @@ __device__ void phaseScatter(const AarRankParams& p, const AarLayout& l, int cta
     const int n = min(segElems, clen - off);
     const long long inOff = blockStart(l, dest) + (long long)c * l.maxChunk + off;
     const T* src = reinterpret_cast<const T*>(p.input) + inOff;
-    if (kStage) {
+    bool skip = false;
+    if (elide && k1Late) {  // CTA-uniform: k1Late was published before a barrier
+      if (threadIdx.x == 0) {
+        const uint64_t d = ld_relaxed_sys_u64(reinterpret_cast<const uint64_t*>(regionOf(p, dest) + l.k2DecOff) + (long long)slot * C + c);
+        k1Skip = ((d >> 32) == (uint64_t)epoch && !((d >> p.rank) & 1u)) ? 1 : 0;
+      }
+      __syncthreads();
+      skip = k1Skip != 0;
+    }
+    if (skip) {
+      // nothing to move
+    } else if (kStage) {
       if (!inPlace) copyTile<T, false, false>(stage + inOff, src, n, vecOk);
     } else {
       T* dst = reinterpret_cast<T*>(regionOf(p, dest) + l.scatterOff) + ((long long)slot * P + p.rank) * l.blkStride +
@@ -159,12 +191,24 @@ __device__ void phaseScatter(const AarRankParams& p, const AarLayout& l, int cta
     if (threadIdx.x == 0) {
       __threadfence_system();
       unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k1CtrOff) + ((long long)slot * P + dest) * C + c;
-      const unsigned old = atomicAdd(ctr, 1u);
-      if (old + 1 == plan.liveSegs(l, clen)) {  // last segment of this "ScatterBlock": publish its arrival
-        atomicExch(ctr, 0u);
-        __threadfence_system();
-        uint32_t* flag = reinterpret_cast<uint32_t*>(regionOf(p, dest) + l.sflagOff) + ((long long)slot * C + c) * AAR_MAXP + p.rank;
-        st_release_sys_u32(flag, epoch);
+      if (kElide) {
+        const unsigned old = atomicAdd(ctr, skip ? 0x10001u : 1u);
+        if ((old & 0xffffu) + 1 == plan.liveSegs(l, clen)) {
+          atomicExch(ctr, 0u);
+          if (!skip && (old >> 16) == 0) {  // no segment of this message was skipped: publish its arrival
+            __threadfence_system();
+            uint32_t* flag = reinterpret_cast<uint32_t*>(regionOf(p, dest) + l.sflagOff) + ((long long)slot * C + c) * AAR_MAXP + p.rank;
+            st_release_sys_u32(flag, epoch);
+          }
+        }
+      } else {
+        const unsigned old = atomicAdd(ctr, 1u);
+        if (old + 1 == plan.liveSegs(l, clen)) {  // last segment of this "ScatterBlock": publish its arrival
+          atomicExch(ctr, 0u);
+          __threadfence_system();
+          uint32_t* flag = reinterpret_cast<uint32_t*>(regionOf(p, dest) + l.sflagOff) + ((long long)slot * C + c) * AAR_MAXP + p.rank;
+          st_release_sys_u32(flag, epoch);
+        }
       }
     }
     // Nobody starts the next segment before the fence above has drained: the SM-wide write drain would otherwise
@@ -378,6 +422,20 @@ __device__ unsigned bcastDestMask(const AarRankParams& p, const AarLayout& l, Sm
   for (int i2 = 0; i2 < l.P; ++i2) {
     const int dest = (i2 + p.rank) % l.P;
     if (dest == p.rank || scatterDecision(p, l, dest, sm)) m |= 1u << dest;
+  }
+  if (p.flags & AAR_FLAG_ELIDE_LATE) {
+    // late-work elision: a destination that has already retired this round will never gather this rank's chunks
+    __shared__ unsigned k2Dest;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const uint32_t* base = reinterpret_cast<const uint32_t*>(regionOf(p, p.rank) + l.peerBaseOff);
+      unsigned e = m;
+      for (int d = 0; d < l.P; ++d)
+        if (d != p.rank && (int)ld_relaxed_sys_u32(base + d) > p.round) e &= ~(1u << d);
+      k2Dest = e;
+    }
+    __syncthreads();
+    m = k2Dest;
   }
   return m;
 }
@@ -795,7 +853,7 @@ __global__ void __launch_bounds__(kThreads, 1) roundKernel(const AarRankParams p
   __shared__ Smem sm;
   initSmem(sm);
   traceMark(p, l, 0);
-  if (phases & 1) phaseScatter<T, kNvls>(p, l, blockIdx.x, gridDim.x, sm);
+  if (phases & 1) phaseScatter<T, kNvls, kFC>(p, l, blockIdx.x, gridDim.x, sm);
   traceMark(p, l, 1);
   if (phases & 2) phaseReduceBcast<T, kNvls, kFC>(p, l, blockIdx.x, gridDim.x, sm);
   traceMark(p, l, 3);
@@ -816,7 +874,7 @@ __global__ void __launch_bounds__(kThreads, 1) p2pPipelinedKernel(const AarRankP
   const int nPush = split & 0xffff, nReduce = split >> 16;
   const int b = blockIdx.x;
   if (b < nPush) {
-    phaseScatter<T, false>(p, l, b, nPush, sm, 1);
+    phaseScatter<T, false, kFC>(p, l, b, nPush, sm, 1);
     traceMark(p, l, 1);
   } else if (b < nPush + nReduce) {
     phaseReduceBcast<T, false, kFC>(p, l, b - nPush, nReduce, sm, 1);
@@ -965,7 +1023,7 @@ int launch(K kernel, const AarRankParams* p, const AarLayout* l, int grid, void*
 
 int launchRound(const AarRankParams* p, const AarLayout* lay, int grid, void* stream, const char* what, int phases) {
   if (!lay) return aar_host::fail(AAR_EINVAL, "%s: null layout", what);
-  if (p && (p->flags & AAR_FLAG_BCAST_FC) && (phases & 2)) {  // opt-in: broadcast obeys the slot flow control
+  if (p && (p->flags & AAR_FLAG_BCAST_FC) && (phases & 3)) {  // opt-in: strict scatter / broadcast variants
     if (lay->dtype == AAR_F32) return launch(roundKernel<float, false, true>, p, lay, grid, stream, what, phases);
     if (lay->dtype == AAR_BF16) return launch(roundKernel<__nv_bfloat16, false, true>, p, lay, grid, stream, what, phases);
   }

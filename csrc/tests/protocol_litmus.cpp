@@ -20,7 +20,7 @@
 // either whole or as zeros, never half and half (`eagerDecision` = 0 reproduces that hole in the eager gather).
 //
 //   protocol_litmus [seed] [P] [rounds] [thresholdPercent] [maxLag] [overlap 0|1] [ctasPerKernel] [bcastFlowControl 0|1]
-//                   [lagger 0|1] [eagerDecision 0|1] [spinBudget]
+//                   [lagger 0|1] [eagerDecision 0|1] [spinBudget] [elide 0|1]
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -62,6 +62,7 @@ struct Config {
   bool bcastFlowControl = true;    // K2 adopts K1's per-destination decision (wait for the slot, or skip a dropped destination)
   bool lagger = false;             // rank 0 is slow in every round: degraded-mode paths (give-ups, drops, forced decisions)
   bool eagerDecision = true;       // eager gather: one decision per (round, chunk) shared by all CTAs (proposed fix)
+  bool elide = false;              // a rank that is a whole round late skips work nobody will read (AAR_FLAG_ELIDE_LATE)
   int spinBudget = 1 << 30;        // stand-in for the %globaltimer deadline of a wait (default: timeoutNs = 0, unbounded)
   unsigned seed = 1;
   int blockLen() const { return C * chunkLen; }
@@ -101,6 +102,7 @@ struct World {
   std::vector<std::vector<std::vector<float>>> input;  // [round][rank][dataSize]
   std::atomic<long> failures{0};
   std::atomic<long> drops{0}, forcedChunks{0}, forcedRounds{0}, abandoned{0};  // how often the degraded paths ran
+  std::atomic<long> elidedPushes{0}, elidedBcasts{0};
 };
 
 float inputValue(int round, int rank, int i) { return (float)((round * 131 + rank * 17 + i * 7) % 1000) * 0.125f + (float)rank; }
@@ -153,6 +155,11 @@ void phaseScatter(World& w, int rank, int round, int cta, int nctas, std::mt1993
   Region& my = *w.region[rank];
   const int segLen = c.chunkLen / c.S;
   const long total = (long)c.C * c.P * c.S;
+  // Late-work elision: some peer has already RETIRED this round, so this rank is at least a round behind.  Owners that
+  // have decided a chunk's contributor set without this rank will never read its copy: do not send it.
+  bool late = false;
+  if (c.elide)
+    for (int j = 0; j < c.P; ++j) late = late || (int)my.peerBase[j].load(std::memory_order_relaxed) > round;
   for (long idx = cta; idx < total; idx += nctas) {
     const int i = (int)(idx % c.P), s = (int)((idx / c.P) % c.S), ch = (int)(idx / ((long)c.S * c.P));
     const int dest = (i + rank) % c.P;
@@ -160,13 +167,25 @@ void phaseScatter(World& w, int rank, int round, int cta, int nctas, std::mt1993
     // flow control: the previous tenant of this slot at `dest` must be retired -- or the push is dropped
     if (!scatterDecision(w, rank, round, dest)) continue;
     jitter(rng);
-    const float* src = w.input[round][rank].data() + dest * c.blockLen() + ch * c.chunkLen + s * segLen;
-    float* dst = peer.scatter.data() + ((size_t)(slot * c.P + rank) * c.blockLen()) + ch * c.chunkLen + s * segLen;
-    for (int k = 0; k < segLen; ++k) dst[k] = src[k];
+    bool skip = false;
+    if (late) {  // one remote load of the owner's decision word
+      const uint64_t d = peer.k2Dec[(size_t)slot * c.C + ch].load(std::memory_order_relaxed);
+      skip = (d >> 32) == (uint64_t)epoch && !((d >> rank) & 1);
+    }
+    if (!skip) {
+      const float* src = w.input[round][rank].data() + dest * c.blockLen() + ch * c.chunkLen + s * segLen;
+      float* dst = peer.scatter.data() + ((size_t)(slot * c.P + rank) * c.blockLen()) + ch * c.chunkLen + s * segLen;
+      for (int k = 0; k < segLen; ++k) dst[k] = src[k];
+    } else {
+      w.elidedPushes++;
+    }
+    // Segments still count (the election word must be back at zero when the slot is reused); a skipped one taints the
+    // message in the upper half of the word, and a tainted message is never flagged.
     std::atomic<uint32_t>& ctr = my.k1Ctr[(size_t)(slot * c.P + dest) * c.C + ch];
-    if (ctr.fetch_add(1, std::memory_order_acq_rel) + 1 == (uint32_t)c.S) {  // last segment: publish the ScatterBlock
+    const uint32_t old = ctr.fetch_add(skip ? 0x10001u : 1u, std::memory_order_acq_rel);
+    if ((old & 0xffffu) + 1 == (uint32_t)c.S) {  // last segment: publish the ScatterBlock
       ctr.store(0, std::memory_order_relaxed);
-      peer.sflag[(size_t)(slot * c.C + ch) * c.P + rank].store(epoch, std::memory_order_release);
+      if (!skip && (old >> 16) == 0) peer.sflag[(size_t)(slot * c.C + ch) * c.P + rank].store(epoch, std::memory_order_release);
     }
   }
 }
@@ -224,6 +243,13 @@ void phaseReduce(World& w, int rank, int round, int cta, int nctas, std::mt19937
       if (d == rank || scatterDecision(w, rank, round, d)) destMask |= 1u << d;
     }
   }
+  // Late-work elision: a destination that has already retired this round will never gather this chunk
+  if (c.elide && cta < (long)c.C * c.S)
+    for (int d = 0; d < c.P; ++d)
+      if (d != rank && (int)my.peerBase[d].load(std::memory_order_acquire) > round && (destMask >> d & 1)) {
+        destMask &= ~(1u << d);
+        w.elidedBcasts++;
+      }
   for (long idx = cta; idx < (long)c.C * c.S; idx += nctas) {
     const int s = (int)(idx % c.S), ch = (int)(idx / c.S);
     const unsigned mask = chunkDecision(w, rank, round, ch, rng);
@@ -397,6 +423,7 @@ int main(int argc, char** argv) {
   c.lagger = argc > 9 ? atoi(argv[9]) != 0 : false;
   c.eagerDecision = argc > 10 ? atoi(argv[10]) != 0 : true;
   c.spinBudget = argc > 11 ? atoi(argv[11]) : (1 << 30);
+  c.elide = argc > 12 ? atoi(argv[12]) != 0 : false;
   c.minRequired = std::max(1, (int)((float)thPct / 100.f * (float)c.P));
   c.minChunks = std::max(1, (int)((float)thPct / 100.f * (float)(c.P * c.C)));
   if (c.L < 2) c.overlap = false;
@@ -441,8 +468,8 @@ int main(int argc, char** argv) {
   for (auto& t : threads) t.join();
   long bad = w.failures.load();
   printf("protocol_litmus seed=%u P=%d rounds=%d th=%d%% L=%d overlap=%d G=%d fc=%d lagger=%d eagerDecision=%d: failures=%ld"
-         " (drops=%ld forcedChunks=%ld forcedRounds=%ld abandoned=%ld)\n", c.seed, c.P,
+         " (drops=%ld forcedChunks=%ld forcedRounds=%ld abandoned=%ld elidedPushes=%ld elidedBcasts=%ld)\n", c.seed, c.P,
          c.rounds, thPct, c.L, (int)c.overlap, c.G, (int)c.bcastFlowControl, (int)c.lagger, (int)c.eagerDecision, bad, w.drops.load(),
-         w.forcedChunks.load(), w.forcedRounds.load(), w.abandoned.load());
+         w.forcedChunks.load(), w.forcedRounds.load(), w.abandoned.load(), w.elidedPushes.load(), w.elidedBcasts.load());
   return bad == 0 ? 0 : 1;
 }

@@ -34,6 +34,9 @@ extern "C" {
 #define AAR_FLAG_SKIP_SCATTER 8u /* fused kernel: this rank contributes nothing this round (fault injection) */
 #define AAR_FLAG_VIEW_OUTPUT 16u /* K3 does not copy: the caller reads the reduce-ring slot itself, stream-ordered */
 #define AAR_FLAG_OVERLAPPED 64u /* consecutive rounds of this rank run on different streams: retire strictly in order */
+#define AAR_FLAG_ELIDE_LATE 512u /* thresholds < 1: a rank that is a whole round late skips pushes whose owner has decided without it
+                                   and broadcasts to peers that have retired the round; needs the strict kernel variants (set
+                                   together with AAR_FLAG_BCAST_FC); opt-in until verified on hardware */
 #define AAR_FLAG_EAGER_DEC 256u /* thComplete = 1: the eager gather takes ONE decision per (round, chunk) -- arrived with this count, or
                                    abandoned -- so a wait that gives up can never leave a chunk half copied, half zero-filled
                                    (docs/PROTOCOL.md "Known limits"); opt-in until verified on hardware */

@@ -98,3 +98,33 @@ def test_eager_decision_matches_the_default_path_when_everything_arrives():
 
     lay = L.compute_layout(8, 1 << 20, 1 << 16, 1, L.AAR_F32, 0, True)
     assert lay.egDecOff > lay.traceOff and lay.egDecOff + lay.L * lay.P * lay.C * 8 <= lay.regionBytes
+
+
+def test_late_rank_elides_work_nobody_will_read():
+    """AAR_FLAG_ELIDE_LATE: ranks 0-2 run round 0 to the end without rank 3 (thresholds 0.75).  Rank 3 then runs the same round:
+    its pushes to owners that decided without it are skipped (their arrival flags for source 3 stay unset, its election counters
+    are back at zero), its broadcast goes to nobody but itself, and its own flushed vector is still exact: blocks of owners 0-2
+    are the sums those owners decided (sources 0-2), its own block sums all four."""
+    P, n, chunk = 4, 4096, 512
+    cl = cluster(P, n, chunk, max_lag=1, th_reduce=0.75, th_complete=0.75, elide_late=True)
+    xs = make_inputs(P, n, torch.float32, 900)
+    live = [0, 1, 2]
+    cl.run_phases(0, xs, scatter=live, reduce=live, gather=live)
+    torch.cuda.synchronize()
+    lay = cl.layout
+    rflag_before = [cl._section(r, lay.rflagOff, lay.L * lay.P * lay.C * 8, torch.int64).clone() for r in live]
+    cl.run_phases(0, xs, scatter=[3], reduce=[3], gather=[3])
+    torch.cuda.synchronize()
+    for r in live:
+        sflags = cl._section(r, lay.sflagOff, lay.L * lay.C * 16 * 4, torch.int32).view(lay.L, lay.C, 16)
+        assert int(sflags[0, :, 3].abs().sum()) == 0, "rank 3 pushed although the owner had decided without it"
+        assert torch.equal(cl._section(r, lay.rflagOff, lay.L * lay.P * lay.C * 8, torch.int64), rflag_before[r]), "late broadcast reached a retired peer"
+    ctr = cl._section(3, lay.k1CtrOff, lay.L * lay.P * lay.C * 4, torch.int32)
+    assert int(ctr.abs().sum()) == 0, "election counters must be back at zero for the slot's next tenant"
+    geo_block = n // P
+    want_others, _ = oracle(xs, P, n, chunk, lambda o, c: live, torch.float32)
+    want_own, _ = oracle(xs, P, n, chunk, lambda o, c: [0, 1, 2, 3], torch.float32)
+    out3 = cl.outputs[3]
+    assert torch.equal(out3[: 3 * geo_block], want_others[: 3 * geo_block])
+    assert torch.equal(out3[3 * geo_block:], want_own[3 * geo_block:])
+    assert cl.status(3) == 0

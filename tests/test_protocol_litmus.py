@@ -63,7 +63,9 @@ def test_partial_thresholds_are_race_free_with_broadcast_flow_control(litmus, cf
 
 # seed, P, rounds, threshold %, maxLag, overlap, CTAs per kernel, bcastFlowControl, lagger, eagerDecision, spinBudget
 DEGRADED = [(3, 4, 14, 75, 1, 1, 4, 1, 1, 1, 64), (4, 4, 14, 100, 1, 1, 4, 1, 1, 1, 64), (6, 3, 16, 60, 2, 1, 3, 1, 1, 1, 128),
-            (12, 4, 14, 75, 1, 0, 4, 1, 1, 1, 32)]
+            (12, 4, 14, 75, 1, 0, 4, 1, 1, 1, 32),
+            # ... and with late-work elision (AAR_FLAG_ELIDE_LATE): a rank a whole round late skips what nobody will read
+            (13, 5, 12, 80, 1, 1, 4, 1, 1, 1, 64, 1), (6, 3, 16, 60, 2, 1, 3, 1, 1, 1, 128, 1)]
 
 
 @pytest.mark.parametrize("cfg", DEGRADED)
@@ -75,4 +77,16 @@ def test_degraded_mode_is_race_free_with_both_fixes(litmus, cfg):
     import re
 
     m = re.search(r"drops=(\d+) forcedChunks=(\d+) forcedRounds=(\d+) abandoned=(\d+)", r.stdout)
+    assert m and int(m.group(1)) > 0 and int(m.group(2)) > 0, r.stdout
+
+
+def test_late_work_elision_is_race_free_and_exact(litmus):
+    """No wait budgets here: the lagger is tolerated purely by the thresholds, falls a round behind, and elides pushes and
+    broadcasts (the counters prove it); every flushed vector still equals the sum over the decided sets."""
+    import re
+
+    r = run(litmus, 5, 4, 14, 75, 3, 1, 4, 1, 1, 1, 1 << 30, 1)
+    assert "WARNING: ThreadSanitizer" not in r.stderr, r.stderr[-3000:]
+    assert r.returncode == 0 and "failures=0" in r.stdout, r.stdout + r.stderr[-1000:]
+    m = re.search(r"elidedPushes=(\d+) elidedBcasts=(\d+)", r.stdout)
     assert m and int(m.group(1)) > 0 and int(m.group(2)) > 0, r.stdout
