@@ -40,3 +40,9 @@ esac
 #   TR 8 P bench/sweep.py --sizes 1048576,2097152,4194304 --algos auto,pipelined,nvls --grid 32      (and 16, 64): fewer CTAs, less sync
 #   AAR_ONESHOT_MAX_BYTES=4194304 TR 8 P bench/sweep.py --sizes 262144,524288,1048576,2097152 --algos oneshot,nvls   one-shot crossover
 #   TR 4 P bench/gpt2_dp.py --comm-ctas 32   (and 16, 48, 64; --algo pipelined)                      SM budget for the DDP buckets
+# Host-side launch cost (small and mid sizes are bound by how fast one Python thread can enqueue rounds, ~28-38 us each):
+#   * residentGrid() runs cudaOccupancyMaxActiveBlocksPerMultiprocessor + cudaDeviceGetAttribute on EVERY launch: cache per
+#     (kernel pointer, device) -- the template parameter K is the function-pointer TYPE, shared by kernels with one signature,
+#     so key the cache by pointer value, not by a static local per instantiation.
+#   * enqueue_round() makes 3-4 torch stream/event calls per round; one C entry point (wait event, launch, record event) would
+#     replace them.  Measure with `python -X importtime`-style timers around enqueue_round before and after.
