@@ -165,7 +165,12 @@ __device__ void phaseScatter(const AarRankParams& p, const AarLayout& l, int cta
     const int clen = chunkLen(l, dest, c);
     const int off = s * segElems;
     if (off >= clen) continue;
-    if (!kStage && !scatterDecision(p, l, dest, sm)) continue;
+    // The shipped NVLS path stages without flow control: the owner of a block is the only reader of that part of the
+    // staging slot, and with thresholds = 1 and no wait that gives up it has finished reading round R - L before this
+    // rank could retire R - L.  Once waits can give up that no longer holds (litmus model, `nvls` = 1 with a lagger), so
+    // the strict variant keeps the check: an owner that has not retired the slot's previous tenant gets no staging write
+    // and no flag from this rank for this round.
+    if ((!kStage || kElide) && !scatterDecision(p, l, dest, sm)) continue;
     const int n = min(segElems, clen - off);
     const long long inOff = blockStart(l, dest) + (long long)c * l.maxChunk + off;
     const T* src = reinterpret_cast<const T*>(p.input) + inOff;
@@ -908,7 +913,7 @@ __global__ void __launch_bounds__(kThreads, 1) nvlsPipelinedKernel(const AarRank
   const int nStage = split & 0xffff, nReduce = split >> 16;
   const int b = blockIdx.x;
   if (b < nStage) {
-    phaseScatter<T, true>(p, l, b, nStage, sm, 1);
+    phaseScatter<T, true, kStrict>(p, l, b, nStage, sm, 1);
     traceMark(p, l, 1);
   } else if (b < nStage + nReduce) {
     phaseReduceBcast<T, true, kStrict>(p, l, b - nStage, nReduce, sm);

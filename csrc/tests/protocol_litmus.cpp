@@ -20,7 +20,7 @@
 // either whole or as zeros, never half and half (`eagerDecision` = 0 reproduces that hole in the eager gather).
 //
 //   protocol_litmus [seed] [P] [rounds] [thresholdPercent] [maxLag] [overlap 0|1] [ctasPerKernel] [bcastFlowControl 0|1]
-//                   [lagger 0|1] [eagerDecision 0|1] [spinBudget] [elide 0|1]
+//                   [lagger 0|1] [eagerDecision 0|1] [spinBudget] [elide 0|1] [nvls 0|1|2]
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -62,6 +62,8 @@ struct Config {
   bool bcastFlowControl = true;    // K2 adopts K1's per-destination decision (wait for the slot, or skip a dropped destination)
   bool lagger = false;             // rank 0 is slow in every round: degraded-mode paths (give-ups, drops, forced decisions)
   bool eagerDecision = true;       // eager gather: one decision per (round, chunk) shared by all CTAs (proposed fix)
+  int nvls = 0;                    // 1 = NVLS path as shipped (staging slots without flow control, the switch sums every rank),
+                                   // 2 = strict NVLS (staging obeys the slot flow control, incomplete decisions are not published)
   bool elide = false;              // a rank that is a whole round late skips work nobody will read (AAR_FLAG_ELIDE_LATE)
   int spinBudget = 1 << 30;        // stand-in for the %globaltimer deadline of a wait (default: timeoutNs = 0, unbounded)
   unsigned seed = 1;
@@ -71,6 +73,7 @@ struct Config {
 
 struct Region {
   std::vector<float> scatter, reduce;                 // [L][P][blockLen]   plain memory on purpose
+  std::vector<float> stage;                           // [L][dataSize]      NVLS staging area (read by the owners through the switch)
   std::vector<std::atomic<uint32_t>> sflag;           // [L][C][P]
   std::vector<std::atomic<uint64_t>> rflag;           // [L][P][C]
   std::vector<std::atomic<uint32_t>> peerBase;        // [P]
@@ -87,7 +90,7 @@ struct Region {
   std::vector<std::vector<float>> output;             // [L][dataSize]      what the sink would see
   std::vector<std::vector<int>> outCounts;            // [L][P*C]
   explicit Region(const Config& c)
-      : scatter((size_t)c.L * c.P * c.blockLen()), reduce((size_t)c.L * c.P * c.blockLen()), sflag((size_t)c.L * c.C * c.P),
+      : scatter((size_t)c.L * c.P * c.blockLen()), reduce((size_t)c.L * c.P * c.blockLen()), stage((size_t)c.L * c.dataSize()), sflag((size_t)c.L * c.C * c.P),
         rflag((size_t)c.L * c.P * c.C), peerBase(c.P), k1Ctr((size_t)c.L * c.P * c.C), k1Dec((size_t)c.L * c.P),
         egDec((size_t)c.L * c.P * c.C), k2Dec((size_t)c.L * c.C), k2Ctr((size_t)c.L * c.C),
         k3Dec(c.L), k3Ctr(c.L), counts((size_t)c.L * c.P * c.C), consumed(c.L), output(c.L, std::vector<float>(c.dataSize())),
@@ -164,9 +167,22 @@ void phaseScatter(World& w, int rank, int round, int cta, int nctas, std::mt1993
     const int i = (int)(idx % c.P), s = (int)((idx / c.P) % c.S), ch = (int)(idx / ((long)c.S * c.P));
     const int dest = (i + rank) % c.P;
     Region& peer = *w.region[dest];
-    // flow control: the previous tenant of this slot at `dest` must be retired -- or the push is dropped
-    if (!scatterDecision(w, rank, round, dest)) continue;
+    // flow control: the previous tenant of this slot at `dest` must be retired -- or the push is dropped.  The shipped NVLS
+    // path stages without it (the owner of a block is the only reader of that part of the staging slot, and at thresholds
+    // = 1 it has finished reading round R - L before this rank could retire R - L); the strict variant keeps the check.
+    if (c.nvls != 1 && !scatterDecision(w, rank, round, dest)) continue;
     jitter(rng);
+    if (c.nvls) {
+      const float* src = w.input[round][rank].data() + dest * c.blockLen() + ch * c.chunkLen + s * segLen;
+      float* dst = my.stage.data() + (size_t)slot * c.dataSize() + dest * c.blockLen() + ch * c.chunkLen + s * segLen;
+      for (int k = 0; k < segLen; ++k) dst[k] = src[k];
+      std::atomic<uint32_t>& sctr = my.k1Ctr[(size_t)(slot * c.P + dest) * c.C + ch];
+      if (sctr.fetch_add(1, std::memory_order_acq_rel) + 1 == (uint32_t)c.S) {  // only the flag travels
+        sctr.store(0, std::memory_order_relaxed);
+        peer.sflag[(size_t)(slot * c.C + ch) * c.P + rank].store(epoch, std::memory_order_release);
+      }
+      continue;
+    }
     bool skip = false;
     if (late) {  // one remote load of the owner's decision word
       const uint64_t d = peer.k2Dec[(size_t)slot * c.C + ch].load(std::memory_order_relaxed);
@@ -236,7 +252,7 @@ void phaseReduce(World& w, int rank, int round, int cta, int nctas, std::mt19937
   // this model: data race between the store below and copyChunk).  So the broadcast adopts the scatter's per-destination
   // decision: it waits for it like a push CTA would, and leaves a dropped destination alone (bcastDestMask in the kernels).
   unsigned destMask = ~0u;
-  if (c.bcastFlowControl && cta < (long)c.C * c.S) {
+  if (c.bcastFlowControl && !c.nvls && cta < (long)c.C * c.S) {
     destMask = 0;
     for (int i = 0; i < c.P; ++i) {
       const int d = (i + rank) % c.P;
@@ -255,6 +271,27 @@ void phaseReduce(World& w, int rank, int round, int cta, int nctas, std::mt19937
     const unsigned mask = chunkDecision(w, rank, round, ch, rng);
     const int count = __builtin_popcount(mask);
     jitter(rng);
+    if (c.nvls) {
+      // The switch cannot leave a rank out.  Shipped kernel: sums every staging slot whatever the decision says.  Strict: a
+      // decision forced over an incomplete set is not carried out and not published (every gather gives up on the chunk).
+      const bool incomplete = count != c.P;
+      if (!(c.nvls == 2 && incomplete)) {
+        for (int k = 0; k < segLen; ++k) {
+          const int e = ch * c.chunkLen + s * segLen + k;
+          float acc = 0.f;
+          for (int src = 0; src < c.P; ++src) acc += w.region[src]->stage[(size_t)slot * c.dataSize() + rank * c.blockLen() + e];  // multimem.ld_reduce
+          for (int d = 0; d < c.P; ++d) w.region[d]->reduce[(size_t)(slot * c.P + rank) * c.blockLen() + e] = acc;               // multimem.st
+        }
+      }
+      std::atomic<uint32_t>& nctr = my.k2Ctr[(size_t)slot * c.C + ch];
+      if (nctr.fetch_add(1, std::memory_order_acq_rel) + 1 == (uint32_t)c.S) {
+        nctr.store(0, std::memory_order_relaxed);
+        if (!(c.nvls == 2 && incomplete))
+          for (int d = 0; d < c.P; ++d)
+            w.region[d]->rflag[(size_t)(slot * c.P + rank) * c.C + ch].store((epoch << 32) | (uint64_t)count, std::memory_order_release);
+      }
+      continue;
+    }
     for (int k = 0; k < segLen; ++k) {
       const int e = ch * c.chunkLen + s * segLen + k;
       float acc = 0.f;
@@ -424,6 +461,7 @@ int main(int argc, char** argv) {
   c.eagerDecision = argc > 10 ? atoi(argv[10]) != 0 : true;
   c.spinBudget = argc > 11 ? atoi(argv[11]) : (1 << 30);
   c.elide = argc > 12 ? atoi(argv[12]) != 0 : false;
+  c.nvls = argc > 13 ? atoi(argv[13]) : 0;
   c.minRequired = std::max(1, (int)((float)thPct / 100.f * (float)c.P));
   c.minChunks = std::max(1, (int)((float)thPct / 100.f * (float)(c.P * c.C)));
   if (c.L < 2) c.overlap = false;
@@ -467,6 +505,7 @@ int main(int argc, char** argv) {
     }
   for (auto& t : threads) t.join();
   long bad = w.failures.load();
+  if (c.nvls) printf("nvls=%d ", c.nvls);
   printf("protocol_litmus seed=%u P=%d rounds=%d th=%d%% L=%d overlap=%d G=%d fc=%d lagger=%d eagerDecision=%d: failures=%ld"
          " (drops=%ld forcedChunks=%ld forcedRounds=%ld abandoned=%ld elidedPushes=%ld elidedBcasts=%ld)\n", c.seed, c.P,
          c.rounds, thPct, c.L, (int)c.overlap, c.G, (int)c.bcastFlowControl, (int)c.lagger, (int)c.eagerDecision, bad, w.drops.load(),

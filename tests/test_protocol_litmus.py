@@ -90,3 +90,28 @@ def test_late_work_elision_is_race_free_and_exact(litmus):
     assert r.returncode == 0 and "failures=0" in r.stdout, r.stdout + r.stderr[-1000:]
     m = re.search(r"elidedPushes=(\d+) elidedBcasts=(\d+)", r.stdout)
     assert m and int(m.group(1)) > 0 and int(m.group(2)) > 0, r.stdout
+
+
+# seed, P, rounds, threshold %, maxLag, overlap, CTAs, fc, lagger, eagerDecision, spinBudget, elide, nvls
+NVLS_SHIPPED = [(1, 4, 12, 100, 1, 1, 4, 0, 0, 0, 1 << 30, 0, 1), (2, 4, 12, 100, 1, 0, 4, 0, 0, 0, 1 << 30, 0, 1),
+                (3, 3, 12, 100, 2, 1, 3, 0, 0, 0, 1 << 30, 0, 1), (4, 5, 8, 100, 3, 1, 4, 0, 0, 0, 1 << 30, 0, 1)]
+NVLS_STRICT_DEGRADED = [(5, 4, 12, 100, 1, 1, 4, 0, 1, 1, 64, 0, 2), (6, 3, 14, 100, 2, 1, 3, 0, 1, 1, 128, 0, 2), (8, 4, 12, 100, 1, 0, 4, 0, 1, 1, 32, 0, 2)]
+
+
+@pytest.mark.parametrize("cfg", NVLS_SHIPPED)
+def test_nvls_path_as_shipped_is_race_free_at_full_thresholds(litmus, cfg):
+    """The in-switch path of the headline number: staging slots WITHOUT flow control, the switch sums every rank's slot, multicast
+    store into every reduce ring, eager gather, two rounds in flight -- race-free and exact as long as no wait gives up."""
+    r = run(litmus, *cfg)
+    assert "WARNING: ThreadSanitizer" not in r.stderr, r.stderr[-3000:]
+    assert r.returncode == 0 and "failures=0" in r.stdout, r.stdout + r.stderr[-1000:]
+
+
+@pytest.mark.parametrize("cfg", NVLS_STRICT_DEGRADED)
+def test_strict_nvls_survives_degraded_mode(litmus, cfg):
+    """With a persistent lagger and waits that give up, the shipped NVLS path races (staging slot rewritten under a late reduce)
+    and publishes sums that do not match their counts; the strict variant -- staging obeys the slot flow control, a decision
+    forced over an incomplete set is not carried out, the eager gather decides once -- stays race-free and exact."""
+    r = run(litmus, *cfg)
+    assert "WARNING: ThreadSanitizer" not in r.stderr, r.stderr[-3000:]
+    assert r.returncode == 0 and "failures=0" in r.stdout, r.stdout + r.stderr[-1000:]
