@@ -20,7 +20,7 @@
 // either whole or as zeros, never half and half (`eagerDecision` = 0 reproduces that hole in the eager gather).
 //
 //   protocol_litmus [seed] [P] [rounds] [thresholdPercent] [maxLag] [overlap 0|1] [ctasPerKernel] [bcastFlowControl 0|1]
-//                   [lagger 0|1] [eagerDecision 0|1] [spinBudget] [elide 0|1] [nvls 0|1|2]
+//                   [lagger 0|1] [eagerDecision 0|1] [spinBudget] [elide 0|1] [nvls 0|1|2] [oneshot 0|1]
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -64,6 +64,7 @@ struct Config {
   bool eagerDecision = true;       // eager gather: one decision per (round, chunk) shared by all CTAs (proposed fix)
   int nvls = 0;                    // 1 = NVLS path as shipped (staging slots without flow control, the switch sums every rank),
                                    // 2 = strict NVLS (staging obeys the slot flow control, incomplete decisions are not published)
+  bool oneshot = false;            // K5: every rank pushes its whole vector to every peer and sums the arrived set locally
   bool elide = false;              // a rank that is a whole round late skips work nobody will read (AAR_FLAG_ELIDE_LATE)
   int spinBudget = 1 << 30;        // stand-in for the %globaltimer deadline of a wait (default: timeoutNs = 0, unbounded)
   unsigned seed = 1;
@@ -74,6 +75,8 @@ struct Config {
 struct Region {
   std::vector<float> scatter, reduce;                 // [L][P][blockLen]   plain memory on purpose
   std::vector<float> stage;                           // [L][dataSize]      NVLS staging area (read by the owners through the switch)
+  std::vector<float> oneshot;                         // [L][P][dataSize]   K5 one-shot buffers, written by peers
+  std::vector<std::atomic<uint32_t>> osflag;          // [L][P]
   std::vector<std::atomic<uint32_t>> sflag;           // [L][C][P]
   std::vector<std::atomic<uint64_t>> rflag;           // [L][P][C]
   std::vector<std::atomic<uint32_t>> peerBase;        // [P]
@@ -90,7 +93,8 @@ struct Region {
   std::vector<std::vector<float>> output;             // [L][dataSize]      what the sink would see
   std::vector<std::vector<int>> outCounts;            // [L][P*C]
   explicit Region(const Config& c)
-      : scatter((size_t)c.L * c.P * c.blockLen()), reduce((size_t)c.L * c.P * c.blockLen()), stage((size_t)c.L * c.dataSize()), sflag((size_t)c.L * c.C * c.P),
+      : scatter((size_t)c.L * c.P * c.blockLen()), reduce((size_t)c.L * c.P * c.blockLen()), stage((size_t)c.L * c.dataSize()),
+        oneshot(c.oneshot ? (size_t)c.L * c.P * c.dataSize() : 0), osflag((size_t)c.L * c.P), sflag((size_t)c.L * c.C * c.P),
         rflag((size_t)c.L * c.P * c.C), peerBase(c.P), k1Ctr((size_t)c.L * c.P * c.C), k1Dec((size_t)c.L * c.P),
         egDec((size_t)c.L * c.P * c.C), k2Dec((size_t)c.L * c.C), k2Ctr((size_t)c.L * c.C),
         k3Dec(c.L), k3Ctr(c.L), counts((size_t)c.L * c.P * c.C), consumed(c.L), output(c.L, std::vector<float>(c.dataSize())),
@@ -406,6 +410,87 @@ void phaseGather(World& w, int rank, int round, int cta, int nctas, std::mt19937
   }
 }
 
+// ---------------------------------------------------------------------------------------------- K5 one-shot
+// Tiles of C * chunkLen / S elements; one arrival flag per (round, source).  The contributor decision reuses chunkDecision's
+// word for chunk 0 of the slot, as the kernel does.
+void phaseOneshot(World& w, int rank, int round, int cta, int nctas, std::mt19937& rng) {
+  const Config& c = w.cfg;
+  const int slot = round % c.L;
+  const uint64_t epoch = (uint64_t)round + 1;
+  Region& my = *w.region[rank];
+  const int tile = c.chunkLen / c.S, Tn = c.dataSize() / tile;
+  for (long idx = cta; idx < (long)c.P * Tn; idx += nctas) {  // push
+    const int t = (int)(idx % Tn), dest = ((int)(idx / Tn) + rank) % c.P;
+    if (!scatterDecision(w, rank, round, dest)) continue;
+    jitter(rng);
+    Region& peer = *w.region[dest];
+    float* dst = peer.oneshot.data() + (size_t)(slot * c.P + rank) * c.dataSize() + (size_t)t * tile;
+    for (int k = 0; k < tile; ++k) dst[k] = w.input[round][rank][(size_t)t * tile + k];
+    std::atomic<uint32_t>& ctr = my.k1Ctr[(size_t)(slot * c.P + dest) * c.C];
+    if (ctr.fetch_add(1, std::memory_order_acq_rel) + 1 == (uint32_t)Tn) {
+      ctr.store(0, std::memory_order_relaxed);
+      peer.osflag[(size_t)slot * c.P + rank].store((uint32_t)epoch, std::memory_order_release);
+    }
+  }
+  // reduce: one contributor decision per round
+  std::atomic<uint64_t>& word = my.k2Dec[(size_t)slot * c.C];
+  uint64_t v = word.load(std::memory_order_acquire);
+  unsigned mask;
+  if ((v >> 32) == epoch) {
+    mask = (unsigned)v;
+  } else {
+    int spins = 0;
+    for (;;) {
+      mask = 0;
+      for (int src = 0; src < c.P; ++src)
+        if (my.osflag[(size_t)slot * c.P + src].load(std::memory_order_acquire) == (uint32_t)epoch) mask |= 1u << src;
+      if (__builtin_popcount(mask) >= c.minRequired) break;
+      if ((++spins & 31) == 0 && (forced(w, rank, round) || spins > c.spinBudget)) {
+        w.forcedChunks++;
+        mask = 0;
+        for (int src = 0; src < c.P; ++src)
+          if (my.osflag[(size_t)slot * c.P + src].load(std::memory_order_acquire) == (uint32_t)epoch) mask |= 1u << src;
+        break;
+      }
+      std::this_thread::yield();
+    }
+    if (!word.compare_exchange_strong(v, (epoch << 32) | mask, std::memory_order_acq_rel, std::memory_order_acquire)) {
+      if ((v >> 32) == epoch) mask = (unsigned)v;
+      else w.failures++;
+    }
+  }
+  const int count = __builtin_popcount(mask);
+  if (cta == 0)
+    for (int i = 0; i < c.P * c.C; ++i) my.outCounts[slot][i] = count;
+  for (int t = cta; t < Tn; t += nctas) {
+    jitter(rng);
+    for (int k = 0; k < tile; ++k) {
+      float acc = 0.f;
+      for (int src = 0; src < c.P; ++src)
+        if (mask >> src & 1) acc += my.oneshot[(size_t)(slot * c.P + src) * c.dataSize() + (size_t)t * tile + k];
+      my.output[slot][(size_t)t * tile + k] = acc;
+    }
+  }
+}
+
+void verifyOneshot(World& w, int rank, int round) {
+  const Config& c = w.cfg;
+  const int slot = round % c.L;
+  Region& my = *w.region[rank];
+  const uint64_t dec = my.k2Dec[(size_t)slot * c.C].load(std::memory_order_acquire);
+  if ((dec >> 32) != (uint64_t)round + 1) {
+    w.failures++;
+    return;
+  }
+  if (__builtin_popcount((unsigned)dec) != my.outCounts[slot][0]) w.failures++;
+  for (int e = 0; e < c.dataSize(); ++e) {
+    float want = 0.f;
+    for (int src = 0; src < c.P; ++src)
+      if ((unsigned)dec >> src & 1) want += w.input[round][src][e];
+    if (my.output[slot][e] != want) w.failures++;
+  }
+}
+
 // K6: last CTA of the kernel retires the slot; with two rounds in flight retirement stays in order
 void retire(World& w, int rank, int round, int nctas) {
   const Config& c = w.cfg;
@@ -462,6 +547,7 @@ int main(int argc, char** argv) {
   c.spinBudget = argc > 11 ? atoi(argv[11]) : (1 << 30);
   c.elide = argc > 12 ? atoi(argv[12]) != 0 : false;
   c.nvls = argc > 13 ? atoi(argv[13]) : 0;
+  c.oneshot = argc > 14 ? atoi(argv[14]) != 0 : false;
   c.minRequired = std::max(1, (int)((float)thPct / 100.f * (float)c.P));
   c.minChunks = std::max(1, (int)((float)thPct / 100.f * (float)(c.P * c.C)));
   if (c.L < 2) c.overlap = false;
@@ -488,15 +574,20 @@ int main(int argc, char** argv) {
               while (w.region[rank]->consumed[round % cf.L].load(std::memory_order_acquire) != round - cf.L) std::this_thread::yield();
             if (rank == (round % cf.P) && (rng() % 3 == 0)) std::this_thread::sleep_for(std::chrono::microseconds(300));  // straggler
             if (cf.lagger && rank == 0 && cta == 0) std::this_thread::sleep_for(std::chrono::microseconds(1500 + rng() % 2000));
-            phaseScatter(w, rank, round, cta, cf.G, rng);
-            phaseReduce(w, rank, round, cta, cf.G, rng);
-            phaseGather(w, rank, round, cta, cf.G, rng);
+            if (cf.oneshot) {
+              phaseOneshot(w, rank, round, cta, cf.G, rng);
+            } else {
+              phaseScatter(w, rank, round, cta, cf.G, rng);
+              phaseReduce(w, rank, round, cta, cf.G, rng);
+              phaseGather(w, rank, round, cta, cf.G, rng);
+            }
             retire(w, rank, round, cf.G);
             b->wait();  // kernel boundary: the stream's next kernel starts when every CTA of this one is done
             if (cta == 0) {
               // host side: wait for the completion word, then consume this round's output slot before it is reused
               while ((int)w.region[rank]->flushed.load(std::memory_order_acquire) < round + 1) std::this_thread::yield();
-              verifyRound(w, rank, round);
+              if (cf.oneshot) verifyOneshot(w, rank, round);
+              else verifyRound(w, rank, round);
               w.region[rank]->consumed[round % cf.L].store(round, std::memory_order_release);
             }
             b->wait();
@@ -506,6 +597,7 @@ int main(int argc, char** argv) {
   for (auto& t : threads) t.join();
   long bad = w.failures.load();
   if (c.nvls) printf("nvls=%d ", c.nvls);
+  if (c.oneshot) printf("oneshot ");
   printf("protocol_litmus seed=%u P=%d rounds=%d th=%d%% L=%d overlap=%d G=%d fc=%d lagger=%d eagerDecision=%d: failures=%ld"
          " (drops=%ld forcedChunks=%ld forcedRounds=%ld abandoned=%ld elidedPushes=%ld elidedBcasts=%ld)\n", c.seed, c.P,
          c.rounds, thPct, c.L, (int)c.overlap, c.G, (int)c.bcastFlowControl, (int)c.lagger, (int)c.eagerDecision, bad, w.drops.load(),

@@ -115,3 +115,17 @@ def test_strict_nvls_survives_degraded_mode(litmus, cfg):
     r = run(litmus, *cfg)
     assert "WARNING: ThreadSanitizer" not in r.stderr, r.stderr[-3000:]
     assert r.returncode == 0 and "failures=0" in r.stdout, r.stdout + r.stderr[-1000:]
+
+
+# seed, P, rounds, threshold %, maxLag, overlap, CTAs, fc, lagger, eagerDecision, spinBudget, elide, nvls, oneshot
+ONESHOT = [(1, 4, 12, 100, 1, 1, 4, 0, 0, 0, 1 << 30, 0, 0, 1), (2, 4, 12, 75, 1, 1, 4, 0, 0, 0, 1 << 30, 0, 0, 1),
+           (4, 5, 10, 80, 1, 0, 4, 0, 1, 0, 64, 0, 0, 1), (5, 4, 12, 100, 3, 1, 4, 0, 1, 0, 64, 0, 0, 1)]
+
+
+@pytest.mark.parametrize("cfg", ONESHOT)
+def test_oneshot_path_as_shipped_is_race_free_also_in_degraded_mode(litmus, cfg):
+    """K5 (small messages): whole-vector pushes under the per-destination flow control, one arrival flag per source, one
+    contributor decision per round, local sum -- clean at full and partial thresholds, with and without a lagger and give-ups."""
+    r = run(litmus, *cfg)
+    assert "WARNING: ThreadSanitizer" not in r.stderr, r.stderr[-3000:]
+    assert r.returncode == 0 and "failures=0" in r.stdout, r.stdout + r.stderr[-1000:]
