@@ -49,6 +49,9 @@ class AllreduceWorker:
         self.delivered = 0          # rounds handed to the sink (= reference `round` on this in-order data plane)
         self.rounds_forced = 0
         self.lag_hist: dict[int, int] = {}   # (master's newest round - round) at the moment a round reached the sink
+        self.start_round = 0        # first round of this incarnation (> 0 when the master resumed from a checkpoint)
+        self._t_first: float | None = None   # wall clock of the first / latest delivery (rounds_per_sec in metrics())
+        self._t_last = 0.0
         self._stream = None
         self._inputs = {}           # round -> input tensor kept alive until the round is flushed
         self._cpu_worker = None
@@ -103,8 +106,8 @@ class AllreduceWorker:
         if self.engine is not None:
             m.update(self.engine.metrics())
         m["lag_hist"] = dict(sorted(self.lag_hist.items()))
-        done = self.delivered - getattr(self, "start_round", 0)
-        if getattr(self, "_t_first", None) is not None and done > 1:
+        done = self.delivered - self.start_round
+        if self._t_first is not None and done > 1:
             m["rounds_per_sec"] = rps = (done - 1) / max(1e-9, self._t_last - self._t_first)
             lay = getattr(self.engine, "layout", None)
             if lay is not None and getattr(lay, "P", 0) > 1:  # NCCL's bus-bandwidth convention: algbw * 2(P-1)/P
@@ -223,7 +226,7 @@ class AllreduceWorker:
                 self.node.send_complete(self.id, r, self.generation)
                 self.delivered += 1
                 self._t_last = time.time()
-                if getattr(self, "_t_first", None) is None:
+                if self._t_first is None:
                     self._t_first = self._t_last
                 progressed = True
             if not block or progressed or self.delivered >= self.max_scattered + 1:

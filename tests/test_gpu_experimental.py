@@ -90,7 +90,7 @@ def test_engine_start_at_continues_the_round_numbering():
     eng.close()
 
 
-def test_eager_decision_matches_the_default_path_when_everything_arrives():
+def test_eager_decision_words_exist_in_the_layout():
     """AAR_FLAG_EAGER_DEC on the pipelined kernel is not reachable on one GPU (the emulation launches phases separately with the
     leader gather), so the single-GPU check is the layout: the decision words exist, sit behind every older section and start
     zeroed; the kernel path itself is covered by tests/multi_gpu_worker.py run with AAR_STRICT=1."""
