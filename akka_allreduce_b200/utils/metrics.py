@@ -10,6 +10,11 @@ from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
 from typing import Callable, Mapping
 
 
+def _esc(v: object) -> str:
+    """Label values: backslash, double quote and newline are escaped (Prometheus text format)."""
+    return str(v).replace("\\", "\\\\").replace('"', '\\"').replace("\n", "\\n")
+
+
 def render_prometheus(metrics: Mapping[str, object], prefix: str = "aar", labels: Mapping[str, str] | None = None) -> str:
     lab = ""
     if labels:
@@ -21,8 +26,13 @@ def render_prometheus(metrics: Mapping[str, object], prefix: str = "aar", labels
             value = int(value)
         if isinstance(value, (int, float)):
             lines.append(f"{key}{lab} {value}")
+        elif isinstance(value, Mapping):  # histograms (e.g. lag_hist): one series per bucket
+            for k, v in sorted(value.items(), key=lambda kv: str(kv[0])):
+                if isinstance(v, (int, float)) and not isinstance(v, bool):
+                    extra = (lab[:-1] + "," if lab else "{") + f'bucket="{_esc(k)}"' + "}"
+                    lines.append(f"{key}{extra} {v}")
         else:  # strings become info-style series
-            extra = (lab[:-1] + "," if lab else "{") + f'value="{value}"' + "}"
+            extra = (lab[:-1] + "," if lab else "{") + f'value="{_esc(value)}"' + "}"
             lines.append(f"{key}_info{extra} 1")
     return "\n".join(lines) + "\n"
 

@@ -114,6 +114,9 @@ def test_metrics_endpoint_serves_master_and_worker_counters():
     assert 'aar_rounds_completed{role="worker"} 4' in text
     assert render_prometheus({"algo": "nvls", "push_dropped": False}, labels={"rank": "3"}) == \
         'aar_algo_info{rank="3",value="nvls"} 1\naar_push_dropped{rank="3"} 0\n'
+    # histograms (the device-plane worker's lag_hist) become one series per bucket; label values are escaped
+    assert render_prometheus({"lag_hist": {0: 5, 1: 2}, "note": 'a"b'}, labels={"role": "worker"}) == \
+        'aar_lag_hist{role="worker",bucket="0"} 5\naar_lag_hist{role="worker",bucket="1"} 2\naar_note_info{role="worker",value="a\\"b"} 1\n'
 
 
 def test_log_level_applies_to_both_runtimes():
