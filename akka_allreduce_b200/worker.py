@@ -116,6 +116,14 @@ class AllreduceWorker:
 
     def close(self) -> None:
         if self.engine is not None:
+            # Kernels of this incarnation may still be waiting for peers that are being re-initialised themselves (a late joiner
+            # makes the master re-init everyone).  Their region, doorbell and completion words are about to be unmapped: ring the
+            # doorbell far ahead so that every device-side wait gives up (the catch-up predicate), let them finish, then free.
+            try:
+                self.engine.set_doorbell(1 << 30)
+                self.engine.synchronize()
+            except Exception:   # teardown is best effort: a dead context must not mask the error that brought us here
+                pass
             self.engine.close()
             self.engine = None
         if self.symm is not None:

@@ -232,3 +232,61 @@ def test_resumed_master_makes_the_device_plane_continue_at_its_round(tmp_path):
             np.testing.assert_array_equal(data, np.arange(n, dtype=np.float32) * 3 + 2 * it)
         m = w.metrics()
         assert m["rounds_delivered"] == 25 and m["rounds_forced"] == 0 and sum(m["lag_hist"].values()) == 15
+
+
+def test_late_joiner_reinitialises_the_device_plane_workers():
+    """AllreduceMaster.scala:40-47 on the device plane: a third worker joins after two were admitted (thAllreduce 0.67 of 3), the
+    master re-initialises everyone with a new generation and restarts at round 0.  The old engines are wound down first (doorbell
+    rung far ahead so that waiting kernels give up, synchronised, then closed), new ones are built for the new peer table."""
+    n, rounds = 8, 30
+    fabrics, lock, closed = {}, threading.Lock(), []
+
+    class TrackedEngine(FakeEngine):
+        def __init__(self, *a):
+            super().__init__(*a)
+            self.synced = False
+
+        def synchronize(self):
+            self.synced = True
+
+        def close(self):
+            closed.append((self.rank, self.doorbell, self.synced))
+
+    class W(FakeWorker):
+        def _make_engine(self, m):
+            with lock:
+                fab = fabrics.setdefault(m.generation, Fabric(len(m.workers), m.data_size))
+            return TrackedEngine(fab, m.dest_id, m.data_size, m.max_lag)
+
+    master = AllreduceMaster(3, 0.67, 1.0, 1.0, 1, n, rounds - 1, 4, pipeline_depth=1)
+    master.start(60)
+    sunk = [[], [], []]
+    gens = [[], [], []]
+    workers = []
+    for i in range(3):
+        w = W(None, lambda req: AllReduceInput(np.full(n, 1.0, dtype=np.float32)),
+              (lambda k: lambda out: sunk[k].append((out.iteration, float(out.data[0]))))(i))
+        w.on_init = (lambda k: lambda ww: gens[k].append(ww.generation))(i)
+        workers.append(w)
+    threads = [threading.Thread(target=w.run, args=("127.0.0.1", master.port, 60)) for w in workers]
+    threads[0].start()
+    threads[1].start()
+    deadline = time.time() + 20
+    while not sunk[0] and time.time() < deadline:   # the two-worker incarnation is really running
+        time.sleep(0.01)
+    threads[2].start()
+    for t in threads:
+        t.join(90)
+    assert master.join(30)
+    # the first two workers lived through two incarnations, the third only through the second
+    assert gens == [[1, 2], [1, 2], [2]]
+    for k in range(3):
+        its = [it for it, _ in sunk[k]]
+        restart = its.index(0, 1) if k < 2 else 0          # round numbering restarts at 0 with the new incarnation
+        assert its[restart:] == list(range(rounds))
+        assert all(v == 3.0 for _, v in sunk[k][restart:])   # three contributors after the re-init
+        if k < 2:
+            assert all(v == 2.0 for _, v in sunk[k][:restart])
+    # both old engines were rung out and synchronised before they were closed
+    old = [c for c in closed if c[1] >= (1 << 30)]
+    assert len(old) >= 2 and all(s for _, _, s in old)
