@@ -109,6 +109,7 @@ def load():
         "aar_launch_delay": [C.c_ulonglong, C.c_void_p],
         "aar_bench_all2all": [C.c_int, C.c_int, C.c_int, P(C.c_void_p), C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p],
         "aar_bench_link": [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p],
+        "aar_bench_bulk_copy": [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p],
     }
     for name, argtypes in sigs.items():
         fn = getattr(lib, name, None)

@@ -19,6 +19,7 @@ ap.add_argument("--mib", type=int, default=64)
 ap.add_argument("--grids", default="16,32,64,148")
 ap.add_argument("--unrolls", default="4,8")
 ap.add_argument("--iters", type=int, default=5)
+ap.add_argument("--bulk", action="store_true", help="also run the cp.async.bulk copy-role micro-benchmark (aar_bench_bulk_copy; first run on hardware pending)")
 a = ap.parse_args()
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 lr = int(os.environ.get("LOCAL_RANK", rank))
@@ -75,6 +76,28 @@ if world > 2 or True:
                 torch.cuda.synchronize(); rdv.barrier()
                 us = gmax(e0.elapsed_time(e1) / a.iters * 1e3)
                 res[f"{a2a[mode]}_g{grid}_u{un}"] = {"us": round(us, 1), "GBps_per_gpu": round(per_peer * len(others) / us / 1e3, 1)}
+# register-free copy role: one issuing thread per CTA, bulk async-copy engine, local -> local and local -> peer
+if a.bulk:
+    err = torch.zeros(1, dtype=torch.int32, device=f"cuda:{lr}")
+    src_view = symm.tensor(rank, 0, nbytes, torch.int32)
+    src_view.copy_(torch.arange(nbytes // 4, dtype=torch.int32, device=f"cuda:{lr}"))
+    torch.cuda.synchronize(); rdv.barrier()
+    for name, dst in (("bulk_local", local + nbytes), ("bulk_peer_st", peer + nbytes)):
+        for stages, tile in ((4, 16384), (4, 32768), (8, 16384)):
+            for grid in (16, 32, 74, 148, 296):
+                args = (grid, stages, tile, C.c_void_p(local), C.c_void_p(dst), nbytes)
+                L.check(lib.aar_bench_bulk_copy(*args, 1, s, C.c_void_p(err.data_ptr())))
+                torch.cuda.synchronize(); rdv.barrier()
+                ok = True
+                if name == "bulk_local":   # verify once per configuration on the local destination
+                    ok = bool(torch.equal(symm.tensor(rank, nbytes, nbytes, torch.int32), src_view))
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                L.check(lib.aar_bench_bulk_copy(*args, a.iters, s, C.c_void_p(err.data_ptr())))
+                e1.record()
+                torch.cuda.synchronize(); rdv.barrier()
+                us = gmax(e0.elapsed_time(e1) / a.iters * 1e3)
+                res[f"{name}_s{stages}_t{tile}_g{grid}"] = {"us": round(us, 1), "GBps_per_gpu": round(nbytes / us / 1e3, 1), "ok": ok, "gave_up": int(err.item())}
 if rank == 0:
     print(json.dumps(res))
 rdv.barrier()

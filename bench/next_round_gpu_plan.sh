@@ -46,3 +46,4 @@ esac
 #     so key the cache by pointer value, not by a static local per instantiation.
 #   * enqueue_round() makes 3-4 torch stream/event calls per round; one C entry point (wait event, launch, record event) would
 #     replace them.  Measure with `python -X importtime`-style timers around enqueue_round before and after.
+#   TR 2 P bench/link_bench.py --bulk --mib 64        cp.async.bulk copy role: GB/s per GPU with 32-thread CTAs, local and to a peer

@@ -149,6 +149,101 @@ AAR_API int aar_bench_all2all(int mode, int grid, int unroll, void** peers, int 
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------------ TMA bulk copy
+// A copy role that holds no data in registers: ONE thread per CTA drives a ring of shared-memory tiles with the bulk
+// async-copy engine -- cp.async.bulk global -> shared (completion counted in bytes on an mbarrier), then cp.async.bulk
+// shared -> (peer) global as a bulk group.  The fused kernels' copy roles (stage, gather, push) spend 512 threads x 128
+// registers per SM on the same job; this measures what a 32-thread CTA can move, to decide whether those roles should be
+// rebuilt on it (it would free SMs for the caller's compute).  Written without GPU access: every wait is bounded and
+// reports through `err` instead of hanging.
+namespace {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity) {
+  for (unsigned tries = 0; tries < (1u << 20); ++tries) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) return true;
+  }
+  return false;
+}
+
+template <int kStages>
+__global__ void __launch_bounds__(32, 1) bulkCopyBench(const char* src, char* dst, size_t bytes, int tileBytes, unsigned* err) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)kStages * tileBytes);
+  if (threadIdx.x != 0) return;  // one thread issues everything; the copy engine does the work
+  for (int s = 0; s < kStages; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(bars + s)) : "memory");
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");  // make the initialised barriers visible to the async proxy
+  const size_t nTiles = (bytes + tileBytes - 1) / tileBytes;
+  const size_t mine = nTiles > blockIdx.x ? (nTiles - blockIdx.x - 1) / gridDim.x + 1 : 0;
+  auto tileOff = [&](size_t k) { return (blockIdx.x + k * gridDim.x) * (size_t)tileBytes; };
+  auto tileLen = [&](size_t k) {
+    const size_t off = tileOff(k);
+    return (uint32_t)(bytes - off < (size_t)tileBytes ? bytes - off : (size_t)tileBytes);
+  };
+  auto load = [&](size_t k) {
+    const int s = (int)(k % kStages);
+    const uint32_t bar = smem_u32(bars + s), n = tileLen(k);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(n) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem + (size_t)s * tileBytes)),
+                 "l"(src + tileOff(k)), "r"(n), "r"(bar)
+                 : "memory");
+  };
+  for (size_t k = 0; k < mine && k < (size_t)kStages; ++k) load(k);
+  for (size_t k = 0; k < mine; ++k) {
+    const int s = (int)(k % kStages);
+    if (!mbar_wait(smem_u32(bars + s), (uint32_t)((k / kStages) & 1))) {
+      atomicExch(err, 1u);
+      return;
+    }
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst + tileOff(k)), "r"(smem_u32(smem + (size_t)s * tileBytes)), "r"(tileLen(k))
+                 : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    // the store of tile k-1 has finished READING its stage once at most one newer group is pending: refill that stage
+    if (k >= 1 && k - 1 + kStages < mine) {
+      asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+      load(k - 1 + kStages);
+    }
+  }
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // writes complete (not only their reads) before the CTA exits
+}
+
+}  // namespace
+
+// `iters` launches of the bulk-copy kernel on `stream` (timed by the caller).  src / dst: `bytes` each, 16-byte aligned,
+// bytes a multiple of 16; dst may be a peer mapping.  stages in {2, 4, 8}; tileBytes a multiple of 128 with
+// stages * tileBytes + 64 <= 227 KiB.  *errOut (device word, may be NULL) becomes 1 if a wait ran out of patience.
+AAR_API int aar_bench_bulk_copy(int grid, int stages, int tileBytes, const void* src, void* dst, size_t bytes, int iters, void* stream, unsigned* errOut) {
+  if (grid <= 0 || tileBytes <= 0 || tileBytes % 128 || bytes % 16 || !src || !dst) return aar_host::fail(-1, "aar_bench_bulk_copy: bad arguments");
+  const size_t smem = (size_t)stages * tileBytes + 64;
+  if (smem > 227 * 1024) return aar_host::fail(-1, "aar_bench_bulk_copy: %d stages x %d bytes do not fit in shared memory", stages, tileBytes);
+  static unsigned* fallbackErr = nullptr;
+  if (!errOut) {
+    if (!fallbackErr && cudaMalloc(&fallbackErr, 4) != cudaSuccess) return aar_host::fail(-2, "aar_bench_bulk_copy: cudaMalloc failed");
+    cudaMemsetAsync(fallbackErr, 0, 4, (cudaStream_t)stream);
+    errOut = fallbackErr;
+  }
+  void (*k)(const char*, char*, size_t, int, unsigned*) = nullptr;
+  if (stages == 2) k = bulkCopyBench<2>;
+  else if (stages == 4) k = bulkCopyBench<4>;
+  else if (stages == 8) k = bulkCopyBench<8>;
+  else return aar_host::fail(-1, "aar_bench_bulk_copy: stages must be 2, 4 or 8");
+  cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return aar_host::fail(-2, "aar_bench_bulk_copy: shared memory opt-in: %s", cudaGetErrorString(e));
+  for (int i = 0; i < iters; ++i) k<<<grid, 32, smem, (cudaStream_t)stream>>>((const char*)src, (char*)dst, bytes, tileBytes, errOut);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return aar_host::fail(-2, "aar_bench_bulk_copy: %s", cudaGetErrorString(e));
+  return 0;
+}
+
 // Runs `iters` launches on `stream`; the caller times them with events.  The buffers need 2 * bytes (read half, write half).
 AAR_API int aar_bench_link(int mode, int grid, int unroll, void* mc, void* peer, void* local, size_t bytes, int iters, void* stream) {
   if (mode < 0 || mode > 6 || grid <= 0) return aar_host::fail(-1, "aar_bench_link: bad arguments");

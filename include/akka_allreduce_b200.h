@@ -191,6 +191,11 @@ int aar_bench_link(int mode, int grid, int unroll, void* mc, void* peer, void* l
  * peer, 3 like 0 with 32-byte stores.  Every peer buffer holds 2 * bytesPerPeer. */
 int aar_bench_all2all(int mode, int grid, int unroll, void** peers, int nPeers, void* local, size_t bytesPerPeer, int iters, void* stream);
 
+/* Copy by the bulk async-copy engine (cp.async.bulk + mbarrier), one issuing thread per CTA: what a register-free copy role
+ * could move.  stages in {2,4,8}, tileBytes % 128 == 0; *errOut (device word, may be NULL) is set to 1 if a wait gave up.
+ * Bench only -- written without GPU access, not used by any allreduce path. */
+int aar_bench_bulk_copy(int grid, int stages, int tileBytes, const void* src, void* dst, size_t bytes, int iters, void* stream, unsigned* errOut);
+
 /* Spin kernel used by the straggler injector: busy-waits `ns` nanoseconds on `stream`. */
 int aar_launch_delay(unsigned long long ns, void* stream);
 
