@@ -357,30 +357,42 @@ std::string Config::render() const {
 AllreduceSettings AllreduceSettings::fromConfig(const Config& c) {
   AllreduceSettings s;
   MasterConfig& m = s.master;
-  m.totalWorkers = (int)c.getInt("allreduce.total-workers", m.totalWorkers);
+  // every integer is range-checked BEFORE it is narrowed to int (a value like 99999999999 must be an error, not garbage)
+  auto intIn = [&](const char* key, long def, long lo, long hi) {
+    const long v = c.getInt(key, def);
+    if (v < lo || v > hi)
+      throw std::runtime_error(std::string("config: ") + key + " = " + std::to_string(v) + " is outside " + std::to_string(lo) + ".." + std::to_string(hi));
+    return (int)v;
+  };
+  constexpr long kIntMax = 2147483647L;
+  m.totalWorkers = intIn("allreduce.total-workers", m.totalWorkers, 1, 1 << 16);
   m.thAllreduce = (float)c.getDouble("allreduce.th-allreduce", m.thAllreduce);
   m.thReduce = (float)c.getDouble("allreduce.th-reduce", m.thReduce);
   m.thComplete = (float)c.getDouble("allreduce.th-complete", m.thComplete);
-  m.maxLag = (int)c.getInt("allreduce.max-lag", m.maxLag);
-  m.maxRound = (int)c.getInt("allreduce.max-round", m.maxRound);
-  m.maxChunkSize = (int)c.getInt("allreduce.max-chunk-size", m.maxChunkSize);
+  m.maxLag = intIn("allreduce.max-lag", m.maxLag, 0, 1 << 20);
+  m.maxRound = intIn("allreduce.max-round", m.maxRound, -1, kIntMax - 1);
+  m.maxChunkSize = intIn("allreduce.max-chunk-size", m.maxChunkSize, 1, kIntMax);
   // AllreduceMaster.scala:113 -- dataSize defaults to totalWorkers * 5
-  m.dataSize = (int)c.getInt("allreduce.data-size", (long)m.totalWorkers * 5);
-  m.pipelineDepth = (int)c.getInt("allreduce.pipeline-depth", m.pipelineDepth);
+  m.dataSize = intIn("allreduce.data-size", (long)m.totalWorkers * 5, 0, kIntMax);
+  m.pipelineDepth = intIn("allreduce.pipeline-depth", m.pipelineDepth, 0, 1 << 20);
+  m.startRound = intIn("allreduce.start-round", m.startRound, 0, kIntMax - 1);
   s.dtype = c.getString("allreduce.dtype", s.dtype);
   s.algo = c.getString("allreduce.algo", s.algo);
   s.normalize = c.getBool("allreduce.normalize", s.normalize);
   s.quorumPolicy = c.getString("allreduce.quorum-policy", s.quorumPolicy);
   s.spinTimeoutUs = c.has("allreduce.spin-timeout") ? c.getDurationMs("allreduce.spin-timeout") * 1e3 : s.spinTimeoutUs;
   s.hostname = c.getString("allreduce.transport.hostname", c.getString("akka.remote.netty.tcp.hostname", s.hostname));
-  s.port = (int)c.getInt("allreduce.transport.port", s.port);
+  s.port = intIn("allreduce.transport.port", s.port, 0, 65535);
   s.heartbeatMs = c.getDurationMs("allreduce.transport.heartbeat-interval", s.heartbeatMs);
   s.autoDownAfterMs = c.getDurationMs("allreduce.transport.auto-down-unreachable-after",
                                       c.getDurationMs("akka.cluster.auto-down-unreachable-after", s.autoDownAfterMs));
   s.loglevel = c.getString("allreduce.loglevel", c.getString("akka.loglevel", s.loglevel));
-  if (m.totalWorkers <= 0) throw std::runtime_error("config: allreduce.total-workers must be positive");
-  if (m.maxLag < 0) throw std::runtime_error("config: allreduce.max-lag must be >= 0");
-  if (m.maxChunkSize <= 0) throw std::runtime_error("config: allreduce.max-chunk-size must be positive");
+  if (!(s.heartbeatMs > 0) || !(s.autoDownAfterMs > 0)) throw std::runtime_error("config: transport intervals must be positive");
+  if (s.quorumPolicy != "all-arrived" && s.quorumPolicy != "exact")
+    throw std::runtime_error("config: allreduce.quorum-policy must be all-arrived or exact");
+  bool algoOk = false;
+  for (const char* a : {"auto", "oneshot", "twoshot", "pipelined", "nvls"}) algoOk = algoOk || s.algo == a;
+  if (!algoOk) throw std::runtime_error("config: allreduce.algo must be one of auto, oneshot, twoshot, pipelined, nvls");
   for (float th : {m.thAllreduce, m.thReduce, m.thComplete})
     if (!(th > 0.f && th <= 1.f)) throw std::runtime_error("config: thresholds must be in (0, 1]");
   if (s.dtype != "fp32" && s.dtype != "bf16") throw std::runtime_error("config: allreduce.dtype must be fp32 or bf16");

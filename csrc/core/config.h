@@ -62,7 +62,7 @@ class Config {
 struct AllreduceSettings {
   MasterConfig master;           // total-workers, th-*, max-lag, data-size, max-round, max-chunk-size, pipeline-depth
   std::string dtype = "fp32";    // wire/output dtype of the CUDA data plane: fp32 | bf16
-  std::string algo = "auto";     // auto | twoshot | oneshot | nvls
+  std::string algo = "auto";     // auto | twoshot | pipelined | oneshot | nvls
   bool normalize = false;        // divide by the actual contributor count (the intent behind AllReduceOutput.count)
   std::string quorumPolicy = "all-arrived";  // all-arrived | exact
   double spinTimeoutUs = 0;      // device-side liveness guard; 0 = wait for the host doorbell only

@@ -115,3 +115,18 @@ def test_settings_validation():
         core.AllreduceSettings.from_config(core.Config.parse_string("allreduce.th-reduce = 1.5"))
     with pytest.raises(Exception, match="dtype"):
         core.AllreduceSettings.from_config(core.Config.parse_string("allreduce.dtype = fp8"))
+
+
+def test_settings_reject_out_of_range_and_unknown_values():
+    """Found by fuzzing fromConfig: a negative data-size, an integer that does not fit in 32 bits, a port above 65535 or an unknown
+    algorithm / quorum policy used to be accepted (or narrowed to garbage)."""
+    def settings(body):
+        return core.AllreduceSettings.from_config(core.Config.parse_string("allreduce {\n" + body + "\n}"))
+
+    for body in ("data-size = -1", "data-size = 99999999999", "max-round = 99999999999", "transport.port = 70000", "transport.port = -1",
+                 "pipeline-depth = -2", "algo = fastest", "quorum-policy = most", "total-workers = 0", "max-chunk-size = 0",
+                 "th-reduce = nan", "th-complete = 1.5", "start-round = -3", "transport.heartbeat-interval = 0s"):
+        with pytest.raises(Exception):
+            settings(body)
+    s = settings("start-round = 7\n algo = pipelined\n quorum-policy = exact\n data-size = 0")
+    assert s.master.start_round == 7 and s.algo == "pipelined" and s.quorum_policy == "exact" and s.master.data_size == 0
