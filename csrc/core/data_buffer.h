@@ -63,7 +63,7 @@ class DataBuffer {
     if (row < 0 || row >= peers_ || chunk < 0 || chunk >= std::max(1, maxChunks_)) throw std::out_of_range("DataBuffer::store index");
     if ((int64_t)chunk * maxChunk_ + n > rowLen_) throw std::out_of_range("DataBuffer::store overflows the row");
     int s = slotOf(round);
-    std::memcpy(rowPtr(s, row) + (size_t)chunk * maxChunk_, v, sizeof(float) * (size_t)n);
+    if (n > 0) std::memcpy(rowPtr(s, row) + (size_t)chunk * maxChunk_, v, sizeof(float) * (size_t)n);  // an empty payload may come with a null pointer
     uint8_t& a = arrived_[flagIndex(s, row, chunk)];
     aux_[flagIndex(s, row, chunk)] = aux;
     bool fresh = !a;

@@ -82,6 +82,13 @@ void Worker::allocate() {
 
 // AllreduceWorker.scala:84-104
 void Worker::onStart(const StartAllreduce& m) {
+  // The catch-up below fetches and scatters EVERY round up to m.round (AllreduceWorker.scala:98-102); a round number that
+  // is absurdly far ahead (corrupt frame, wrong master) would keep this worker busy for hours.  The master is never more
+  // than pipelineDepth + 1 rounds ahead of a quorum, and a resumed master sends its start round in InitWorkers.
+  constexpr int kMaxCatchUp = 1 << 20;
+  if (m.round < 0 || (long long)m.round - maxScattered_ > kMaxCatchUp)
+    throw std::invalid_argument("StartAllreduce: round " + std::to_string(m.round) + " is out of range (last scattered " +
+                                std::to_string(maxScattered_) + ")");
   maxRound_ = std::max(maxRound_, m.round);
   metrics_.maxLagSeen = std::max<int64_t>(metrics_.maxLagSeen, maxRound_ - round_);
   // Fell out of the maxLag window: force the oldest rounds through with whatever has arrived.
