@@ -661,9 +661,14 @@ int WorkerNode::poll(int timeoutMs) {
       bool alive = true;
       if (fds[1].revents & POLLOUT) alive = masterConn_->flush();
       if (alive && (fds[1].revents & (POLLIN | POLLHUP | POLLERR))) alive = masterConn_->readAvailable();
-      while (masterConn_->next(body)) {
-        ++handled;
-        dispatch(body);
+      try {
+        while (masterConn_->next(body)) {
+          ++handled;
+          dispatch(body);
+        }
+      } catch (const WireError& e) {  // a coordinator that speaks garbage is as good as gone (handler errors still propagate)
+        AAR_WARN("worker: protocol error on the master link: %s", e.what());
+        alive = false;
       }
       if (!alive) {
         AAR_WARN("worker: master link closed");

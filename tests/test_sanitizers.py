@@ -37,6 +37,14 @@ def test_protocol_engine_survives_hostile_messages_under_asan_ubsan(tmp_path):
         assert r.returncode == 0 and "accepted=" in r.stdout, (r.stdout + r.stderr)[-2000:]
 
 
+def test_transport_survives_garbage_on_live_sockets_under_asan_ubsan(tmp_path):
+    """csrc/tests/fuzz_wire.cpp: raw clients throw random frames at a MasterNode, a fake master does the same to WorkerNodes."""
+    exe = _build(tmp_path, "fuzz_wire", "fuzz_wire.cpp", CORE)
+    r = subprocess.run([str(exe), "1", "200"], capture_output=True, text=True, timeout=280)
+    assert "runtime error" not in r.stderr and "AddressSanitizer" not in r.stderr, r.stderr[-3000:]
+    assert r.returncode == 0 and "0 threw" in r.stdout, (r.stdout + r.stderr)[-2000:]
+
+
 def test_tcp_cluster_is_clean_under_asan_ubsan(tmp_path):
     exe = _build(tmp_path, "asan_cluster", "tsan_cluster.cpp", CORE)
     r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=280)
