@@ -154,6 +154,14 @@ void loadWorkerCheckpoint(const std::string& path, Worker& w) {
   if (s.maxLag < 0 || s.dataSize < 0 || s.maxChunkSize <= 0 || s.numPeers <= 0 || (size_t)s.numPeers != peers.size() ||
       (uint64_t)(s.maxLag + 1) * (uint64_t)s.dataSize * sizeof(float) > in.size)
     throw std::runtime_error("checkpoint: worker fields are inconsistent with the file");
+  // round bookkeeping as the state machine leaves it after any message: round <= maxScattered + 1 <= maxRound + 1, and the
+  // catch-up loop keeps round within maxLag of maxRound.  A file that says otherwise would send the restored worker into a
+  // catch-up of billions of rounds on its next StartAllreduce.
+  if (s.round < 0 || s.maxScattered < -1 || s.maxRound < -1 || s.maxScattered > s.maxRound || s.round > s.maxScattered + 1 ||
+      (long long)s.maxRound - s.round > (long long)s.maxLag + 1 || s.id < 0 || s.id >= s.numPeers)
+    throw std::runtime_error("checkpoint: worker round state is inconsistent");
+  for (int r : s.completed)
+    if (r < s.round || r > s.maxRound) throw std::runtime_error("checkpoint: completed set is inconsistent with the round state");
   w.restore(s, peers, master);
   readBuffer(in, w.scatterBuffer());
   readBuffer(in, w.reduceBuffer());

@@ -45,6 +45,17 @@ def test_transport_survives_garbage_on_live_sockets_under_asan_ubsan(tmp_path):
     assert r.returncode == 0 and "0 threw" in r.stdout, (r.stdout + r.stderr)[-2000:]
 
 
+def test_checkpoint_loaders_refuse_damaged_files_under_asan_ubsan(tmp_path):
+    """csrc/tests/fuzz_checkpoint.cpp: valid worker / master / ring files flipped, truncated and spliced at random, then loaded (and the
+    restored worker is driven one step).  First run found a restored round state that sent the worker into a catch-up of billions
+    of rounds; the loader now checks the state machine's invariants."""
+    exe = _build(tmp_path, "fuzz_checkpoint", "fuzz_checkpoint.cpp", ["worker.cpp", "master.cpp", "checkpoint.cpp"])
+    for seed in (1, 3):
+        r = subprocess.run([str(exe), str(seed), "800", str(tmp_path)], capture_output=True, text=True, timeout=280)
+        assert "runtime error" not in r.stderr and "AddressSanitizer" not in r.stderr, r.stderr[-3000:]
+        assert r.returncode == 0 and "refused=" in r.stdout, (r.stdout + r.stderr)[-2000:]
+
+
 def test_tcp_cluster_is_clean_under_asan_ubsan(tmp_path):
     exe = _build(tmp_path, "asan_cluster", "tsan_cluster.cpp", CORE)
     r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=280)
