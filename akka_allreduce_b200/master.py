@@ -48,7 +48,8 @@ class AllreduceMaster:
     def from_settings(cls, s: core.AllreduceSettings, **kw):
         m = s.master
         return cls(m.total_workers, m.th_allreduce, m.th_reduce, m.th_complete, m.max_lag, m.data_size, m.max_round, m.max_chunk_size,
-                   pipeline_depth=m.pipeline_depth, host=s.hostname, port=s.port, auto_down_after_ms=s.auto_down_after_ms, **kw)
+                   pipeline_depth=m.pipeline_depth, host=s.hostname, port=s.port, auto_down_after_ms=s.auto_down_after_ms,
+                   **{"start_round": m.start_round, **kw})
 
     @property
     def port(self) -> int:
