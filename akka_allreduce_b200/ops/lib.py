@@ -109,6 +109,15 @@ def load():
         "aar_launch_delay": [C.c_ulonglong, C.c_void_p],
         "aar_bench_all2all": [C.c_int, C.c_int, C.c_int, P(C.c_void_p), C.c_int, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p],
         "aar_bench_link": [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p],
+        "aar_engine_create": [P(AarLayout), C.c_int, P(C.c_void_p), C.c_void_p, C.c_int, C.c_int, C.c_uint, C.c_ulonglong, C.c_int, C.c_int, C.c_int,
+                              P(C.c_void_p)],
+        "aar_engine_tune": [C.c_void_p, C.c_int, C.c_int],
+        "aar_engine_enqueue": [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint, C.c_void_p],
+        "aar_engine_wait": [C.c_void_p, C.c_int, C.c_void_p],
+        "aar_engine_synchronize": [C.c_void_p],
+        "aar_engine_set_doorbell": [C.c_void_p, C.c_int],
+        "aar_engine_rounds_flushed": [C.c_void_p],
+        "aar_engine_destroy": [C.c_void_p],
         "aar_bench_bulk_copy": [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p],
     }
     for name, argtypes in sigs.items():

@@ -75,6 +75,10 @@ class RoundEngine:
         self.rounds_enqueued = 0
         self.launches = 0
         self._nvtx = os.environ.get("AAR_NVTX", "0") not in ("", "0")   # one NVTX range per round launch (off by default)
+        # Opt-in (AAR_NATIVE_ENGINE=1, first hardware run pending): the per-round host work -- order after the caller's stream,
+        # launch, record the slot's event -- in ONE C call (csrc/cuda/aar_engine.cu) instead of four torch / ctypes calls.
+        self._native = None
+        self._slot_round = [-1] * layout.L
         # CTA role split of the pipelined kernels (measured on 8xB200, profiles/r1_phase_bench_*.txt)
         self.split = 32 | (48 << 16)      # nPush | nReduce << 16; the rest gather
         self.nvls_reduce_ctas = 8        # 207.7 us with 8 vs 222 us with 16 reduce CTAs at 8 GPUs, 64 MiB
@@ -86,6 +90,13 @@ class RoundEngine:
         with torch.cuda.device(self.device):
             self._streams = [torch.cuda.Stream(device=self.device) for _ in range(2)] if self.overlap else []
             self._events = [torch.cuda.Event() for _ in range(layout.L)]
+            if os.environ.get("AAR_NATIVE_ENGINE", "0") not in ("", "0"):
+                regs = (C.c_void_p * layout.P)(*[region_ptrs[j] for j in range(layout.P)])
+                h = C.c_void_p(0)
+                code = {"twoshot": 0, "pipelined": 1, "oneshot": 2, "nvls": 3}[self.algo]
+                L.check(self.lib.aar_engine_create(self._lay, rank, regs, C.c_void_p(mc_ptr or None), p.minRequired, p.minChunksRequired,
+                                                   self.base_flags, p.timeoutNs, code, grid, int(self.overlap), C.byref(h)), "aar_engine_create")
+                self._native = h
 
     # ------------------------------------------------------------------ construction helpers
     @classmethod
@@ -123,9 +134,14 @@ class RoundEngine:
     # ------------------------------------------------------------------ rounds
     def set_doorbell(self, newest_round: int) -> None:
         """Host side of StartAllreduce: kernels that wait compare this with their round (catch-up when > maxLag behind)."""
+        if self._native is not None:
+            self.lib.aar_engine_set_doorbell(self._native, int(newest_round))
+            return
         self._host_words[0] = max(int(self._host_words[0]), newest_round) if newest_round >= 0 else 0
 
     def rounds_flushed(self) -> int:
+        if self._native is not None:
+            return int(self.lib.aar_engine_rounds_flushed(self._native))
         return int(self._host_words[1])
 
     def enqueue_round(self, rnd: int, x: torch.Tensor, *, stream: torch.cuda.Stream | None = None, force: bool = False,
@@ -138,6 +154,17 @@ class RoundEngine:
                              f"(AllreduceWorker.scala:174-176 rejects a size that differs from initialisation)")
         slot = rnd % self.layout.L
         output = self.outputs[slot] if out is None else out
+        if self._native is not None:
+            if stream is not None or delay_ns > 0:
+                raise NotImplementedError("the native engine picks its own stream and has no straggler injector")
+            extra = (L.FLAG_FORCE if force else 0) | (L.FLAG_SKIP_SCATTER if skip_scatter else 0)
+            L.check(self.lib.aar_engine_enqueue(self._native, rnd, C.c_void_p(x.data_ptr()), C.c_void_p(output.data_ptr()),
+                                                C.c_void_p(self.counts[slot].data_ptr()), extra,
+                                                C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)), "aar_engine_enqueue")
+            self._slot_round[slot] = rnd
+            self.launches += 1
+            self.rounds_enqueued = max(self.rounds_enqueued, rnd + 1)
+            return output, self.counts[slot]
         p = self.params
         p.round = rnd
         p.input = x.data_ptr()
@@ -191,15 +218,27 @@ class RoundEngine:
 
     def wait_round(self, rnd: int, stream: torch.cuda.Stream | None = None) -> None:
         """Make `stream` (default: the current stream) wait for round `rnd`; call before consuming its output on a stream."""
+        if self._native is not None:
+            st = stream or torch.cuda.current_stream(self.device)
+            L.check(self.lib.aar_engine_wait(self._native, rnd, C.c_void_p(st.cuda_stream)), "aar_engine_wait")
+            return
         (stream or torch.cuda.current_stream(self.device)).wait_event(self._events[rnd % self.layout.L])
 
     def synchronize(self) -> None:
         """Host waits until every launched round of this rank has finished."""
+        if self._native is not None:
+            L.check(self.lib.aar_engine_synchronize(self._native), "aar_engine_synchronize")
+            return
         for ev in self._events:
             ev.synchronize()
 
     def wait_all(self, stream: torch.cuda.Stream | None = None) -> None:
         st = stream or torch.cuda.current_stream(self.device)
+        if self._native is not None:
+            for r in self._slot_round:
+                if r >= 0:
+                    L.check(self.lib.aar_engine_wait(self._native, r, C.c_void_p(st.cuda_stream)), "aar_engine_wait")
+            return
         for ev in self._events:
             st.wait_event(ev)
 
@@ -245,6 +284,8 @@ class RoundEngine:
         """Begin the round numbering at `rnd` on a fresh engine (a master that resumed from a checkpoint): every rank counts as
         having retired all earlier rounds, so the slot flow control of round `rnd` has nothing to wait for.  Every rank calls
         this on its own region before the first launch (the worker does, between mapping the regions and its first round)."""
+        if self._native is not None:
+            raise NotImplementedError("start_at / restore are not wired into the native engine yet (it owns its completion word)")
         lay = self.layout
         self._region_view(lay.peerBaseOff, L.AAR_MAXP * 4, torch.int32)[: lay.P] = rnd
         self._region_view(lay.statusOff, 8, torch.int32)[1] = rnd
@@ -255,6 +296,8 @@ class RoundEngine:
     def restore(self, s: "core.RingSnapshot") -> None:
         """Inverse of snapshot(): the ring payload and the arrival words go back into this rank's region; round numbering
         continues at s.round.  The geometry must match."""
+        if self._native is not None:
+            raise NotImplementedError("start_at / restore are not wired into the native engine yet (it owns its completion word)")
         lay = self.layout
         if (s.P, s.L, s.data_size, s.max_chunk_size) != (lay.P, lay.L, lay.dataSize, lay.maxChunk):
             raise ValueError("ring snapshot was taken with a different geometry")
@@ -283,6 +326,9 @@ class RoundEngine:
                 "rounds_in_flight": 2 if self.overlap else 1, "multicast": bool(self.mc_ptr)}
 
     def close(self) -> None:
+        if self._native is not None:
+            self.lib.aar_engine_destroy(self._native)
+            self._native = None
         if self._host_words:
             self.lib.aar_host_words_free(self._host_words)
             self._host_words = None

@@ -183,6 +183,28 @@ int aar_host_words_free(unsigned* hostPtr);
 int aar_device_sm_count(int device, int* out);
 int aar_enable_peer_access(int device, int peer);
 
+/* ---------------------------------------------------------------------------------------------------------------------
+ * Native round engine: what parallel/engine.py does per round (order after the caller's stream, pick the kernel, launch,
+ * record the slot's event; two internal streams so that consecutive rounds overlap) behind one C call, for C/C++ callers and
+ * as a cheaper enqueue path for the Python engine (AAR_NATIVE_ENGINE=1).  Written without GPU access: opt-in, not used by
+ * any default path yet.  algo: 0 two-shot fused, 1 pipelined P2P, 2 one-shot, 3 NVLS.  The engine owns its doorbell and
+ * completion words (pinned host memory); regions[] are the peers' regions as mapped here (AarRankParams.region). */
+typedef struct AarEngine AarEngine;
+int aar_engine_create(const AarLayout* layout, int rank, void* const* regions, void* mcRegion, int minRequired, int minChunksRequired,
+                      unsigned flags, unsigned long long timeoutNs, int algo, int grid, int overlap, AarEngine** out);
+/* knobs of the role-specialised kernels (0 keeps the default): split = nPush | nReduce << 16, nvlsCtas = nReduce | nStage << 8 */
+int aar_engine_tune(AarEngine* e, int split, int nvlsCtas);
+/* Launch round `round`: input / output / outCounts as in AarRankParams; extraFlags are OR-ed into the engine's flags for this
+ * round (AAR_FLAG_FORCE, AAR_FLAG_SKIP_SCATTER).  callerStream: the stream that produced `input` (the round is ordered after
+ * what it holds now).  With overlap the round runs on an internal stream; use aar_engine_wait before consuming the output. */
+int aar_engine_enqueue(AarEngine* e, int round, const void* input, void* output, int* outCounts, unsigned extraFlags, void* callerStream);
+int aar_engine_wait(AarEngine* e, int round, void* stream);   /* `stream` waits for the round (no host blocking) */
+int aar_engine_synchronize(AarEngine* e);                      /* host waits for every launched round */
+int aar_engine_set_doorbell(AarEngine* e, int newestRound);    /* StartAllreduce from the master: monotone */
+int aar_engine_rounds_flushed(AarEngine* e);                   /* completion word written by the last CTA of a round */
+long long aar_engine_launches(AarEngine* e);
+int aar_engine_destroy(AarEngine* e);
+
 /* Link micro-benchmark (roofline denominators): mode 0 multimem.ld_reduce, 1 multimem.st, 2 both, 3 peer load, 4 peer
  * store, 5 local copy; buffers hold 2 * bytes; `iters` launches on `stream`, timed by the caller. */
 int aar_bench_link(int mode, int grid, int unroll, void* mc, void* peer, void* local, size_t bytes, int iters, void* stream);

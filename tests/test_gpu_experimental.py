@@ -128,3 +128,23 @@ def test_late_rank_elides_work_nobody_will_read():
     assert torch.equal(out3[: 3 * geo_block], want_others[: 3 * geo_block])
     assert torch.equal(out3[3 * geo_block:], want_own[3 * geo_block:])
     assert cl.status(3) == 0
+
+
+def test_native_engine_runs_the_same_rounds_as_the_python_engine(monkeypatch):
+    """AAR_NATIVE_ENGINE=1 (csrc/cuda/aar_engine.cu): one C call per round instead of the Python stream / event choreography.
+    Single rank, ring of two slots reused three times: bit-exact, completion word advances, counts filled."""
+    from akka_allreduce_b200.parallel.engine import RoundEngine
+
+    monkeypatch.setenv("AAR_NATIVE_ENGINE", "1")
+    n = 1 << 16
+    eng = RoundEngine.single_process(n, 1 << 12, max_lag=1, timeout_ms=2000.0)
+    assert eng._native is not None
+    for rnd in range(6):
+        x = make_inputs(1, n, torch.float32, 800 + rnd)[0]
+        out, counts = eng.enqueue_round(rnd, x)
+        eng.wait_round(rnd)
+        torch.cuda.synchronize()
+        assert torch.equal(out, x) and int(counts.min()) == 1
+    eng.synchronize()
+    assert eng.rounds_flushed() == 6 and eng.launches == 6
+    eng.close()
