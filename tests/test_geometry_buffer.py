@@ -90,3 +90,32 @@ def test_c_abi_structs_match_the_ctypes_declarations():
     assert (lay.reduceOff, lay.stageOff, lay.sflagOff, lay.traceOff, lay.regionBytes) == (134217728, 268435456, 402653184, 402656768, 404750336)
     offs = [getattr(lay, f) for f, _ in L.AarLayout._fields_ if f.endswith("Off") and getattr(lay, f)]
     assert len(set(offs)) == len(offs) and max(offs) == lay.egDecOff and lay.egDecOff + lay.L * lay.P * lay.C * 8 <= lay.regionBytes
+
+
+def test_c_header_is_plain_c_and_the_native_engine_example_links(tmp_path):
+    """examples/native_round.c: a C (not C++) caller of include/akka_allreduce_b200.h -- layout, local region, native round engine.
+    On a box without a GPU it must stop at the first CUDA call with a clean error (exit 3), with a GPU it runs four rounds."""
+    import shutil
+    import subprocess
+    from pathlib import Path
+
+    import pytest
+
+    from akka_allreduce_b200.ops import lib as L
+
+    root = Path(__file__).resolve().parents[1]
+    cuda = Path("/usr/local/cuda")
+    if shutil.which("gcc") is None or not (cuda / "include/cuda_runtime.h").exists():
+        pytest.skip("needs gcc and the CUDA headers")
+    L.load()
+    so = L.lib_path()
+    exe = tmp_path / "native_round"
+    b = subprocess.run(["gcc", "-std=c11", "-Wall", "-Werror", f"-I{root / 'include'}", f"-I{cuda / 'include'}", str(root / "examples/native_round.c"), "-o", str(exe),
+                        str(so), f"-L{cuda / 'lib64'}", "-lcudart", f"-Wl,-rpath,{so.parent}"], capture_output=True, text=True, timeout=120)
+    assert b.returncode == 0, b.stderr[-2000:]
+    r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=120)
+    assert r.returncode in (0, 3), (r.stdout + r.stderr)[-1000:]
+    if r.returncode == 0:
+        assert "4 rounds flushed, 0 mismatches" in r.stdout
+    else:
+        assert "failed" in r.stderr
