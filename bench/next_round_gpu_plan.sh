@@ -16,6 +16,7 @@ one)
   timeout 600 python -m pytest tests -x -q -m gpu 2>&1 | tail -5 | tee gpurun_out/r2_gpu_suite.txt
   AAR_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_gpu_experimental.py -q -m gpu 2>&1 | tail -15 | tee gpurun_out/r2_experimental.txt
   timeout 300 python bench.py --steps 30 --warmup 5 | tee gpurun_out/r2_bench_n1.json
+  timeout 300 python -m pytest tests/test_geometry_buffer.py -q -k native_engine_example 2>&1 | tail -3 | tee gpurun_out/r2_c_example.txt
   AAR_NATIVE_ENGINE=1 timeout 300 python bench.py --steps 30 --warmup 5 --no-e2e | tee gpurun_out/r2_bench_n1_native.json
   ;;
 two)
