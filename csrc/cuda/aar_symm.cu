@@ -170,18 +170,27 @@ static int mapAndAccess(CUmemGenericAllocationHandle h, size_t bytes, int device
   DRV(cuMemAddressReserve, CUresult(*)(CUdeviceptr*, size_t, size_t, CUdeviceptr, unsigned long long));
   DRV(cuMemMap, CUresult(*)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long));
   DRV(cuMemSetAccess, CUresult(*)(CUdeviceptr, size_t, const CUmemAccessDesc*, size_t));
+  DRV(cuMemUnmap, CUresult(*)(CUdeviceptr, size_t));
+  DRV(cuMemAddressFree, CUresult(*)(CUdeviceptr, size_t));
   CUdeviceptr va = 0;
   CUresult r = cuMemAddressReserve(&va, bytes, 0, 0, 0);
   if (r != CUDA_SUCCESS) return fail(AAR_ECUDA, "cuMemAddressReserve(%zu): %s", bytes, cuErr(r));
   r = cuMemMap(va, bytes, 0, h, 0);
-  if (r != CUDA_SUCCESS) return fail(AAR_ECUDA, "cuMemMap: %s", cuErr(r));
+  if (r != CUDA_SUCCESS) {
+    cuMemAddressFree(va, bytes);  // failure paths give back what they took
+    return fail(AAR_ECUDA, "cuMemMap: %s", cuErr(r));
+  }
   CUmemAccessDesc acc;
   memset(&acc, 0, sizeof acc);
   acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
   acc.location.id = device;
   acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
   r = cuMemSetAccess(va, bytes, &acc, 1);
-  if (r != CUDA_SUCCESS) return fail(AAR_ECUDA, "cuMemSetAccess(device %d): %s", device, cuErr(r));
+  if (r != CUDA_SUCCESS) {
+    cuMemUnmap(va, bytes);
+    cuMemAddressFree(va, bytes);
+    return fail(AAR_ECUDA, "cuMemSetAccess(device %d): %s", device, cuErr(r));
+  }
   *ptr = reinterpret_cast<void*>(va);
   return AAR_OK;
 }
@@ -193,19 +202,35 @@ AAR_API int aar_vmm_create(int device, size_t bytes, AarVmm* out) {
   cudaFree(0);
   DRV(cuMemCreate, CUresult(*)(CUmemGenericAllocationHandle*, size_t, const CUmemAllocationProp*, unsigned long long));
   DRV(cuMemExportToShareableHandle, CUresult(*)(void*, CUmemGenericAllocationHandle, CUmemAllocationHandleType, unsigned long long));
+  DRV(cuMemRelease, CUresult(*)(CUmemGenericAllocationHandle));
   CUmemAllocationProp prop = deviceProp(device);
   CUmemGenericAllocationHandle h = 0;
   CUresult r = cuMemCreate(&h, bytes, &prop, 0);
   if (r != CUDA_SUCCESS) return fail(AAR_ECUDA, "cuMemCreate(%zu bytes on device %d): %s (size must be a multiple of the granularity)", bytes, device, cuErr(r));
   void* ptr = nullptr;
   int rc = mapAndAccess(h, bytes, device, &ptr);
-  if (rc) return rc;
+  if (rc) {
+    cuMemRelease(h);
+    return rc;
+  }
+  AarVmm partial;  // what aar_vmm_release needs to undo the steps above
+  partial.handle = (uint64_t)h;
+  partial.ptr = ptr;
+  partial.bytes = bytes;
+  partial.fd = -1;
+  partial.device = device;
   ce = cudaMemset(ptr, 0, bytes);
   if (ce == cudaSuccess) ce = cudaDeviceSynchronize();
-  if (ce != cudaSuccess) return fail(AAR_ECUDA, "zero-fill of the region failed: %s", cudaGetErrorString(ce));
+  if (ce != cudaSuccess) {
+    aar_vmm_release(&partial);
+    return fail(AAR_ECUDA, "zero-fill of the region failed: %s", cudaGetErrorString(ce));
+  }
   int fd = -1;
   r = cuMemExportToShareableHandle(&fd, h, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0);
-  if (r != CUDA_SUCCESS) return fail(AAR_ECUDA, "cuMemExportToShareableHandle: %s", cuErr(r));
+  if (r != CUDA_SUCCESS) {
+    aar_vmm_release(&partial);
+    return fail(AAR_ECUDA, "cuMemExportToShareableHandle: %s", cuErr(r));
+  }
   out->handle = (uint64_t)h;
   out->ptr = ptr;
   out->bytes = bytes;
@@ -218,12 +243,16 @@ AAR_API int aar_vmm_import(int device, int fd, size_t bytes, AarVmm* out) {
   if (!out || fd < 0) return fail(AAR_EINVAL, "aar_vmm_import: bad arguments");
   cudaFree(0);
   DRV(cuMemImportFromShareableHandle, CUresult(*)(CUmemGenericAllocationHandle*, void*, CUmemAllocationHandleType));
+  DRV(cuMemRelease, CUresult(*)(CUmemGenericAllocationHandle));
   CUmemGenericAllocationHandle h = 0;
   CUresult r = cuMemImportFromShareableHandle(&h, reinterpret_cast<void*>(static_cast<uintptr_t>(fd)), CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
   if (r != CUDA_SUCCESS) return fail(AAR_ECUDA, "cuMemImportFromShareableHandle(fd %d): %s", fd, cuErr(r));
   void* ptr = nullptr;
   int rc = mapAndAccess(h, bytes, device, &ptr);
-  if (rc) return rc;
+  if (rc) {
+    cuMemRelease(h);
+    return rc;
+  }
   out->handle = (uint64_t)h;
   out->ptr = ptr;
   out->bytes = bytes;
@@ -272,7 +301,12 @@ AAR_API int aar_mc_create(int nDevices, size_t bytes, uint64_t* mcHandle, int* f
   if (r != CUDA_SUCCESS) return fail(AAR_ECUDA, "cuMulticastCreate(%d devices, %zu bytes): %s", nDevices, bytes, cuErr(r));
   int f = -1;
   r = cuMemExportToShareableHandle(&f, h, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0);
-  if (r != CUDA_SUCCESS) return fail(AAR_ECUDA, "export of the multicast handle: %s", cuErr(r));
+  if (r != CUDA_SUCCESS) {
+    using rel_fn = CUresult (*)(CUmemGenericAllocationHandle);
+    rel_fn rel = nullptr;
+    if (driverFn("cuMemRelease", &rel)) rel(h);
+    return fail(AAR_ECUDA, "export of the multicast handle: %s", cuErr(r));
+  }
   *mcHandle = (uint64_t)h;
   *fd = f;
   return AAR_OK;
