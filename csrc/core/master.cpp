@@ -85,7 +85,10 @@ void Master::advance() {
   }
   // Reference clock: start round r+1 when round r reached quorum and r < maxRound.  With a pipeline
   // depth d the master may be d rounds ahead of the newest quorum.
-  while (round_ < cfg_.maxRound && round_ < quorumRound_ + 1 + cfg_.pipelineDepth) {
+  // The depth is capped at maxLag: a master further ahead than the workers' window would make them force-complete rounds
+  // that nothing is wrong with (found by csrc/tests/fuzz_cluster.cpp: thresholds 1.0, no faults, partial sums).
+  const int depth = std::min(cfg_.pipelineDepth, cfg_.maxLag);
+  while (round_ < cfg_.maxRound && round_ < quorumRound_ + 1 + depth) {
     round_++;
     startAllreduce(round_);
   }

@@ -103,9 +103,13 @@ void Worker::onStart(const StartAllreduce& m) {
   }
   // Every round number is fetched and scattered exactly once, in order.
   while (maxScattered_ < maxRound_) {
-    fetch(maxScattered_ + 1);
-    scatter(maxScattered_ + 1);
+    const int r = maxScattered_ + 1;
+    fetch(r);
+    scatter(r);
     maxScattered_ += 1;
+    // An empty vector has no chunk whose arrival could complete the round: it is complete as soon as it is scattered
+    // (found by csrc/tests/fuzz_cluster.cpp: dataSize = 0 used to wait forever).
+    if (geo_.totalChunks() == 0 && r >= round_ && !completed_.count(r)) complete(r, /*forced=*/false);
   }
   for (auto it = completed_.begin(); it != completed_.end();) it = (*it < round_) ? completed_.erase(it) : std::next(it);
 }

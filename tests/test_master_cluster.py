@@ -101,7 +101,7 @@ def test_termination_removes_worker_and_ids_are_redensified_on_reinit():
 
 def test_pipelined_round_clock():
     r = Recorder()
-    m = core.Master(cfg(total_workers=1, max_round=10, pipeline_depth=2), r.port, 0)
+    m = core.Master(cfg(total_workers=1, max_round=10, pipeline_depth=2, max_lag=2), r.port, 0)
     m.member_up(1, "worker")
     assert m.round == 2  # rounds 0,1,2 issued up front
     m.receive(core.CompleteAllreduce(0, 0, 1))
@@ -110,6 +110,10 @@ def test_pipelined_round_clock():
     assert m.round == 3
     m.receive(core.CompleteAllreduce(0, 1, 1))
     assert m.round == 5 and m.quorum_round == 2
+    # the depth is capped at maxLag: further ahead, workers would force-complete rounds that nothing is wrong with
+    capped = core.Master(cfg(total_workers=1, max_round=10, pipeline_depth=5, max_lag=1), Recorder().port, 0)
+    capped.member_up(1, "worker")
+    assert capped.round == 1
 
 
 # ------------------------------------------------------------------ full in-process clusters

@@ -56,6 +56,19 @@ def test_checkpoint_loaders_refuse_damaged_files_under_asan_ubsan(tmp_path):
         assert r.returncode == 0 and "refused=" in r.stdout, (r.stdout + r.stderr)[-2000:]
 
 
+def test_random_clusters_keep_the_invariants_under_asan_ubsan(tmp_path):
+    """csrc/tests/fuzz_cluster.cpp: whole in-process clusters with random geometry (uneven and empty blocks, dataSize 0), thresholds,
+    ring and pipeline depth, message loss, parked workers and late joiners.  Every flushed element must be count x input, nothing
+    is flushed twice, and a fault-free run at thresholds 1.0 flushes every round on every worker with count = P.  (First run found
+    a pipeline depth above maxLag forcing partial sums in a fault-free run -- the master now caps it -- and dataSize = 0 never
+    completing.)"""
+    exe = _build(tmp_path, "fuzz_cluster", "fuzz_cluster.cpp", ["worker.cpp", "master.cpp", "local_cluster.cpp"])
+    for seed in (1, 2):
+        r = subprocess.run([str(exe), str(seed), "250"], capture_output=True, text=True, timeout=280)
+        assert "runtime error" not in r.stderr and "AddressSanitizer" not in r.stderr, r.stderr[-3000:]
+        assert r.returncode == 0 and "violations=0" in r.stdout, (r.stdout + r.stderr)[-2000:]
+
+
 def test_tcp_cluster_is_clean_under_asan_ubsan(tmp_path):
     exe = _build(tmp_path, "asan_cluster", "tsan_cluster.cpp", CORE)
     r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=280)
