@@ -1,5 +1,5 @@
 // Whole in-process clusters under AddressSanitizer / UBSan: random geometry (including uneven and empty blocks), thresholds, ring
-// depth, pipeline depth, message loss, parked (straggling) workers, late joiners and terminated workers.
+// depth, pipeline depth, message loss, parked (straggling) workers and late joiners.
 //
 // Invariants checked on every flushed vector (the ones the reference's tests pin for one worker, here for all of them):
 //   * no worker flushes a round twice; rounds below startRound are never flushed;
