@@ -594,7 +594,9 @@ Connection* WorkerNode::peer(int id) {
   auto ep = endpoints_.find(id);
   if (ep == endpoints_.end()) return nullptr;
   try {
-    auto c = std::make_unique<Connection>(connectTo(ep->second.host, ep->second.port, 10.0));
+    // Every worker listens before it joins the master, so by the time InitWorkers names a peer that peer accepts connections:
+    // a refusal means it is gone.  A short patience (not the 10 s of a start-up race) keeps the survivors of a crash moving.
+    auto c = std::make_unique<Connection>(connectTo(ep->second.host, ep->second.port, 1.0));
     Connection* raw = c.get();
     outPeers_[id] = std::move(c);
     return raw;
