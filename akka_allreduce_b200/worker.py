@@ -49,6 +49,7 @@ class AllreduceWorker:
         self.delivered = 0          # rounds handed to the sink (= reference `round` on this in-order data plane)
         self.rounds_forced = 0
         self.lag_hist: dict[int, int] = {}   # (master's newest round - round) at the moment a round reached the sink
+        self.master_lost = False    # run() ended because the coordinator's link closed without a Shutdown
         self.start_round = 0        # first round of this incarnation (> 0 when the master resumed from a checkpoint)
         self._t_first: float | None = None   # wall clock of the first / latest delivery (rounds_per_sec in metrics())
         self._t_last = 0.0
@@ -82,6 +83,7 @@ class AllreduceWorker:
         if self.backend == "cpu":
             ok = self.node.run(timeout_sec)
             self.id = self._cpu_worker.id
+            self.master_lost = ok and not self.node.shutdown_by_master
             return ok
         deadline = time.time() + timeout_sec
         while not self.node.shutdown_requested and time.time() < deadline:
@@ -89,6 +91,8 @@ class AllreduceWorker:
             self.node.poll(0 if busy else 2)
             self._deliver_flushed()
         self._drain()
+        # True also when the master's link closed without a Shutdown message: `master_lost` tells the two apart
+        self.master_lost = self.node.shutdown_requested and not self.node.shutdown_by_master
         return self.node.shutdown_requested
 
     def step(self, timeout_ms: int = 0) -> None:

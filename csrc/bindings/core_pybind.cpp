@@ -378,6 +378,7 @@ PYBIND11_MODULE(_core, m) {
       .def_property_readonly("listen_port", &WorkerNode::listenPort)
       .def_property_readonly("shutdown_requested", &WorkerNode::shutdownRequested)
       .def_property_readonly("master_alive", &WorkerNode::masterAlive)
+      .def_property_readonly("shutdown_by_master", &WorkerNode::shutdownByMaster)
       .def("poll", &WorkerNode::poll, py::arg("timeout_ms") = 0, py::call_guard<py::gil_scoped_release>())
       .def("run", &WorkerNode::run, py::arg("timeout_sec") = 60.0, py::call_guard<py::gil_scoped_release>())
       .def("send_complete",

@@ -66,7 +66,11 @@ int main(int argc, char** argv) {
     self = &worker;
     node.setHandler([&](const Message& m) { worker.receive(m); });
     bool ok = node.run(args.timeoutSec);
-    printf("worker %d: shutdown=%d rounds_flushed=%ld mismatches=%ld\n", worker.id(), ok ? 1 : 0, flushed, bad);
+    // shutdown=1: the master said so; master_lost=1: its link closed without a Shutdown (crash, network) -- a different exit code,
+    // so that a supervisor can tell "job done" from "coordinator gone"
+    const bool lost = ok && !node.shutdownByMaster();
+    printf("worker %d: shutdown=%d master_lost=%d rounds_flushed=%ld mismatches=%ld\n", worker.id(), ok ? 1 : 0, lost ? 1 : 0, flushed, bad);
+    if (lost) return 3;
     return (ok && bad == 0) ? 0 : 2;
   } catch (const std::exception& e) {
     fprintf(stderr, "aar_worker: %s\n", e.what());

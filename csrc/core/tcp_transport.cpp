@@ -623,6 +623,7 @@ void WorkerNode::dispatch(const Frame& body) {
   uint8_t type = (uint8_t)body.data[0];
   if (type == wire::Shutdown) {
     shutdown_ = true;
+    shutdownByMaster_ = true;
     return;
   }
   Message msg;

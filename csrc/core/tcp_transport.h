@@ -80,6 +80,8 @@ class WorkerNode : public WorkerPort {
   int listenPort() const { return listenPort_; }
   bool shutdownRequested() const { return shutdown_; }
   bool masterAlive() const { return masterConn_ != nullptr; }
+  // true: the master sent Shutdown (job done); false with shutdownRequested(): its link closed without one (coordinator gone)
+  bool shutdownByMaster() const { return shutdownByMaster_; }
   int poll(int timeoutMs);
   // Loop until the master says Shutdown, the master link drops, or the timeout expires.
   bool run(double timeoutSec);
@@ -97,6 +99,7 @@ class WorkerNode : public WorkerPort {
   std::map<int, std::unique_ptr<Connection>> outPeers_;
   std::vector<std::unique_ptr<Connection>> inPeers_;
   bool shutdown_ = false;
+  bool shutdownByMaster_ = false;
 };
 
 }  // namespace aar

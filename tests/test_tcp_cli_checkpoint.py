@@ -285,3 +285,21 @@ def test_cluster_survives_a_worker_killed_mid_run():
         flushed = int(wo.split("rounds_flushed=")[1].split()[0])
         assert flushed >= 3001 - 3, wo      # every round (a few may have been force-completed twice is impossible; at most skipped never)
     ws[2].wait(timeout=10)
+
+
+def test_workers_tell_a_lost_master_from_a_finished_job():
+    """The master is killed mid-run: its workers stop (the link closed) but report master_lost=1 and exit with 3, not 0."""
+    import signal
+
+    build.build_cli()
+    port = _free_port()
+    common = ["--set", f"allreduce.transport.port={port}", "--set", "allreduce.loglevel=ERROR", "--timeout", "60"]
+    m = subprocess.Popen([str(ROOT / "bin/aar_master"), str(port), "2", "10", "2", "--set", "allreduce.max-round=100000000", *common],
+                         stdout=subprocess.PIPE, text=True, cwd=ROOT)
+    ws = [subprocess.Popen([str(ROOT / "bin/aar_worker"), "0", "10", *common], stdout=subprocess.PIPE, text=True, cwd=ROOT) for _ in range(2)]
+    time.sleep(0.5)
+    m.send_signal(signal.SIGKILL)
+    m.wait(timeout=10)
+    for w in ws:
+        wo, _ = w.communicate(timeout=60)
+        assert w.returncode == 3 and "master_lost=1" in wo, (w.returncode, wo)
