@@ -246,6 +246,10 @@ class AllreduceWorker:
             time.sleep(0)  # blocking mode: yield until the next round flushes
 
     def _drain(self) -> None:
+        """The job is over (Shutdown, lost master or timeout).  Rounds still in flight here can only be ones the master no longer
+        waits for (thAllreduce < 1) or ones whose peers are gone: ring the doorbell far ahead so that their device-side waits give
+        up instead of spinning on peers that have exited, then deliver what they flush."""
         if self.engine is not None:
+            self.engine.set_doorbell(1 << 30)
             self.engine.synchronize()
             self._deliver_flushed()
