@@ -238,6 +238,20 @@ class Connection {
       if (!flush()) return;
     }
   }
+  // Orderly goodbye: no more writes from this side, and whatever the peer still sends is read and thrown away.  Closing a
+  // socket with unread input makes the kernel answer with RST, and an RST lets the peer's kernel discard data it has not
+  // read yet -- such as the Shutdown frame just sent.  Returns false once the peer has closed its side.
+  void finishWrites() { ::shutdown(fd_, SHUT_WR); }
+  bool discardInput() {
+    char buf[65536];
+    for (;;) {
+      ssize_t n = ::recv(fd_, buf, sizeof buf, 0);
+      if (n > 0) continue;
+      if (n == 0) return false;
+      if (errno == EINTR) continue;
+      return errno == EAGAIN || errno == EWOULDBLOCK;
+    }
+  }
   Clock::time_point lastSeen = Clock::now();
 
  private:
@@ -543,6 +557,29 @@ void MasterNode::broadcastShutdown() {
   for (auto& kv : members_) {
     kv.second->conn->queue(wire::encodeSimple(wire::Shutdown));
     kv.second->conn->drain(1.0);
+    kv.second->conn->finishWrites();
+  }
+  // Workers that lag (thAllreduce < 1) are still sending completions.  Keep reading until every peer has seen the Shutdown and
+  // closed its side (or two seconds have passed): closing with unread input would turn into an RST that can cost the peer
+  // the Shutdown frame itself -- it would then report a lost master although the job finished.
+  std::map<Address, bool> open;
+  for (auto& kv : members_) open[kv.first] = true;
+  auto deadline = Clock::now() + std::chrono::seconds(2);
+  size_t left = open.size();
+  while (left > 0 && Clock::now() < deadline) {
+    std::vector<pollfd> fds;
+    std::vector<Address> addrs;
+    for (auto& kv : members_)
+      if (open[kv.first]) {
+        fds.push_back({kv.second->conn->fd(), POLLIN, 0});
+        addrs.push_back(kv.first);
+      }
+    if (::poll(fds.data(), fds.size(), 50) <= 0) continue;
+    for (size_t k = 0; k < fds.size(); ++k)
+      if ((fds[k].revents & (POLLIN | POLLHUP | POLLERR)) && !members_[addrs[k]]->conn->discardInput()) {
+        open[addrs[k]] = false;
+        --left;
+      }
   }
 }
 

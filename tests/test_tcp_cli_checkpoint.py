@@ -303,3 +303,23 @@ def test_workers_tell_a_lost_master_from_a_finished_job():
     for w in ws:
         wo, _ = w.communicate(timeout=60)
         assert w.returncode == 3 and "master_lost=1" in wo, (w.returncode, wo)
+
+
+def test_lagging_workers_still_receive_the_shutdown():
+    """thAllreduce 0.5 of 8: the master finishes while slower workers are still sending completions.  Closing their sockets with that
+    input unread used to answer with an RST, which let the workers' kernels discard the Shutdown frame they had not read yet
+    (they then reported a lost master).  The master now half-closes and reads until every peer has gone: all eight exit with 0."""
+    build.build_cli()
+    for attempt in range(2):
+        port = _free_port()
+        common = ["--set", f"allreduce.transport.port={port}", "--set", "allreduce.loglevel=ERROR", "--timeout", "90"]
+        th = ["--set", "allreduce.th-allreduce=0.5", "--set", "allreduce.th-reduce=0.5", "--set", "allreduce.th-complete=0.5",
+              "--set", "allreduce.max-round=1000", "--set", "allreduce.max-lag=3", "--set", "allreduce.pipeline-depth=2"]
+        m = subprocess.Popen([str(ROOT / "bin/aar_master"), str(port), "8", "8", "1", *th, *common], stdout=subprocess.PIPE, text=True, cwd=ROOT)
+        ws = [subprocess.Popen([str(ROOT / "bin/aar_worker"), "0", "8", "--check", *common], stdout=subprocess.PIPE, text=True, cwd=ROOT)
+              for _ in range(8)]
+        mo, _ = m.communicate(timeout=120)
+        assert m.returncode == 0 and "finished=1" in mo, mo
+        for w in ws:
+            wo, _ = w.communicate(timeout=60)
+            assert w.returncode == 0 and "master_lost=0" in wo and "mismatches=0" in wo, (w.returncode, wo)
