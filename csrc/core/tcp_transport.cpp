@@ -661,6 +661,10 @@ void WorkerNode::dispatch(const Frame& body) {
   if (type == wire::Shutdown) {
     shutdown_ = true;
     shutdownByMaster_ = true;
+    if (masterConn_) {  // tell the master we are done talking: it waits for this before it closes (see broadcastShutdown)
+      masterConn_->drain(0.2);
+      masterConn_->finishWrites();
+    }
     return;
   }
   Message msg;
