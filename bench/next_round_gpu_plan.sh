@@ -33,7 +33,9 @@ eight)
   TR 8 29613 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8.json
   AAR_STRICT=1 TR 8 29616 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8_strict.json
   TR 8 29614 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e --stage-input 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8_stage_input.json
-  for ctas in 48:4 48:6 48:8 32:8 64:8; do
+  TR 8 29618 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e --no-nccl --view 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8_view.json
+  TR 8 29619 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e --no-nccl --view --stage-input 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8_view_stage.json
+  for ctas in 48:4 48:6 48:8 32:8 64:8 80:8; do
     TR 8 29615 bench.py --gpus 8 --steps 50 --warmup 5 --no-e2e --no-nccl --nvls-ctas $ctas 2>&1 | grep "^{" | tee gpurun_out/r2_bench_n8_ctas_${ctas/:/_}.json
   done
   ;;
