@@ -63,11 +63,13 @@ class GradientBucket:
 class ThresholdDDP:
     def __init__(self, module: torch.nn.Module, rank: int, world: int, device: int, *, bucket_mb: float = 32.0, max_chunk: int = 1 << 20,
                  max_lag: int = 1, th_reduce: float = 1.0, th_complete: float = 1.0, session: str = "ddp", algo: str = "auto",
-                 sink: Callable[[int, AllReduceOutput], None] | None = None, comm_ctas: int = 0):
+                 sink: Callable[[int, AllReduceOutput], None] | None = None, comm_ctas: int = 0, engine_factory=None):
         """comm_ctas: SM budget of the gradient allreduce (CTAs per launch, one CTA occupies one SM); 0 = all SMs.  A bucket's
-        round runs while backward is still producing the next bucket, so every SM it holds is taken from the GEMMs."""
+        round runs while backward is still producing the next bucket, so every SM it holds is taken from the GEMMs.
+        engine_factory(bucket_index, numel, chunk) -> engine: replaces the data plane (the hook / bucket bookkeeping is then
+        testable without a GPU, tests/test_models_ddp_cpu.py); `device` may then be a torch.device such as cpu."""
         self.module, self.rank, self.world = module, rank, world
-        self.device = torch.device("cuda", device)
+        self.device = device if isinstance(device, torch.device) else torch.device("cuda", device)
         self.step = 0
         self.user_sink = sink
         params = [p for p in module.parameters() if p.requires_grad]
@@ -90,7 +92,9 @@ class ThresholdDDP:
                 b.params.append(p)
                 p.register_post_accumulate_grad_hook(self._make_hook(b))
             chunk = max(1, min(max_chunk, (n + world - 1) // world))
-            if world > 1:
+            if engine_factory is not None:
+                b.engine = engine_factory(i, n, chunk)
+            elif world > 1:
                 lay = L.compute_layout(world, n, chunk, max_lag, code, 0, True)
                 b.symm = SymmetricMemory(UnixRendezvous(rank, world, f"{session}_b{i}"), lay.regionBytes, device, want_multicast=True)
                 b.engine = RoundEngine.from_symmetric(b.symm, lay, th_reduce=th_reduce, th_complete=th_complete, normalize=True, algo=algo,

@@ -56,3 +56,69 @@ def test_bucket_plan_for_gpt2_small_matches_the_benchmark_shape():
     assert sum(n for _, n in plan) >= sum(sizes)
     assert all(n % 256 == 0 for _, n in plan)
     assert max(n for _, n in plan) <= 50304 * 768 + 256    # the embedding is the largest single tensor
+
+
+class _FakeEngine:
+    """Stands in for RoundEngine: 'averages' in place over `world` identical contributions and records what was asked of it."""
+
+    def __init__(self, index, numel, chunk, log):
+        self.index, self.numel, self.chunk, self.log = index, numel, chunk, log
+        self.launches = 0
+        self.closed = False
+
+    def enqueue_round(self, rnd, x, out=None):
+        assert x.numel() == self.numel and out is x, "the bucket buffer is reduced in place"
+        self.log.append(("enqueue", self.index, rnd))
+        self.launches += 1
+        return x, torch.full((4,), 2, dtype=torch.int32)
+
+    def wait_round(self, rnd):
+        self.log.append(("wait", self.index, rnd))
+
+    def close(self):
+        self.closed = True
+
+
+def test_threshold_ddp_bookkeeping_with_a_fake_data_plane():
+    """ThresholdDDP without a GPU (engine_factory): .grad tensors are views into the bucket buffers, a bucket is launched by the hook
+    of its LAST gradient (so early buckets go out while backward is still running), finish() waits for every bucket in order,
+    launches what a parameter without gradient left behind, hands the counts to the sink and re-arms the hooks."""
+    from akka_allreduce_b200.parallel.ddp import ThresholdDDP
+
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.ReLU(), torch.nn.Linear(16, 16), torch.nn.ReLU(), torch.nn.Linear(16, 4))
+    unused = torch.nn.Parameter(torch.zeros(5))          # never takes part in the loss: no gradient, no hook call
+    model.register_parameter("unused", unused)
+    log, engines, sunk = [], [], []
+
+    def factory(i, n, chunk):
+        engines.append(_FakeEngine(i, n, chunk, log))
+        return engines[-1]
+
+    ddp = ThresholdDDP(model, 0, 2, torch.device("cpu"), bucket_mb=300 * 4 / (1 << 20), engine_factory=factory,
+                       sink=lambda idx, out: sunk.append((idx, out.iteration, int(out.count[0]))))
+    assert len(ddp.buckets) >= 3 and all(b.buffer.numel() % (2 * 64) == 0 for b in ddp.buckets)
+    for b in ddp.buckets:
+        for p in b.params:
+            assert p.grad.data_ptr() >= b.buffer.data_ptr() and p.grad.data_ptr() < b.buffer.data_ptr() + b.buffer.numel() * 4
+    for step in range(2):
+        ddp.zero_grad()
+        log.clear()
+        loss = model(torch.randn(3, 8)).square().mean()
+        loss.backward()
+        launched_in_backward = [e for e in log if e[0] == "enqueue"]
+        assert launched_in_backward and all(r == step for _, _, r in launched_in_backward)
+        ddp.finish()
+        enq = [i for k, i, _ in log if k == "enqueue"]
+        assert sorted(enq) == list(range(len(ddp.buckets))), "every bucket exactly once per step (the one holding `unused` from finish())"
+        assert [i for k, i, _ in log if k == "wait"] == list(range(len(ddp.buckets)))
+        assert ddp.step == step + 1
+    assert len(sunk) == 2 * len(ddp.buckets) and all(c == 2 for _, _, c in sunk)
+    # gradients really live in the buckets: what autograd accumulated is what the engine was handed
+    w = model[4].weight
+    assert torch.count_nonzero(w.grad) > 0
+    owner = next(b for b in ddp.buckets if any(p is w for p in b.params))
+    assert torch.count_nonzero(owner.buffer) > 0
+    assert ddp.launches() == 2 * len(ddp.buckets)
+    ddp.close()
+    assert all(e.closed for e in engines)
