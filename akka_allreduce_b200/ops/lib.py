@@ -12,11 +12,12 @@ from pathlib import Path
 AAR_MAXP = 16
 AAR_F32, AAR_BF16 = 0, 1
 FLAG_NORMALIZE, FLAG_EXACT_QUORUM, FLAG_FORCE, FLAG_SKIP_SCATTER, FLAG_VIEW_OUTPUT, FLAG_TRACE, FLAG_OVERLAPPED = 1, 2, 4, 8, 16, 32, 64
+FLAG_SELF_DIRECT = 1024  # bulk kernels: own contribution read in place, own reduced block straight to the output
 FLAG_ELIDE_LATE = 512  # opt-in (AAR_ELIDE_LATE=1): a rank a whole round late skips work nobody will read; implies FLAG_BCAST_FC
 FLAG_EAGER_DEC = 256  # opt-in (AAR_STRICT=1): eager gather decides once per chunk (no half-flushed chunk when a wait gives up)
 FLAG_BCAST_FC = 128  # opt-in (AAR_BCAST_FC=1): reduce-broadcast obeys the slot flow control at thresholds < 1
 TRACE_CTAS, TRACE_MARKS = 512, 8
-ST_TIMEOUT_SCATTER, ST_TIMEOUT_REDUCE, ST_TIMEOUT_GATHER, ST_PUSH_DROPPED = 1, 2, 4, 8
+ST_TIMEOUT_SCATTER, ST_TIMEOUT_REDUCE, ST_TIMEOUT_GATHER, ST_PUSH_DROPPED, ST_BULK_FAULT = 1, 2, 4, 8, 16
 
 
 class AarLayout(C.Structure):
@@ -31,6 +32,7 @@ class AarLayout(C.Structure):
         ("statusOff", C.c_uint64), ("oneshotOff", C.c_uint64), ("oneshotFlagOff", C.c_uint64), ("stageOff", C.c_uint64),
         ("barrierOff", C.c_uint64), ("traceOff", C.c_uint64), ("ctrlBytes", C.c_uint64), ("regionBytes", C.c_uint64),
         ("egDecOff", C.c_uint64),
+        ("tilesPerPiece", C.c_int), ("piecesPerChunk", C.c_int), ("pflagSOff", C.c_uint64), ("pflagROff", C.c_uint64),
     ]
 
 
@@ -85,6 +87,8 @@ def load():
         "aar_launch_gather": [P(AarRankParams), P(AarLayout), C.c_int, C.c_void_p],
         "aar_launch_round_fused": [P(AarRankParams), P(AarLayout), C.c_int, C.c_void_p],
         "aar_launch_round_pipelined": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_void_p],
+        "aar_launch_round_bulk": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p],
+        "aar_bulk_supported": [P(AarRankParams), P(AarLayout), C.c_int],
         "aar_launch_persistent": [P(AarRankParams), P(AarLayout), C.c_void_p, C.c_int, C.c_int, C.c_void_p],
         "aar_launch_oneshot": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_void_p],
         "aar_launch_nvls": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_void_p],

@@ -24,7 +24,7 @@ class LocalGpuCluster:
     def __init__(self, P: int, data_size: int, max_chunk: int, max_lag: int = 1, th_reduce: float = 1.0, th_complete: float = 1.0,
                  dtype: torch.dtype = torch.float32, normalize: bool = False, exact_quorum: bool = False, timeout_ms: float = 2000.0,
                  device: str | torch.device = "cuda:0", grid: int = 0, oneshot: bool = False, bcast_fc: bool = False, eager_dec: bool = False,
-                 elide_late: bool = False):
+                 elide_late: bool = False, impl: str = "reg", self_direct: bool = False):
         self.lib = L.load()
         self.P, self.data_size, self.max_chunk, self.max_lag = P, data_size, max_chunk, max_lag
         self.dtype = dtype
@@ -35,6 +35,11 @@ class LocalGpuCluster:
         self.min_chunks_required = self.geo.min_chunks_required(th_complete)
         self.base_flags = (L.FLAG_NORMALIZE if normalize else 0) | (L.FLAG_EXACT_QUORUM if exact_quorum else 0) | (L.FLAG_BCAST_FC if bcast_fc else 0) | (L.FLAG_EAGER_DEC if eager_dec else 0) | ((L.FLAG_ELIDE_LATE | L.FLAG_BCAST_FC) if elide_late else 0)
         self.timeout_ns = int(timeout_ms * 1e6)
+        # impl = "bulk": the phases run on the bulk async-copy engine kernels (csrc/cuda/aar_bulk.cu) wherever the geometry and the
+        # pointers allow it, rank by rank; anything else falls back to the register kernels, exactly as RoundEngine does
+        self.impl = impl
+        if self_direct:
+            self.base_flags |= L.FLAG_SELF_DIRECT
         self.layout = L.compute_layout(P, data_size, max_chunk, max_lag, _TORCH2AAR[dtype], data_size if oneshot else 0, False)
         with torch.cuda.device(self.device):
             self.regions = [torch.zeros(self.layout.regionBytes, dtype=torch.uint8, device=self.device) for _ in range(P)]
@@ -68,9 +73,29 @@ class LocalGpuCluster:
             mask |= 1 << r
         return mask
 
+    def _phase(self, r: int, phase: int, stream) -> None:
+        """One phase (1 scatter, 2 reduce + broadcast, 4 gather) of rank r on the kernels `impl` selects."""
+        lay = C.byref(self.layout)
+        pr = C.byref(self.params[r])
+        if self.impl == "bulk" and self.lib.aar_bulk_supported(pr, lay, 0):
+            L.check(self.lib.aar_launch_round_bulk(pr, lay, 0, phase, self.grid, 0, stream), "aar_launch_round_bulk")
+            self.bulk_launches = getattr(self, "bulk_launches", 0) + 1
+            return
+        fn = {1: self.lib.aar_launch_scatter, 2: self.lib.aar_launch_reduce_bcast, 4: self.lib.aar_launch_gather}[phase]
+        L.check(fn(pr, lay, self.grid, stream), "phase launch")
+
     def run_round(self, rnd: int, inputs: Sequence[torch.Tensor], skip: Iterable[int] = (), force: bool = False):
         """One allreduce round for all ranks: returns (outputs, counts) -- per-rank tensors owned by the cluster."""
         mask = self._prep(rnd, inputs, force, skip)
+        if self.impl == "bulk":
+            st = C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+            with torch.cuda.device(self.device):
+                for phase in (1, 2, 4):  # phase order matters on a single device: no kernel may wait for a later launch
+                    for r in range(self.P):
+                        if phase == 1 and (mask >> r) & 1:
+                            continue
+                        self._phase(r, phase, st)
+            return self.outputs, self.counts
         stream = torch.cuda.current_stream(self.device).cuda_stream
         with torch.cuda.device(self.device):
             L.check(self.lib.aar_local_round(self.params, self.P, C.byref(self.layout), mask, self.grid, C.c_void_p(stream)), "aar_local_round")
@@ -84,11 +109,11 @@ class LocalGpuCluster:
         lay = C.byref(self.layout)
         with torch.cuda.device(self.device):
             for r in scatter:
-                L.check(self.lib.aar_launch_scatter(C.byref(self.params[r]), lay, self.grid, stream), "scatter")
+                self._phase(r, 1, stream)
             for r in reduce:
-                L.check(self.lib.aar_launch_reduce_bcast(C.byref(self.params[r]), lay, self.grid, stream), "reduce_bcast")
+                self._phase(r, 2, stream)
             for r in gather:
-                L.check(self.lib.aar_launch_gather(C.byref(self.params[r]), lay, self.grid, stream), "gather")
+                self._phase(r, 4, stream)
 
     def run_oneshot(self, rnd: int, inputs: Sequence[torch.Tensor], skip: Iterable[int] = (), force: bool = False):
         skip = set(skip)

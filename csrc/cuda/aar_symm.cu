@@ -120,7 +120,16 @@ AAR_API int aar_layout_compute(int P, int dataSize, int maxChunkSize, int maxLag
   l.oneshotFlagOff = take((uint64_t)l.L * AAR_MAXP * 4);
   l.barrierOff = take(8 * 4 * 16);
   l.traceOff = take((uint64_t)AAR_TRACE_CTAS * AAR_TRACE_MARKS * 8);
-  l.egDecOff = take((uint64_t)l.L * P * l.C * 8);  // last: every older offset stays where it was
+  l.egDecOff = take((uint64_t)l.L * P * l.C * 8);  // appended: every older offset stays where it was
+  // pieces of the in-switch path: about 16 per block, 1..8 tiles each
+  {
+    const int tilesPerBlock = (l.stepSize + l.tileElems - 1) / l.tileElems;
+    int tpp = tilesPerBlock / 16;
+    l.tilesPerPiece = tpp < 1 ? 1 : (tpp > 8 ? 8 : tpp);
+    l.piecesPerChunk = (l.tilesPerChunk + l.tilesPerPiece - 1) / l.tilesPerPiece;
+  }
+  l.pflagSOff = take((uint64_t)l.L * l.C * l.piecesPerChunk * AAR_MAXP * 4);
+  l.pflagROff = take((uint64_t)l.L * P * l.C * l.piecesPerChunk * 4);
   l.regionBytes = alignUp(off, 2ull << 20);
   *out = l;
   return AAR_OK;

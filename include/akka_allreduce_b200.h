@@ -42,6 +42,8 @@ extern "C" {
                                    (docs/PROTOCOL.md "Known limits"); opt-in until verified on hardware */
 #define AAR_FLAG_BCAST_FC 128u  /* thresholds < 1: the reduce-broadcast adopts the scatter's per-destination slot flow control
                                    (docs/PROTOCOL.md "Known limits"); opt-in until verified on hardware */
+#define AAR_FLAG_SELF_DIRECT 1024u /* aar_launch_round_bulk: a rank's own contribution is read from its input (no copy into its own
+                                   scatter ring) and, when every chunk is required, its own reduced block goes straight to the output */
 #define AAR_FLAG_TRACE 32u      /* every CTA stamps %globaltimer at its phase boundaries into the trace section */
 #define AAR_TRACE_CTAS 512
 #define AAR_TRACE_MARKS 8
@@ -51,6 +53,7 @@ extern "C" {
 #define AAR_ST_TIMEOUT_REDUCE 2u
 #define AAR_ST_TIMEOUT_GATHER 4u
 #define AAR_ST_PUSH_DROPPED 8u
+#define AAR_ST_BULK_FAULT 16u /* a bulk load never completed (bad address): the kernel trapped instead of hanging */
 
 /* Byte offsets of the sections of one rank's symmetric region; identical on every rank. */
 typedef struct AarLayout {
@@ -79,6 +82,12 @@ typedef struct AarLayout {
   uint64_t ctrlBytes;        /* first byte of the control area that must be zeroed at allocation */
   uint64_t regionBytes;      /* total, rounded up to 2 MiB */
   uint64_t egDecOff;         /* u64 [L][P][C]                   local: eager gather, epoch<<32 | count+1 (0 = abandoned); AAR_FLAG_EAGER_DEC */
+  /* pieces: sub-chunk granules of the in-switch (NVLS) path of aar_launch_round_bulk.  That path has no contributor decision to
+   * take (the switch sums every rank), so it can publish and consume a chunk piece by piece; a 4 MiB chunk is then no longer
+   * the smallest thing one role can hand to the next. */
+  int tilesPerPiece, piecesPerChunk;
+  uint64_t pflagSOff;        /* u32 [L][C][piecesPerChunk][AAR_MAXP]   epoch, written by src: "my piece of your block is staged" */
+  uint64_t pflagROff;        /* u32 [L][P(owner)][C][piecesPerChunk]   epoch, written by owner: "reduced piece has landed" */
 } AarLayout;
 
 /* Per-rank launch parameters (passed to the kernels by value). */
@@ -121,6 +130,18 @@ int aar_launch_round_fused(const AarRankParams* p, const AarLayout* lay, int gri
 /* Same round with the CTAs specialised by role (push / reduce+broadcast / gather) so the phases overlap chunk by chunk.
  * split = nPush | nReduce << 16, 0 = heuristic; the remaining CTAs gather. */
 int aar_launch_round_pipelined(const AarRankParams* p, const AarLayout* lay, int grid, int split, void* stream);
+/* The same round on the bulk async-copy engine (csrc/cuda/aar_bulk.cu): every copy is cp.async.bulk through a shared-memory
+ * ring driven by one thread per CTA, every completion is a bulk-group wait (no store-queue drain), roles sweep the block
+ * chunk by chunk so push, reduce and gather of one round overlap.  Same flags, decisions and thresholds as the kernels above
+ * (a rank may use either for any round); slot flow control for the broadcast and one eager-gather decision per chunk are
+ * always on.  algo 0 = two-shot P2P, 1 = NVLS (thresholds must be 1.0; piece-granular flags, every rank must use it).
+ * phases: 7 = one launch, CTAs specialised by role (split = nA | nB << 16: push/stage CTAs, reduce CTAs; 0 = heuristic);
+ * 1 / 2 / 4 = one phase with the whole grid (single-device emulation).  Needs 16-byte aligned geometry and pointers
+ * (AAR_EUNSUPPORTED otherwise: use the kernels above). */
+int aar_launch_round_bulk(const AarRankParams* p, const AarLayout* lay, int algo, int phases, int grid, int split, void* stream);
+/* 1 if aar_launch_round_bulk can run this geometry / these pointers */
+int aar_bulk_supported(const AarRankParams* p, const AarLayout* lay, int algo);
+
 /* K7 persistent round engine: one resident kernel per rank, driven through a command ring in pinned host memory
  * (8 entries x 16 u32: {seq, flags, round, exit, input lo/hi, output lo/hi, counts lo/hi}); the host writes an entry, then
  * its seq word (= command number + 1).  algo 0 = fused two-shot, 1 = one-shot.  Returns after launching; the kernel ends

@@ -41,10 +41,71 @@ def oracle(inputs, P, n, chunk, contributors, dtype, normalize=False, missing_ow
     return out, torch.tensor(counts, dtype=torch.int32, device=out.device)
 
 
+# Every scenario runs on both generations of kernels: the register kernels (csrc/cuda/aar_kernels.cu) and the bulk async-copy
+# engine kernels (csrc/cuda/aar_bulk.cu), the latter also with AAR_FLAG_SELF_DIRECT (own contribution read in place, own
+# reduced block written straight to the output).  Geometries the bulk kernels cannot take (blocks or chunks that are not
+# multiples of 16 bytes) fall back to the register kernels inside LocalGpuCluster, exactly as RoundEngine does.
+_IMPL = {"impl": "reg", "self_direct": False}
+
+
+@pytest.fixture(autouse=True, params=["reg", "bulk", "bulk_sd"])
+def kernel_impl(request):
+    _IMPL["impl"] = "bulk" if request.param.startswith("bulk") else "reg"
+    _IMPL["self_direct"] = request.param == "bulk_sd"
+    yield request.param
+    _IMPL["impl"], _IMPL["self_direct"] = "reg", False
+
+
 def cluster(*a, **kw):
     from akka_allreduce_b200.parallel.local_gpu import LocalGpuCluster
 
+    kw.setdefault("impl", _IMPL["impl"])
+    kw.setdefault("self_direct", _IMPL["self_direct"])
     return LocalGpuCluster(*a, **kw)
+
+
+def test_bulk_kernels_really_run(kernel_impl):
+    """Guard against a silent fallback: on an aligned geometry impl=bulk must launch aar_launch_round_bulk for every phase."""
+    P, n, chunk = 4, 1 << 18, 1 << 14
+    cl = cluster(P, n, chunk)
+    xs = make_inputs(P, n, torch.float32, 3)
+    outs, counts = cl.run_round(0, xs)
+    want, wc = oracle(xs, P, n, chunk, lambda o, c: list(range(P)), torch.float32)
+    torch.cuda.synchronize()
+    for r in range(P):
+        assert torch.equal(outs[r], want) and torch.equal(counts[r], wc) and cl.status(r) == 0
+    assert getattr(cl, "bulk_launches", 0) == (3 * P if kernel_impl != "reg" else 0)
+
+
+@pytest.mark.parametrize("P,n,chunk", [(2, 1 << 22, 1 << 18), (4, 1 << 22, 1 << 20), (8, 1 << 23, 1 << 18), (3, 3 * 70000 * 4, 100000)])
+def test_large_rounds_bit_exact_many_tiles(P, n, chunk):
+    """Sizes where a segment spans many tiles and a CTA owns several segments (pipelines run across segment and chunk
+    boundaries), over three ring revolutions."""
+    cl = cluster(P, n, chunk, max_lag=1)
+    for rnd in range(5):
+        xs = make_inputs(P, n, torch.float32, 1000 + rnd)
+        outs, counts = cl.run_round(rnd, xs)
+        want, wc = oracle(xs, P, n, chunk, lambda o, c: list(range(P)), torch.float32)
+        torch.cuda.synchronize()
+        for r in range(P):
+            assert torch.equal(outs[r], want), f"rank {r} round {rnd}"
+            assert torch.equal(counts[r], wc) and cl.status(r) == 0
+
+
+def test_in_place_round_output_aliases_input():
+    """ThresholdDDP reduces gradient buckets in place (out = x): every phase must read a location before it is overwritten."""
+    P, n, chunk = 4, 1 << 20, 1 << 16
+    cl = cluster(P, n, chunk, max_lag=1)
+    for rnd in range(3):
+        xs = make_inputs(P, n, torch.float32, 2000 + rnd)
+        want, wc = oracle(xs, P, n, chunk, lambda o, c: list(range(P)), torch.float32)
+        for r in range(P):
+            cl.params[r].output = xs[r].data_ptr()
+        cl.outputs = xs
+        outs, counts = cl.run_round(rnd, xs)
+        torch.cuda.synchronize()
+        for r in range(P):
+            assert torch.equal(outs[r], want) and torch.equal(counts[r], wc)
 
 
 @pytest.mark.parametrize(

@@ -1,21 +1,14 @@
-"""GPU tests of code paths that are built but have NOT yet run on hardware (written after the round's GPU budget was spent).
-
-They are skipped unless AAR_EXPERIMENTAL=1, so that an unverified path can never turn the regular GPU suite red; the first GPU
-session of the next round runs them (`AAR_EXPERIMENTAL=1 python -m pytest tests/test_gpu_experimental.py -m gpu`), and whatever
-passes moves into the regular files.
-
-Currently: AAR_FLAG_BCAST_FC -- the reduce-broadcast adopts the scatter's per-destination slot flow control at thresholds < 1
-(docs/PROTOCOL.md "Known limits"; model: csrc/tests/protocol_litmus.cpp).
+"""GPU tests of the strict protocol variants on one device: the reduce-broadcast obeys the scatter's per-destination slot flow
+control at thresholds < 1 (AAR_FLAG_BCAST_FC on the register kernels, always on in the bulk kernels), late-work elision, the
+resumed round numbering and the native round engine (docs/PROTOCOL.md; model: csrc/tests/protocol_litmus.cpp).  First run on
+B200 at the start of round 2: all green, so they are part of the regular suite.
 """
-import os
-
 import pytest
 import torch
 
-from test_gpu_local import cluster, make_inputs, oracle
+from test_gpu_local import cluster, kernel_impl, make_inputs, oracle  # noqa: F401  (kernel_impl: autouse fixture, both kernel generations)
 
-pytestmark = [pytest.mark.gpu,
-              pytest.mark.skipif(os.environ.get("AAR_EXPERIMENTAL", "0") in ("", "0"), reason="unverified paths: set AAR_EXPERIMENTAL=1")]
+pytestmark = [pytest.mark.gpu]
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
@@ -106,7 +99,7 @@ def test_late_rank_elides_work_nobody_will_read():
     are back at zero), its broadcast goes to nobody but itself, and its own flushed vector is still exact: blocks of owners 0-2
     are the sums those owners decided (sources 0-2), its own block sums all four."""
     P, n, chunk = 4, 4096, 512
-    cl = cluster(P, n, chunk, max_lag=1, th_reduce=0.75, th_complete=0.75, elide_late=True)
+    cl = cluster(P, n, chunk, max_lag=1, th_reduce=0.75, th_complete=0.75, elide_late=True, impl="reg")   # elision lives in the register kernels
     xs = make_inputs(P, n, torch.float32, 900)
     live = [0, 1, 2]
     cl.run_phases(0, xs, scatter=live, reduce=live, gather=live)
