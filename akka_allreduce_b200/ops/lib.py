@@ -57,7 +57,10 @@ _lib = None
 
 
 def lib_path() -> Path:
-    return Path(__file__).resolve().parents[1] / "libaar_cuda.so"
+    import os
+
+    override = os.environ.get("AAR_CUDA_LIB")   # e.g. an instrumented build (bench/prof_reduce.py)
+    return Path(override) if override else Path(__file__).resolve().parents[1] / "libaar_cuda.so"
 
 
 def load():
@@ -122,6 +125,8 @@ def load():
         "aar_engine_set_doorbell": [C.c_void_p, C.c_int],
         "aar_engine_rounds_flushed": [C.c_void_p],
         "aar_engine_destroy": [C.c_void_p],
+        "aar_bench_litmus_bulk_flag": [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p],
+        "aar_bench_bulk_copy_multi": [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p],
         "aar_bench_bulk_copy": [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p],
     }
     for name, argtypes in sigs.items():

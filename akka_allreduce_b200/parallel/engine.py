@@ -83,6 +83,13 @@ class RoundEngine:
         self.split = 32 | (48 << 16)      # nPush | nReduce << 16; the rest gather
         self.nvls_reduce_ctas = 8        # 207.7 us with 8 vs 222 us with 16 reduce CTAs at 8 GPUs, 64 MiB
         self.nvls_stage_ctas = 48
+        # role split of the bulk async-copy engine kernels (0 = the library's heuristic): nA | nB << 16
+        self.bulk_split = 0
+        self.nvls_bulk_split = 0
+        # own contribution read in place / own reduced block written straight to the output: only when there are peers (a
+        # world of one keeps the full three-pass loop-back, which is what one rank of a larger world does per round)
+        if self.algo == "bulk" and layout.P > 1 and os.environ.get("AAR_SELF_DIRECT", "1") not in ("", "0"):
+            self.base_flags |= L.FLAG_SELF_DIRECT
         # The maxLag window lets two consecutive rounds of one worker be in flight: they alternate between two internal
         # streams, so the push of round r+1 starts on the SMs that round r's push CTAs have already left while round r is
         # still reducing and gathering.  Needs two ring slots (maxLag >= 1) and peers to overlap with.
@@ -127,8 +134,8 @@ class RoundEngine:
             return "pipelined" if lay.P > 1 else "twoshot"
         if algo == "oneshot" and not lay.oneshotOff:
             raise ValueError("algo=oneshot needs a layout with one-shot buffers")
-        if algo == "nvls" and not (self.mc_ptr and lay.stageOff):
-            raise ValueError("algo=nvls needs a multicast mapping and the staging area")
+        if algo in ("nvls", "nvls_bulk") and not (self.mc_ptr and lay.stageOff):
+            raise ValueError(f"algo={algo} needs a multicast mapping and the staging area")
         return algo
 
     # ------------------------------------------------------------------ rounds
@@ -188,6 +195,20 @@ class RoundEngine:
             L.check(self.lib.aar_launch_round_pipelined(self._pref, self._lay, self.grid, self.split, s), "aar_launch_round_pipelined")
         elif self.algo == "oneshot":
             L.check(self.lib.aar_launch_oneshot(self._pref, self._lay, 2, self.grid, s), "aar_launch_oneshot")
+        elif self.algo in ("bulk", "nvls_bulk"):
+            which = 1 if self.algo == "nvls_bulk" else 0
+            if self.lib.aar_bulk_supported(self._pref, self._lay, which):
+                L.check(self.lib.aar_launch_round_bulk(self._pref, self._lay, which, 7, self.grid, self.nvls_bulk_split if which else self.bulk_split, s),
+                        "aar_launch_round_bulk")
+            elif which == 0:   # unaligned input / output pointer or geometry: the register kernels take anything
+                p.flags &= ~L.FLAG_SELF_DIRECT
+                if self.layout.P > 1:
+                    L.check(self.lib.aar_launch_round_pipelined(self._pref, self._lay, self.grid, self.split, s), "aar_launch_round_pipelined")
+                else:
+                    L.check(self.lib.aar_launch_round_fused(self._pref, self._lay, self.grid, s), "aar_launch_round_fused")
+                self.fallback_launches = getattr(self, "fallback_launches", 0) + 1
+            else:
+                raise L.AarError("algo=nvls_bulk: " + (self.lib.aar_last_error() or b"").decode())
         elif self.algo == "nvls":
             L.check(self.lib.aar_launch_nvls(self._pref, self._lay, 7 | (self.nvls_reduce_ctas << 8) | (self.nvls_stage_ctas << 16), self.grid, s), "aar_launch_nvls")
         else:
@@ -207,7 +228,7 @@ class RoundEngine:
         The slot was last read by the peers' reduce of round rnd - L; every owner had finished that before this rank's round
         rnd - L could retire, so ordering after that round's event is enough: `stream` (default: current) is made to wait."""
         lay = self.layout
-        if self.algo != "nvls" or not lay.stageOff:
+        if self.algo not in ("nvls", "nvls_bulk") or not lay.stageOff:
             return None
         if rnd >= lay.L:
             (stream or torch.cuda.current_stream(self.device)).wait_event(self._events[rnd % lay.L])

@@ -40,6 +40,8 @@ class LocalGpuCluster:
         self.impl = impl
         if self_direct:
             self.base_flags |= L.FLAG_SELF_DIRECT
+        import os
+        self.base_flags |= int(os.environ.get("AAR_DEBUG_FLAGS", "0"), 0)
         self.layout = L.compute_layout(P, data_size, max_chunk, max_lag, _TORCH2AAR[dtype], data_size if oneshot else 0, False)
         with torch.cuda.device(self.device):
             self.regions = [torch.zeros(self.layout.regionBytes, dtype=torch.uint8, device=self.device) for _ in range(P)]

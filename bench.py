@@ -178,7 +178,7 @@ def main():
             eng.nvls_stage_ctas, eng.nvls_reduce_ctas = (int(v) for v in a.nvls_ctas.split(":"))
         if a.split:
             ps, rs = (int(v) for v in a.split.split(":"))
-            eng.split = ps | (rs << 16)
+            eng.split = eng.bulk_split = eng.nvls_bulk_split = ps | (rs << 16)
         staged = False
         if a.stage_input and a.max_lag == 1 and eng.stage_input(0) is not None:   # slot of round r is r % 2 = index of its input
             xs = [eng.stage_input(k).copy_(xs[k]) for k in range(2)]

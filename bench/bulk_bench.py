@@ -57,4 +57,13 @@ for grid in [int(g) for g in a.grids.split(",")]:
         ok = bool(torch.equal(bufs[0][nbytes:], bufs[0][:nbytes]))
         res[f"bulk_s{stages}_t{tile}_g{grid}"] = {"us": round(us, 1), "GBps": round(nbytes / us / 1e3, 1), "GBps_per_cta": round(nbytes / us / 1e3 / grid, 2),
                                                  "ok": ok, "gave_up": int(err.item())}
+# several issuing threads per CTA (each its own ring): does the per-copy issue cost overlap?
+for grid in (8, 32):
+    for warps, stages, tile in ((1, 4, 8192), (2, 4, 8192), (4, 4, 8192), (8, 2, 8192), (1, 4, 16384), (2, 4, 16384), (4, 2, 16384), (2, 2, 32768), (4, 2, 16384)):
+        def run(k):
+            L.check(lib.aar_bench_bulk_copy_multi(grid, warps, stages, tile, C.c_void_p(bufs[k].data_ptr()), C.c_void_p(bufs[k].data_ptr() + nbytes), nbytes, 1, s,
+                                                  C.c_void_p(err.data_ptr())))
+        us = timed(run)
+        ok = bool(torch.equal(bufs[0][nbytes:], bufs[0][:nbytes]))
+        res[f"multi_w{warps}_s{stages}_t{tile}_g{grid}"] = {"us": round(us, 1), "GBps_per_cta": round(nbytes / us / 1e3 / grid, 2), "ok": ok, "gave_up": int(err.item())}
 print(json.dumps(res))

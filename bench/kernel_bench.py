@@ -40,12 +40,15 @@ def main():
     ap.add_argument("--dtype", default="fp32")
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--grid", type=int, default=0)
+    ap.add_argument("--impl", default="reg", choices=["reg", "bulk"])
+    ap.add_argument("--self-direct", action="store_true")
+    ap.add_argument("--split", default="", help="nA:nB for the role-specialised single-rank round")
     a = ap.parse_args()
     dtype = torch.float32 if a.dtype == "fp32" else torch.bfloat16
     es = 4 if dtype == torch.float32 else 2
-    res = {"P": a.P, "n": a.n, "chunk": a.chunk, "dtype": a.dtype, "bytes": a.n * es, "grid": a.grid}
+    res = {"P": a.P, "n": a.n, "chunk": a.chunk, "dtype": a.dtype, "bytes": a.n * es, "grid": a.grid, "impl": a.impl, "self_direct": a.self_direct}
 
-    cl = LocalGpuCluster(a.P, a.n, a.chunk, max_lag=1, dtype=dtype, grid=a.grid, timeout_ms=5000)
+    cl = LocalGpuCluster(a.P, a.n, a.chunk, max_lag=1, dtype=dtype, grid=a.grid, timeout_ms=5000, impl=a.impl, self_direct=a.self_direct)
     xs = [torch.randn(a.n, device="cuda:0").to(dtype) for _ in range(a.P)]
     lay = C.byref(cl.layout)
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
@@ -66,19 +69,19 @@ def main():
         out = {}
         e = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
         for k in range(1, a.P):
-            L.check(cl.lib.aar_launch_scatter(C.byref(cl.params[k]), lay, a.grid, stream))
+            cl._phase(k, 1, stream)
         e[0].record()
-        L.check(cl.lib.aar_launch_scatter(C.byref(cl.params[0]), lay, a.grid, stream))
+        cl._phase(0, 1, stream)
         e[1].record()
         for k in range(1, a.P):
-            L.check(cl.lib.aar_launch_reduce_bcast(C.byref(cl.params[k]), lay, a.grid, stream))
+            cl._phase(k, 2, stream)
         e[2].record()
-        L.check(cl.lib.aar_launch_reduce_bcast(C.byref(cl.params[0]), lay, a.grid, stream))
+        cl._phase(0, 2, stream)
         e[3].record()
         for k in range(1, a.P):
-            L.check(cl.lib.aar_launch_gather(C.byref(cl.params[k]), lay, a.grid, stream))
+            cl._phase(k, 4, stream)
         e[4].record()
-        L.check(cl.lib.aar_launch_gather(C.byref(cl.params[0]), lay, a.grid, stream))
+        cl._phase(0, 4, stream)
         e[5].record()
         torch.cuda.synchronize()
         out["K1_scatter_us"] = e[0].elapsed_time(e[1]) * 1e3
@@ -97,7 +100,10 @@ def main():
     res["K3_GBps"] = 2 * nb / res["K3_gather_us"] / 1e3
     del cl
 
-    eng = RoundEngine.single_process(a.n, a.chunk, dtype=dtype, grid=a.grid, algo="twoshot")
+    eng = RoundEngine.single_process(a.n, a.chunk, dtype=dtype, grid=a.grid, algo="twoshot" if a.impl == "reg" else "bulk")
+    if a.split:
+        na, nb_ = (int(v) for v in a.split.split(":"))
+        eng.bulk_split = na | (nb_ << 16)
     x = xs[0]
     k = [0]
 

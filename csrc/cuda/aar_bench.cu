@@ -175,16 +175,22 @@ __device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity) {
   return false;
 }
 
+// blockDim.x = 32 * W: lane 0 of every warp drives its own ring of kStages tiles (its own slice of shared memory, its own
+// barriers, every W-th tile of the CTA's share).  W > 1 answers whether the cost of issuing a bulk copy (a few hundred
+// cycles of the issuing thread) is a per-thread latency that several issuers hide, or a limit of the SM's copy engine.
 template <int kStages>
-__global__ void __launch_bounds__(32, 1) bulkCopyBench(const char* src, char* dst, size_t bytes, int tileBytes, unsigned* err) {
-  extern __shared__ __align__(128) unsigned char smem[];
+__global__ void __launch_bounds__(256, 1) bulkCopyBench(const char* src, char* dst, size_t bytes, int tileBytes, unsigned* err) {
+  extern __shared__ __align__(128) unsigned char smemAll[];
+  const int W = blockDim.x / 32, w = threadIdx.x / 32;
+  unsigned char* smem = smemAll + (size_t)w * ((size_t)kStages * tileBytes + 64);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)kStages * tileBytes);
-  if (threadIdx.x != 0) return;  // one thread issues everything; the copy engine does the work
+  if ((threadIdx.x & 31) != 0) return;  // one thread per warp issues everything; the copy engine does the work
   for (int s = 0; s < kStages; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(bars + s)) : "memory");
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");  // make the initialised barriers visible to the async proxy
   const size_t nTiles = (bytes + tileBytes - 1) / tileBytes;
-  const size_t mine = nTiles > blockIdx.x ? (nTiles - blockIdx.x - 1) / gridDim.x + 1 : 0;
-  auto tileOff = [&](size_t k) { return (blockIdx.x + k * gridDim.x) * (size_t)tileBytes; };
+  const size_t me = (size_t)blockIdx.x * W + w, lanes = (size_t)gridDim.x * W;
+  const size_t mine = nTiles > me ? (nTiles - me - 1) / lanes + 1 : 0;
+  auto tileOff = [&](size_t k) { return (me + k * lanes) * (size_t)tileBytes; };
   auto tileLen = [&](size_t k) {
     const size_t off = tileOff(k);
     return (uint32_t)(bytes - off < (size_t)tileBytes ? bytes - off : (size_t)tileBytes);
@@ -218,12 +224,21 @@ __global__ void __launch_bounds__(32, 1) bulkCopyBench(const char* src, char* ds
 
 }  // namespace
 
+AAR_API int aar_bench_bulk_copy_multi(int grid, int warps, int stages, int tileBytes, const void* src, void* dst, size_t bytes, int iters, void* stream,
+                                      unsigned* errOut);
+
 // `iters` launches of the bulk-copy kernel on `stream` (timed by the caller).  src / dst: `bytes` each, 16-byte aligned,
 // bytes a multiple of 16; dst may be a peer mapping.  stages in {2, 4, 8}; tileBytes a multiple of 128 with
 // stages * tileBytes + 64 <= 227 KiB.  *errOut (device word, may be NULL) becomes 1 if a wait ran out of patience.
 AAR_API int aar_bench_bulk_copy(int grid, int stages, int tileBytes, const void* src, void* dst, size_t bytes, int iters, void* stream, unsigned* errOut) {
-  if (grid <= 0 || tileBytes <= 0 || tileBytes % 128 || bytes % 16 || !src || !dst) return aar_host::fail(-1, "aar_bench_bulk_copy: bad arguments");
-  const size_t smem = (size_t)stages * tileBytes + 64;
+  return aar_bench_bulk_copy_multi(grid, 1, stages, tileBytes, src, dst, bytes, iters, stream, errOut);
+}
+
+AAR_API int aar_bench_bulk_copy_multi(int grid, int warps, int stages, int tileBytes, const void* src, void* dst, size_t bytes, int iters, void* stream,
+                                      unsigned* errOut) {
+  if (grid <= 0 || warps < 1 || warps > 8 || tileBytes <= 0 || tileBytes % 128 || bytes % 16 || !src || !dst)
+    return aar_host::fail(-1, "aar_bench_bulk_copy: bad arguments");
+  const size_t smem = (size_t)warps * ((size_t)stages * tileBytes + 64);
   if (smem > 227 * 1024) return aar_host::fail(-1, "aar_bench_bulk_copy: %d stages x %d bytes do not fit in shared memory", stages, tileBytes);
   static unsigned* fallbackErr = nullptr;
   if (!errOut) {
@@ -238,9 +253,96 @@ AAR_API int aar_bench_bulk_copy(int grid, int stages, int tileBytes, const void*
   else return aar_host::fail(-1, "aar_bench_bulk_copy: stages must be 2, 4 or 8");
   cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return aar_host::fail(-2, "aar_bench_bulk_copy: shared memory opt-in: %s", cudaGetErrorString(e));
-  for (int i = 0; i < iters; ++i) k<<<grid, 32, smem, (cudaStream_t)stream>>>((const char*)src, (char*)dst, bytes, tileBytes, errOut);
+  for (int i = 0; i < iters; ++i) k<<<grid, 32 * warps, smem, (cudaStream_t)stream>>>((const char*)src, (char*)dst, bytes, tileBytes, errOut);
   e = cudaGetLastError();
   if (e != cudaSuccess) return aar_host::fail(-2, "aar_bench_bulk_copy: %s", cudaGetErrorString(e));
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ litmus: bulk store + flag
+// Does completion of a bulk async-group (cp.async.bulk.wait_group) mean that the bytes have LANDED in a peer GPU's memory,
+// so that a flag written afterwards -- with no fence -- can never be seen before the data?  The kernels want to know: a
+// system fence on an SM that streams remote stores waits for all of them, newer ones included (measured: tens of
+// microseconds), while the bulk-group wait is precise.  Sender CTA b on one GPU, receiver CTA b on the other, `iters` rounds:
+//   sender:   fill shared memory with the round number, bulk-store `bytes` of it into the peer's buffer,
+//             mode 0: wait_group 0, then st.relaxed.sys flag            (the candidate)
+//             mode 1: NO wait, flag at once                              (control: must show violations, or the test sees nothing)
+//             mode 2: wait_group 0, fence.acq_rel.sys, st.relaxed flag   (the textbook form)
+//   receiver: polls the flag (relaxed), then reads the whole buffer through L2 and counts words that are not the round number.
+namespace {
+
+__global__ void __launch_bounds__(256, 1) litmusBulkFlag(int sender, int mode, char* peerBuf, char* myBuf, uint32_t* peerWord, uint32_t* myWord, int bytes,
+                                                         int iters, unsigned long long* violations, unsigned* gaveUp) {
+  extern __shared__ __align__(128) unsigned char smem[];  // one 32 KiB tile
+  const int b = blockIdx.x;
+  char* pbuf = peerBuf + (size_t)b * bytes;
+  char* mbuf = myBuf + (size_t)b * bytes;
+  // word 2b: flag (sender -> receiver), word 2b+1: ack (receiver -> sender); each side polls its OWN copy
+  uint32_t* peerFlag = peerWord + 32 * b;
+  uint32_t* myFlag = myWord + 32 * b;
+  uint32_t* peerAck = peerWord + 32 * b + 16;
+  uint32_t* myAck = myWord + 32 * b + 16;
+  unsigned long long bad = 0;
+  for (int k = 1; k <= iters; ++k) {
+    if (sender) {
+      for (int i = threadIdx.x; i < 32768 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = (uint32_t)k;
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        unsigned spins = 0;
+        while (ld_relaxed_sys_u32(myAck) != (uint32_t)(k - 1)) {
+          if (++spins > (1u << 26)) {
+            atomicExch(gaveUp, 1u);
+            break;
+          }
+        }
+        for (int o = 0; o < bytes; o += 32768) {
+          asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(pbuf + o), "r"(smem_u32(smem)), "r"(32768) : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        if (mode != 1) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+        if (mode == 2) asm volatile("fence.acq_rel.sys;" ::: "memory");
+        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(peerFlag), "r"((uint32_t)k) : "memory");
+        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // shared memory is rewritten next round
+      }
+      __syncthreads();
+    } else {
+      if (threadIdx.x == 0) {
+        unsigned spins = 0;
+        while (ld_relaxed_sys_u32(myFlag) != (uint32_t)k) {
+          if (++spins > (1u << 26)) {
+            atomicExch(gaveUp, 1u);
+            break;
+          }
+        }
+      }
+      __syncthreads();
+      for (int i = threadIdx.x; i < bytes / 4; i += blockDim.x) {
+        uint32_t v;
+        asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mbuf + (size_t)i * 4) : "memory");
+        if (v != (uint32_t)k) ++bad;
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        asm volatile("fence.acq_rel.sys;" ::: "memory");
+        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(peerAck), "r"((uint32_t)k) : "memory");
+      }
+    }
+  }
+  if (bad) atomicAdd(violations, bad);
+}
+
+}  // namespace
+
+// One launch on the caller's GPU; the peer runs the other role at the same time.  Buffers: grid * bytes each; words: grid * 32
+// u32 each (zeroed by the caller before both sides start).  bytes: multiple of 32768.
+AAR_API int aar_bench_litmus_bulk_flag(int sender, int mode, int grid, void* peerBuf, void* myBuf, void* peerWords, void* myWords, int bytes, int iters,
+                                       unsigned long long* violations, unsigned* gaveUp, void* stream) {
+  if (grid <= 0 || bytes <= 0 || bytes % 32768 || iters <= 0) return aar_host::fail(-1, "aar_bench_litmus_bulk_flag: bad arguments");
+  litmusBulkFlag<<<grid, 256, 32768, (cudaStream_t)stream>>>(sender, mode, (char*)peerBuf, (char*)myBuf, (uint32_t*)peerWords, (uint32_t*)myWords, bytes, iters,
+                                                              violations, gaveUp);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return aar_host::fail(-2, "aar_bench_litmus_bulk_flag: %s", cudaGetErrorString(e));
   return 0;
 }
 

@@ -15,9 +15,14 @@
 //     after 1/C of the role's time and the next role starts on it: push, reduce and gather of one round overlap;
 //   * AAR_FLAG_SELF_DIRECT: a rank's own contribution is read from its input instead of being copied into its own ring,
 //     and (when every chunk is required) its own reduced block is written straight to the output;
-//   * the in-switch (NVLS) form publishes and consumes PIECES (sub-chunk granules): it has no contributor decision to
-//     take, so nothing forces it to wait for a whole 4 MiB chunk;
-//   * always strict: the broadcast obeys the slot flow control, the eager gather decides once per chunk.
+//   * arrival is published per PIECE (a fixed sub-chunk granule of the layout, <= 256 KiB) instead of per chunk: exactly
+//     one CTA moves a piece, so its flag costs one fence of the CTA's publishing thread and one relaxed store -- no
+//     election, no second fence; the contributor decision is still taken per chunk (a source has delivered a chunk when
+//     all its pieces are flagged), the gather starts on a reduced chunk's first piece, and the in-switch (NVLS) form,
+//     which has no decision to take, pipelines piece by piece throughout;
+//   * always strict: the broadcast obeys the slot flow control, a chunk that is given up is zero-filled as a whole.
+// Every rank of a job must run the bulk kernels for a given geometry (they do not read or write the per-chunk flags of
+// aar_kernels.cu); RoundEngine selects them from the layout, which is the same on all ranks.
 #include <cuda_runtime.h>
 
 #include <mutex>
@@ -37,29 +42,15 @@ __device__ __forceinline__ bool selfOut(const AarRankParams& p, const AarLayout&
   return selfDirect(p) && eagerMode(p, l) && !(p.flags & AAR_FLAG_VIEW_OUTPUT);
 }
 
-// Segments per message such that `lanes` messages (the ones a role works on at the same time: one chunk of every
-// destination) give about one segment per CTA: the role's CTAs finish chunk c together and move on to chunk c + 1.
-struct SweepPlan {
-  int tilesPerSeg, segs;
-  __device__ SweepPlan(const AarLayout& l, int lanes, int nctas) {
-    const int Tm = l.tilesPerChunk;
-    int want = (nctas + lanes - 1) / (lanes > 0 ? lanes : 1);
-    const int S = want < 1 ? 1 : (want > Tm ? Tm : want);
-    tilesPerSeg = (Tm + S - 1) / S;
-    segs = (Tm + tilesPerSeg - 1) / tilesPerSeg;
-  }
-  __device__ int segElems(const AarLayout& l) const { return tilesPerSeg * l.tileElems; }
-  __device__ unsigned liveSegs(const AarLayout& l, int len) const { return (unsigned)((len + segElems(l) - 1) / segElems(l)); }
-};
-
 // ------------------------------------------------------------------------------------------------ K1 on the copy engine
 template <typename T>
 struct PushRole {
+  static constexpr bool kPublishes = true;
   const AarRankParams& p;
   const AarLayout& l;
-  int nctas, slot, R, first, S, segElems;
+  int nctas, slot, R, first, Sp, pieceElems;
   uint32_t epoch;
-  long long total, idx;
+  int total, idx;
   bool rotate;
   unsigned known, go;
 
@@ -68,52 +59,43 @@ struct PushRole {
     epoch = (uint32_t)(p.round + 1);
     first = selfDirect(p) ? 1 : 0;
     R = l.P - first;
-    const SweepPlan plan(l, R > 0 ? R : 1, nctas);
-    S = plan.segs;
-    segElems = plan.segElems(l);
-    total = (long long)l.C * R * S;
+    Sp = l.piecesPerChunk;
+    pieceElems = l.tilesPerPiece * l.tileElems;
+    total = l.C * R * Sp;
     idx = cta;
     rotate = R > 0 && (nctas % R) == 0;
   }
-  // chunk-major, then segment, then destination staggered from self (AllreduceWorker.scala:195-196); when the CTA count is
-  // a multiple of the destination count each pass rotates by one so a CTA does not always draw the same peer
+  // chunk-major, then piece, then destination staggered from self (AllreduceWorker.scala:195-196): the role's CTAs sweep
+  // the block chunk by chunk together, so chunk c is complete after (c + 1) / C of the role's time; when the CTA count is a
+  // multiple of the destination count each pass rotates by one so a CTA does not always draw the same peer
   __device__ int nextUnit(CopyUnit& u, bool blocking) {
     for (; idx < total; idx += nctas) {
-      const int i = (int)((idx % R + (rotate ? idx / nctas : 0)) % R);
-      const int s = (int)((idx / R) % S);
-      const int c = (int)(idx / ((long long)S * R));
+      const int i = (idx % R + (rotate ? idx / nctas : 0)) % R;
+      const int s = (idx / R) % Sp;
+      const int c = idx / (Sp * R);
       const int dest = (p.rank + first + i) % l.P;
       const int clen = chunkLen(l, dest, c);
-      const int off = s * segElems;
+      const int off = s * pieceElems;
       if (off >= clen) continue;
       const int d = destDecision1(p, l, dest, known, go, blocking);
       if (d < 0) return -1;
       if (d == 0) continue;  // the peer fell out of the window: its copy of this contribution is dropped
-      const int n = min(segElems, clen - off);
+      const int n = min(pieceElems, clen - off);
       const long long inOff = blockStart(l, dest) + (long long)c * l.maxChunk + off;
       u.src = reinterpret_cast<const char*>(reinterpret_cast<const T*>(p.input) + inOff);
       u.dst = regionOf(p, dest) + l.scatterOff + (((long long)slot * l.P + p.rank) * l.blkStride + (long long)c * l.maxChunk + off) * (long long)sizeof(T);
       u.bytes = (uint32_t)n * (uint32_t)sizeof(T);
       u.a = (uint32_t)dest;
       u.b = (uint32_t)c;
-      u.c = (uint32_t)clen;
+      u.c = (uint32_t)s;
       idx += nctas;
       return 1;
     }
     return 0;
   }
-  // last segment of this "ScatterBlock": publish its arrival
-  __device__ void complete(uint32_t dest, uint32_t c, uint32_t clen) {
-    fence_proxy_async();
-    fence_sys();
-    unsigned* ctr = reinterpret_cast<unsigned*>(regionOf(p, p.rank) + l.k1CtrOff) + ((long long)slot * l.P + dest) * l.C + c;
-    const unsigned old = atomicAdd(ctr, 1u);
-    if (old + 1 == (unsigned)((clen + segElems - 1) / segElems)) {
-      atomicExch(ctr, 0u);
-      fence_sys();
-      uint32_t* flag = reinterpret_cast<uint32_t*>(regionOf(p, dest) + l.sflagOff) + ((long long)slot * l.C + c) * AAR_MAXP + p.rank;
-      st_release_sys_u32(flag, epoch);
-    }
+  // this piece of the "ScatterBlock" has landed (runs after the publishing thread's fence)
+  __device__ void complete(uint32_t dest, uint32_t c, uint32_t s) {
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(pflagS(p, l, (int)dest, slot, (int)c, (int)s) + p.rank), "r"(epoch) : "memory");
   }
 };
 
@@ -121,26 +103,35 @@ template <typename T>
 __device__ void rolePush(const AarRankParams& p, const AarLayout& l, int cta, int nctas, BulkShared& bs, unsigned char* dsm) {
   bulkInit(bs, dsm);
   if (p.flags & AAR_FLAG_SKIP_SCATTER) return;
+  if (threadIdx.x == 32) {  // publishing thread: arrival flags of the pieces thread 0 has finished
+    PushRole<T> role(p, l, cta, nctas);
+    doneDrain(bs.done, role);
+    return;
+  }
   if (threadIdx.x != 0) return;
   if (selfDirect(p) && cta == 0) {
     // my own contribution stays where it is (the reduce role reads it from the input): only its arrival is announced
     const int slot = p.round % l.L;
-    uint32_t* flags = reinterpret_cast<uint32_t*>(regionOf(p, p.rank) + l.sflagOff) + (long long)slot * l.C * AAR_MAXP + p.rank;
     const int mine = numChunks(l, p.rank);
-    for (int c = 0; c < mine; ++c) st_release_sys_u32(flags + (long long)c * AAR_MAXP, (uint32_t)(p.round + 1));
+    for (int c = 0; c < mine; ++c) {
+      const int np = piecesOf(l, chunkLen(l, p.rank, c));
+      for (int s = 0; s < np; ++s) st_release_sys_u32(pflagS(p, l, p.rank, slot, c, s) + p.rank, (uint32_t)(p.round + 1));
+    }
   }
   PushRole<T> role(p, l, cta, nctas);
   if (role.R > 0) runCopyRole(p, l, role, bs, dsm);
+  else doneClose(bs.done);
 }
 
 // NVLS: the input is staged in MY region (the switch pulls it); only the flag travels, one per piece.
 template <typename T>
 struct StageRole {
+  static constexpr bool kPublishes = true;
   const AarRankParams& p;
   const AarLayout& l;
   int nctas, slot, Sp, pieceElems;
   uint32_t epoch;
-  long long total, idx;
+  int total, idx;
   unsigned known, go;
   char* stage;
   bool inPlace;
@@ -150,16 +141,16 @@ struct StageRole {
     epoch = (uint32_t)(p.round + 1);
     Sp = l.piecesPerChunk;
     pieceElems = l.tilesPerPiece * l.tileElems;
-    total = (long long)l.C * l.P * Sp;
+    total = l.C * l.P * Sp;
     idx = cta;
     stage = regionOf(p, p.rank) + l.stageOff + (long long)slot * paddedData(l) * (long long)sizeof(T);
     inPlace = reinterpret_cast<const char*>(p.input) == stage;  // the source wrote straight into the stage
   }
   __device__ int nextUnit(CopyUnit& u, bool blocking) {
     for (; idx < total; idx += nctas) {
-      const int b = ((int)(idx % l.P) + p.rank) % l.P;
-      const int s = (int)((idx / l.P) % Sp);
-      const int c = (int)(idx / ((long long)Sp * l.P));
+      const int b = (idx % l.P + p.rank) % l.P;
+      const int s = (idx / l.P) % Sp;
+      const int c = idx / (Sp * l.P);
       const int clen = chunkLen(l, b, c);
       const int off = s * pieceElems;
       if (off >= clen) continue;
@@ -181,11 +172,8 @@ struct StageRole {
     }
     return 0;
   }
-  __device__ void complete(uint32_t b, uint32_t c, uint32_t s) {
-    fence_proxy_async();
-    fence_sys();
-    uint32_t* flag = reinterpret_cast<uint32_t*>(regionOf(p, (int)b) + l.pflagSOff) + (((long long)slot * l.C + c) * Sp + s) * AAR_MAXP + p.rank;
-    st_release_sys_u32(flag, epoch);
+  __device__ void complete(uint32_t b, uint32_t c, uint32_t s) {  // after the publishing thread's fence
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(pflagS(p, l, (int)b, slot, (int)c, (int)s) + p.rank), "r"(epoch) : "memory");
   }
 };
 
@@ -193,200 +181,155 @@ template <typename T>
 __device__ void roleStage(const AarRankParams& p, const AarLayout& l, int cta, int nctas, BulkShared& bs, unsigned char* dsm) {
   bulkInit(bs, dsm);
   if (p.flags & AAR_FLAG_SKIP_SCATTER) return;
-  if (threadIdx.x != 0) return;
+  if (threadIdx.x != 0 && threadIdx.x != 32) return;
   StageRole<T> role(p, l, cta, nctas);
-  runCopyRole(p, l, role, bs, dsm);
+  if (threadIdx.x == 32) doneDrain(bs.done, role);
+  else runCopyRole(p, l, role, bs, dsm);
 }
 
 // ------------------------------------------------------------------------------------------------ K2 on the copy engine
 // Ordered fp32 sum of the decided contributor set (peer-index order from 0.0f, AllreduceWorker.scala:245-249), tile by
-// tile: thread 0 bulk-loads the tile of every contributor into shared memory, all 512 threads add (one 16-byte vector
-// each) and write the result tile to shared memory, thread 0 bulk-stores it into every destination's reduce ring.  The
-// loads run up to (stages - 2) tiles ahead of the adds, across segment and chunk boundaries whenever the next chunk's
-// contributor set is already decided.
+// tile, with the CTA's warps specialised:
+//   warp 0 (one thread)   loader: takes the chunk's contributor decision and the destinations' flow-control decisions, then
+//                         bulk-loads the tile of every contributor into the stage (own contribution straight from the input
+//                         with AAR_FLAG_SELF_DIRECT); runs ahead of the adds by the number of stages, across segments and chunks
+//   warps 3..15           adders: two (or one) 16-byte vectors per thread, shared memory in, shared memory out
+//   warp 1 (one thread)   storer: bulk-stores the result tile into every destination's reduce ring (own block straight to the
+//                         output when every chunk is required), one bulk group per tile
+//   warp 2 (one thread)   publisher: last-segment election and the ReduceBlock flags (epoch | count) -- the only thread that
+//                         fences, and it has no copies of its own in flight
+// Stages hand over through mbarriers: full (loads landed) -> computed (result written, inputs consumed) -> outFree (stores
+// have read the result).  Issuing one bulk copy costs the issuing thread about 300 cycles (measured), which is why loads,
+// stores and adds each get their own thread(s) instead of taking turns on one.
+constexpr int kAdderWarp0 = 3, kAdderWarps = kThreads / 32 - kAdderWarp0, kAdders = kAdderWarps * 32;  // 13 warps, 416 threads
+
+struct ReducePublisher {
+  const AarRankParams& p;
+  const AarLayout& l;
+  int slot;
+  bool so;
+  // this piece of the "ReduceBlock" has landed everywhere it was sent: tell those peers, count included (runs after the
+  // publishing thread's fence)
+  __device__ void complete(uint32_t c, uint32_t destCount, uint32_t s) {
+    const int P = l.P;
+    const unsigned dm = destCount & 0xffffu, count = destCount >> 16;
+    if (so && s == 0 && p.outCounts) p.outCounts[p.rank * l.C + (int)c] = (int)count;
+    const uint64_t word = ((uint64_t)(p.round + 1) << 32) | (uint64_t)count;
+    for (int i2 = 0; i2 < P; ++i2) {
+      const int dest = (i2 + p.rank) % P;
+      if (!((dm >> dest) & 1u)) continue;  // no data was written there: no flag either
+      asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(pflagR(p, l, dest, slot, p.rank, (int)c, (int)s)), "l"(word) : "memory");
+    }
+  }
+};
+
 template <typename T>
 __device__ void roleReduceP2P(const AarRankParams& p, const AarLayout& l, int cta, int nctas, BulkShared& bs, unsigned char* dsm) {
-  bulkInit(bs, dsm);
+  bulkInit(bs, dsm, kAdderWarps);
   constexpr int V = Elem<T>::kPerVec;
-  const int P = l.P, C = l.C;
+  const int P = l.P;
   const int myChunks = numChunks(l, p.rank);
   if (myChunks == 0) return;
   const int slot = p.round % l.L;
-  const uint64_t epoch = (uint64_t)(p.round + 1);
   char* my = regionOf(p, p.rank);
   const bool sd = selfDirect(p), so = selfOut(p, l);
-  const int tileB = P <= 8 ? 8192 : 4096;
+  const int tileB = kAdders * 16 * (P <= 4 ? 2 : 1) / (P <= 8 ? 1 : 2);  // 13312 / 6656 / 3328 bytes per contributor per tile
   const int stageB = (P + 1) * tileB;
   int nst = kStageBytes / stageB;
-  if (nst > 6) nst = 6;
-  const SweepPlan plan(l, 1, nctas);
-  const int S = plan.segs, segElems = plan.segElems(l);
-  const long long total = (long long)myChunks * S;
+  if (nst > kMaxStages) nst = kMaxStages;
+  const int S = l.piecesPerChunk, segElems = l.tilesPerPiece * l.tileElems;  // units are pieces, swept chunk by chunk
+  const int total = myChunks * S;
   const uint32_t stage0 = smem_u32(dsm);
   const long long blockIn = blockStart(l, p.rank);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr uint32_t kStop = 0xffffffffu;
 
-  auto unitLen = [&](long long idx) {  // elements of unit idx (0: nothing there)
-    const int c = (int)(idx / S), s = (int)(idx % S);
-    const int r = chunkLen(l, p.rank, c) - s * segElems;
-    return r <= 0 ? 0 : (r < segElems ? r : segElems);
-  };
-  auto tilesOf = [&](int n) { return (int)(((long long)n * (long long)sizeof(T) + tileB - 1) / tileB); };
-
-  // load side (thread 0)
-  long long lIdx = cta;
-  int lTile = 0, lTiles = 0, lOrd = -1, lLen = 0;
-  bool lOpen = false;
-  unsigned known = 0, go = 0, cachedMask = 0, lDest = 0;
-  int cachedChunk = -1;
-  uint32_t GL = 0, head = 0, tail = 0;
-  // compute side (all threads)
-  long long cIdx = cta;
-  int cTile = 0, cTiles = 0, cOrd = -1, cLen = 0;
-  uint32_t G = 0, phaseBits = 0;
-
-  auto complete = [&](uint32_t c, uint32_t destCount, uint32_t clen) {
-    const unsigned dm = destCount & 0xffffu, count = destCount >> 16;
-    fence_proxy_async();
-    fence_sys();
-    unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k2CtrOff) + (long long)slot * C + c;
-    const unsigned old = atomicAdd(ctr, 1u);
-    if (old + 1 == (unsigned)(((int)clen + segElems - 1) / segElems)) {  // last segment of this "ReduceBlock": tell every peer, count included
-      atomicExch(ctr, 0u);
-      if (so && p.outCounts) p.outCounts[p.rank * C + (int)c] = (int)count;
-      fence_sys();
-      const uint64_t word = (epoch << 32) | (uint64_t)count;
+  if (warp == 0) {
+    if (lane != 0) return;
+    // ------------------------------------------------------------ loader
+    unsigned known = 0, go = 0, mask = 0;
+    int cachedChunk = -1, st = 0;
+    uint32_t use = 0;  // how often stage `st` has been used before
+    auto arm = [&](uint32_t bytes, unsigned contributors, unsigned dm, long long byteOff, uint32_t a, uint32_t b, uint32_t c, bool last) -> uint32_t {
+      // the stage's previous tenant must be gone altogether -- inputs added, result stored, its job words read by the storer:
+      // phase (use - 1) of `outFree` (which the storer signals one tile after the stores were issued)
+      mbar_wait(p, l, smem_u32(&bs.outFree[st]), (use + 1u) & 1u);
+      bs.jobBytes[st] = bytes;
+      bs.jobInfo[st] = contributors;
+      bs.jobDst[st] = (unsigned long long)byteOff;
+      bs.unitA[st] = a;
+      bs.unitB[st] = dm | (b << 16);
+      bs.unitC[st] = c | (last ? 0x80000000u : 0u);
+      return smem_u32(&bs.full[st]);
+    };
+    auto advance = [&]() {
+      if (++st == nst) {
+        st = 0;
+        ++use;
+      }
+    };
+    for (int idx = cta; idx < total; idx += nctas) {
+      const int c = idx / S, s = idx - c * S;
+      const int clen = chunkLen(l, p.rank, c);
+      const int rest = clen - s * segElems;
+      if (rest <= 0) continue;
+      const int len = rest < segElems ? rest : segElems;
+      if (c != cachedChunk) {
+        chunkDecision1(p, l, c, clen, p.minRequired, true, mask);
+        fence_proxy_async();  // the flagged rows are read by bulk loads
+        if (cachedChunk < 0) traceMark(p, l, 2);
+        cachedChunk = c;
+      }
+      // Slot flow control for the broadcast: round R may overwrite slot R % L of a peer's reduce ring only after that peer
+      // retired round R - L; a peer that fell out of the window is skipped (no data, no flag).
+      unsigned dm = 0;
       for (int i2 = 0; i2 < P; ++i2) {
         const int dest = (i2 + p.rank) % P;
-        if (!((dm >> dest) & 1u)) continue;  // no data was written there: no flag either
-        st_release_sys_u64(reinterpret_cast<uint64_t*>(regionOf(p, dest) + l.rflagOff) + ((long long)slot * P + p.rank) * C + c, word);
+        if (destDecision1(p, l, dest, known, go, true)) dm |= 1u << dest;
       }
-    }
-  };
-  auto retireDone = [&](uint32_t lastCompleteGroup) {
-    while (head != tail && bs.fifoGroup[head & 15] <= lastCompleteGroup) {
-      complete(bs.fifoA[head & 15], bs.fifoB[head & 15], bs.fifoC[head & 15]);
-      ++head;
-    }
-  };
-
-  for (;;) {
-    if (threadIdx.x == 0) {
-      while (GL - G <= (uint32_t)(nst - 2)) {
-        if (!lOpen) {
-          while (lIdx < total && unitLen(lIdx) == 0) lIdx += nctas;
-          if (lIdx >= total) break;
-          const int c = (int)(lIdx / S);
-          const bool block = GL == G;
-          if (block && head != tail) {  // about to wait with nothing in flight: do not sit on finished segments' flags
-            bulk_wait<0>();
-            retireDone(G - 1);
-          }
-          if (c != cachedChunk) {
-            unsigned m = 0;
-            if (!chunkDecision1(p, l, reinterpret_cast<uint64_t*>(my + l.k2DecOff) + (long long)slot * C + c,
-                                reinterpret_cast<const uint32_t*>(my + l.sflagOff) + ((long long)slot * C + c) * AAR_MAXP, p.minRequired, block, m))
-              break;
-            fence_proxy_async();  // the flagged rows are read by bulk loads
-            if (cachedChunk < 0) traceMark(p, l, 2);
-            cachedChunk = c;
-            cachedMask = m;
-          }
-          // Slot flow control for the broadcast: round R may overwrite slot R % L of a peer's reduce ring only after that
-          // peer retired round R - L; a peer that fell out of the window is skipped (no data, no flag).
-          unsigned dm = 0;
-          bool ready = true;
-          for (int i2 = 0; i2 < P; ++i2) {
-            const int dest = (i2 + p.rank) % P;
-            const int d = destDecision1(p, l, dest, known, go, block);
-            if (d < 0) {
-              ready = false;
-              break;
-            }
-            if (d) dm |= 1u << dest;
-          }
-          if (!ready) break;
-          ++lOrd;
-          bs.openMask[lOrd % kMaxStages] = cachedMask;
-          lDest = dm;
-          lLen = unitLen(lIdx);
-          lTiles = tilesOf(lLen);
-          lTile = 0;
-          lOpen = true;
-        }
-        const int st = (int)(GL % (uint32_t)nst);
-        const int c = (int)(lIdx / S), s = (int)(lIdx % S);
-        const long long elemOff = (long long)c * l.maxChunk + (long long)s * segElems;  // inside my block
-        const uint32_t bytes = (uint32_t)min((long long)tileB, (long long)lLen * (long long)sizeof(T) - (long long)lTile * tileB);
-        const uint32_t bar = smem_u32(&bs.full[st]);
-        const int nsrc = __popc(cachedMask);
-        bs.jobBytes[st] = bytes;
-        bs.jobInfo[st] = lDest;
+      const int nsrc = __popc(mask);
+      const long long unitOff = ((long long)c * l.maxChunk + (long long)s * segElems) * (long long)sizeof(T);
+      const long long lenB = (long long)len * (long long)sizeof(T);
+      for (long long o = 0; o < lenB; o += tileB) {
+        const uint32_t bytes = (uint32_t)(lenB - o < tileB ? lenB - o : tileB);
+        const uint32_t bar = arm(bytes, mask, dm, unitOff + o, (uint32_t)c, (uint32_t)nsrc, (uint32_t)s, o + tileB >= lenB);
         if (nsrc == 0) {
-          asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");  // nothing to load: the phase completes at once
+          mbar_arrive(bar);  // nothing to load: the phase completes at once
         } else {
           mbar_expect_tx(bar, bytes * (uint32_t)nsrc);
           int j = 0;
-          for (int src = 0; src < P; ++src) {
-            if (!((cachedMask >> src) & 1u)) continue;
-            const char* row = (src == p.rank && sd)
-                                  ? reinterpret_cast<const char*>(reinterpret_cast<const T*>(p.input) + blockIn + elemOff)
-                                  : my + l.scatterOff + (((long long)slot * P + src) * l.blkStride + elemOff) * (long long)sizeof(T);
-            bulk_g2s(stage0 + (uint32_t)(st * stageB + j * tileB), row + (long long)lTile * tileB, bytes, bar);
-            ++j;
+          for (unsigned m = mask; m; m &= m - 1, ++j) {
+            const int src = __ffs(m) - 1;
+            const char* row = (src == p.rank && sd) ? reinterpret_cast<const char*>(p.input) + blockIn * (long long)sizeof(T)
+                                                    : my + l.scatterOff + ((long long)slot * P + src) * l.blkStride * (long long)sizeof(T);
+            bulk_g2s(stage0 + (uint32_t)(st * stageB + j * tileB), row + unitOff + o, bytes, bar);
           }
         }
-        ++GL;
-        if (++lTile == lTiles) {
-          lOpen = false;
-          lIdx += nctas;
-        }
+        advance();
       }
     }
-    // ---- compute side: every thread, in lockstep
-    if (cTile == cTiles) {
-      while (cIdx < total && unitLen(cIdx) == 0) cIdx += nctas;
-      if (cIdx >= total) break;
-      ++cOrd;
-      cLen = unitLen(cIdx);
-      cTiles = tilesOf(cLen);
-      cTile = 0;
-    }
-    const int st = (int)(G % (uint32_t)nst);
-    mbar_wait(p, l, smem_u32(&bs.full[st]), (phaseBits >> st) & 1u);
-    phaseBits ^= 1u << st;
-    const unsigned mask = bs.openMask[cOrd % kMaxStages];
-    const int count = __popc(mask);
-    const float divisor = ((p.flags & AAR_FLAG_NORMALIZE) && count > 1) ? (float)count : 1.f;
-    const uint32_t bytes = (uint32_t)min((long long)tileB, (long long)cLen * (long long)sizeof(T) - (long long)cTile * tileB);
-    const unsigned char* in = dsm + (size_t)st * stageB;
-    unsigned char* out = dsm + (size_t)st * stageB + (size_t)P * tileB;
-    for (uint32_t i = threadIdx.x; i < bytes / 16; i += kThreads) {
-      float acc[V];
-#pragma unroll
-      for (int k = 0; k < V; ++k) acc[k] = 0.f;
-      int j = 0;
-      for (int src = 0; src < P; ++src) {
-        if (!((mask >> src) & 1u)) continue;
-        const uint4 v = *reinterpret_cast<const uint4*>(in + (size_t)j * tileB + (size_t)i * 16);
-        float f[V];
-        Elem<T>::unpack(v, f);
-#pragma unroll
-        for (int k = 0; k < V; ++k) acc[k] += f[k];
-        ++j;
+    mbar_arrive(arm(kStop, 0, 0, 0, 0, 0, 0, false));  // no more tiles
+    traceMarkAny(p, l, 6);
+    return;
+  }
+
+  if (warp == 1) {
+    if (lane != 0) return;
+    // ------------------------------------------------------------ storer
+    int st = 0, prev = -1;
+    uint32_t use = 0, G = 0, head = 0, tail = 0;
+    auto retireDone = [&](uint32_t lastCompleteGroup) {
+      while (head != tail && bs.fifoGroup[head & 15] <= lastCompleteGroup) {
+        donePush(bs.done, bs.fifoA[head & 15], bs.fifoB[head & 15], bs.fifoC[head & 15]);
+        ++head;
       }
-      if (divisor != 1.f) {
-#pragma unroll
-        for (int k = 0; k < V; ++k) acc[k] = acc[k] / divisor;
-      }
-      *reinterpret_cast<uint4*>(out + (size_t)i * 16) = Elem<T>::pack(acc);
-    }
-    fence_proxy_async_smem();  // the result tile is read by the bulk stores below
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      const int c = (int)(cIdx / S), s = (int)(cIdx % S);
-      const long long elemOff = (long long)c * l.maxChunk + (long long)s * segElems;
-      const long long byteOff = elemOff * (long long)sizeof(T) + (long long)cTile * tileB;
-      const unsigned dm = bs.jobInfo[st];
+    };
+    for (;;) {
+      mbar_wait(p, l, smem_u32(&bs.computed[st]), use & 1u);
+      const uint32_t bytes = bs.jobBytes[st];
+      if (bytes == kStop) break;
+      const unsigned dm = bs.unitB[st] & 0xffffu;
+      const long long byteOff = (long long)bs.jobDst[st];
       const uint32_t outS = stage0 + (uint32_t)(st * stageB + P * tileB);
       for (int i2 = 0; i2 < P; ++i2) {
         const int dest = (i2 + p.rank) % P;
@@ -397,26 +340,84 @@ __device__ void roleReduceP2P(const AarRankParams& p, const AarLayout& l, int ct
         bulk_s2g(dst, outS, bytes);
       }
       bulk_commit();
-      if (cTile + 1 == cTiles) {
+      if (G == 0) traceMarkAny(p, l, 7);
+      if (bs.unitC[st] & 0x80000000u) {  // last tile of its segment
         bs.fifoGroup[tail & 15] = G;
-        bs.fifoA[tail & 15] = (uint32_t)c;
-        bs.fifoB[tail & 15] = dm | ((uint32_t)count << 16);
-        bs.fifoC[tail & 15] = (uint32_t)chunkLen(l, p.rank, c);
+        bs.fifoA[tail & 15] = bs.unitA[st];
+        bs.fifoB[tail & 15] = bs.unitB[st];
+        bs.fifoC[tail & 15] = bs.unitC[st] & 0x7fffffffu;
         ++tail;
       }
-      bulk_wait_read<1>();
+      bulk_wait_read<1>();  // the stores of the tile before this one have read their result tile: its stage may be rewritten
+      if (prev >= 0) mbar_arrive(smem_u32(&bs.outFree[prev]));
+      prev = st;
       if (head != tail && G + 1 > (uint32_t)kDoneLag && bs.fifoGroup[head & 15] + kDoneLag < G + 1) {
         bulk_wait<kDoneLag>();
         retireDone(G - kDoneLag);
       }
+      ++G;
+      if (++st == nst) {
+        st = 0;
+        ++use;
+      }
     }
-    ++G;
-    if (++cTile == cTiles) cIdx += nctas;
-  }
-  if (threadIdx.x == 0) {
     bulk_wait<0>();
     if (G > 0) retireDone(G - 1);
-    traceMark(p, l, 3);
+    doneClose(bs.done);
+    traceMarkAny(p, l, 3);
+    return;
+  }
+
+  if (warp == 2) {
+    if (lane != 0) return;
+    // ------------------------------------------------------------ publisher
+    ReducePublisher pub{p, l, slot, so};
+    doneDrain(bs.done, pub);
+    return;
+  }
+
+  // ---------------------------------------------------------------- adders
+  const int t = threadIdx.x - kAdderWarp0 * 32;
+  int st = 0;
+  uint32_t use = 0;
+  for (;;) {
+    mbar_wait(p, l, smem_u32(&bs.full[st]), use & 1u);
+    const uint32_t bytes = bs.jobBytes[st];
+    if (bytes == kStop) {
+      if (lane == 0) mbar_arrive(smem_u32(&bs.computed[st]));
+      break;
+    }
+    const int count = __popc(bs.jobInfo[st]);
+    const float divisor = ((p.flags & AAR_FLAG_NORMALIZE) && count > 1) ? (float)count : 1.f;
+    // the result tile of this stage is free once the stores of its previous tenant have read it
+    mbar_wait(p, l, smem_u32(&bs.outFree[st]), (use + 1u) & 1u);
+    const unsigned char* in = dsm + (size_t)st * stageB;
+    unsigned char* out = dsm + (size_t)st * stageB + (size_t)P * tileB;
+    for (uint32_t i = (uint32_t)t; i < bytes / 16; i += kAdders) {
+      float acc[V];
+#pragma unroll
+      for (int k = 0; k < V; ++k) acc[k] = 0.f;
+      const unsigned char* src = in + (size_t)i * 16;
+      for (int j = 0; j < count; ++j, src += tileB) {  // contributors sit in the stage in peer-index order
+        const uint4 v = *reinterpret_cast<const uint4*>(src);
+        float f[V];
+        Elem<T>::unpack(v, f);
+#pragma unroll
+        for (int k = 0; k < V; ++k) acc[k] += f[k];
+      }
+      if (divisor != 1.f) {
+#pragma unroll
+        for (int k = 0; k < V; ++k) acc[k] = acc[k] / divisor;
+      }
+      *reinterpret_cast<uint4*>(out + (size_t)i * 16) = Elem<T>::pack(acc);
+    }
+    fence_proxy_async_smem();  // the result tile is read by the storer's bulk stores
+    __syncwarp();
+    if (lane == 0) mbar_arrive(smem_u32(&bs.computed[st]));
+    if (++st == nst) {
+      st = 0;
+      ++use;
+    }
   }
 }
 
@@ -450,23 +451,23 @@ __device__ __forceinline__ void nvlsSpanBulk(const char* mcStage, char* mcOut, i
 template <typename T>
 __device__ void roleReduceNvls(const AarRankParams& p, const AarLayout& l, int cta, int nctas, BulkShared& bs) {
   __syncthreads();
-  const int P = l.P, C = l.C, Sp = l.piecesPerChunk;
+  const int P = l.P, Sp = l.piecesPerChunk;
   const int myChunks = numChunks(l, p.rank);
   if (myChunks == 0) return;
   const int slot = p.round % l.L;
   const uint32_t epoch = (uint32_t)(p.round + 1);
   char* my = regionOf(p, p.rank);
   const int pieceElems = l.tilesPerPiece * l.tileElems;
-  const long long total = (long long)myChunks * Sp;
+  const int total = myChunks * Sp;
   bool first = true;
-  for (long long idx = cta; idx < total; idx += nctas) {
-    const int c = (int)(idx / Sp), s = (int)(idx % Sp);
+  for (int idx = cta; idx < total; idx += nctas) {
+    const int c = idx / Sp, s = idx - c * Sp;
     const int clen = chunkLen(l, p.rank, c);
     const int off = s * pieceElems;
     if (off >= clen) continue;
     const int n = min(pieceElems, clen - off);
     if (threadIdx.x == 0) {
-      const uint32_t* flags = reinterpret_cast<const uint32_t*>(my + l.pflagSOff) + (((long long)slot * C + c) * Sp + s) * AAR_MAXP;
+      const uint32_t* flags = pflagS(p, l, p.rank, slot, c, s);
       Deadline dl(p.timeoutNs);
       unsigned spins = 0, backoff = 32;
       int ok = 0;
@@ -504,10 +505,10 @@ __device__ void roleReduceNvls(const AarRankParams& p, const AarLayout& l, int c
     __syncthreads();
     if (threadIdx.x == 0 && ok) {
       __threadfence_system();
+      const uint64_t word = ((uint64_t)epoch << 32) | (uint64_t)P;
       for (int i2 = 0; i2 < P; ++i2) {
         const int dest = (i2 + p.rank) % P;
-        uint32_t* flag = reinterpret_cast<uint32_t*>(regionOf(p, dest) + l.pflagROff) + (((long long)slot * P + p.rank) * C + c) * Sp + s;
-        st_release_sys_u32(flag, epoch);
+        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(pflagR(p, l, dest, slot, p.rank, c, s)), "l"(word) : "memory");
       }
     }
   }
@@ -515,181 +516,60 @@ __device__ void roleReduceNvls(const AarRankParams& p, const AarLayout& l, int c
 }
 
 // ------------------------------------------------------------------------------------------------ K3 on the copy engine
-// Eager gather (every chunk required): a segment of chunk (owner, c) is copied as soon as the chunk's ReduceBlock flag
-// lands, while other chunks are still in flight; a chunk that never shows up (forced round, timeout) is zero-filled --
-// decided once per chunk (eagerChunkDecision1).
-template <typename T>
-struct GatherEagerRole {
-  const AarRankParams& p;
-  const AarLayout& l;
-  int nctas, slot, R, first, S, segElems, lastKey, lastCnt;
-  long long total, idx;
-  bool view;
-
-  __device__ GatherEagerRole(const AarRankParams& p_, const AarLayout& l_, int cta, int nctas_) : p(p_), l(l_), nctas(nctas_), lastKey(-1), lastCnt(-1) {
-    slot = p.round % l.L;
-    first = selfOut(p, l) ? 1 : 0;  // my own block was written by my reduce role
-    R = l.P - first;
-    const SweepPlan plan(l, R > 0 ? R : 1, nctas);
-    S = plan.segs;
-    segElems = plan.segElems(l);
-    total = (long long)l.C * R * S;
-    idx = cta;
-    view = (p.flags & AAR_FLAG_VIEW_OUTPUT) != 0;
-  }
-  // chunk-major (chunk c of every owner is reduced at about the same time), owners staggered from self
-  __device__ int nextUnit(CopyUnit& u, bool blocking) {
-    for (; idx < total; idx += nctas) {
-      const int s = (int)(idx % S);
-      const int owner = (p.rank + first + (int)((idx / S) % R)) % l.P;
-      const int c = (int)(idx / ((long long)S * R));
-      const int clen = chunkLen(l, owner, c);
-      const int off = s * segElems;
-      if (off >= clen) continue;
-      const int key = owner * l.C + c;
-      if (key != lastKey) {
-        const int cnt = eagerChunkDecision1(p, l, key, blocking);
-        if (cnt == -2) return -1;
-        fence_proxy_async();  // the chunk is read by bulk loads
-        lastKey = key;
-        lastCnt = cnt;
-      }
-      const int cnt = lastCnt;
-      if (s == 0 && p.outCounts) p.outCounts[key] = cnt < 0 ? 0 : cnt;
-      const int n = min(segElems, clen - off);
-      char* ring = regionOf(p, p.rank) + l.reduceOff + (((long long)slot * l.P + owner) * l.blkStride + (long long)c * l.maxChunk + off) * (long long)sizeof(T);
-      idx += nctas;
-      if (view) {  // the caller reads the ring slot itself: only chunks that never arrived are touched
-        if (cnt >= 0) {
-          idx -= nctas;
-          continue;
-        }
-        u.src = nullptr;
-        u.dst = ring;
-      } else {
-        u.src = cnt >= 0 ? ring : nullptr;  // chunks whose ReduceBlock never arrived stay zero (AllreduceWorker.scala:183)
-        u.dst = reinterpret_cast<char*>(p.output) + (blockStart(l, owner) + (long long)c * l.maxChunk + off) * (long long)sizeof(T);
-      }
-      u.bytes = (uint32_t)n * (uint32_t)sizeof(T);
-      u.a = u.b = u.c = 0;
-      return 1;
-    }
-    return 0;
-  }
-  __device__ void complete(uint32_t, uint32_t, uint32_t) {}
-};
-
-// Gather from the round's snapshot (thComplete < 1 or a forced round): gatherDecision() has counted the arrivals against
-// minChunksRequired and recorded which chunks made it; nothing is waited for here.
-template <typename T>
-struct GatherSnapshotRole {
-  const AarRankParams& p;
-  const AarLayout& l;
-  int nctas, slot, S, segElems;
-  long long total, idx;
-  bool view;
-  const int* counts;
-
-  __device__ GatherSnapshotRole(const AarRankParams& p_, const AarLayout& l_, int cta, int nctas_) : p(p_), l(l_), nctas(nctas_) {
-    slot = p.round % l.L;
-    const SweepPlan plan(l, l.P, nctas);
-    S = plan.segs;
-    segElems = plan.segElems(l);
-    total = (long long)l.C * l.P * S;
-    idx = cta;
-    view = (p.flags & AAR_FLAG_VIEW_OUTPUT) != 0;
-    counts = reinterpret_cast<const int*>(regionOf(p, p.rank) + l.countsOff) + (long long)slot * l.totalChunks;
-  }
-  __device__ int nextUnit(CopyUnit& u, bool) {
-    for (; idx < total; idx += nctas) {
-      const int s = (int)(idx % S);
-      const int owner = (p.rank + (int)((idx / S) % l.P)) % l.P;
-      const int c = (int)(idx / ((long long)S * l.P));
-      const int clen = chunkLen(l, owner, c);
-      const int off = s * segElems;
-      if (off >= clen) continue;
-      const int cnt = __ldcg(counts + owner * l.C + c);
-      if (view && cnt >= 0) continue;
-      const int n = min(segElems, clen - off);
-      char* ring = regionOf(p, p.rank) + l.reduceOff + (((long long)slot * l.P + owner) * l.blkStride + (long long)c * l.maxChunk + off) * (long long)sizeof(T);
-      if (view) {
-        u.src = nullptr;
-        u.dst = ring;
-      } else {
-        u.src = cnt >= 0 ? ring : nullptr;
-        u.dst = reinterpret_cast<char*>(p.output) + (blockStart(l, owner) + (long long)c * l.maxChunk + off) * (long long)sizeof(T);
-      }
-      u.bytes = (uint32_t)n * (uint32_t)sizeof(T);
-      u.a = u.b = u.c = 0;
-      idx += nctas;
-      return 1;
-    }
-    return 0;
-  }
-  __device__ void complete(uint32_t, uint32_t, uint32_t) {}
-};
-
-template <typename T>
-__device__ void roleGatherP2P(const AarRankParams& p, const AarLayout& l, int cta, int nctas, BulkShared& bs, Smem& sm, unsigned char* dsm) {
-  bulkInit(bs, dsm);
-  if (eagerMode(p, l)) {
-    if (threadIdx.x == 0) {
-      GatherEagerRole<T> role(p, l, cta, nctas);
-      if (role.R > 0) runCopyRole(p, l, role, bs, dsm);
-      traceMark(p, l, 4);
-    }
-  } else {
-    gatherDecision(p, l, p.round % l.L, sm);  // every thread
-    if (threadIdx.x == 0) {
-      traceMark(p, l, 4);
-      fence_proxy_async();  // the ring was written by peers' generic stores, acquired through the snapshot
-      GatherSnapshotRole<T> role(p, l, cta, nctas);
-      runCopyRole(p, l, role, bs, dsm);
-    }
-  }
-}
-
-// NVLS gather: piece by piece.  Exactly one CTA handles a piece, so "arrived or not" needs no shared decision; a piece
-// that never arrives marks its chunk abandoned (the eager-gather decision word), and the round's last CTA zero-fills
-// abandoned chunks as a whole before the slot retires (NvlsCleanup), so a chunk is never left half copied.
+// Eager gather (every chunk required): piece (owner, c, s) is copied to the output as soon as its flag lands, while the
+// rest of the chunk is still being reduced.  Exactly one CTA handles a piece, so "arrived or not" needs no shared decision
+// -- except for giving up: a piece that never shows up (forced round, timeout) marks its CHUNK abandoned in the eager
+// decision word, later pieces of that chunk are not waited for, and the round's last CTA zero-fills abandoned chunks as a
+// whole before the slot retires (ChunkCleanup), so a chunk is never flushed half copied (AllreduceWorker.scala:183: a
+// ReduceBlock that never arrived stays zero).
 template <typename T>
 struct GatherPieceRole {
+  static constexpr bool kPublishes = false;
   const AarRankParams& p;
   const AarLayout& l;
-  int nctas, slot, Sp, pieceElems;
-  uint32_t epoch;
-  long long total, idx;
+  int nctas, slot, R, first, Sp, pieceElems;
+  uint64_t epoch;
+  int total, idx;
   bool view;
 
-  __device__ GatherPieceRole(const AarRankParams& p_, const AarLayout& l_, int cta, int nctas_) : p(p_), l(l_), nctas(nctas_) {
+  __device__ GatherPieceRole(const AarRankParams& p_, const AarLayout& l_, int cta, int nctas_, bool skipOwn) : p(p_), l(l_), nctas(nctas_) {
     slot = p.round % l.L;
-    epoch = (uint32_t)(p.round + 1);
+    epoch = (uint64_t)(p.round + 1);
+    first = skipOwn ? 1 : 0;  // my own block was written by my reduce role
+    R = l.P - first;
     Sp = l.piecesPerChunk;
     pieceElems = l.tilesPerPiece * l.tileElems;
-    total = (long long)l.C * l.P * Sp;
+    total = l.C * R * Sp;
     idx = cta;
     view = (p.flags & AAR_FLAG_VIEW_OUTPUT) != 0;
   }
+  // chunk-major (chunk c of every owner is reduced at about the same time), then piece, owners staggered from self
   __device__ int nextUnit(CopyUnit& u, bool blocking) {
     for (; idx < total; idx += nctas) {
-      const int owner = (p.rank + (int)(idx % l.P)) % l.P;
-      const int s = (int)((idx / l.P) % Sp);
-      const int c = (int)(idx / ((long long)Sp * l.P));
+      const int owner = (p.rank + first + idx % R) % l.P;
+      const int s = (idx / R) % Sp;
+      const int c = idx / (Sp * R);
       const int clen = chunkLen(l, owner, c);
       const int off = s * pieceElems;
       if (off >= clen) continue;
       char* my = regionOf(p, p.rank);
-      const uint32_t* flag = reinterpret_cast<const uint32_t*>(my + l.pflagROff) + (((long long)slot * l.P + owner) * l.C + c) * Sp + s;
-      bool arrived = ld_relaxed_sys_u32(flag) == epoch;
+      const int key = owner * l.C + c;
+      const uint64_t* flag = pflagR(p, l, p.rank, slot, owner, c, s);
+      uint64_t* dec = reinterpret_cast<uint64_t*>(my + l.egDecOff) + (long long)slot * l.P * l.C + key;
+      const uint64_t abandoned = epoch << 32;
+      uint64_t f = ld_relaxed_sys_u64(flag);
+      bool arrived = (f >> 32) == epoch;
       if (!arrived) {
         if (!blocking) return -1;
         Deadline dl(p.timeoutNs);
         unsigned spins = 0, backoff = 32;
         for (;;) {
-          if (ld_relaxed_sys_u32(flag) == epoch) {
+          f = ld_relaxed_sys_u64(flag);
+          if ((f >> 32) == epoch) {
             arrived = true;
             break;
           }
+          if ((spins & 15u) == 0 && ld_acquire_gpu_u64(dec) == abandoned) break;  // somebody already gave this chunk up
           if ((p.flags & AAR_FLAG_FORCE) || ((++spins & 255u) == 0)) {
             if (forcedByHost(p, l)) break;
             if (dl.expired()) {
@@ -701,22 +581,17 @@ struct GatherPieceRole {
           if (backoff < 512) backoff *= 2;
         }
       }
-      fence_sys();          // acquire side of the piece flag
-      fence_proxy_async();  // ... for the bulk loads that follow
-      const int key = owner * l.C + c;
-      if (!arrived) {
-        uint64_t* dec = reinterpret_cast<uint64_t*>(my + l.egDecOff) + (long long)slot * l.P * l.C + key;
-        atomicExch(reinterpret_cast<unsigned long long*>(dec), (unsigned long long)((uint64_t)epoch << 32));  // abandoned
+      if (arrived) {
+        (void)ld_acquire_sys_u64(flag);  // acquire (a fence would wait for the copies this thread has in flight)
+        fence_proxy_async();             // ... for the bulk loads that follow
+      } else {
+        atomicExch(reinterpret_cast<unsigned long long*>(dec), (unsigned long long)abandoned);
       }
-      if (s == 0 && p.outCounts) p.outCounts[key] = arrived ? l.P : 0;
+      if (s == 0 && p.outCounts) p.outCounts[key] = arrived ? (int)(f & 0xffffffffu) : 0;
       const int n = min(pieceElems, clen - off);
       char* ring = my + l.reduceOff + (((long long)slot * l.P + owner) * l.blkStride + (long long)c * l.maxChunk + off) * (long long)sizeof(T);
-      idx += nctas;
-      if (view) {
-        if (arrived) {
-          idx -= nctas;
-          continue;
-        }
+      if (view) {  // the caller reads the ring slot itself: only pieces that never arrived are touched
+        if (arrived) continue;
         u.src = nullptr;
         u.dst = ring;
       } else {
@@ -725,6 +600,141 @@ struct GatherPieceRole {
       }
       u.bytes = (uint32_t)n * (uint32_t)sizeof(T);
       u.a = u.b = u.c = 0;
+      idx += nctas;
+      return 1;
+    }
+    return 0;
+  }
+  __device__ void complete(uint32_t, uint32_t, uint32_t) {}
+};
+
+// Round decision for thComplete < 1 or a forced round (see gatherDecision in aar_protocol.cuh, which reads per-chunk flags):
+// one CTA becomes the leader, counts the chunks whose EVERY piece has landed against minChunksRequired
+// (DataBuffer.scala:69-75 with the true chunk total), snapshots which chunks made it with their contributor counts, and
+// publishes the snapshot; every CTA then gathers from that one snapshot.
+static __device__ void gatherDecisionPieces(const AarRankParams& p, const AarLayout& l, int slot, Smem& sm) {
+  char* my = regionOf(p, p.rank);
+  uint64_t* word = reinterpret_cast<uint64_t*>(my + l.k3DecOff) + slot;
+  const uint64_t epoch = (uint64_t)(p.round + 1);
+  const uint64_t busy = (epoch << 32) | 1u, done = (epoch << 32) | 2u;
+  if (threadIdx.x == 0) {
+    int leader = 0;
+    uint64_t v = ld_acquire_gpu_u64(word);
+    if (v != done && v != busy) {
+      uint64_t old = atomicCAS(reinterpret_cast<unsigned long long*>(word), (unsigned long long)v, (unsigned long long)busy);
+      leader = (old == v) ? 1 : 0;
+    }
+    sm.k3Leader = leader;
+  }
+  __syncthreads();
+  const int P = l.P, C = l.C;
+  int* counts = reinterpret_cast<int*>(my + l.countsOff) + (long long)slot * l.totalChunks;
+  auto chunkCount = [&](int owner, int c) {  // contributor count of a chunk whose every piece has landed, else -1
+    const int np = piecesOf(l, chunkLen(l, owner, c));
+    int cnt = -1;
+    for (int s = 0; s < np; ++s) {
+      const uint64_t f = ld_relaxed_sys_u64(pflagR(p, l, p.rank, slot, owner, c, s));
+      if ((f >> 32) != epoch) return -1;
+      cnt = (int)(f & 0xffffffffu);
+    }
+    return cnt;
+  };
+  if (sm.k3Leader) {
+    Deadline dl(p.timeoutNs);
+    unsigned spins = 0, backoff = 32;
+    for (;;) {
+      if (threadIdx.x == 0) sm.k3Count = 0;
+      __syncthreads();
+      int local = 0;
+      for (int i = threadIdx.x; i < P * C; i += kThreads) {
+        const int owner = i / C, c = i % C;
+        if (c < numChunks(l, owner) && chunkCount(owner, c) >= 0) ++local;
+      }
+      if (local) atomicAdd(&sm.k3Count, local);
+      __syncthreads();
+      int stop = (sm.k3Count >= p.minChunksRequired) ? 1 : 0;
+      if (!stop && threadIdx.x == 0 && ((p.flags & AAR_FLAG_FORCE) || (++spins & 127u) == 0)) {
+        if (forcedByHost(p, l)) sm.scratch = 1;
+        else if (dl.expired()) {
+          sm.scratch = 1;
+          atomicOr(statusWord(p, l, 0), AAR_ST_TIMEOUT_GATHER);
+        }
+      }
+      __syncthreads();
+      if (stop || sm.scratch) break;
+      __nanosleep(backoff);
+      if (backoff < 512) backoff *= 2;
+    }
+    __threadfence_system();  // acquire side of the piece flags
+    for (int i = threadIdx.x; i < P * C; i += kThreads) {
+      const int owner = i / C, c = i % C;
+      if (c >= numChunks(l, owner)) continue;
+      const int cnt = chunkCount(owner, c);
+      counts[i] = cnt;  // valid (owner, c) pairs are exactly the indices [0, totalChunks)
+      if (p.outCounts) p.outCounts[i] = cnt < 0 ? 0 : cnt;
+    }
+    __threadfence_system();  // chunks that landed between the count and the snapshot
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      sm.scratch = 0;
+      __threadfence();
+      st_release_gpu_u64(word, done);
+    }
+  } else {
+    if (threadIdx.x == 0) {
+      unsigned backoff = 64;
+      while (ld_acquire_gpu_u64(word) != done) {
+        __nanosleep(backoff);
+        if (backoff < 1024) backoff *= 2;
+      }
+      __threadfence_system();
+    }
+  }
+  __syncthreads();
+}
+
+// Gather from the round's snapshot: nothing is waited for here.
+template <typename T>
+struct GatherSnapshotRole {
+  static constexpr bool kPublishes = false;
+  const AarRankParams& p;
+  const AarLayout& l;
+  int nctas, slot, Sp, pieceElems;
+  int total, idx;
+  bool view;
+  const int* counts;
+
+  __device__ GatherSnapshotRole(const AarRankParams& p_, const AarLayout& l_, int cta, int nctas_) : p(p_), l(l_), nctas(nctas_) {
+    slot = p.round % l.L;
+    Sp = l.piecesPerChunk;
+    pieceElems = l.tilesPerPiece * l.tileElems;
+    total = l.C * l.P * Sp;
+    idx = cta;
+    view = (p.flags & AAR_FLAG_VIEW_OUTPUT) != 0;
+    counts = reinterpret_cast<const int*>(regionOf(p, p.rank) + l.countsOff) + (long long)slot * l.totalChunks;
+  }
+  __device__ int nextUnit(CopyUnit& u, bool) {
+    for (; idx < total; idx += nctas) {
+      const int s = idx % Sp;
+      const int owner = (p.rank + (idx / Sp) % l.P) % l.P;
+      const int c = idx / (Sp * l.P);
+      const int clen = chunkLen(l, owner, c);
+      const int off = s * pieceElems;
+      if (off >= clen) continue;
+      const int cnt = __ldcg(counts + owner * l.C + c);
+      if (view && cnt >= 0) continue;
+      const int n = min(pieceElems, clen - off);
+      char* ring = regionOf(p, p.rank) + l.reduceOff + (((long long)slot * l.P + owner) * l.blkStride + (long long)c * l.maxChunk + off) * (long long)sizeof(T);
+      if (view) {
+        u.src = nullptr;
+        u.dst = ring;
+      } else {
+        u.src = cnt >= 0 ? ring : nullptr;  // chunks whose ReduceBlock never arrived stay zero (AllreduceWorker.scala:183)
+        u.dst = reinterpret_cast<char*>(p.output) + (blockStart(l, owner) + (long long)c * l.maxChunk + off) * (long long)sizeof(T);
+      }
+      u.bytes = (uint32_t)n * (uint32_t)sizeof(T);
+      u.a = u.b = u.c = 0;
+      idx += nctas;
       return 1;
     }
     return 0;
@@ -733,18 +743,29 @@ struct GatherPieceRole {
 };
 
 template <typename T>
-__device__ void roleGatherNvls(const AarRankParams& p, const AarLayout& l, int cta, int nctas, BulkShared& bs, unsigned char* dsm) {
+__device__ void roleGather(const AarRankParams& p, const AarLayout& l, int cta, int nctas, BulkShared& bs, Smem& sm, unsigned char* dsm, bool nvls) {
   bulkInit(bs, dsm);
-  if (threadIdx.x != 0) return;
-  GatherPieceRole<T> role(p, l, cta, nctas);
-  runCopyRole(p, l, role, bs, dsm);
-  traceMark(p, l, 4);
+  if (nvls || eagerMode(p, l)) {
+    if (threadIdx.x == 0) {
+      GatherPieceRole<T> role(p, l, cta, nctas, !nvls && selfOut(p, l));
+      if (role.R > 0) runCopyRole(p, l, role, bs, dsm);
+      traceMark(p, l, 4);
+    }
+  } else {
+    gatherDecisionPieces(p, l, p.round % l.L, sm);  // every thread
+    if (threadIdx.x == 0) {
+      traceMark(p, l, 4);
+      fence_proxy_async();  // the ring was written by peers, acquired through the snapshot; bulk loads read it
+      GatherSnapshotRole<T> role(p, l, cta, nctas);
+      runCopyRole(p, l, role, bs, dsm);
+    }
+  }
 }
 
-// Runs on thread 0 of the round's last CTA, after every other CTA has finished: chunks that were abandoned piecewise are
+// Runs on thread 0 of the round's last CTA, after every other CTA has finished: chunks that were given up piecewise are
 // zero-filled as a whole and reported with count 0.
 template <typename T>
-struct NvlsCleanup {
+struct ChunkCleanup {
   unsigned char* dsm;
   __device__ void operator()(const AarRankParams& p, const AarLayout& l) const {
     char* my = regionOf(p, p.rank);
@@ -818,14 +839,8 @@ __global__ void __launch_bounds__(kThreads, 1) bulkRoundKernel(const AarRankPara
     if (kNvls) roleReduceNvls<T>(p, l, cta, n, bs);
     else roleReduceP2P<T>(p, l, cta, n, bs, dsm);
   }
-  if (role & 4) {
-    if (kNvls) roleGatherNvls<T>(p, l, cta, n, bs, dsm);
-    else roleGatherP2P<T>(p, l, cta, n, bs, sm, dsm);
-  }
-  if (phases & 4) {
-    if (kNvls) retireRoundWith(p, l, nctas, NvlsCleanup<T>{dsm});
-    else retireRound(p, l, nctas);
-  }
+  if (role & 4) roleGather<T>(p, l, cta, n, bs, sm, dsm, kNvls);
+  if (phases & 4) retireRoundWith(p, l, nctas, ChunkCleanup<T>{dsm});
   traceMark(p, l, 5);
 }
 

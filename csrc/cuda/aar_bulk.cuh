@@ -66,25 +66,53 @@ static __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence
 static __device__ __forceinline__ void fence_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
 static __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// Units whose last byte is written, handed from the thread that issues the copies to the thread that publishes them.
+// Why two threads: the flag of a unit needs a system fence after the unit's bulk stores have completed (a fence-less flag
+// written after cp.async.bulk.wait_group WAS seen before the data by a peer: bench/litmus_bulk_flag.py, 64 stale words in
+// 1.3 M rounds), and a fence issued by the thread that keeps the copies going stalls that thread for as long as the stores
+// in flight take to be acknowledged.  The publishing thread fences (once per batch of finished units), the issuing thread
+// never stops.
+struct DoneRing {
+  uint32_t a[16], b[16], c[16];
+  uint32_t tail, head, closed;
+};
+
 struct BulkShared {
-  unsigned long long full[kMaxStages];   // mbarriers: "the loads of the tile in this stage have landed"
-  unsigned long long jobDst[kMaxStages]; // per stage: destination of the tile (copy roles) / element offset (reduce)
+  unsigned long long full[kMaxStages];      // mbarriers: "the loads of the tile in this stage have landed"
+  unsigned long long computed[kMaxStages];  // reduce role: "the result tile of this stage is written (and its inputs are read)"
+  unsigned long long outFree[kMaxStages];   // reduce role: "the stores of this stage's result tile have read it"
+  unsigned long long jobDst[kMaxStages];    // per stage: destination of the tile (copy roles) / byte offset inside the block (reduce)
   uint32_t jobBytes[kMaxStages];
-  uint32_t jobInfo[kMaxStages];          // bit 0: last tile of its unit, bit 1: zero-fill (no load)
+  uint32_t jobInfo[kMaxStages];             // copy roles: bit 0 last tile of its unit, bit 1 zero-fill (no load)
   uint32_t unitA[kMaxStages], unitB[kMaxStages], unitC[kMaxStages];  // the unit's words for complete(), parked with its last tile
   uint32_t fifoGroup[16], fifoA[16], fifoB[16], fifoC[16];  // units whose stores are committed but not yet known complete
-  unsigned openMask[kMaxStages];         // reduce role: contributor mask of the open units (indexed by unit ordinal % kMaxStages)
+  DoneRing done;
   int bcast[4];
 };
 
-// Wait for the loads of a stage.  A bulk load that never completes means a bad address or a broken pipeline, not a slow
-// peer (the data is local or already flagged): report and trap rather than hang the GPU.
+static __device__ __forceinline__ uint32_t ld_acquire_cta_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
+  return v;
+}
+static __device__ __forceinline__ void st_release_cta_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(smem_u32(p)), "r"(v) : "memory");
+}
+static __device__ __forceinline__ void mbar_arrive(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
+static __device__ __forceinline__ uint64_t atom_cas_acq_rel_gpu_u64(uint64_t* p, uint64_t cmp, uint64_t val) {
+  uint64_t old;
+  asm volatile("atom.acq_rel.gpu.global.cas.b64 %0, [%1], %2, %3;" : "=l"(old) : "l"(p), "l"(cmp), "l"(val) : "memory");
+  return old;
+}
+
+// Wait for an mbarrier phase.  A wait that never ends here means a bad address or a broken pipeline, not a slow peer (the
+// data is local or already flagged): report and trap rather than hang the GPU.
 static __device__ __forceinline__ void mbar_wait(const AarRankParams& p, const AarLayout& l, uint32_t bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const unsigned long long t0 = globaltimer_ns();
   unsigned spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if ((++spins & 1023u) == 0 && globaltimer_ns() - t0 > 4000000000ull) {
+    if ((++spins & 1023u) == 0 && globaltimer_ns() - t0 > 8000000000ull) {
       atomicOr(statusWord(p, l, 0), AAR_ST_BULK_FAULT);
       __threadfence_system();
       __trap();
@@ -92,17 +120,57 @@ static __device__ __forceinline__ void mbar_wait(const AarRankParams& p, const A
   }
 }
 
-// (Re)arm the pipeline of this CTA: called by every thread at the start of a role.
-static __device__ __forceinline__ void bulkInit(BulkShared& bs, unsigned char* dsm) {
+// (Re)arm the pipeline of this CTA: called by every thread at the start of a role.  computedCount = number of arrivals
+// that complete a `computed` phase (the reduce role's compute warps).
+static __device__ __forceinline__ void bulkInit(BulkShared& bs, unsigned char* dsm, uint32_t computedCount = 1) {
   __syncthreads();
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kMaxStages; ++s) mbar_init(smem_u32(&bs.full[s]), 1);
+    for (int s = 0; s < kMaxStages; ++s) {
+      mbar_init(smem_u32(&bs.full[s]), 1);
+      mbar_init(smem_u32(&bs.computed[s]), computedCount);
+      mbar_init(smem_u32(&bs.outFree[s]), 1);
+    }
+    bs.done.tail = bs.done.head = bs.done.closed = 0;
     mbar_init_fence();
   }
   uint4* z = reinterpret_cast<uint4*>(dsm + kStageBytes);
   for (int i = threadIdx.x; i < kZeroTile / 16; i += kThreads) z[i] = make_uint4(0, 0, 0, 0);
   fence_proxy_async_smem();  // the zero tile is read by bulk stores
   __syncthreads();
+}
+
+// issuing side of the hand-over
+static __device__ __forceinline__ void donePush(DoneRing& d, uint32_t a, uint32_t b, uint32_t c) {
+  const uint32_t t = d.tail;  // only this thread writes it
+  while (t - ld_acquire_cta_u32(&d.head) >= 16u) __nanosleep(32);
+  d.a[t & 15] = a;
+  d.b[t & 15] = b;
+  d.c[t & 15] = c;
+  st_release_cta_u32(&d.tail, t + 1);
+}
+static __device__ __forceinline__ void doneClose(DoneRing& d) { st_release_cta_u32(&d.closed, 1u); }
+// publishing side: runs until the ring is closed and empty
+template <class Role>
+static __device__ void doneDrain(DoneRing& d, Role& role) {
+  uint32_t h = 0;
+  for (;;) {
+    uint32_t t = ld_acquire_cta_u32(&d.tail);
+    if (h == t) {
+      if (ld_acquire_cta_u32(&d.closed)) {
+        t = ld_acquire_cta_u32(&d.tail);
+        if (h == t) return;
+        continue;
+      }
+      __nanosleep(64);
+      continue;
+    }
+    // ONE fence for everything that is waiting: a system fence on an SM that streams stores to a peer takes as long as the
+    // link's queue is deep (measured: ~10 us when the link is oversubscribed), so units are published in batches
+    fence_proxy_async();
+    fence_sys();
+    for (; h != t; ++h) role.complete(d.a[h & 15], d.b[h & 15], d.c[h & 15]);
+    st_release_cta_u32(&d.head, h);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------ single-thread decisions
@@ -136,8 +204,7 @@ static __device__ int destDecision1(const AarRankParams& p, const AarLayout& l, 
           __nanosleep(64);
         }
       }
-      __threadfence();
-      const uint64_t old = atomicCAS(reinterpret_cast<unsigned long long*>(word), (unsigned long long)v, (unsigned long long)((epoch << 32) | g));
+      const uint64_t old = atom_cas_acq_rel_gpu_u64(word, v, (epoch << 32) | g);
       if (old != v && (old >> 32) == epoch) g = (unsigned)(old & 1u);
       if (!g) atomicOr(statusWord(p, l, 0), AAR_ST_PUSH_DROPPED);
     }
@@ -147,36 +214,61 @@ static __device__ int destDecision1(const AarRankParams& p, const AarLayout& l, 
   return (int)g;
 }
 
-// Contributor set of a chunk (see chunkDecision).  Returns false only when !blocking and the quorum is not there yet.
-static __device__ bool chunkDecision1(const AarRankParams& p, const AarLayout& l, uint64_t* word, const uint32_t* flags, int minRequired, bool blocking,
-                                      unsigned& maskOut) {
+// ---- piece flags
+// The bulk kernels publish arrival per PIECE (a fixed sub-chunk granule of the layout, at most 8 tiles = 256 KiB), not per
+// chunk: exactly one CTA moves a piece, so its flag needs no election among CTAs -- one fence of the publishing thread, one
+// relaxed store -- and the consumer of a reduced chunk can start on its first piece.  What the reference calls a ScatterBlock
+// has arrived from a source when ALL pieces of the chunk carry the round's epoch; the contributor decision stays per chunk.
+static __device__ __forceinline__ int piecesOf(const AarLayout& l, int clen) {
+  const int pe = l.tilesPerPiece * l.tileElems;
+  return (clen + pe - 1) / pe;
+}
+static __device__ __forceinline__ uint32_t* pflagS(const AarRankParams& p, const AarLayout& l, int rankOfRegion, int slot, int c, int s) {
+  return reinterpret_cast<uint32_t*>(regionOf(p, rankOfRegion) + l.pflagSOff) + (((long long)slot * l.C + c) * l.piecesPerChunk + s) * AAR_MAXP;
+}
+static __device__ __forceinline__ uint64_t* pflagR(const AarRankParams& p, const AarLayout& l, int rankOfRegion, int slot, int owner, int c, int s) {
+  return reinterpret_cast<uint64_t*>(regionOf(p, rankOfRegion) + l.pflagROff) + (((long long)slot * l.P + owner) * l.C + c) * l.piecesPerChunk + s;
+}
+
+// Contributor set of one of my chunks (see chunkDecision): wait until at least minRequired sources have delivered every piece
+// of the chunk (or the round is forced), snapshot the arrived mask, make it the single decision for all CTAs.  Returns false
+// only when !blocking and the quorum is not there yet.
+static __device__ bool chunkDecision1(const AarRankParams& p, const AarLayout& l, int c, int clen, int minRequired, bool blocking, unsigned& maskOut) {
+  const int slot = p.round % l.L;
   const uint64_t epoch = (uint64_t)(p.round + 1);
+  uint64_t* word = reinterpret_cast<uint64_t*>(regionOf(p, p.rank) + l.k2DecOff) + (long long)slot * l.C + c;
   const uint64_t v = ld_acquire_gpu_u64(word);
   if ((v >> 32) == epoch) {
     maskOut = (unsigned)(v & 0xffffffffu);
     return true;
   }
-  auto look = [&]() {
-    unsigned a = 0;
-    for (int j = 0; j < l.P; ++j)
-      if (ld_relaxed_sys_u32(flags + j) == (uint32_t)epoch) a |= 1u << j;
+  const int np = piecesOf(l, clen);
+  const unsigned all = l.P >= 32 ? 0xffffffffu : ((1u << l.P) - 1u);
+  auto look = [&](bool acquire) {
+    unsigned a = all;
+    for (int s = np - 1; s >= 0 && a; --s) {  // pieces land roughly in order: the last one decides most polls
+      const uint32_t* f = pflagS(p, l, p.rank, slot, c, s);
+      unsigned here = 0;
+      for (int j = 0; j < l.P; ++j)
+        if (((a >> j) & 1u) && (acquire ? ld_acquire_sys_u32(f + j) : ld_relaxed_sys_u32(f + j)) == (uint32_t)epoch) here |= 1u << j;
+      a &= here;
+    }
     return a;
   };
-  unsigned arrived = look();
+  unsigned arrived = look(false);
   bool forced = false;
   if (__popc(arrived) < minRequired) {
     if (!blocking) return false;
     Deadline dl(p.timeoutNs);
     unsigned spins = 0, backoff = 32;
     for (;;) {
-      arrived = look();
+      arrived = look(false);
       if (__popc(arrived) >= minRequired) break;
       if ((p.flags & AAR_FLAG_FORCE) || ((++spins & 31u) == 0)) {
         int stop = forcedByHost(p, l) ? 1 : (dl.expired() ? 2 : 0);
         if (stop) {
           if (stop == 2) atomicOr(statusWord(p, l, 0), AAR_ST_TIMEOUT_REDUCE);
           forced = true;
-          arrived = look();  // as fresh as the decision
           break;
         }
       }
@@ -184,62 +276,17 @@ static __device__ bool chunkDecision1(const AarRankParams& p, const AarLayout& l
       if (backoff < 512) backoff *= 2;
     }
   }
-  __threadfence_system();  // acquire: the flagged sources' data is visible to everything after this point
+  // acquire: one more pass with acquire loads (a fence here would wait for the stores this SM has in flight); as fresh as the
+  // decision, and the flagged sources' data is visible to everything after this point
+  arrived = look(true);
   if ((p.flags & AAR_FLAG_EXACT_QUORUM) && !forced) {
     while (__popc(arrived) > minRequired) arrived &= ~(1u << (31 - __clz(arrived)));  // keep the lowest ids
   }
   unsigned mask = arrived;
-  __threadfence();
-  const uint64_t old = atomicCAS(reinterpret_cast<unsigned long long*>(word), (unsigned long long)v, (unsigned long long)((epoch << 32) | mask));
+  const uint64_t old = atom_cas_acq_rel_gpu_u64(word, v, (epoch << 32) | mask);  // release: whoever adopts the word also sees the data
   if (old != v && (old >> 32) == epoch) mask = (unsigned)(old & 0xffffffffu);
   maskOut = mask;
   return true;
-}
-
-// One decision per (round, owner, chunk) of the eager gather: "arrived with this count" or "abandoned" -- whoever stops
-// waiting first decides, everybody else adopts, so a chunk is never flushed half copied and half zero-filled.
-// Returns the count (>= 0), -1 = abandoned, -2 = not there yet (only when !blocking).
-static __device__ int eagerChunkDecision1(const AarRankParams& p, const AarLayout& l, int key, bool blocking) {
-  char* my = regionOf(p, p.rank);
-  const int slot = p.round % l.L;
-  const uint64_t epoch = (uint64_t)(p.round + 1);
-  uint64_t* dec = reinterpret_cast<uint64_t*>(my + l.egDecOff) + (long long)slot * l.P * l.C + key;
-  const uint64_t* flag = reinterpret_cast<const uint64_t*>(my + l.rflagOff) + (long long)slot * l.P * l.C + key;
-  const uint64_t d = ld_acquire_gpu_u64(dec);
-  if ((d >> 32) == epoch) return (int)(d & 0xffffffffu) - 1;
-  int cnt = -1;
-  uint64_t f = ld_relaxed_sys_u64(flag);
-  if ((f >> 32) == epoch) {
-    cnt = (int)(f & 0xffffffffu);
-  } else {
-    if (!blocking) return -2;
-    Deadline dl(p.timeoutNs);
-    unsigned spins = 0, backoff = 32;
-    for (;;) {
-      f = ld_relaxed_sys_u64(flag);
-      if ((f >> 32) == epoch) {
-        cnt = (int)(f & 0xffffffffu);
-        break;
-      }
-      if ((p.flags & AAR_FLAG_FORCE) || ((++spins & 255u) == 0)) {
-        if (forcedByHost(p, l)) break;
-        if (dl.expired()) {
-          atomicOr(statusWord(p, l, 0), AAR_ST_TIMEOUT_GATHER);
-          break;
-        }
-      }
-      __nanosleep(backoff);
-      if (backoff < 512) backoff *= 2;
-    }
-  }
-  __threadfence_system();  // acquire for the flag; cumulative, so also the release for the word below
-  const uint64_t want = (epoch << 32) | (uint64_t)(uint32_t)(cnt + 1);
-  const uint64_t old = atomicCAS(reinterpret_cast<unsigned long long*>(dec), (unsigned long long)d, (unsigned long long)want);
-  if (old != d && (old >> 32) == epoch) {
-    cnt = (int)(old & 0xffffffffu) - 1;
-    __threadfence();
-  }
-  return cnt;
 }
 
 // ------------------------------------------------------------------------------------------------ the copy pipeline
@@ -256,7 +303,7 @@ struct CopyUnit {
 
 template <class Role>
 static __device__ void runCopyRole(const AarRankParams& p, const AarLayout& l, Role& role, BulkShared& bs, unsigned char* dsm) {
-  // thread 0 only
+  // thread 0 only; role.complete() runs on the publishing thread (doneDrain) when Role::kPublishes
   const uint32_t stage0 = smem_u32(dsm), zero = smem_u32(dsm + kStageBytes);
   uint32_t L = 0, S = 0, head = 0, tail = 0, phaseBits = 0;
   bool exhausted = false, haveUnit = false;
@@ -264,7 +311,7 @@ static __device__ void runCopyRole(const AarRankParams& p, const AarLayout& l, R
   uint32_t off = 0;
   auto retireDone = [&](uint32_t lastCompleteGroup) {
     while (head != tail && bs.fifoGroup[head & 15] <= lastCompleteGroup) {
-      role.complete(bs.fifoA[head & 15], bs.fifoB[head & 15], bs.fifoC[head & 15]);
+      if (Role::kPublishes) donePush(bs.done, bs.fifoA[head & 15], bs.fifoB[head & 15], bs.fifoC[head & 15]);
       ++head;
     }
   };
@@ -276,13 +323,14 @@ static __device__ void runCopyRole(const AarRankParams& p, const AarLayout& l, R
           retireDone(S - 1);
         }
         const int r = role.nextUnit(u, L == S);
+        if (r > 0 && L == 0) traceMarkAny(p, l, 6);  // first unit in hand (its flag / flow-control word was there)
         if (r == 0) {
           exhausted = true;
           break;
         }
         if (r < 0) break;
         if (u.bytes == 0) {
-          role.complete(u.a, u.b, u.c);
+          if (Role::kPublishes) donePush(bs.done, u.a, u.b, u.c);
           continue;
         }
         haveUnit = true;
@@ -339,6 +387,7 @@ static __device__ void runCopyRole(const AarRankParams& p, const AarLayout& l, R
   }
   bulk_wait<0>();
   if (S > 0) retireDone(S - 1);
+  doneClose(bs.done);
 }
 
 }  // namespace aar_dev

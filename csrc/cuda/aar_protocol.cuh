@@ -25,6 +25,11 @@ static __device__ __forceinline__ void traceMark(const AarRankParams& p, const A
   if ((p.flags & AAR_FLAG_TRACE) && threadIdx.x == 0 && blockIdx.x < AAR_TRACE_CTAS)
     reinterpret_cast<unsigned long long*>(regionOf(p, p.rank) + l.traceOff)[blockIdx.x * AAR_TRACE_MARKS + mark] = globaltimer_ns();
 }
+// the same from whichever thread runs the role
+static __device__ __forceinline__ void traceMarkAny(const AarRankParams& p, const AarLayout& l, int mark) {
+  if ((p.flags & AAR_FLAG_TRACE) && blockIdx.x < AAR_TRACE_CTAS)
+    reinterpret_cast<unsigned long long*>(regionOf(p, p.rank) + l.traceOff)[blockIdx.x * AAR_TRACE_MARKS + mark] = globaltimer_ns();
+}
 template <typename T>
 static __device__ __forceinline__ bool geomVecOk(const AarLayout& l) {
   constexpr int V = Elem<T>::kPerVec;

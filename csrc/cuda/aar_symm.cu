@@ -129,7 +129,7 @@ AAR_API int aar_layout_compute(int P, int dataSize, int maxChunkSize, int maxLag
     l.piecesPerChunk = (l.tilesPerChunk + l.tilesPerPiece - 1) / l.tilesPerPiece;
   }
   l.pflagSOff = take((uint64_t)l.L * l.C * l.piecesPerChunk * AAR_MAXP * 4);
-  l.pflagROff = take((uint64_t)l.L * P * l.C * l.piecesPerChunk * 4);
+  l.pflagROff = take((uint64_t)l.L * P * l.C * l.piecesPerChunk * 8);
   l.regionBytes = alignUp(off, 2ull << 20);
   *out = l;
   return AAR_OK;

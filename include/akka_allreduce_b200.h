@@ -82,12 +82,11 @@ typedef struct AarLayout {
   uint64_t ctrlBytes;        /* first byte of the control area that must be zeroed at allocation */
   uint64_t regionBytes;      /* total, rounded up to 2 MiB */
   uint64_t egDecOff;         /* u64 [L][P][C]                   local: eager gather, epoch<<32 | count+1 (0 = abandoned); AAR_FLAG_EAGER_DEC */
-  /* pieces: sub-chunk granules of the in-switch (NVLS) path of aar_launch_round_bulk.  That path has no contributor decision to
-   * take (the switch sums every rank), so it can publish and consume a chunk piece by piece; a 4 MiB chunk is then no longer
-   * the smallest thing one role can hand to the next. */
+  /* pieces: sub-chunk granules (<= 8 tiles) in which the kernels of aar_launch_round_bulk publish arrival.  Exactly one CTA moves
+   * a piece, so its flag needs no election; a chunk has arrived from a source when all its pieces are flagged. */
   int tilesPerPiece, piecesPerChunk;
   uint64_t pflagSOff;        /* u32 [L][C][piecesPerChunk][AAR_MAXP]   epoch, written by src: "my piece of your block is staged" */
-  uint64_t pflagROff;        /* u32 [L][P(owner)][C][piecesPerChunk]   epoch, written by owner: "reduced piece has landed" */
+  uint64_t pflagROff;        /* u64 [L][P(owner)][C][piecesPerChunk]   epoch<<32 | contributor count, written by owner: "reduced piece has landed" */
 } AarLayout;
 
 /* Per-rank launch parameters (passed to the kernels by value). */
@@ -238,6 +237,14 @@ int aar_bench_all2all(int mode, int grid, int unroll, void** peers, int nPeers, 
  * could move.  stages in {2,4,8}, tileBytes % 128 == 0; *errOut (device word, may be NULL) is set to 1 if a wait gave up.
  * Bench only -- written without GPU access, not used by any allreduce path. */
 int aar_bench_bulk_copy(int grid, int stages, int tileBytes, const void* src, void* dst, size_t bytes, int iters, void* stream, unsigned* errOut);
+/* The same with `warps` (1..8) issuing threads per CTA, each with its own ring of `stages` tiles. */
+int aar_bench_bulk_copy_multi(int grid, int warps, int stages, int tileBytes, const void* src, void* dst, size_t bytes, int iters, void* stream,
+                              unsigned* errOut);
+
+/* Two-GPU litmus (bench/litmus_bulk_flag.py): is a flag written after cp.async.bulk.wait_group -- without a fence -- ever seen
+ * by the peer before the bulk-stored data?  sender = 1 on one GPU, 0 on the other, launched at the same time. */
+int aar_bench_litmus_bulk_flag(int sender, int mode, int grid, void* peerBuf, void* myBuf, void* peerWords, void* myWords, int bytes, int iters,
+                               unsigned long long* violations, unsigned* gaveUp, void* stream);
 
 /* Spin kernel used by the straggler injector: busy-waits `ns` nanoseconds on `stream`. */
 int aar_launch_delay(unsigned long long ns, void* stream);

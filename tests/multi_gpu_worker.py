@@ -67,6 +67,7 @@ def engine_case(n, chunk, dtype, algo, rounds=5, th=1.0, normalize=False, overla
         return
     good = True
     keep = []
+    first_pass = []
     for r in range(rounds):
         xs = inputs_for(n, dtype, 1000 + r)
         keep.append(xs)
@@ -74,12 +75,24 @@ def engine_case(n, chunk, dtype, algo, rounds=5, th=1.0, normalize=False, overla
         eng.wait_round(r)
         torch.cuda.synchronize()
         want = ordered_sum(xs, list(range(world)), dtype, normalize)
-        if algo == "nvls":  # the switch does not promise peer-index order: equal up to fp32 reassociation
+        if eng.algo in ("nvls", "nvls_bulk"):  # the switch does not promise peer-index order: equal up to fp32 reassociation
             good &= bool(torch.allclose(out.float(), want.float(), rtol=2e-5 if dtype == torch.float32 else 2e-2, atol=1e-4))
+            # ... but every rank must hold the SAME bits (one multimem.st lands everywhere), and the same inputs must give the
+            # same bits again (round r + rounds below repeats round r's inputs)
+            digest = struct.pack("q", int(out.view(torch.int16 if dtype == torch.bfloat16 else torch.int32).to(torch.int64).sum().item()))
+            good &= len(set(rdv.all_gather_bytes(digest))) == 1
+            first_pass.append(out.clone())
         else:
             good &= bool(torch.equal(out, want))
         good &= int(counts.min()) == world and int(counts.max()) == world
         rdv.barrier()
+    if first_pass:   # run-to-run determinism of the in-switch sum
+        for r in range(rounds):
+            out, counts = eng.enqueue_round(rounds + r, keep[r][rank])
+            eng.wait_round(rounds + r)
+            torch.cuda.synchronize()
+            good &= bool(torch.equal(out, first_pass[r]))
+            rdv.barrier()
     good &= eng.status() == 0
     check(name + f" -> {eng.algo}", good)
     eng.close()
@@ -199,7 +212,15 @@ for dtype in (torch.float32, torch.bfloat16):
     engine_case(1 << 20, 1 << 16, dtype, "pipelined")
     engine_case(1 << 20, 1 << 16, dtype, "nvls")
     engine_case(8192, 1024, dtype, "oneshot")
+    engine_case(1 << 20, 1 << 16, dtype, "bulk")
+    engine_case(1 << 22, 1 << 18, dtype, "bulk", rounds=8, overlap=False)
+    engine_case(1 << 22, 1 << 18, dtype, "nvls_bulk", rounds=6)
+    engine_case(1 << 18, 1 << 18, dtype, "nvls_bulk")
 engine_case((1 << 20) + 8, 40000, torch.float32, "pipelined")      # unaligned blocks and chunks: scalar path
+engine_case((1 << 20) + 8, 40000, torch.float32, "bulk")           # ... which the bulk engine hands to the register kernels
+engine_case(1 << 24, 1 << 20, torch.float32, "bulk", rounds=6, max_lag=1)   # the headline geometry
+engine_case(1 << 24, 1 << 20, torch.float32, "nvls_bulk", rounds=4, max_lag=1)
+engine_case(1 << 22, 1 << 16, torch.float32, "bulk", rounds=12, max_lag=3, normalize=True)
 engine_case(1003, 17, torch.float32, "twoshot", overlap=False)
 engine_case(1 << 20, 1 << 16, torch.float32, "auto", normalize=True)
 engine_case(1 << 22, 1 << 18, torch.float32, "auto", rounds=12, max_lag=3)

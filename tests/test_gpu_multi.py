@@ -15,12 +15,15 @@ pytestmark = pytest.mark.gpu
 ROOT = Path(__file__).resolve().parents[1]
 
 
-@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs at least two GPUs")
-def test_multi_gpu_suite():
-    n = 2   # the suite is size-independent; two real peers are enough for NVLink, VMM and multicast, and cheapest to run
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_multi_gpu_suite(n):
+    """The whole suite at 2, 4 and 8 ranks (whichever the box has): real peers for NVLink, VMM and multicast; 8 ranks is where the
+    selector takes the in-switch path and every destination-rotation and role split differs from the 2-rank run."""
+    if not torch.cuda.is_available() or torch.cuda.device_count() < n:
+        pytest.skip(f"needs {n} GPUs")
     env = dict(os.environ)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
-           "--master-port", "29631", str(ROOT / "tests" / "multi_gpu_worker.py")]
+           "--master-port", str(29631 + n), str(ROOT / "tests" / "multi_gpu_worker.py")]
     p = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=900)
     tail = "\n".join((p.stdout + p.stderr).splitlines()[-40:])
     assert p.returncode == 0 and "ALL PASSED" in p.stdout, tail
