@@ -50,7 +50,7 @@ if split == 0:
 names = {"push/stage": (0, na, {0: "entry", 6: "first unit", 1: "done", 5: "exit"}),
          "reduce": (na, na + nb, {0: "entry", 2: "first decision", 7: "first tile stored", 6: "last load issued", 3: "stores done", 5: "exit"}),
          "gather": (na + nb, n, {0: "entry", 6: "first unit", 4: "done", 5: "exit"})}
-out = {"world": world, "algo": eng.algo, "ctas": n, "split": [na, nb]}
+out = {"world": world, "algo": eng.algo, "ctas": n, "split": [na, nb], "t0_us_mod_1s": round((t0 % 1e9) / 1e3, 1)}
 for role, (lo, hi, marks) in names.items():
     prof = {}
     for k, nm in marks.items():
@@ -62,6 +62,6 @@ for role, (lo, hi, marks) in names.items():
     out[role] = prof
 res = rdv.all_gather_bytes(json.dumps(out).encode())
 if rank == 0:
-    for b in res[:2]:
+    for b in res:
         print(b.decode())
 rdv.barrier()

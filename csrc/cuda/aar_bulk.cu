@@ -93,7 +93,7 @@ struct PushRole {
     }
     return 0;
   }
-  // this piece of the "ScatterBlock" has landed (runs after the publishing thread's fence)
+  // this piece of the "ScatterBlock" has landed (runs on the publishing thread, after its fence)
   __device__ void complete(uint32_t dest, uint32_t c, uint32_t s) {
     asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(pflagS(p, l, (int)dest, slot, (int)c, (int)s) + p.rank), "r"(epoch) : "memory");
   }
@@ -115,7 +115,8 @@ __device__ void rolePush(const AarRankParams& p, const AarLayout& l, int cta, in
     const int mine = numChunks(l, p.rank);
     for (int c = 0; c < mine; ++c) {
       const int np = piecesOf(l, chunkLen(l, p.rank, c));
-      for (int s = 0; s < np; ++s) st_release_sys_u32(pflagS(p, l, p.rank, slot, c, s) + p.rank, (uint32_t)(p.round + 1));
+      for (int s = 0; s < np; ++s)  // relaxed: the input was complete before this kernel started, there is nothing to order
+        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(pflagS(p, l, p.rank, slot, c, s) + p.rank), "r"((uint32_t)(p.round + 1)) : "memory");
     }
   }
   PushRole<T> role(p, l, cta, nctas);
@@ -172,7 +173,7 @@ struct StageRole {
     }
     return 0;
   }
-  __device__ void complete(uint32_t b, uint32_t c, uint32_t s) {  // after the publishing thread's fence
+  __device__ void complete(uint32_t b, uint32_t c, uint32_t s) {  // on the publishing thread, after its fence
     asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(pflagS(p, l, (int)b, slot, (int)c, (int)s) + p.rank), "r"(epoch) : "memory");
   }
 };
@@ -196,8 +197,8 @@ __device__ void roleStage(const AarRankParams& p, const AarLayout& l, int cta, i
 //   warps 3..15           adders: two (or one) 16-byte vectors per thread, shared memory in, shared memory out
 //   warp 1 (one thread)   storer: bulk-stores the result tile into every destination's reduce ring (own block straight to the
 //                         output when every chunk is required), one bulk group per tile
-//   warp 2 (one thread)   publisher: last-segment election and the ReduceBlock flags (epoch | count) -- the only thread that
-//                         fences, and it has no copies of its own in flight
+//   warp 2 (one thread)   publisher: the ReduceBlock flags (epoch | count) of the pieces whose stores have completed -- the
+//                         only thread that fences, and it has no copies of its own in flight
 // Stages hand over through mbarriers: full (loads landed) -> computed (result written, inputs consumed) -> outFree (stores
 // have read the result).  Issuing one bulk copy costs the issuing thread about 300 cycles (measured), which is why loads,
 // stores and adds each get their own thread(s) instead of taking turns on one.
@@ -341,7 +342,7 @@ __device__ void roleReduceP2P(const AarRankParams& p, const AarLayout& l, int ct
       }
       bulk_commit();
       if (G == 0) traceMarkAny(p, l, 7);
-      if (bs.unitC[st] & 0x80000000u) {  // last tile of its segment
+      if (bs.unitC[st] & 0x80000000u) {  // last tile of its piece
         bs.fifoGroup[tail & 15] = G;
         bs.fifoA[tail & 15] = bs.unitA[st];
         bs.fifoB[tail & 15] = bs.unitB[st];
@@ -926,8 +927,8 @@ AAR_API int aar_launch_round_bulk(const AarRankParams* p, const AarLayout* lay, 
         nB = g / 8 > 0 ? g / 8 : 1;   // few CTAs saturate the switch
         nA = (g - nB) * 2 / 5;
       } else {
-        nA = g / 5;                   // remote copies only: the link, not the SMs, bounds this role
-        nB = g * 2 / 5;
+        nA = g / 9;                   // 16 of 148: remote copies only, and 16 CTAs already saturate the link (measured, 2 GPUs)
+        nB = g / 2;
       }
     }
     if (nA < 1) nA = 1;

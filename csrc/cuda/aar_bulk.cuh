@@ -71,7 +71,8 @@ static __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("
 // written after cp.async.bulk.wait_group WAS seen before the data by a peer: bench/litmus_bulk_flag.py, 64 stale words in
 // 1.3 M rounds), and a fence issued by the thread that keeps the copies going stalls that thread for as long as the stores
 // in flight take to be acknowledged.  The publishing thread fences (once per batch of finished units), the issuing thread
-// never stops.
+// never stops.  (Tried and measured worse: pausing the stores at the end of every unit so that the issuing thread's own
+// fence is cheap -- the pause costs one link round trip per 256 KiB, 18 instead of 42 GB/s per pushing CTA.)
 struct DoneRing {
   uint32_t a[16], b[16], c[16];
   uint32_t tail, head, closed;
@@ -164,8 +165,7 @@ static __device__ void doneDrain(DoneRing& d, Role& role) {
       __nanosleep(64);
       continue;
     }
-    // ONE fence for everything that is waiting: a system fence on an SM that streams stores to a peer takes as long as the
-    // link's queue is deep (measured: ~10 us when the link is oversubscribed), so units are published in batches
+    // ONE fence for everything that is waiting, then one relaxed store per flag
     fence_proxy_async();
     fence_sys();
     for (; h != t; ++h) role.complete(d.a[h & 15], d.b[h & 15], d.c[h & 15]);
@@ -293,7 +293,8 @@ static __device__ bool chunkDecision1(const AarRankParams& p, const AarLayout& l
 // A copy role describes its work as a sequence of units {src, dst, bytes}; src == nullptr means "fill with zeros",
 // bytes == 0 means "nothing to move, only the completion action".  Role::nextUnit(u, blocking) returns 1 (unit), 0 (no
 // more units) or -1 (the next unit's precondition -- a flag, a flow-control word -- is not there yet; only when !blocking).
-// Role::complete(a, b, c) runs once the unit's last byte is written and visible to this thread.
+//
+// Role::complete(a, b, c) runs on the CTA's publishing thread (doneDrain) once the unit's last byte is written.
 struct CopyUnit {
   const char* src;
   char* dst;
@@ -303,7 +304,7 @@ struct CopyUnit {
 
 template <class Role>
 static __device__ void runCopyRole(const AarRankParams& p, const AarLayout& l, Role& role, BulkShared& bs, unsigned char* dsm) {
-  // thread 0 only; role.complete() runs on the publishing thread (doneDrain) when Role::kPublishes
+  // thread 0 only
   const uint32_t stage0 = smem_u32(dsm), zero = smem_u32(dsm + kStageBytes);
   uint32_t L = 0, S = 0, head = 0, tail = 0, phaseBits = 0;
   bool exhausted = false, haveUnit = false;
@@ -371,7 +372,7 @@ static __device__ void runCopyRole(const AarRankParams& p, const AarLayout& l, R
       bulk_s2g(dst, stage0 + (uint32_t)st * kCopyTile, n);
     }
     bulk_commit();
-    if (info & 1u) {
+    if (Role::kPublishes && (info & 1u)) {
       bs.fifoGroup[tail & 15] = S;
       bs.fifoA[tail & 15] = bs.unitA[st];
       bs.fifoB[tail & 15] = bs.unitB[st];
@@ -387,7 +388,7 @@ static __device__ void runCopyRole(const AarRankParams& p, const AarLayout& l, R
   }
   bulk_wait<0>();
   if (S > 0) retireDone(S - 1);
-  doneClose(bs.done);
+  if (Role::kPublishes) doneClose(bs.done);
 }
 
 }  // namespace aar_dev
