@@ -25,6 +25,9 @@ class AllReduceInputRequest:
 @dataclass
 class AllReduceInput:
     data: Any
+    # Device plane, optional: the tensor the reduced vector is written to.  None = the worker's own output buffer of the round's
+    # ring slot; the SAME tensor as `data` = in place (gradient buckets: no copy on either side of the allreduce).
+    out: Any = None
 
 
 @dataclass

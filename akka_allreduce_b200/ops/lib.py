@@ -92,7 +92,6 @@ def load():
         "aar_launch_round_pipelined": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_void_p],
         "aar_launch_round_bulk": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p],
         "aar_bulk_supported": [P(AarRankParams), P(AarLayout), C.c_int],
-        "aar_launch_persistent": [P(AarRankParams), P(AarLayout), C.c_void_p, C.c_int, C.c_int, C.c_void_p],
         "aar_launch_oneshot": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_void_p],
         "aar_launch_nvls": [P(AarRankParams), P(AarLayout), C.c_int, C.c_int, C.c_void_p],
         "aar_local_round": [P(AarRankParams), C.c_int, P(AarLayout), C.c_uint, C.c_int, C.c_void_p],
@@ -120,6 +119,9 @@ def load():
                               P(C.c_void_p)],
         "aar_engine_tune": [C.c_void_p, C.c_int, C.c_int],
         "aar_engine_enqueue": [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint, C.c_void_p],
+        "aar_engine_enqueue_ex": [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint, C.c_void_p, C.c_ulonglong],
+        "aar_engine_tune_bulk": [C.c_void_p, C.c_int],
+        "aar_engine_start_at": [C.c_void_p, C.c_int],
         "aar_engine_wait": [C.c_void_p, C.c_int, C.c_void_p],
         "aar_engine_synchronize": [C.c_void_p],
         "aar_engine_set_doorbell": [C.c_void_p, C.c_int],

@@ -1,12 +1,18 @@
 """Data-parallel gradient averaging through the worker source/sink contract, overlapped with backward.
 
 dataSize is fixed when a worker is initialised (AllreduceWorker.scala:174-176), so the flat gradient is cut into equal
-fixed-size buckets and every bucket gets its own round engine ("one round stream per bucket").
-Parameters' `.grad` tensors are views into the bucket buffers, so autograd accumulates straight into the memory the
-kernels read.  A post-accumulate-grad hook counts down each bucket; the moment a bucket is complete its source callback
-hands the buffer to the engine, which launches the round on its own streams while autograd keeps running.  The sink
-callback sees the averaged gradients (normalisation by the ACTUAL contributor count is fused into the reduce kernel) --
-written in place into the same bucket, so the optimizer needs no copy.
+fixed-size buckets and every bucket gets its own AllreduceWorker ("one worker per bucket") in
+masterless mode: the training step is the round clock (AllreduceWorker.local / start_allreduce), so no control message crosses a
+socket per round, but the data still flows through the worker contract -- the worker calls the bucket's data_source for the
+round's input and its data_sink with the result.  Parameters' `.grad` tensors are views into the bucket buffers, so autograd
+accumulates straight into the memory the kernels read.  A post-accumulate-grad hook counts down each bucket; the moment a
+bucket is complete its worker is started on the step's round: the source hands over the buffer (AllReduceInput.out = the same
+buffer: in place), the engine launches the round on its own streams while autograd keeps running.  The sink sees the averaged
+gradients (normalisation by the ACTUAL contributor count is fused into the reduce kernel), stream-ordered.
+
+`zero_grad()` of THIS class must be used (it zeroes the buckets); `optimizer.zero_grad(set_to_none=True)` -- the torch default --
+would detach the gradients from the buckets.  The hook notices a detached or re-bound `.grad` and copies it back in (correct,
+one extra copy), and a second backward before finish() -- gradient accumulation -- defers the launch to finish().
 """
 from __future__ import annotations
 
@@ -49,14 +55,19 @@ class GradientBucket:
         self.buffer = torch.zeros(numel, dtype=dtype, device=device)
         self.params: list[torch.nn.Parameter] = []
         self.pending = 0
+        self.launched_step = -1     # last training step whose round was started
         self.engine: RoundEngine | None = None
         self.symm: SymmetricMemory | None = None
+        self.worker = None          # AllreduceWorker in masterless mode
+        self.views: dict[int, torch.Tensor] = {}   # id(param) -> its view of the buffer
+        self.last_out: AllReduceOutput | None = None
 
     # the worker contract (DataWrapper.scala:3-7)
     def data_source(self, req: AllReduceInputRequest) -> AllReduceInput:
-        return AllReduceInput(self.buffer)
+        return AllReduceInput(self.buffer, out=self.buffer)   # in place
 
     def data_sink(self, out: AllReduceOutput) -> None:
+        self.last_out = out
         self.last_counts = out.count
 
 
@@ -71,6 +82,7 @@ class ThresholdDDP:
         self.module, self.rank, self.world = module, rank, world
         self.device = device if isinstance(device, torch.device) else torch.device("cuda", device)
         self.step = 0
+        self.rebinds = 0      # how often a hook found .grad detached from its bucket and copied it back in
         self.user_sink = sink
         params = [p for p in module.parameters() if p.requires_grad]
         dtype = params[0].dtype
@@ -87,7 +99,7 @@ class ThresholdDDP:
             b = GradientBucket(i, n, dtype, self.device)
             off = 0
             for p in g:
-                p.grad = b.buffer[off:off + p.numel()].view_as(p)   # autograd accumulates in place from now on
+                p.grad = b.views[id(p)] = b.buffer[off:off + p.numel()].view_as(p)   # autograd accumulates in place from now on
                 off += p.numel()
                 b.params.append(p)
                 p.register_post_accumulate_grad_hook(self._make_hook(b))
@@ -101,6 +113,9 @@ class ThresholdDDP:
                                                       grid=comm_ctas)
             else:
                 b.engine = RoundEngine.single_process(n, chunk, max_lag, dtype=dtype, device=device, normalize=True, grid=comm_ctas)
+            from ..worker import AllreduceWorker
+
+            b.worker = AllreduceWorker.local(b.data_source, b.data_sink, b.engine, worker_id=rank)
             self.buckets.append(b)
         self._arm()
 
@@ -109,30 +124,57 @@ class ThresholdDDP:
             b.pending = len(b.params)
 
     def _make_hook(self, b: GradientBucket):
-        def hook(_param):
+        def hook(param):
+            view = b.views[id(param)]
+            g = param.grad
+            if g is not None and g.data_ptr() != view.data_ptr():
+                # .grad was re-bound (optimizer.zero_grad(set_to_none=True), a hook, manual assignment): the bucket would
+                # reduce stale memory while the optimizer steps on un-reduced gradients.  Copy in and re-attach.
+                view.copy_(g)
+                param.grad = view
+                self.rebinds += 1
             b.pending -= 1
-            if b.pending == 0:
+            if b.pending == 0 and b.launched_step < self.step:
                 self._launch(b)
+            # pending < 0: a second backward before finish() (gradient accumulation).  The round of this step is already in
+            # flight on memory autograd is accumulating into again; finish() notices and refuses.
         return hook
 
     def _launch(self, b: GradientBucket):
-        x = b.data_source(AllReduceInputRequest(self.step)).data
         # in place: every element range is pushed (read) before the chunk that overwrites it can have been reduced
-        out, counts = b.engine.enqueue_round(self.step, x, out=x)
-        b._out = (out, counts)
+        b.launched_step = self.step
+        b.worker.start_allreduce(self.step)   # -> data_source -> kernels -> (stream-ordered) data_sink
 
     def finish(self) -> None:
-        """Call after backward(): the current stream waits for every bucket's round, sinks are invoked, hooks re-armed."""
+        """Call after backward(): the current stream waits for every bucket's round, sinks have been invoked, hooks re-armed."""
         for b in self.buckets:
-            if b.pending != 0:   # a parameter without gradient this step: launch what we have
+            if b.pending < 0:
+                raise RuntimeError("ThresholdDDP: a second backward() ran before finish(): this step's gradient rounds were launched after "
+                                   "the first one and are reducing memory that autograd has written again.  For gradient accumulation call "
+                                   "backward() under ddp.no_sync() for all but the last micro-batch.")
+            if b.launched_step < self.step:   # a parameter without gradient this step, or no_sync(): launch what we have
                 self._launch(b)
-            b.engine.wait_round(self.step)
-            out = AllReduceOutput(b._out[0], b._out[1], self.step)
-            b.data_sink(out)
-            if self.user_sink:
-                self.user_sink(b.index, out)
+            if self.user_sink and b.last_out is not None:
+                self.user_sink(b.index, b.last_out)
         self.step += 1
         self._arm()
+
+    def no_sync(self):
+        """Context manager: backward() inside it accumulates into the buckets without starting their rounds (gradient
+        accumulation); the last micro-batch runs outside it, or finish() launches whatever was deferred."""
+        ddp = self
+
+        class _NoSync:
+            def __enter__(self_inner):
+                for b in ddp.buckets:
+                    b.pending = 1 << 30   # never reaches zero inside the block
+                return ddp
+
+            def __exit__(self_inner, *exc):
+                ddp._arm()
+                return False
+
+        return _NoSync()
 
     def zero_grad(self) -> None:
         for b in self.buckets:

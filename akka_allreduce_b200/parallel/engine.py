@@ -23,10 +23,30 @@ from .local_gpu import _TORCH2AAR
 ONESHOT_MAX_BYTES = int(os.environ.get("AAR_ONESHOT_MAX_BYTES", 256 * 1024))
 
 
+_ALGO_CODE = {"twoshot": 0, "pipelined": 1, "oneshot": 2, "nvls": 3, "bulk": 4, "nvls_bulk": 5}
+_TABLE = None
+
+
+def selector_table() -> dict:
+    """The measured selection table (written by bench/sweep.py --write-table on the 8-GPU box, committed next to this file):
+    {"<P>": {"fp32" | "bf16": [[max_bytes, algo, split], ...]}} -- first row whose max_bytes covers the message wins."""
+    global _TABLE
+    if _TABLE is None:
+        import json
+        from pathlib import Path
+
+        path = Path(os.environ.get("AAR_SELECTOR_TABLE", Path(__file__).with_name("selector_table.json")))
+        try:
+            _TABLE = json.loads(path.read_text())
+        except (OSError, ValueError):
+            _TABLE = {}
+    return _TABLE
+
+
 class RoundEngine:
     def __init__(self, rank: int, region_ptrs: Sequence[int], layout: L.AarLayout, *, th_reduce: float = 1.0, th_complete: float = 1.0,
                  normalize: bool = False, exact_quorum: bool = False, timeout_ms: float = 0.0, device: int = 0, grid: int = 0,
-                 algo: str = "auto", mc_ptr: int = 0, keepalive=None, overlap: bool | None = None):
+                 algo: str = "auto", mc_ptr: int = 0, keepalive=None, overlap: bool | None = None, max_inflight: int = 2):
         self.lib = L.load()
         self.rank, self.P = rank, layout.P
         self.layout = layout
@@ -38,7 +58,15 @@ class RoundEngine:
         self.data_size = layout.dataSize
         self.max_lag = layout.L - 1
         self.mc_ptr = mc_ptr
-        self.algo = self._select(algo, th_reduce, th_complete)
+        p = L.AarRankParams()
+        p.rank = rank
+        p.minRequired = core.Geometry.min_required(th_reduce, layout.P)
+        p.minChunksRequired = self.geo.min_chunks_required(th_complete)
+        p.maxLag = self.max_lag
+        self.full_thresholds = p.minRequired >= layout.P and p.minChunksRequired >= layout.totalChunks
+        self.bulk_split = 0          # role split of the bulk kernels (nA | nB << 16, 0 = the library's heuristic)
+        self.nvls_bulk_split = 0
+        self.algo = self._select(algo, normalize, exact_quorum)
         with torch.cuda.device(self.device):
             self.outputs = [torch.empty(self.data_size, dtype=self.dtype, device=self.device) for _ in range(layout.L)]
             self.counts = [torch.zeros(layout.totalChunks, dtype=torch.int32, device=self.device) for _ in range(layout.L)]
@@ -46,21 +74,23 @@ class RoundEngine:
             dev = C.POINTER(C.c_uint)()
             L.check(self.lib.aar_host_words_alloc(16, C.byref(host), C.byref(dev)), "aar_host_words_alloc")
         self._host_words, self._dev_words = host, dev
-        p = L.AarRankParams()
-        p.rank = rank
-        p.minRequired = core.Geometry.min_required(th_reduce, layout.P)
-        p.minChunksRequired = self.geo.min_chunks_required(th_complete)
-        p.maxLag = self.max_lag
         p.flags = (L.FLAG_NORMALIZE if normalize else 0) | (L.FLAG_EXACT_QUORUM if exact_quorum else 0)
-        # Opt-in until it has run on hardware (docs/PROTOCOL.md, "Known limits"): with a partial quorum the broadcast waits
-        # for / skips destinations exactly like the scatter does.  Full thresholds never need it.
-        strict = os.environ.get("AAR_STRICT", "0") not in ("", "0")
-        if (strict or os.environ.get("AAR_BCAST_FC", "0") not in ("", "0")) and (p.minRequired < layout.P or p.minChunksRequired < layout.totalChunks):
+        # Strict protocol by default (docs/PROTOCOL.md; all variants verified on B200 at the start of round 2).  The bulk kernels
+        # are always strict; on the register kernels:
+        #   * partial quorum: the reduce-broadcast obeys the scatter's per-destination slot flow control (AAR_STRICT=0 opts out);
+        #   * every chunk required: the eager gather takes ONE decision per chunk, so a wait that gives up (timeout, doorbell)
+        #     can never leave a chunk half copied.
+        strict = os.environ.get("AAR_STRICT", "1") not in ("", "0")
+        if strict and not self.full_thresholds:
             p.flags |= L.FLAG_BCAST_FC
-        if os.environ.get("AAR_ELIDE_LATE", "0") not in ("", "0") and (p.minRequired < layout.P or p.minChunksRequired < layout.totalChunks):
-            p.flags |= L.FLAG_ELIDE_LATE | L.FLAG_BCAST_FC   # lives in the strict kernel variants
-        if strict and p.minChunksRequired >= layout.totalChunks:   # eager gather: one decision per chunk (no half-flushed chunks)
+        if strict and p.minChunksRequired >= layout.totalChunks:
             p.flags |= L.FLAG_EAGER_DEC
+        if os.environ.get("AAR_ELIDE_LATE", "0") not in ("", "0") and not self.full_thresholds:
+            p.flags |= L.FLAG_ELIDE_LATE | L.FLAG_BCAST_FC   # late-work elision lives in the strict register kernels
+        # Bulk kernels: own contribution read in place, own reduced block written straight to the output -- only when there
+        # are peers (a world of one keeps the full three-pass loop-back, which is what one rank of a larger world does per round)
+        if self.algo == "bulk" and layout.P > 1 and os.environ.get("AAR_SELF_DIRECT", "1") not in ("", "0"):
+            p.flags |= L.FLAG_SELF_DIRECT
         p.timeoutNs = int(timeout_ms * 1e6)
         dev_addr = C.cast(dev, C.c_void_p).value
         p.doorbell = dev_addr            # word 0: newest round announced by the master
@@ -74,36 +104,41 @@ class RoundEngine:
         self._pref = C.byref(self.params)
         self.rounds_enqueued = 0
         self.launches = 0
+        self.fallback_launches = 0
         self._nvtx = os.environ.get("AAR_NVTX", "0") not in ("", "0")   # one NVTX range per round launch (off by default)
-        # Opt-in (AAR_NATIVE_ENGINE=1, first hardware run pending): the per-round host work -- order after the caller's stream,
-        # launch, record the slot's event -- in ONE C call (csrc/cuda/aar_engine.cu) instead of four torch / ctypes calls.
-        self._native = None
         self._slot_round = [-1] * layout.L
-        # CTA role split of the pipelined kernels (measured on 8xB200, profiles/r1_phase_bench_*.txt)
+        self._bounce: dict[int, torch.Tensor] = {}
+        # CTA role split of the register pipelined kernels (measured on 8xB200 in round 1)
         self.split = 32 | (48 << 16)      # nPush | nReduce << 16; the rest gather
-        self.nvls_reduce_ctas = 8        # 207.7 us with 8 vs 222 us with 16 reduce CTAs at 8 GPUs, 64 MiB
+        self.nvls_reduce_ctas = 8
         self.nvls_stage_ctas = 48
-        # role split of the bulk async-copy engine kernels (0 = the library's heuristic): nA | nB << 16
-        self.bulk_split = 0
-        self.nvls_bulk_split = 0
-        # own contribution read in place / own reduced block written straight to the output: only when there are peers (a
-        # world of one keeps the full three-pass loop-back, which is what one rank of a larger world does per round)
-        if self.algo == "bulk" and layout.P > 1 and os.environ.get("AAR_SELF_DIRECT", "1") not in ("", "0"):
-            self.base_flags |= L.FLAG_SELF_DIRECT
         # The maxLag window lets two consecutive rounds of one worker be in flight: they alternate between two internal
         # streams, so the push of round r+1 starts on the SMs that round r's push CTAs have already left while round r is
         # still reducing and gathering.  Needs two ring slots (maxLag >= 1) and peers to overlap with.
         self.overlap = (layout.L >= 2 and layout.P > 1) if overlap is None else (overlap and layout.L >= 2)
+        # rounds of this rank in flight at once: 2 by default; a deeper ring (maxLag > 1) may use more, which is what lets a rank
+        # whose round r starts late keep up with rounds r+1 .. r+maxLag meanwhile (straggler mode)
+        self.inflight = max(2, min(int(max_inflight), layout.L, 8)) if self.overlap else 1
+        if self.inflight > 2 and grid == 0:
+            # every round in flight must be able to hold ALL its CTAs at once: a kernel that waits for peers while it occupies the
+            # SMs an earlier round of this rank still needs is a resource deadlock (seen at 4 in flight with full-size grids)
+            sms = C.c_int(0)
+            L.check(self.lib.aar_device_sm_count(device, C.byref(sms)), "aar_device_sm_count")
+            self.grid = grid = max(3, sms.value // self.inflight)
+        # The per-round host work -- order after the caller's stream, launch, record the slot's event -- is ONE C call
+        # (csrc/cuda/aar_engine.cu); AAR_NATIVE_ENGINE=0 keeps the Python choreography (NVTX ranges, explicit streams).
+        self._native = None
         with torch.cuda.device(self.device):
-            self._streams = [torch.cuda.Stream(device=self.device) for _ in range(2)] if self.overlap else []
+            self._streams = [torch.cuda.Stream(device=self.device) for _ in range(self.inflight)] if self.overlap else []
             self._events = [torch.cuda.Event() for _ in range(layout.L)]
-            if os.environ.get("AAR_NATIVE_ENGINE", "0") not in ("", "0"):
+            if os.environ.get("AAR_NATIVE_ENGINE", "1") not in ("", "0") and not self._nvtx:
                 regs = (C.c_void_p * layout.P)(*[region_ptrs[j] for j in range(layout.P)])
                 h = C.c_void_p(0)
-                code = {"twoshot": 0, "pipelined": 1, "oneshot": 2, "nvls": 3}[self.algo]
                 L.check(self.lib.aar_engine_create(self._lay, rank, regs, C.c_void_p(mc_ptr or None), p.minRequired, p.minChunksRequired,
-                                                   self.base_flags, p.timeoutNs, code, grid, int(self.overlap), C.byref(h)), "aar_engine_create")
+                                                   self.base_flags, p.timeoutNs, _ALGO_CODE[self.algo], grid, self.inflight if self.overlap else 0, C.byref(h)), "aar_engine_create")
                 self._native = h
+        self._native_flags = self.base_flags   # what the native engine was created with; later additions travel per round
+        self._native_tuning = None
 
     # ------------------------------------------------------------------ construction helpers
     @classmethod
@@ -118,24 +153,51 @@ class RoundEngine:
     def from_symmetric(cls, symm, layout: L.AarLayout, **kw):
         return cls(symm.rank, symm.ptrs, layout, device=symm.device, mc_ptr=symm.mc_ptr, keepalive=symm, **kw)
 
-    def _select(self, algo: str, th_reduce: float, th_complete: float) -> str:
+    def _bulk_geometry(self) -> bool:
+        """The bulk kernels move 16-byte aligned pieces: blocks, chunks and the vector length must be multiples of 16 bytes."""
+        lay = self.layout
+        V = 16 // lay.elemSize
+        return lay.stepSize % V == 0 and lay.maxChunk % V == 0 and lay.dataSize % V == 0 and lay.blkStride % V == 0
+
+    def _select(self, algo: str, normalize: bool, exact_quorum: bool) -> str:
+        """auto: from the measured table (world size, dtype, bytes) -> kernel family + role split; thresholds < 1, normalisation
+        and the exact-quorum policy rule the in-switch path out (the switch sums every bound GPU)."""
         lay = self.layout
         nbytes = lay.dataSize * lay.elemSize
+        bulk_ok = self._bulk_geometry()
+        nvls_ok = bool(self.mc_ptr and lay.stageOff and bulk_ok and self.full_thresholds and not exact_quorum)   # normalisation: sum / P in registers
         if algo == "auto":
-            if lay.oneshotOff and nbytes <= ONESHOT_MAX_BYTES and lay.P > 1:
+            if lay.P == 1:
+                return "bulk" if bulk_ok else "twoshot"
+            rows = selector_table().get(str(lay.P), {}).get("fp32" if lay.elemSize == 4 else "bf16", [])
+            for max_bytes, name, split in rows:
+                if nbytes > max_bytes:
+                    continue
+                if name == "oneshot" and not lay.oneshotOff:
+                    continue
+                if (name == "nvls_bulk" and not nvls_ok) or (name == "nvls" and not (nvls_ok and not normalize)):
+                    continue
+                if name in ("bulk", "nvls_bulk") and not bulk_ok:
+                    continue
+                if name == "bulk":
+                    self.bulk_split = int(split)
+                elif name == "nvls_bulk":
+                    self.nvls_bulk_split = int(split)
+                return name
+            # no table row: small messages take the one-hop kernel, the rest the bulk engine kernels
+            if lay.oneshotOff and nbytes <= ONESHOT_MAX_BYTES:
                 return "oneshot"
-            # In-switch reduction moves N(1 + 1/P) bytes per direction against 2N(P-1)/P for two-shot P2P: it only pays
-            # from four GPUs up (at P = 2 it is 1.5N against N).  The switch sums every bound GPU, so thresholds must be 1.
-            V = 16 // lay.elemSize
-            aligned = lay.stepSize % V == 0 and lay.maxChunk % V == 0 and lay.dataSize % V == 0
-            if self.mc_ptr and lay.stageOff and lay.P >= 8 and aligned and th_reduce >= 1.0 and th_complete >= 1.0:
-                return "nvls"  # measured: 222 us vs NCCL 277 us at 8 GPUs; at 4 GPUs the pipelined P2P kernel is faster (182 vs 205 us)
-            # role-specialised CTAs overlap push / reduce / gather chunk by chunk; with one rank there is nothing to overlap
-            return "pipelined" if lay.P > 1 else "twoshot"
+            if nvls_ok and lay.P >= 8:
+                return "nvls_bulk"
+            return "bulk" if bulk_ok else "pipelined"
         if algo == "oneshot" and not lay.oneshotOff:
             raise ValueError("algo=oneshot needs a layout with one-shot buffers")
         if algo in ("nvls", "nvls_bulk") and not (self.mc_ptr and lay.stageOff):
             raise ValueError(f"algo={algo} needs a multicast mapping and the staging area")
+        if algo in ("bulk", "nvls_bulk") and not bulk_ok:
+            raise ValueError(f"algo={algo} needs blocks and chunks that are multiples of 16 bytes")
+        if algo not in _ALGO_CODE:
+            raise ValueError(f"unknown algo {algo}")
         return algo
 
     # ------------------------------------------------------------------ rounds
@@ -161,13 +223,29 @@ class RoundEngine:
                              f"(AllreduceWorker.scala:174-176 rejects a size that differs from initialisation)")
         slot = rnd % self.layout.L
         output = self.outputs[slot] if out is None else out
+        if self.algo == "oneshot" and output.data_ptr() == x.data_ptr():
+            # the one-shot kernel has no barrier between its push and its reduce: a CTA may store output tile t while another
+            # CTA of this rank has not pushed that part of the input to a slower peer yet
+            raise ValueError("in-place rounds (out aliasing the input) are not supported by the one-shot kernel")
+        if self.algo in ("bulk", "nvls_bulk") and x.data_ptr() % 16:
+            # the bulk copy engine needs 16-byte aligned addresses: bounce an oddly offset view through an aligned buffer
+            b = self._bounce.get(slot)
+            if b is None:
+                b = self._bounce[slot] = torch.empty_like(self.outputs[slot])
+            b.copy_(x)
+            x = b
         if self._native is not None:
-            if stream is not None or delay_ns > 0:
-                raise NotImplementedError("the native engine picks its own stream and has no straggler injector")
-            extra = (L.FLAG_FORCE if force else 0) | (L.FLAG_SKIP_SCATTER if skip_scatter else 0)
-            L.check(self.lib.aar_engine_enqueue(self._native, rnd, C.c_void_p(x.data_ptr()), C.c_void_p(output.data_ptr()),
-                                                C.c_void_p(self.counts[slot].data_ptr()), extra,
-                                                C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)), "aar_engine_enqueue")
+            if stream is not None:
+                raise NotImplementedError("the native engine picks its own stream (AAR_NATIVE_ENGINE=0 for explicit streams)")
+            tuning = (self.split, self.nvls_reduce_ctas | (self.nvls_stage_ctas << 8), self.nvls_bulk_split if self.algo == "nvls_bulk" else self.bulk_split)
+            if tuning != self._native_tuning:   # knobs changed since the last round (benchmarks sweep them)
+                L.check(self.lib.aar_engine_tune(self._native, tuning[0], tuning[1]), "aar_engine_tune")
+                L.check(self.lib.aar_engine_tune_bulk(self._native, tuning[2]), "aar_engine_tune_bulk")
+                self._native_tuning = tuning
+            extra = (L.FLAG_FORCE if force else 0) | (L.FLAG_SKIP_SCATTER if skip_scatter else 0) | (self.base_flags & ~self._native_flags)
+            L.check(self.lib.aar_engine_enqueue_ex(self._native, rnd, C.c_void_p(x.data_ptr()), C.c_void_p(output.data_ptr()),
+                                                   C.c_void_p(self.counts[slot].data_ptr()), extra,
+                                                   C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream), int(delay_ns)), "aar_engine_enqueue")
             self._slot_round[slot] = rnd
             self.launches += 1
             self.rounds_enqueued = max(self.rounds_enqueued, rnd + 1)
@@ -180,7 +258,7 @@ class RoundEngine:
         p.flags = self.base_flags | (L.FLAG_FORCE if force else 0) | (L.FLAG_SKIP_SCATTER if skip_scatter else 0)
         cur = torch.cuda.current_stream(self.device)
         if stream is None and self.overlap:
-            stream = self._streams[rnd % 2]
+            stream = self._streams[rnd % self.inflight]
             stream.wait_stream(cur)          # x was produced on the caller's stream
             p.flags |= L.FLAG_OVERLAPPED
         run_stream = stream or cur
@@ -270,6 +348,12 @@ class RoundEngine:
         self.wait_round(rnd)
         return out
 
+    def clear_status(self) -> None:
+        """Zero the sticky status bits of this rank's region (benchmarks that reuse one region for several engines)."""
+        torch.cuda.synchronize(self.device)
+        self._region_view(self.layout.statusOff, 4, torch.int32).zero_()
+        torch.cuda.synchronize(self.device)
+
     def status(self) -> int:
         """Device status bits (timeouts, dropped pushes) of this rank; synchronises."""
         torch.cuda.synchronize(self.device)
@@ -305,20 +389,18 @@ class RoundEngine:
         """Begin the round numbering at `rnd` on a fresh engine (a master that resumed from a checkpoint): every rank counts as
         having retired all earlier rounds, so the slot flow control of round `rnd` has nothing to wait for.  Every rank calls
         this on its own region before the first launch (the worker does, between mapping the regions and its first round)."""
-        if self._native is not None:
-            raise NotImplementedError("start_at / restore are not wired into the native engine yet (it owns its completion word)")
         lay = self.layout
         self._region_view(lay.peerBaseOff, L.AAR_MAXP * 4, torch.int32)[: lay.P] = rnd
         self._region_view(lay.statusOff, 8, torch.int32)[1] = rnd
         self._host_words[1] = rnd
+        if self._native is not None:
+            L.check(self.lib.aar_engine_start_at(self._native, rnd), "aar_engine_start_at")
         self.rounds_enqueued = rnd
         torch.cuda.synchronize(self.device)
 
     def restore(self, s: "core.RingSnapshot") -> None:
         """Inverse of snapshot(): the ring payload and the arrival words go back into this rank's region; round numbering
         continues at s.round.  The geometry must match."""
-        if self._native is not None:
-            raise NotImplementedError("start_at / restore are not wired into the native engine yet (it owns its completion word)")
         lay = self.layout
         if (s.P, s.L, s.data_size, s.max_chunk_size) != (lay.P, lay.L, lay.dataSize, lay.maxChunk):
             raise ValueError("ring snapshot was taken with a different geometry")
@@ -335,6 +417,8 @@ class RoundEngine:
         self._region_view(lay.peerBaseOff, L.AAR_MAXP * 4, torch.int32)[: lay.P] = s.round
         self._region_view(lay.statusOff, 8, torch.int32)[1] = s.round
         self._host_words[1] = s.round
+        if self._native is not None:
+            L.check(self.lib.aar_engine_start_at(self._native, s.round), "aar_engine_start_at")
         self.rounds_enqueued = s.round
         torch.cuda.synchronize(self.device)
 
@@ -344,7 +428,7 @@ class RoundEngine:
         return {"algo": self.algo, "rounds_enqueued": self.rounds_enqueued, "rounds_flushed": self.rounds_flushed(), "launches": self.launches,
                 "timeout_scatter": bool(st & L.ST_TIMEOUT_SCATTER), "timeout_reduce": bool(st & L.ST_TIMEOUT_REDUCE),
                 "timeout_gather": bool(st & L.ST_TIMEOUT_GATHER), "push_dropped": bool(st & L.ST_PUSH_DROPPED),
-                "rounds_in_flight": 2 if self.overlap else 1, "multicast": bool(self.mc_ptr)}
+                "rounds_in_flight": self.inflight, "multicast": bool(self.mc_ptr)}
 
     def close(self) -> None:
         if self._native is not None:
@@ -353,89 +437,3 @@ class RoundEngine:
         if self._host_words:
             self.lib.aar_host_words_free(self._host_words)
             self._host_words = None
-
-
-class PersistentEngine:
-    """K7: a resident kernel per rank driven by a doorbell instead of one launch per round.
-
-    The host posts {round, input, output} into a ring in pinned memory (a few stores, ~1 us of Python) and the kernel
-    picks it up after one PCIe poll; completion comes back through the engine's host-mapped completion word.  Meant for
-    the latency-bound sizes, where a launch per round costs more than the round.  The inputs must already be complete
-    when a round is posted (the resident kernel cannot wait on a stream), and the kernel keeps `grid` SMs until stop().
-    While it runs, never synchronise the whole device (torch.cuda.synchronize / cudaDeviceSynchronize wait for the resident
-    kernel, which only ends at stop()); synchronise streams or use wait().  For the same reason every kernel that will be
-    launched while it runs must have been launched once before (CUDA loads modules lazily, and loading waits for an idle
-    device), or run with CUDA_MODULE_LOADING=EAGER.
-    """
-
-    DEPTH, WORDS, MAX_OUTSTANDING = 8, 16, 4
-
-    def __init__(self, eng: RoundEngine, algo: str = "oneshot", grid: int = 16):
-        if algo not in ("oneshot", "twoshot"):
-            raise ValueError("persistent algo must be 'oneshot' or 'twoshot'")
-        if algo == "oneshot" and not eng.layout.oneshotOff:
-            raise ValueError("the layout has no one-shot buffers")
-        self.eng, self.algo = eng, algo
-        lib = eng.lib
-        host = C.POINTER(C.c_uint)()
-        dev = C.POINTER(C.c_uint)()
-        with torch.cuda.device(eng.device):
-            L.check(lib.aar_host_words_alloc(self.DEPTH * self.WORDS, C.byref(host), C.byref(dev)), "aar_host_words_alloc")
-            self.stream = torch.cuda.Stream(device=eng.device)
-        self._ring, self._ring_dev = host, dev
-        self.posted = 0
-        self.first_round: int | None = None
-        p = L.AarRankParams.from_buffer_copy(eng.params)
-        p.flags = eng.base_flags
-        self._params = p
-        with torch.cuda.device(eng.device):
-            L.check(lib.aar_launch_persistent(C.byref(p), eng._lay, C.cast(dev, C.c_void_p), 1 if algo == "oneshot" else 0, grid,
-                                              C.c_void_p(self.stream.cuda_stream)), "aar_launch_persistent")
-        self.running = True
-
-    def _completed(self) -> int:
-        return 0 if self.first_round is None else max(0, self.eng.rounds_flushed() - self.first_round)
-
-    def post(self, rnd: int, x: torch.Tensor, out: torch.Tensor | None = None, flags: int = 0):
-        """Ring the doorbell for round `rnd` (rounds must be consecutive).  Returns (output, counts) tensors of the slot."""
-        eng = self.eng
-        if self.first_round is None:
-            self.first_round = rnd
-        elif rnd != self.first_round + self.posted:
-            raise ValueError("persistent rounds must be posted in consecutive order")
-        while self.posted - self._completed() >= self.MAX_OUTSTANDING:
-            pass  # the ring entry (and the output slot) of an unfinished round may not be reused
-        slot = rnd % eng.layout.L
-        output = eng.outputs[slot] if out is None else out
-        counts = eng.counts[slot]
-        r = self._ring
-        e = (self.posted % self.DEPTH) * self.WORDS
-        r[e + 1] = flags
-        r[e + 2] = rnd
-        r[e + 3] = 0
-        for k, ptr in ((4, x.data_ptr()), (6, output.data_ptr()), (8, counts.data_ptr())):
-            r[e + k] = ptr & 0xFFFFFFFF
-            r[e + k + 1] = ptr >> 32
-        r[e] = self.posted + 1  # the doorbell: written last (x86 keeps the store order)
-        self.posted += 1
-        eng.rounds_enqueued = max(eng.rounds_enqueued, rnd + 1)
-        return output, counts
-
-    def wait(self, rnd: int, timeout_s: float = 30.0) -> None:
-        import time
-
-        t0 = time.time()
-        while self.eng.rounds_flushed() < rnd + 1:
-            if time.time() - t0 > timeout_s:
-                raise TimeoutError(f"persistent engine: round {rnd} did not complete (flushed {self.eng.rounds_flushed()})")
-
-    def stop(self) -> None:
-        if not self.running:
-            return
-        e = (self.posted % self.DEPTH) * self.WORDS
-        self._ring[e + 3] = 1
-        self._ring[e] = self.posted + 1
-        self.posted += 1
-        self.stream.synchronize()
-        self.running = False
-        self.eng.lib.aar_host_words_free(self._ring)

@@ -55,7 +55,9 @@ class AllreduceWorker:
         self._t_last = 0.0
         self._stream = None
         self._inputs = {}           # round -> input tensor kept alive until the round is flushed
+        self._outs = {}             # round -> caller-provided output tensor (AllReduceInput.out), else the ring slot's buffer
         self._cpu_worker = None
+        self.stream_ordered = False  # local mode: the sink runs right after the launch, ordered on the CUDA stream
 
     # ------------------------------------------------------------------ lifecycle
     def connect(self, master_host: str = "127.0.0.1", master_port: int = 2551, listen_port: int = 0, heartbeat_ms: float = 1000.0):
@@ -137,6 +139,42 @@ class AllreduceWorker:
             self.rdv.close()
             self.rdv = None
 
+    # ------------------------------------------------------------------ masterless mode
+    @classmethod
+    def local(cls, data_source: DataSource, data_sink: DataSink, engine, *, worker_id: int = 0, stream_ordered: bool = True) -> "AllreduceWorker":
+        """A worker whose round clock is its caller instead of an AllreduceMaster: `start_allreduce(r)` is the StartAllreduce message,
+        completions are counted locally.  For callers that are already in lock-step -- a data-parallel training step is one
+        round per gradient bucket (parallel/ddp.py) -- and must not pay a TCP round trip per round.  Same contract otherwise:
+        every round is fetched from the source exactly once, in order, and its result reaches the sink.  stream_ordered: the sink
+        is called as soon as the round is launched, with tensors that are valid in CUDA stream order (the current stream has
+        been made to wait for the round) -- the host never blocks; False: the sink is called when the host sees the round flushed."""
+        w = cls(data_source, data_sink, backend="cuda")
+        w.engine = engine
+        w.id = worker_id
+        w.node = _LocalClock()
+        w.stream_ordered = stream_ordered
+        w.max_round = w.max_scattered = -1
+        return w
+
+    def start_allreduce(self, rnd: int) -> None:
+        """Local mode: StartAllreduce(rnd) from the caller's clock."""
+        self._on_start(rnd)
+        if self.stream_ordered:
+            self._deliver_stream_ordered()
+        else:
+            self._deliver_flushed()
+
+    def _deliver_stream_ordered(self) -> None:
+        eng = self.engine
+        while self.delivered <= self.max_scattered:
+            r = self.delivered
+            slot = r % eng.layout.L
+            eng.wait_round(r)           # the CURRENT stream waits for the round; nothing blocks on the host
+            self._inputs.pop(r, None)
+            self.data_sink(AllReduceOutput(self._outs.pop(r, eng.outputs[slot]), eng.counts[slot], r))
+            self.node.send_complete(self.id, r, self.generation)
+            self.delivered += 1
+
     # ------------------------------------------------------------------ device data plane
     def _on_message(self, msg) -> None:
         if isinstance(msg, core.InitWorkers):
@@ -162,6 +200,7 @@ class AllreduceWorker:
         self.lag_hist = {}
         self._t_first = None
         self._inputs.clear()
+        self._outs.clear()
         if self.on_init:
             self.on_init(self)
 
@@ -204,17 +243,26 @@ class AllreduceWorker:
             r = self.max_scattered + 1
             # the output / count buffers of round r - L must have reached the sink before round r reuses them
             while self.delivered < r - L + 1:
-                self._deliver_flushed(block=True)
+                if self.stream_ordered:
+                    self._deliver_stream_ordered()
+                else:
+                    self._deliver_flushed(block=True)
             req = AllReduceInputRequest(r)
             if self.zero_copy_input and hasattr(eng, "stage_input"):
                 req.buffer = eng.stage_input(r)   # None unless the in-switch path is active
-            x = self.data_source(req).data
+            inp = self.data_source(req)
+            x = inp.data
             n = x.numel() if hasattr(x, "numel") else len(x)
             if n != eng.data_size:
                 raise ValueError(f"Input data size {n} is different from initialization time {eng.data_size}!")
             # The engine orders its launch after the current stream (where the source produced x) and, when the ring has
             # two slots, alternates rounds between two internal streams so consecutive rounds overlap (the maxLag window).
-            eng.enqueue_round(r, x)
+            out = getattr(inp, "out", None)
+            if out is not None:
+                eng.enqueue_round(r, x, out=out)
+                self._outs[r] = out
+            else:
+                eng.enqueue_round(r, x)
             self._inputs[r] = x
             self.max_scattered = r
 
@@ -234,7 +282,7 @@ class AllreduceWorker:
                 self.lag_hist[lag] = self.lag_hist.get(lag, 0) + 1
                 if lag > eng.max_lag:
                     self.rounds_forced += 1
-                self.data_sink(AllReduceOutput(eng.outputs[slot], eng.counts[slot], r))
+                self.data_sink(AllReduceOutput(self._outs.pop(r, eng.outputs[slot]), eng.counts[slot], r))
                 self.node.send_complete(self.id, r, self.generation)
                 self.delivered += 1
                 self._t_last = time.time()
@@ -253,3 +301,19 @@ class AllreduceWorker:
             self.engine.set_doorbell(1 << 30)
             self.engine.synchronize()
             self._deliver_flushed()
+
+
+class _LocalClock:
+    """Stands in for the control channel of a masterless worker: completions are counted, nothing is sent."""
+
+    shutdown_requested = False
+    shutdown_by_master = False
+
+    def __init__(self):
+        self.completed: list[int] = []
+
+    def send_complete(self, worker_id: int, rnd: int, generation: int) -> None:
+        self.completed.append(rnd)
+
+    def poll(self, timeout_ms: int = 0) -> None:
+        pass

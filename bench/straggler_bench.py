@@ -27,6 +27,8 @@ ap.add_argument("--warmup", type=int, default=8)
 ap.add_argument("--delays-us", default="100,250,500")
 ap.add_argument("--max-lag", type=int, default=4)
 ap.add_argument("--th", type=float, default=0.75)
+ap.add_argument("--inflight", type=int, default=2, help="rounds of one rank in flight (internal streams), at most maxLag + 1")
+ap.add_argument("--algo", default="auto")
 a = ap.parse_args()
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 lr = int(os.environ.get("LOCAL_RANK", rank))
@@ -48,12 +50,15 @@ def sync():
 
 xs = [torch.randn(a.n, device=dev) for _ in range(2)]
 res = {"world": world, "n": a.n, "chunk": a.chunk, "max_lag": a.max_lag, "threshold": a.th, "rounds": a.rounds}
-lay = L.compute_layout(world, a.n, a.chunk, a.max_lag, L.AAR_F32, 0, False)
-symm = SymmetricMemory(UnixRendezvous(rank, world, sess + "_m"), lay.regionBytes, lr, want_multicast=False)
+lay = L.compute_layout(world, a.n, a.chunk, a.max_lag, L.AAR_F32, 0, True)
+symm = SymmetricMemory(UnixRendezvous(rank, world, sess + "_m"), lay.regionBytes, lr, want_multicast=True)
 
 
 def run_engine(th, delay_us, tag):
-    eng = RoundEngine.from_symmetric(symm, lay, th_reduce=th, th_complete=th, timeout_ms=2000.0)
+    # more than two rounds in flight only with a partial quorum: at thresholds 1.0 every round waits for the delayed rank, and
+    # later rounds' kernels holding SMs while they wait can starve the round everybody is waiting for
+    eng = RoundEngine.from_symmetric(symm, lay, th_reduce=th, th_complete=th, timeout_ms=2000.0, max_inflight=a.inflight if th < 1.0 else 2, algo=a.algo)
+    eng.clear_status()   # the region is reused from run to run and its status bits are sticky
     import time
     base = run_engine.next_round
     tw = time.time()
@@ -74,7 +79,11 @@ def run_engine(th, delay_us, tag):
     sync()
     ms = gmax(e0.elapsed_time(e1) / a.rounds)
     cmin, cmax = int(counts.min()), int(counts.max())
-    res[tag] = {"ms_per_round": round(ms, 4), "rounds_per_sec": round(1e3 / ms, 1), "last_round_counts_min_max": [cmin, cmax], "status_bits": eng.status(), "status_after_warmup": st_warm, "warmup_wall_s": round(warm_s, 3), "algo": eng.algo}
+    # what the partial quorum cost in the last maxLag + 1 rounds: chunks flushed as zeros (count 0) and the mean contributor count
+    recent = torch.stack(eng.counts).float()
+    zero_frac = float((recent == 0).float().mean())
+    mean_cnt = float(recent.mean())
+    res[tag] = {"zero_chunk_fraction_last_rounds": round(zero_frac, 4), "mean_contributors_last_rounds": round(mean_cnt, 3), "rounds_in_flight": eng.inflight,"ms_per_round": round(ms, 4), "rounds_per_sec": round(1e3 / ms, 1), "last_round_counts_min_max": [cmin, cmax], "status_bits": eng.status(), "status_after_warmup": st_warm, "warmup_wall_s": round(warm_s, 3), "algo": eng.algo}
     run_engine.next_round = first + a.rounds
     eng.close()
     # the region keeps its flags: continue with later round numbers so epochs stay monotone

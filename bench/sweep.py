@@ -77,8 +77,9 @@ for nbytes in [int(s) for s in a.sizes.split(",")]:
         k += 1
         symm = SymmetricMemory(UnixRendezvous(rank, world, f"{sess}_m{k}"), lay.regionBytes, lr, want_multicast=True)
         for algo in a.algos.split(","):
-            try:
-                eng = RoundEngine.from_symmetric(symm, lay, algo=algo, timeout_ms=5000.0, grid=a.grid)
+            try:   # "name:noov" = that kernel with one round in flight (no use of the maxLag window)
+                eng = RoundEngine.from_symmetric(symm, lay, algo=algo.split(":")[0], timeout_ms=5000.0, grid=a.grid,
+                                                 overlap=False if algo.endswith(":noov") else None)
             except ValueError:
                 continue
             try:

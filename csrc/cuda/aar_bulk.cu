@@ -425,8 +425,9 @@ __device__ void roleReduceP2P(const AarRankParams& p, const AarLayout& l, int ct
 // NVLS (K4): the NVSwitch sums the staged inputs of all ranks (multimem.ld_reduce) and replicates the result into every
 // rank's reduce ring (multimem.st); per direction each GPU moves about N(1 + 1/P) bytes instead of 2N(P-1)/P.
 template <typename T>
-__device__ __forceinline__ void nvlsSpanBulk(const char* mcStage, char* mcOut, int nv) {
+__device__ __forceinline__ void nvlsSpanBulk(const char* mcStage, char* mcOut, int nv, float divisor) {
   constexpr int U = 8;
+  constexpr int V = Elem<T>::kPerVec;
   for (int base = threadIdx.x; base < nv; base += kThreads * U) {
     uint4 v[U];
 #pragma unroll
@@ -435,6 +436,16 @@ __device__ __forceinline__ void nvlsSpanBulk(const char* mcStage, char* mcOut, i
       if (i < nv) {
         if (sizeof(T) == 4) v[u] = multimem_ld_reduce_f32x4(mcStage + (size_t)i * 16);
         else v[u] = multimem_ld_reduce_bf16x8(mcStage + (size_t)i * 16);
+      }
+    }
+    if (divisor != 1.f) {  // AAR_FLAG_NORMALIZE: the switch sums all P ranks, so the contributor count is P
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        float f[V];
+        Elem<T>::unpack(v[u], f);
+#pragma unroll
+        for (int k = 0; k < V; ++k) f[k] = f[k] / divisor;
+        v[u] = Elem<T>::pack(f);
       }
     }
 #pragma unroll
@@ -501,7 +512,7 @@ __device__ void roleReduceNvls(const AarRankParams& p, const AarLayout& l, int c
       const char* mcStage = reinterpret_cast<const char*>(p.mcRegion) + l.stageOff +
                             ((long long)slot * paddedData(l) + blockStart(l, p.rank) + (long long)c * l.maxChunk + off) * (long long)sizeof(T);
       char* mcOut = reinterpret_cast<char*>(p.mcRegion) + l.reduceOff + outElemOff * (long long)sizeof(T);
-      nvlsSpanBulk<T>(mcStage, mcOut, n / Elem<T>::kPerVec);
+      nvlsSpanBulk<T>(mcStage, mcOut, n / Elem<T>::kPerVec, ((p.flags & AAR_FLAG_NORMALIZE) && P > 1) ? (float)P : 1.f);
     }
     __syncthreads();
     if (threadIdx.x == 0 && ok) {
@@ -883,7 +894,7 @@ int supported(const AarRankParams* p, const AarLayout* lay, int algo, const char
   else if (lay->tileElems * lay->elemSize != kCopyTile) *why = "layout tile size differs from the copy tile";
   else if (algo == 1) {
     if (!p->mcRegion || lay->stageOff == 0) *why = "the in-switch path needs a multicast mapping and the staging area";
-    else if (p->minRequired != lay->P || p->minChunksRequired != lay->totalChunks || (p->flags & (AAR_FLAG_SKIP_SCATTER | AAR_FLAG_EXACT_QUORUM | AAR_FLAG_NORMALIZE)))
+    else if (p->minRequired != lay->P || p->minChunksRequired != lay->totalChunks || (p->flags & (AAR_FLAG_SKIP_SCATTER | AAR_FLAG_EXACT_QUORUM)))
       *why = "the switch sums every bound GPU, so thresholds must be 1.0 (use the P2P path otherwise)";
   }
   return *why == nullptr;
@@ -934,6 +945,17 @@ AAR_API int aar_launch_round_bulk(const AarRankParams* p, const AarLayout* lay, 
     if (nA < 1) nA = 1;
     if (nB < 1) nB = 1;
     if (nA + nB >= g) return aar_host::fail(AAR_EINVAL, "%s: split %d + %d leaves no gather CTA in a grid of %d", what, nA, nB, g);
+    // A role never needs more CTAs than it has pieces to move: small messages get a small grid (less to launch, to initialise
+    // and to wait for at retirement).
+    const int Sp = lay->piecesPerChunk, P = lay->P;
+    const bool sd = (p->flags & AAR_FLAG_SELF_DIRECT) && algo == 0;
+    const int remote = sd ? P - 1 : P;
+    long long unitsA = (long long)lay->C * (remote > 0 ? remote : 1) * Sp, unitsB = (long long)lay->C * Sp, unitsC = (long long)lay->C * P * Sp;
+    int nC = g - nA - nB;
+    if (unitsA < nA) nA = (int)(unitsA < 1 ? 1 : unitsA);
+    if (unitsB < nB) nB = (int)(unitsB < 1 ? 1 : unitsB);
+    if (unitsC < nC) nC = (int)(unitsC < 1 ? 1 : unitsC);
+    g = nA + nB + nC;
     sp = nA | (nB << 16);
   }
   cudaStream_t s = (cudaStream_t)stream;

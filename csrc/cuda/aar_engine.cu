@@ -3,7 +3,7 @@
 // Reference steps covered: StartAllreduce -> fetch -> scatter (AllreduceWorker.scala:84-104) and complete (:253-268) as far
 // as they touch the data plane; the actor mailbox is replaced by stream order.  Rounds of one rank alternate between two
 // internal streams when the ring has at least two slots (the maxLag window), exactly like the Python engine.
-// Written without GPU access: opt-in (AAR_NATIVE_ENGINE=1 in parallel/engine.py), every CUDA call is checked.
+// The default enqueue path of parallel/engine.py (AAR_NATIVE_ENGINE=0 switches back to the Python choreography).
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string.h>
@@ -17,10 +17,10 @@ struct AarEngine {
   AarLayout lay;
   AarRankParams p;
   unsigned baseFlags = 0;
-  int algo = 0, grid = 0, split = 32 | (48 << 16), nvlsReduce = 8, nvlsStage = 48;
-  bool overlap = false;
+  int algo = 0, grid = 0, split = 32 | (48 << 16), nvlsReduce = 8, nvlsStage = 48, bulkSplit = 0;
+  int nStreams = 0;   // internal streams the rounds rotate over (0: rounds run on the caller's stream)
   int device = 0;
-  cudaStream_t streams[2] = {nullptr, nullptr};
+  cudaStream_t streams[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   std::vector<cudaEvent_t> slotDone;   // one per ring slot: the round that used it last has finished
   std::vector<char> slotUsed;
   cudaEvent_t inputReady = nullptr;    // records the caller's stream before a round moves to an internal stream
@@ -55,9 +55,9 @@ AAR_API int aar_engine_create(const AarLayout* layout, int rank, void* const* re
   const char* what = "aar_engine_create";
   if (!layout || !regions || !out) return fail(AAR_EINVAL, "%s: null argument", what);
   if (rank < 0 || rank >= layout->P || layout->P > AAR_MAXP) return fail(AAR_EINVAL, "%s: bad rank %d for P=%d", what, rank, layout->P);
-  if (algo < 0 || algo > 3) return fail(AAR_EINVAL, "%s: algo %d (0 two-shot, 1 pipelined, 2 one-shot, 3 NVLS)", what, algo);
+  if (algo < 0 || algo > 5) return fail(AAR_EINVAL, "%s: algo %d (0 two-shot, 1 pipelined, 2 one-shot, 3 NVLS, 4 bulk P2P, 5 bulk NVLS)", what, algo);
   if (algo == 2 && !layout->oneshotOff) return fail(AAR_EINVAL, "%s: the layout has no one-shot buffers", what);
-  if (algo == 3 && !(mcRegion && layout->stageOff)) return fail(AAR_EINVAL, "%s: NVLS needs a multicast mapping and the staging area", what);
+  if ((algo == 3 || algo == 5) && !(mcRegion && layout->stageOff)) return fail(AAR_EINVAL, "%s: NVLS needs a multicast mapping and the staging area", what);
   AarEngine* e = new AarEngine();
   e->lay = *layout;
   memset(&e->p, 0, sizeof e->p);
@@ -71,7 +71,11 @@ AAR_API int aar_engine_create(const AarLayout* layout, int rank, void* const* re
   e->baseFlags = flags;
   e->algo = algo;
   e->grid = grid;
-  e->overlap = overlap && layout->L >= 2;
+  // overlap: 0 / 1 = one round at a time, n >= 2 = up to n rounds of this rank in flight (never more than the ring has slots)
+  e->nStreams = overlap >= 2 ? overlap : (overlap == 1 ? 2 : 0);
+  if (e->nStreams > layout->L) e->nStreams = layout->L;
+  if (e->nStreams > 8) e->nStreams = 8;
+  if (e->nStreams < 2) e->nStreams = 0;
   auto bail = [&](cudaError_t err, const char* step) {
     int rc = fail(AAR_ECUDA, "%s: %s: %s", what, step, cudaGetErrorString(err));
     destroyParts(e);
@@ -91,8 +95,8 @@ AAR_API int aar_engine_create(const AarLayout* layout, int rank, void* const* re
   e->devWords = static_cast<unsigned*>(d);
   e->p.doorbell = reinterpret_cast<const int*>(e->devWords);
   e->p.hostDone = e->devWords + 1;
-  if (e->overlap)
-    for (int i = 0; i < 2; ++i) {
+  if (e->nStreams)
+    for (int i = 0; i < e->nStreams; ++i) {
       err = cudaStreamCreateWithFlags(&e->streams[i], cudaStreamNonBlocking);
       if (err != cudaSuccess) return bail(err, "cudaStreamCreateWithFlags");
     }
@@ -119,6 +123,24 @@ AAR_API int aar_engine_tune(AarEngine* e, int split, int nvlsCtas) {
 }
 
 AAR_API int aar_engine_enqueue(AarEngine* e, int round, const void* input, void* output, int* outCounts, unsigned extraFlags, void* callerStream) {
+  return aar_engine_enqueue_ex(e, round, input, output, outCounts, extraFlags, callerStream, 0ull);
+}
+
+AAR_API int aar_engine_tune_bulk(AarEngine* e, int split) {
+  if (!e) return fail(AAR_EINVAL, "aar_engine_tune_bulk: null engine");
+  e->bulkSplit = split;
+  return AAR_OK;
+}
+
+// Round numbering that does not begin at 0 (a master resumed from a checkpoint): the completion word starts at `round`.
+AAR_API int aar_engine_start_at(AarEngine* e, int round) {
+  if (!e || round < 0) return fail(AAR_EINVAL, "aar_engine_start_at: bad argument");
+  static_cast<volatile unsigned*>(e->hostWords)[1] = (unsigned)round;
+  return AAR_OK;
+}
+
+AAR_API int aar_engine_enqueue_ex(AarEngine* e, int round, const void* input, void* output, int* outCounts, unsigned extraFlags, void* callerStream,
+                                  unsigned long long delayNs) {
   const char* what = "aar_engine_enqueue";
   if (!e || !input || !output) return fail(AAR_EINVAL, "%s: null argument", what);
   if (round < 0) return fail(AAR_EINVAL, "%s: round %d", what, round);
@@ -131,13 +153,17 @@ AAR_API int aar_engine_enqueue(AarEngine* e, int round, const void* input, void*
   p.output = output;
   p.outCounts = outCounts;
   p.flags = e->baseFlags | extraFlags;
-  if (e->overlap) {
-    run = e->streams[round & 1];
+  if (e->nStreams) {
+    run = e->streams[round % e->nStreams];
     AAR_CUDA(cudaEventRecord(e->inputReady, caller), "cudaEventRecord(input)");   // the input was produced on the caller's stream
     AAR_CUDA(cudaStreamWaitEvent(run, e->inputReady, 0), "cudaStreamWaitEvent(input)");
     p.flags |= AAR_FLAG_OVERLAPPED;
   }
   int rc;
+  if (delayNs) {  // straggler injection: this rank's round starts late
+    rc = aar_launch_delay(delayNs, run);
+    if (rc) return rc;
+  }
   switch (e->algo) {
     case 0:
       rc = aar_launch_round_fused(&p, &e->lay, e->grid, run);
@@ -148,8 +174,11 @@ AAR_API int aar_engine_enqueue(AarEngine* e, int round, const void* input, void*
     case 2:
       rc = aar_launch_oneshot(&p, &e->lay, 2, e->grid, run);
       break;
-    default:
+    case 3:
       rc = aar_launch_nvls(&p, &e->lay, 7 | (e->nvlsReduce << 8) | (e->nvlsStage << 16), e->grid, run);
+      break;
+    default:
+      rc = aar_launch_round_bulk(&p, &e->lay, e->algo == 5 ? 1 : 0, 7, e->grid, e->bulkSplit, run);
       break;
   }
   if (rc) return rc;

@@ -639,68 +639,6 @@ __global__ void __launch_bounds__(kThreads, 1) oneshotKernel(const AarRankParams
   if (phase == 1 || phase == 2) phaseOneshotReduce<T>(p, l, blockIdx.x, gridDim.x, sm);
 }
 
-// ------------------------------------------------------------------------------------------------ K7 persistent engine
-// A resident kernel driven by a doorbell instead of one launch per round: the host writes a
-// command {round, input, output, counts, flags} into a ring in pinned host memory and bumps its sequence word; CTA 0
-// polls that word across PCIe, republishes the command in device memory, and every CTA then runs the round (fused
-// two-shot or one-shot) and goes back to waiting.  Completion reaches the host through the same host-mapped word the
-// launched kernels use (K6).  What it buys is latency: no launch, no driver, ~2 us of doorbell instead of ~25 us.
-// Command entry: 16 x u32 = {seq, flags, round, exit, input lo/hi, output lo/hi, counts lo/hi, ...}; ring depth 8.
-constexpr int kCmdWords = 16, kCmdDepth = 8;
-
-template <typename T>
-__global__ void __launch_bounds__(kThreads, 1) persistentKernel(const AarRankParams p0, const AarLayout l, const uint32_t* hostRing, int algo) {
-  __shared__ Smem sm;
-  __shared__ uint32_t cmd[kCmdWords];
-  uint32_t* devRing = reinterpret_cast<uint32_t*>(regionOf(p0, p0.rank) + l.barrierOff);
-  for (uint32_t next = 0;; ++next) {
-    const uint32_t want = next + 1;
-    uint32_t* dev = devRing + (next % kCmdDepth) * kCmdWords;
-    if (threadIdx.x == 0) {
-      unsigned backoff = 32;
-      if (blockIdx.x == 0) {
-        const uint32_t* host = hostRing + (next % kCmdDepth) * kCmdWords;
-        while (ld_relaxed_sys_u32(host) != want) {
-          __nanosleep(backoff);
-          if (backoff < 2048) backoff *= 2;
-        }
-        __threadfence_system();
-        for (int i = 1; i < kCmdWords; ++i) dev[i] = ld_relaxed_sys_u32(host + i);
-        __threadfence();
-        asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(dev), "r"(want) : "memory");
-      } else {
-        uint32_t v;
-        do {
-          asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(dev) : "memory");
-          if (v != want) {
-            __nanosleep(backoff);
-            if (backoff < 1024) backoff *= 2;
-          }
-        } while (v != want);
-      }
-      for (int i = 0; i < kCmdWords; ++i) cmd[i] = (i == 0) ? want : __ldcg(dev + i);
-    }
-    __syncthreads();
-    if (cmd[3]) return;  // exit
-    AarRankParams p = p0;
-    p.flags = (p0.flags & ~(AAR_FLAG_FORCE | AAR_FLAG_SKIP_SCATTER)) | cmd[1];
-    p.round = (int)cmd[2];
-    p.input = reinterpret_cast<const void*>(((uint64_t)cmd[5] << 32) | cmd[4]);
-    p.output = reinterpret_cast<void*>(((uint64_t)cmd[7] << 32) | cmd[6]);
-    p.outCounts = reinterpret_cast<int*>(((uint64_t)cmd[9] << 32) | cmd[8]);
-    initSmem(sm);
-    if (algo == 1) {
-      phaseOneshotPush<T>(p, l, blockIdx.x, gridDim.x, sm);
-      phaseOneshotReduce<T>(p, l, blockIdx.x, gridDim.x, sm);
-    } else {
-      phaseScatter<T, false>(p, l, blockIdx.x, gridDim.x, sm);
-      phaseReduceBcast<T, false>(p, l, blockIdx.x, gridDim.x, sm);
-      phaseGather<T>(p, l, blockIdx.x, gridDim.x, sm);
-    }
-    __syncthreads();
-  }
-}
-
 __global__ void delayKernel(unsigned long long ns) {
   const unsigned long long t0 = globaltimer_ns();
   while (globaltimer_ns() - t0 < ns) __nanosleep(256);
@@ -781,25 +719,6 @@ AAR_API int aar_launch_round_pipelined(const AarRankParams* p, const AarLayout* 
   if (lay->dtype == AAR_F32) return launch(p2pPipelinedKernel<float>, p, lay, g, stream, what, sp);
   if (lay->dtype == AAR_BF16) return launch(p2pPipelinedKernel<__nv_bfloat16>, p, lay, g, stream, what, sp);
   return aar_host::fail(AAR_EINVAL, "%s: unknown dtype %d", what, lay->dtype);
-}
-
-// K7: start the resident engine on `stream` (it returns when a command with exit = 1 arrives).  algo 0 = fused two-shot,
-// 1 = one-shot.  hostRing: device pointer of the pinned command ring (8 entries x 16 u32).  grid must be co-resident.
-AAR_API int aar_launch_persistent(const AarRankParams* p, const AarLayout* lay, const void* hostRing, int algo, int grid, void* stream) {
-  const char* what = "aar_launch_persistent";
-  if (!p || !lay || !hostRing) return aar_host::fail(AAR_EINVAL, "%s: null argument", what);
-  if (algo == 1 && lay->oneshotOff == 0) return aar_host::fail(AAR_EINVAL, "%s: layout has no one-shot buffers", what);
-  if (p->rank < 0 || p->rank >= lay->P) return aar_host::fail(AAR_EINVAL, "%s: bad rank", what);
-  if (lay->dtype != AAR_F32 && lay->dtype != AAR_BF16) return aar_host::fail(AAR_EINVAL, "%s: unknown dtype", what);
-  int g = lay->dtype == AAR_F32 ? residentGrid(persistentKernel<float>, grid) : residentGrid(persistentKernel<__nv_bfloat16>, grid);
-  if (g <= 0) return aar_host::fail(AAR_ECUDA, "%s: occupancy query failed", what);
-  if (lay->dtype == AAR_F32)
-    persistentKernel<float><<<g, kThreads, 0, (cudaStream_t)stream>>>(*p, *lay, static_cast<const uint32_t*>(hostRing), algo);
-  else
-    persistentKernel<__nv_bfloat16><<<g, kThreads, 0, (cudaStream_t)stream>>>(*p, *lay, static_cast<const uint32_t*>(hostRing), algo);
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return aar_host::fail(AAR_ECUDA, "%s: launch failed: %s", what, cudaGetErrorString(e));
-  return AAR_OK;
 }
 
 AAR_API int aar_launch_oneshot(const AarRankParams* p, const AarLayout* lay, int phase, int grid, void* stream) {

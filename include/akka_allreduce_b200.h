@@ -141,11 +141,6 @@ int aar_launch_round_bulk(const AarRankParams* p, const AarLayout* lay, int algo
 /* 1 if aar_launch_round_bulk can run this geometry / these pointers */
 int aar_bulk_supported(const AarRankParams* p, const AarLayout* lay, int algo);
 
-/* K7 persistent round engine: one resident kernel per rank, driven through a command ring in pinned host memory
- * (8 entries x 16 u32: {seq, flags, round, exit, input lo/hi, output lo/hi, counts lo/hi}); the host writes an entry, then
- * its seq word (= command number + 1).  algo 0 = fused two-shot, 1 = one-shot.  Returns after launching; the kernel ends
- * when it reads a command with exit != 0.  Completion of each round is reported through p->hostDone as usual. */
-int aar_launch_persistent(const AarRankParams* p, const AarLayout* lay, const void* hostRing, int algo, int grid, void* stream);
 /* K5 one-shot: push the whole vector to every peer, then each rank sums the arrived set locally. Two phases so the
  * single-GPU emulation can order them; phase = 0 push, 1 reduce, 2 both. */
 int aar_launch_oneshot(const AarRankParams* p, const AarLayout* lay, int phase, int grid, void* stream);
@@ -206,18 +201,23 @@ int aar_enable_peer_access(int device, int peer);
 /* ---------------------------------------------------------------------------------------------------------------------
  * Native round engine: what parallel/engine.py does per round (order after the caller's stream, pick the kernel, launch,
  * record the slot's event; two internal streams so that consecutive rounds overlap) behind one C call, for C/C++ callers and
- * as a cheaper enqueue path for the Python engine (AAR_NATIVE_ENGINE=1).  Written without GPU access: opt-in, not used by
- * any default path yet.  algo: 0 two-shot fused, 1 pipelined P2P, 2 one-shot, 3 NVLS.  The engine owns its doorbell and
+ * as the enqueue path of the Python engine (AAR_NATIVE_ENGINE=0 switches back to the Python choreography).  algo: 0 two-shot fused, 1 pipelined P2P, 2 one-shot, 3 NVLS, 4 bulk P2P, 5 bulk NVLS.  The engine owns its doorbell and
  * completion words (pinned host memory); regions[] are the peers' regions as mapped here (AarRankParams.region). */
 typedef struct AarEngine AarEngine;
 int aar_engine_create(const AarLayout* layout, int rank, void* const* regions, void* mcRegion, int minRequired, int minChunksRequired,
                       unsigned flags, unsigned long long timeoutNs, int algo, int grid, int overlap, AarEngine** out);
+/* overlap: 0 = one round at a time on the caller's stream; 1 = two rounds in flight; n >= 2 = up to n (capped by the ring depth and 8) */
 /* knobs of the role-specialised kernels (0 keeps the default): split = nPush | nReduce << 16, nvlsCtas = nReduce | nStage << 8 */
 int aar_engine_tune(AarEngine* e, int split, int nvlsCtas);
 /* Launch round `round`: input / output / outCounts as in AarRankParams; extraFlags are OR-ed into the engine's flags for this
  * round (AAR_FLAG_FORCE, AAR_FLAG_SKIP_SCATTER).  callerStream: the stream that produced `input` (the round is ordered after
  * what it holds now).  With overlap the round runs on an internal stream; use aar_engine_wait before consuming the output. */
 int aar_engine_enqueue(AarEngine* e, int round, const void* input, void* output, int* outCounts, unsigned extraFlags, void* callerStream);
+/* The same with a straggler injector: the round starts `delayNs` late on this rank (0 = aar_engine_enqueue). */
+int aar_engine_enqueue_ex(AarEngine* e, int round, const void* input, void* output, int* outCounts, unsigned extraFlags, void* callerStream,
+                          unsigned long long delayNs);
+int aar_engine_tune_bulk(AarEngine* e, int split);            /* role split of the bulk kernels (algo 4 / 5), 0 = heuristic */
+int aar_engine_start_at(AarEngine* e, int round);             /* round numbering begins at `round` (resumed master) */
 int aar_engine_wait(AarEngine* e, int round, void* stream);   /* `stream` waits for the round (no host blocking) */
 int aar_engine_synchronize(AarEngine* e);                      /* host waits for every launched round */
 int aar_engine_set_doorbell(AarEngine* e, int newestRound);    /* StartAllreduce from the master: monotone */

@@ -89,7 +89,11 @@ def test_c_abi_structs_match_the_ctypes_declarations():
     # BASELINE.json config 2: the offsets the round-1 measurements ran with
     assert (lay.reduceOff, lay.stageOff, lay.sflagOff, lay.traceOff, lay.regionBytes) == (134217728, 268435456, 402653184, 402656768, 404750336)
     offs = [getattr(lay, f) for f, _ in L.AarLayout._fields_ if f.endswith("Off") and getattr(lay, f)]
-    assert len(set(offs)) == len(offs) and max(offs) == lay.egDecOff and lay.egDecOff + lay.L * lay.P * lay.C * 8 <= lay.regionBytes
+    # round 2 appended the piece flags of the bulk kernels behind the eager-gather decision words
+    assert len(set(offs)) == len(offs) and max(offs) == lay.pflagROff and lay.egDecOff < lay.pflagSOff < lay.pflagROff
+    assert lay.pflagSOff >= lay.egDecOff + lay.L * lay.P * lay.C * 8
+    assert lay.pflagROff + lay.L * lay.P * lay.C * lay.piecesPerChunk * 8 <= lay.regionBytes
+    assert (lay.tilesPerPiece, lay.piecesPerChunk) == (8, 16)
 
 
 def test_c_header_is_plain_c_and_the_native_engine_example_links(tmp_path):

@@ -284,30 +284,6 @@ def test_oneshot_threshold():
     assert torch.equal(outs[1], acc) and int(counts[1][0]) == 3
 
 
-def test_persistent_engine_single_rank_doorbell():
-    """K7 on one rank: the resident kernel picks rounds up from the host ring, runs them, reports completion, exits on command."""
-    from akka_allreduce_b200.parallel.engine import PersistentEngine, RoundEngine
-
-    n = 1 << 16
-    eng = RoundEngine.single_process(n, 1 << 12)
-    xs = [torch.randn(n, device="cuda:0") for _ in range(3)]
-    # Everything the loop below launches is used once up front: with lazy module loading the FIRST use of a kernel loads
-    # its module, which waits for the device to go idle -- and a resident kernel never lets it.
-    # (two DIFFERENT tensors: torch.equal(t, t) short-circuits on identity and launches nothing)
-    assert not torch.equal(xs[0], xs[1]) and torch.equal(xs[0], xs[0].clone()) and int(eng.counts[0].min()) == 0
-    torch.cuda.synchronize()   # inputs complete BEFORE the resident kernel starts: no device-wide sync while it runs
-    pe = PersistentEngine(eng, algo="twoshot", grid=8)
-    try:
-        for r in range(12):
-            out, counts = pe.post(r, xs[r % 3])
-            pe.wait(r, timeout_s=20)
-            assert torch.equal(out, xs[r % 3]) and int(counts.min()) == 1
-    finally:
-        pe.stop()
-    assert eng.rounds_flushed() == 12
-    eng.close()
-
-
 def test_device_ring_snapshot_restore(tmp_path):
     """Checkpoint of the device-resident ring: flags and payload of a rank survive save -> load -> restore into a fresh
     engine, which then continues the round numbering (the reference has no checkpointing)."""

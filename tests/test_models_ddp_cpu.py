@@ -62,9 +62,19 @@ class _FakeEngine:
     """Stands in for RoundEngine: 'averages' in place over `world` identical contributions and records what was asked of it."""
 
     def __init__(self, index, numel, chunk, log):
+        from types import SimpleNamespace
+
         self.index, self.numel, self.chunk, self.log = index, numel, chunk, log
         self.launches = 0
         self.closed = False
+        # what the masterless AllreduceWorker asks of its data plane
+        self.data_size, self.max_lag, self.layout = numel, 1, SimpleNamespace(L=2)
+        self.outputs = [None, None]
+        self.counts = [torch.full((4,), 2, dtype=torch.int32) for _ in range(2)]
+        self.doorbell = -1
+
+    def set_doorbell(self, r):
+        self.doorbell = max(self.doorbell, r)
 
     def enqueue_round(self, rnd, x, out=None):
         assert x.numel() == self.numel and out is x, "the bucket buffer is reduced in place"
@@ -80,9 +90,10 @@ class _FakeEngine:
 
 
 def test_threshold_ddp_bookkeeping_with_a_fake_data_plane():
-    """ThresholdDDP without a GPU (engine_factory): .grad tensors are views into the bucket buffers, a bucket is launched by the hook
-    of its LAST gradient (so early buckets go out while backward is still running), finish() waits for every bucket in order,
-    launches what a parameter without gradient left behind, hands the counts to the sink and re-arms the hooks."""
+    """ThresholdDDP without a GPU (engine_factory): .grad tensors are views into the bucket buffers, a bucket's AllreduceWorker is
+    started by the hook of its LAST gradient (so early buckets go out while backward is still running) and goes through the
+    worker contract (data_source -> round -> data_sink, CompleteAllreduce counted), finish() launches what a parameter without
+    gradient left behind, hands the counts to the sink and re-arms the hooks."""
     from akka_allreduce_b200.parallel.ddp import ThresholdDDP
 
     torch.manual_seed(0)
@@ -111,7 +122,8 @@ def test_threshold_ddp_bookkeeping_with_a_fake_data_plane():
         ddp.finish()
         enq = [i for k, i, _ in log if k == "enqueue"]
         assert sorted(enq) == list(range(len(ddp.buckets))), "every bucket exactly once per step (the one holding `unused` from finish())"
-        assert [i for k, i, _ in log if k == "wait"] == list(range(len(ddp.buckets)))
+        assert sorted(i for k, i, _ in log if k == "wait") == list(range(len(ddp.buckets))), "the stream waits for every bucket's round"
+        assert all(b.worker.node.completed == list(range(step + 1)) for b in ddp.buckets), "each bucket's worker completed every round, in order"
         assert ddp.step == step + 1
     assert len(sunk) == 2 * len(ddp.buckets) and all(c == 2 for _, _, c in sunk)
     # gradients really live in the buckets: what autograd accumulated is what the engine was handed
@@ -122,3 +134,47 @@ def test_threshold_ddp_bookkeeping_with_a_fake_data_plane():
     assert ddp.launches() == 2 * len(ddp.buckets)
     ddp.close()
     assert all(e.closed for e in engines)
+
+
+def test_threshold_ddp_survives_a_rebound_grad_and_refuses_a_second_backward():
+    """optimizer.zero_grad(set_to_none=True) -- the torch default -- detaches .grad from the bucket: the hook copies the fresh gradient
+    back into the bucket and re-attaches it (the round reduces the real gradient, not stale memory); a second backward() before
+    finish() is refused; under no_sync() it accumulates and finish() launches once."""
+    import pytest
+
+    from akka_allreduce_b200.parallel.ddp import ThresholdDDP
+
+    torch.manual_seed(1)
+    model = torch.nn.Sequential(torch.nn.Linear(8, 8), torch.nn.Tanh(), torch.nn.Linear(8, 2))
+    log = []
+    ddp = ThresholdDDP(model, 0, 2, torch.device("cpu"), bucket_mb=1.0, engine_factory=lambda i, n, c: _FakeEngine(i, n, c, log))
+    opt = torch.optim.SGD(model.parameters(), lr=0.1)
+    opt.zero_grad(set_to_none=True)                 # detaches every .grad from its bucket
+    assert all(p.grad is None for p in model.parameters())
+    x = torch.randn(5, 8)
+    model(x).square().mean().backward()
+    ddp.finish()
+    assert ddp.rebinds == len(list(model.parameters()))
+    for b in ddp.buckets:
+        for p in b.params:
+            assert p.grad.data_ptr() == b.views[id(p)].data_ptr() and torch.count_nonzero(p.grad) > 0
+        assert torch.count_nonzero(b.buffer) > 0, "the bucket holds the real gradient"
+    ddp.zero_grad()
+    model(x).square().mean().backward()
+    model(x).square().mean().backward()             # second backward before finish()
+    with pytest.raises(RuntimeError, match="second backward"):
+        ddp.finish()
+    ddp.close()
+    # gradient accumulation done right: all but the last micro-batch under no_sync()
+    model = torch.nn.Sequential(torch.nn.Linear(8, 8), torch.nn.Tanh(), torch.nn.Linear(8, 2))
+    ddp = ThresholdDDP(model, 0, 2, torch.device("cpu"), bucket_mb=1.0, engine_factory=lambda i, n, c: _FakeEngine(i, n, c, log))
+    ddp.zero_grad()
+    with ddp.no_sync():
+        model(x).square().mean().backward()
+        assert ddp.launches() == 0, "no round inside no_sync()"
+    g1 = model[0].weight.grad.clone()
+    model(x).square().mean().backward()
+    ddp.finish()
+    assert ddp.launches() == len(ddp.buckets)
+    assert torch.allclose(model[0].weight.grad, 2 * g1), "both micro-batches accumulated into the bucket before its round"
+    ddp.close()
