@@ -23,6 +23,7 @@ ap.add_argument("--chunks", default="1048576", help="maxChunkSize values (elemen
 ap.add_argument("--algos", default="auto,oneshot,twoshot,pipelined,nvls")
 ap.add_argument("--dtype", default="fp32")
 ap.add_argument("--grid", type=int, default=0, help="CTAs per launch (0 = one per SM)")
+ap.add_argument("--write-table", default="", help="JSON file to merge this sweep's winners into (akka_allreduce_b200/parallel/selector_table.json format)")
 a = ap.parse_args()
 rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
 lr = int(os.environ.get("LOCAL_RANK", rank))
@@ -116,5 +117,28 @@ for nbytes in [int(s) for s in a.sizes.split(",")]:
         print(json.dumps(row), flush=True)
 if rank == 0:
     print("SWEEP " + json.dumps({"world": world, "dtype": a.dtype, "rows": rows}))
+    if a.write_table:
+        # the selection table: for every measured size the fastest kernel family that verified; a row covers sizes up to the
+        # geometric mean with the next measured size (the last row covers everything above)
+        best = []
+        for row in rows:
+            cands = [(v["us"], k.split(":")[0]) for k, v in row.items() if isinstance(v, dict) and v.get("ok") and "us" in v and ":" not in k and k != "auto"]
+            if cands:
+                best.append((row["bytes"], min(cands)[1]))
+        table_rows = []
+        for i, (nb, algo) in enumerate(best):
+            hi = int((nb * best[i + 1][0]) ** 0.5) if i + 1 < len(best) else 1 << 40
+            if table_rows and table_rows[-1][1] == algo:
+                table_rows[-1][0] = hi
+            else:
+                table_rows.append([hi, algo, 0])
+        path = Path(a.write_table)
+        try:
+            table = json.loads(path.read_text())
+        except (OSError, ValueError):
+            table = {}
+        table.setdefault(str(world), {})[a.dtype] = table_rows
+        path.write_text(json.dumps(table, indent=1))
+        print("TABLE " + json.dumps({str(world): {a.dtype: table_rows}}))
 rdv.barrier()
 dist.destroy_process_group()

@@ -157,7 +157,8 @@ def api_case():
     def sink(out):
         xs = inputs_for(n, torch.float32, 5000 + out.iteration)
         want = ordered_sum(xs, list(range(world)), torch.float32)
-        ok = bool(torch.equal(out.data, want)) if worker.engine.algo != "nvls" else bool(torch.allclose(out.data, want, rtol=2e-5, atol=1e-4))
+        in_switch = worker.engine.algo in ("nvls", "nvls_bulk")   # the switch does not promise peer-index order
+        ok = bool(torch.allclose(out.data, want, rtol=2e-5, atol=1e-4)) if in_switch else bool(torch.equal(out.data, want))
         good[0] &= ok and int(out.count.min()) == world
         seen.append(out.iteration)
 

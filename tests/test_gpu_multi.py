@@ -25,5 +25,10 @@ def test_multi_gpu_suite(n):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}", "--master-addr", "127.0.0.1",
            "--master-port", str(29631 + n), str(ROOT / "tests" / "multi_gpu_worker.py")]
     p = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=900)
-    tail = "\n".join((p.stdout + p.stderr).splitlines()[-40:])
+    log = p.stdout + p.stderr
+    out_dir = ROOT / "gpurun_out"
+    if out_dir.is_dir():   # keep the whole log where the GPU runner brings it back from
+        (out_dir / f"multi_gpu_suite_{n}.log").write_text(log)
+    verdicts = [ln for ln in p.stdout.splitlines() if ln.startswith(("FAIL", "MULTI-GPU RESULT"))]
+    tail = "\n".join(verdicts + log.splitlines()[-25:])
     assert p.returncode == 0 and "ALL PASSED" in p.stdout, tail
