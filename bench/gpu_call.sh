@@ -1,3 +1,6 @@
 set -u
 mkdir -p gpurun_out
-timeout 400 python -m pytest tests/test_gpu_multi.py -x -q -m gpu -k "suite and 8" 2>&1 | tail -5
+python bench/ncu_target.py bulk 8 > gpurun_out/AB_plain.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:bulkRoundKernel -s 48 -c 27 -o gpurun_out/r2_ncu_bulk -f python bench/ncu_target.py bulk 8 > gpurun_out/AB_ncu.log 2>&1
+tail -3 gpurun_out/AB_plain.log gpurun_out/AB_ncu.log
+ls -la gpurun_out/*.ncu-rep

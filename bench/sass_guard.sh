@@ -1,20 +1,31 @@
 #!/bin/bash
-# Compares the opcode sequence of the DEFAULT kernel instantiations in the built library with the archived listings the round-1
-# measurements were taken with (profiles/sass/*.sass.gz).  Used when code is added next to the measured paths (opt-in template
-# variants) without GPU access: identical sequences = the measured paths compile unchanged.  No GPU needed (cuobjdump only).
+# SASS evidence for the built library, no GPU needed (cuobjdump only):
+#   * writes one gzip'd listing per kernel to profiles/sass/ (with --write) and a census of the mnemonics that matter;
+#   * checks what each kernel family must and must not contain:
+#       bulkRoundKernel<*, false>  UBLKCP.S.G + UBLKCP.G.S (cp.async.bulk both ways), SYNCS.*TRANS64 (mbarrier tx), no LDL / STL
+#       bulkRoundKernel<*, true>   the same + LDGMC (multimem.ld_reduce)
+#       nvlsPipelinedKernel        LDGMC
+# Exit code 1 if a check fails.
 cd "$(dirname "$0")/.." || exit 1
 LIB=akka_allreduce_b200/libaar_cuda.so
-ops() { grep -E "^\s+/\*[0-9a-f]{4,6}\*/" | sed -E 's#/\*[0-9a-f]+\*/##g' | awk '{print $1}'; }
-funcs=$(cuobjdump --dump-resource-usage $LIB 2>&1 | grep -o "Function [^:]*" | awk '{print $2}')
+WRITE=0; [ "${1:-}" == "--write" ] && WRITE=1
 rc=0
-for pair in "nvlsPipelinedKernel_f32:19nvlsPipelinedKernelIfLb0EEEv" "nvlsPipelinedKernel_bf16:19nvlsPipelinedKernelI13__nv_bfloat16Lb0EEEv" \
-            "roundKernel_f32:11roundKernelIfLb0ELb0EEEv" "roundKernel_bf16:11roundKernelI13__nv_bfloat16Lb0ELb0EEEv" \
-            "oneshotKernel_f32:13oneshotKernelIfEEv" "persistentKernel_f32:16persistentKernelIfEEv" "p2pPipelinedKernel_f32:18p2pPipelinedKernelIfLb0EEEv"; do
-  f=${pair%%:*}; k=${pair##*:}
-  fn=$(echo "$funcs" | grep "$k" | head -1)
-  if [ -z "$fn" ]; then echo "$f: no function matching $k in $LIB"; rc=1; continue; fi
-  now=$(cuobjdump -sass -fun "$fn" $LIB 2>/dev/null | ops)
-  arch=$(zcat profiles/sass/$f.sass.gz | ops)
-  if [ "$now" == "$arch" ]; then echo "$f: identical ($(echo "$now" | wc -l) instructions)"; else echo "$f: DIFFERS"; rc=1; fi
+census=profiles/r2_sass_census.txt
+[ $WRITE == 1 ] && { mkdir -p profiles/sass; : > $census; }
+funcs=$(cuobjdump --dump-resource-usage $LIB 2>&1 | grep -o "Function [^:]*" | awk '{print $2}')
+for fn in $funcs; do
+  name=$(echo "$fn" | c++filt | sed -E 's/^void //; s/\(anonymous namespace\):://; s/^<unnamed>:://; s/([A-Za-z0-9_]+)(<[^(]*>)?\(.*/\1\2/; s/\(bool\)//g; s/\(int\)//g; s/ //g; s/__nv_bfloat16/bf16/g')
+  sass=$(cuobjdump -sass -fun "$fn" $LIB 2>/dev/null)
+  count() { echo "$sass" | grep -c -E "^\s+/\*[0-9a-f]+\*/\s+(@!?U?P[0-9T] +)?$1"; }
+  line="$name: instr=$(echo "$sass" | grep -c -E '^\s+/\*[0-9a-f]{4,6}\*/') UBLKCP.S.G=$(count 'UBLKCP\.S\.G') UBLKCP.G.S=$(count 'UBLKCP\.G\.S') SYNCS=$(count 'SYNCS') LDGMC=$(count 'LDGMC') STG=$(count 'STG') LDG=$(count 'LDG\.') MEMBAR=$(count 'MEMBAR') ATOMG=$(count 'ATOMG') LDL=$(count 'LDL') STL=$(count 'STL')"
+  echo "$line"
+  [ $WRITE == 1 ] && { echo "$line" >> $census; echo "$sass" | gzip -9 > "profiles/sass/$(echo "$name" | tr '<>,' '___' | sed 's/_$//').sass.gz"; }
+  case "$name" in
+    bulkRoundKernel*)
+      for need in 'UBLKCP\.S\.G' 'UBLKCP\.G\.S' 'SYNCS.*TRANS64'; do [ "$(count "$need")" -gt 0 ] || { echo "  MISSING $need in $name"; rc=1; }; done
+      for bad in LDL STL; do [ "$(count "$bad")" -eq 0 ] || { echo "  SPILL ($bad) in $name"; rc=1; }; done
+      case "$name" in *true*) [ "$(count LDGMC)" -gt 0 ] || { echo "  MISSING LDGMC in $name"; rc=1; };; esac ;;
+    nvlsPipelinedKernel*) [ "$(count LDGMC)" -gt 0 ] || { echo "  MISSING LDGMC in $name"; rc=1; } ;;
+  esac
 done
 exit $rc
