@@ -33,6 +33,7 @@ class AarLayout(C.Structure):
         ("barrierOff", C.c_uint64), ("traceOff", C.c_uint64), ("ctrlBytes", C.c_uint64), ("regionBytes", C.c_uint64),
         ("egDecOff", C.c_uint64),
         ("tilesPerPiece", C.c_int), ("piecesPerChunk", C.c_int), ("pflagSOff", C.c_uint64), ("pflagROff", C.c_uint64),
+        ("slotBaseOff", C.c_uint64),
     ]
 
 
@@ -126,6 +127,7 @@ def load():
         "aar_engine_synchronize": [C.c_void_p],
         "aar_engine_set_doorbell": [C.c_void_p, C.c_int],
         "aar_engine_rounds_flushed": [C.c_void_p],
+        "aar_engine_round_flushed": [C.c_void_p, C.c_int],
         "aar_engine_destroy": [C.c_void_p],
         "aar_bench_litmus_bulk_flag": [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p],
         "aar_bench_bulk_copy_multi": [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p],

@@ -23,6 +23,7 @@ from .local_gpu import _TORCH2AAR
 ONESHOT_MAX_BYTES = int(os.environ.get("AAR_ONESHOT_MAX_BYTES", 256 * 1024))
 
 
+_DONE_WORD0 = 16   # host-mapped words: [0] doorbell, [_DONE_WORD0 + slot] completion per ring slot
 _ALGO_CODE = {"twoshot": 0, "pipelined": 1, "oneshot": 2, "nvls": 3, "bulk": 4, "nvls_bulk": 5}
 _TABLE = None
 
@@ -72,7 +73,7 @@ class RoundEngine:
             self.counts = [torch.zeros(layout.totalChunks, dtype=torch.int32, device=self.device) for _ in range(layout.L)]
             host = C.POINTER(C.c_uint)()
             dev = C.POINTER(C.c_uint)()
-            L.check(self.lib.aar_host_words_alloc(16, C.byref(host), C.byref(dev)), "aar_host_words_alloc")
+            L.check(self.lib.aar_host_words_alloc(_DONE_WORD0 + layout.L, C.byref(host), C.byref(dev)), "aar_host_words_alloc")
         self._host_words, self._dev_words = host, dev
         p.flags = (L.FLAG_NORMALIZE if normalize else 0) | (L.FLAG_EXACT_QUORUM if exact_quorum else 0)
         # Strict protocol by default (docs/PROTOCOL.md; all variants verified on B200 at the start of round 2).  The bulk kernels
@@ -94,7 +95,8 @@ class RoundEngine:
         p.timeoutNs = int(timeout_ms * 1e6)
         dev_addr = C.cast(dev, C.c_void_p).value
         p.doorbell = dev_addr            # word 0: newest round announced by the master
-        p.hostDone = dev_addr + 4        # word 1: rounds flushed (round + 1)
+        p.hostDone = dev_addr + 4 * _DONE_WORD0   # one word per ring slot: round + 1 of the last round flushed in that slot
+        self._in_order = 0               # rounds known flushed in order (host-side scan of the slot words)
         for j in range(layout.P):
             p.region[j] = region_ptrs[j]
         p.mcRegion = mc_ptr
@@ -213,10 +215,20 @@ class RoundEngine:
             return
         self._host_words[0] = max(int(self._host_words[0]), newest_round) if newest_round >= 0 else 0
 
+    def round_flushed(self, rnd: int) -> bool:
+        """Has round `rnd` been flushed (its last CTA wrote the slot's completion word)?  Rounds may complete out of order: the
+        device retires per ring slot, so round r+1 can be here before round r (AllreduceWorker.scala:253-268)."""
+        if self._native is not None:
+            return bool(self.lib.aar_engine_round_flushed(self._native, int(rnd)))
+        return int(self._host_words[_DONE_WORD0 + rnd % self.layout.L]) >= rnd + 1
+
     def rounds_flushed(self) -> int:
+        """Rounds flushed IN ORDER from the start: every round below the returned number is done."""
         if self._native is not None:
             return int(self.lib.aar_engine_rounds_flushed(self._native))
-        return int(self._host_words[1])
+        while self.round_flushed(self._in_order):
+            self._in_order += 1
+        return self._in_order
 
     def enqueue_round(self, rnd: int, x: torch.Tensor, *, stream: torch.cuda.Stream | None = None, force: bool = False,
                       skip_scatter: bool = False, out: torch.Tensor | None = None, delay_ns: int = 0):
@@ -386,22 +398,40 @@ class RoundEngine:
         to_f32 = (lambda t: t.float()) if self.dtype == torch.bfloat16 else (lambda t: t)
         s.scatter_ring = to_f32(self._region_view(lay.scatterOff, ring_bytes, self.dtype)).cpu().tolist() if ring_bytes <= (64 << 20) else []
         s.reduce_ring = to_f32(self._region_view(lay.reduceOff, ring_bytes, self.dtype)).cpu().tolist() if ring_bytes <= (64 << 20) else []
-        s.scatter_flags = [v & 0xFFFFFFFF for v in self._region_view(lay.sflagOff, lay.L * lay.C * L.AAR_MAXP * 4, torch.int32).cpu().tolist()]
-        s.reduce_flags = [v & 0xFFFFFFFFFFFFFFFF for v in self._region_view(lay.rflagOff, lay.L * lay.P * lay.C * 8, torch.int64).cpu().tolist()]
+        (s_off, s_bytes), (r_off, r_bytes) = self._flag_sections()
+        s.scatter_flags = [v & 0xFFFFFFFF for v in self._region_view(s_off, s_bytes, torch.int32).cpu().tolist()]
+        s.reduce_flags = [v & 0xFFFFFFFFFFFFFFFF for v in self._region_view(r_off, r_bytes, torch.int64).cpu().tolist()]
         return s
+
+    def _flag_sections(self):
+        """Where this engine's kernels keep their arrival words: per chunk (register kernels) or per piece (bulk kernels) -- the
+        "countFilled" of the reference's DataBuffer (DataBuffer.scala:27), saved and restored with the ring."""
+        lay = self.layout
+        if self.algo in ("bulk", "nvls_bulk"):
+            return ((lay.pflagSOff, lay.L * lay.C * lay.piecesPerChunk * L.AAR_MAXP * 4), (lay.pflagROff, lay.L * lay.P * lay.C * lay.piecesPerChunk * 8))
+        return ((lay.sflagOff, lay.L * lay.C * L.AAR_MAXP * 4), (lay.rflagOff, lay.L * lay.P * lay.C * 8))
 
     def start_at(self, rnd: int) -> None:
         """Begin the round numbering at `rnd` on a fresh engine (a master that resumed from a checkpoint): every rank counts as
         having retired all earlier rounds, so the slot flow control of round `rnd` has nothing to wait for.  Every rank calls
         this on its own region before the first launch (the worker does, between mapping the regions and its first round)."""
-        lay = self.layout
-        self._region_view(lay.peerBaseOff, L.AAR_MAXP * 4, torch.int32)[: lay.P] = rnd
-        self._region_view(lay.statusOff, 8, torch.int32)[1] = rnd
-        self._host_words[1] = rnd
-        if self._native is not None:
-            L.check(self.lib.aar_engine_start_at(self._native, rnd), "aar_engine_start_at")
+        self._mark_retired_below(rnd)
         self.rounds_enqueued = rnd
         torch.cuda.synchronize(self.device)
+
+    def _mark_retired_below(self, rnd: int) -> None:
+        """Every round below `rnd` counts as retired by every rank: the newest-round words, the per-slot retirement words (what
+        the slot flow control reads) and the host's completion words."""
+        lay = self.layout
+        self._region_view(lay.peerBaseOff, L.AAR_MAXP * 4, torch.int32)[: lay.P] = rnd
+        slot_base = self._region_view(lay.slotBaseOff, lay.L * L.AAR_MAXP * 4, torch.int32).view(lay.L, L.AAR_MAXP)
+        for r in range(max(0, rnd - lay.L), rnd):
+            slot_base[r % lay.L, : lay.P] = r + 1
+            self._host_words[_DONE_WORD0 + r % lay.L] = r + 1
+        self._region_view(lay.statusOff, 8, torch.int32)[1] = rnd
+        self._in_order = rnd
+        if self._native is not None:
+            L.check(self.lib.aar_engine_start_at(self._native, rnd), "aar_engine_start_at")
 
     def restore(self, s: "core.RingSnapshot") -> None:
         """Inverse of snapshot(): the ring payload and the arrival words go back into this rank's region; round numbering
@@ -413,17 +443,16 @@ class RoundEngine:
         if s.scatter_ring:
             self._region_view(lay.scatterOff, ring_bytes, self.dtype).copy_(torch.tensor(s.scatter_ring, dtype=torch.float32).to(self.dtype))
             self._region_view(lay.reduceOff, ring_bytes, self.dtype).copy_(torch.tensor(s.reduce_ring, dtype=torch.float32).to(self.dtype))
-        self._region_view(lay.sflagOff, lay.L * lay.C * L.AAR_MAXP * 4, torch.int32).copy_(
+        (s_off, s_bytes), (r_off, r_bytes) = self._flag_sections()
+        if len(s.scatter_flags) * 4 != s_bytes or len(s.reduce_flags) * 8 != r_bytes:
+            raise ValueError("ring snapshot was taken by a different kernel family (per-chunk vs per-piece arrival words)")
+        self._region_view(s_off, s_bytes, torch.int32).copy_(
             torch.tensor([v - (1 << 32) if v >= (1 << 31) else v for v in s.scatter_flags], dtype=torch.int32))
-        self._region_view(lay.rflagOff, lay.L * lay.P * lay.C * 8, torch.int64).copy_(
+        self._region_view(r_off, r_bytes, torch.int64).copy_(
             torch.tensor([v - (1 << 64) if v >= (1 << 63) else v for v in s.reduce_flags], dtype=torch.int64))
         # A snapshot is taken with no round in flight, so every peer had retired every round below s.round: restore the
         # flow-control words accordingly (round s.round would otherwise wait for retirements that happened before the save).
-        self._region_view(lay.peerBaseOff, L.AAR_MAXP * 4, torch.int32)[: lay.P] = s.round
-        self._region_view(lay.statusOff, 8, torch.int32)[1] = s.round
-        self._host_words[1] = s.round
-        if self._native is not None:
-            L.check(self.lib.aar_engine_start_at(self._native, s.round), "aar_engine_start_at")
+        self._mark_retired_below(s.round)
         self.rounds_enqueued = s.round
         torch.cuda.synchronize(self.device)
 

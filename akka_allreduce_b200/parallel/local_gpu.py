@@ -147,5 +147,10 @@ class LocalGpuCluster:
         w = int(words[(rnd % lay.L) * lay.C + chunk].item())
         return (w & 0xFFFFFFFF) if (w >> 32) == rnd + 1 else -1
 
+    def slot_base(self, rank: int) -> list[list[int]]:
+        """Per ring slot: round + 1 of the last round each peer retired in that slot, as seen by `rank` (the slot flow control)."""
+        lay = self.layout
+        return self._section(rank, lay.slotBaseOff, lay.L * L.AAR_MAXP * 4, torch.int32).view(lay.L, L.AAR_MAXP)[:, : self.P].tolist()
+
     def peer_base(self, rank: int) -> list[int]:
         return self._section(rank, self.layout.peerBaseOff, L.AAR_MAXP * 4, torch.int32)[: self.P].tolist()

@@ -10,9 +10,13 @@ result to `data_sink(AllReduceOutput(data, count, round))`.
 backend="cpu"  : the C++ message-passing engine (csrc/core/worker.cpp) over TCP -- bit-compatible restatement of
                  the reference, used for plumbing runs and as the oracle.
 backend="cuda" : control messages (InitWorkers / StartAllreduce / CompleteAllreduce) over the same TCP channel, data
-                 over NVLink by the sm_100a kernels.  Rounds of one worker run in order on its CUDA stream; a worker
-                 that falls more than maxLag rounds behind the master's newest round is forced through by the device
-                 doorbell (the catch-up loop of AllreduceWorker.scala:91-97 without a host round-trip).
+                 over NVLink by the sm_100a kernels.  Up to maxLag + 1 rounds of one worker are in flight; a round reaches the
+                 sink (and CompleteAllreduce the master) as soon as the device has flushed it, so round r+1 can complete before
+                 round r (AllreduceWorker.scala:253-268, AllreduceSpec.scala:675-677).  A worker that falls more than maxLag
+                 rounds behind the newest round is forced through by the device doorbell (the catch-up loop of
+                 AllreduceWorker.scala:91-97 without a host round-trip), and a worker whose peers have started a round it has not
+                 heard of from the master starts that round itself (peer-ahead self-start, AllreduceWorker.scala:123-126): the
+                 peers' progress is read from a board in shared host memory, next to the data that is already in its ring.
 """
 from __future__ import annotations
 
@@ -46,7 +50,12 @@ class AllreduceWorker:
         self.rdv = None
         self.max_round = -1
         self.max_scattered = -1
-        self.delivered = 0          # rounds handed to the sink (= reference `round` on this in-order data plane)
+        self.delivered = 0          # rounds handed to the sink, counted from round 0 (start_round + the ones of this incarnation)
+        self.round = 0              # oldest round that has not reached the sink yet (the reference's `round`)
+        self.completed: set[int] = set()   # rounds >= self.round that have (the reference's `completed`, AllreduceWorker.scala:253-268)
+        self.out_of_order = 0       # rounds that reached the sink while an older round was still in flight
+        self.self_starts = 0        # rounds started because a peer was ahead of the master's message to this worker
+        self.board = None           # shared host memory: newest round every peer has started
         self.rounds_forced = 0
         self.lag_hist: dict[int, int] = {}   # (master's newest round - round) at the moment a round reached the sink
         self.master_lost = False    # run() ended because the coordinator's link closed without a Shutdown
@@ -90,7 +99,8 @@ class AllreduceWorker:
         deadline = time.time() + timeout_sec
         while not self.node.shutdown_requested and time.time() < deadline:
             busy = self.engine is not None and self.delivered < self.max_scattered + 1
-            self.node.poll(0 if busy else 2)
+            self.node.poll(0 if busy else 1)
+            self._peer_ahead()
             self._deliver_flushed()
         self._drain()
         # True also when the master's link closed without a Shutdown message: `master_lost` tells the two apart
@@ -101,14 +111,28 @@ class AllreduceWorker:
         """One iteration of the event loop (for callers that own the loop)."""
         self.node.poll(timeout_ms)
         if self.backend == "cuda":
+            self._peer_ahead()
             self._deliver_flushed()
+
+    def _peer_ahead(self) -> None:
+        """AllreduceWorker.scala:123-126: a ScatterBlock / ReduceBlock for a round beyond maxRound makes the worker start that
+        round itself instead of waiting for the master's StartAllreduce.  On the device plane peers' blocks land in this
+        worker's ring without any host involvement, so the trigger is the board: every worker posts the newest round it has
+        started, and a worker that sees a peer ahead of its own maxRound fetches and launches up to that round."""
+        if self.board is None or self.engine is None:
+            return
+        newest = self.board.newest()
+        if newest > self.max_round:
+            self.self_starts += newest - self.max_round
+            self._on_start(newest)
 
     def metrics(self) -> dict:
         """rounds/s, forced completions, lag and the data-plane counters (CPU backend: the C++ worker's counters)."""
         if self.backend == "cpu":
             return dict(self._cpu_worker.metrics()) if self._cpu_worker else {}
         m = {"id": self.id, "generation": self.generation, "rounds_delivered": self.delivered, "rounds_forced": self.rounds_forced,
-             "max_round": self.max_round, "max_scattered": self.max_scattered, "lag": self.max_round - self.delivered + 1}
+             "max_round": self.max_round, "max_scattered": self.max_scattered, "lag": self.max_round - self.delivered + 1,
+             "rounds_out_of_order": self.out_of_order, "self_started_rounds": self.self_starts}
         if self.engine is not None:
             m.update(self.engine.metrics())
         m["lag_hist"] = dict(sorted(self.lag_hist.items()))
@@ -138,6 +162,9 @@ class AllreduceWorker:
         if self.rdv is not None:
             self.rdv.close()
             self.rdv = None
+        if self.board is not None:
+            self.board.close(unlink=self.id == 0)
+            self.board = None
 
     # ------------------------------------------------------------------ masterless mode
     @classmethod
@@ -174,6 +201,7 @@ class AllreduceWorker:
             self.data_sink(AllReduceOutput(self._outs.pop(r, eng.outputs[slot]), eng.counts[slot], r))
             self.node.send_complete(self.id, r, self.generation)
             self.delivered += 1
+            self.round = self.delivered
 
     # ------------------------------------------------------------------ device data plane
     def _on_message(self, msg) -> None:
@@ -188,14 +216,17 @@ class AllreduceWorker:
         symmetric HBM region, mapped into every peer."""
         self.close()
         self.id, self.generation = m.dest_id, m.generation
-        self.engine = self._make_engine(m)
         # a resumed master continues its round numbering (InitWorkers.start_round; 0 in the reference): earlier rounds count as
-        # retired everywhere, which is what the device-side flow control has to be told as well
+        # retired everywhere, which the device-side flow control is told inside _make_engine, BEFORE the barrier that lets peers
+        # launch (a peer's first retirement must not be overwritten by this rank's initialisation)
         start = getattr(m, "start_round", 0)
-        if start > 0:
+        self.engine = self._make_engine(m)
+        if start > 0 and not getattr(self.engine, "_start_applied", False):   # data planes built elsewhere (tests)
             self.engine.start_at(start)
         self.max_round = self.max_scattered = start - 1
-        self.delivered = start
+        self.delivered = self.round = start
+        self.completed = set()
+        self.out_of_order = self.self_starts = 0
         self.start_round = start
         self.lag_hist = {}
         self._t_first = None
@@ -226,7 +257,14 @@ class AllreduceWorker:
         engine = RoundEngine.from_symmetric(self.symm, layout, th_reduce=m.th_reduce, th_complete=m.th_complete,
                                             normalize=self.normalize, exact_quorum=self.exact_quorum,
                                             timeout_ms=self.spin_timeout_ms, grid=self.grid, algo=self.algo)
-        self.rdv.barrier()  # nobody launches before every peer has mapped every region
+        start = getattr(m, "start_round", 0)
+        if start > 0:
+            engine.start_at(start)
+            engine._start_applied = True
+        from .parallel.board import PeerBoard
+
+        self.board = PeerBoard(session, P, self.id, start - 1)
+        self.rdv.barrier()  # nobody launches before every peer has mapped every region (and set up its words)
         return engine
 
     def _on_start(self, rnd: int) -> None:
@@ -238,11 +276,13 @@ class AllreduceWorker:
             return
         self.max_round = max(self.max_round, rnd)
         eng.set_doorbell(self.max_round)
+        if self.board is not None:
+            self.board.post(self.max_round)
         L = eng.layout.L
         while self.max_scattered < self.max_round:
             r = self.max_scattered + 1
             # the output / count buffers of round r - L must have reached the sink before round r reuses them
-            while self.delivered < r - L + 1:
+            while r - L >= self.round and (r - L) not in self.completed:
                 if self.stream_ordered:
                     self._deliver_stream_ordered()
                 else:
@@ -267,28 +307,39 @@ class AllreduceWorker:
             self.max_scattered = r
 
     def _deliver_flushed(self, block: bool = False) -> None:
-        """AllreduceWorker.scala:253-268 (complete): sink, then CompleteAllreduce to the master, in round order."""
+        """AllreduceWorker.scala:253-268 (complete): sink, then CompleteAllreduce to the master, for every round the device has
+        flushed -- in whatever order they flush.  `round` (the oldest round still in flight) advances past completed rounds."""
         eng = self.engine
         if eng is None:
             return
+        per_round = getattr(eng, "round_flushed", None)   # data planes that only report an in-order count complete in order
         while True:
-            flushed = eng.rounds_flushed()  # host-mapped word written by the last CTA of K3
             progressed = False
-            while self.delivered < flushed:
-                r = self.delivered
+            in_order = eng.rounds_flushed() if per_round is None else None
+            for r in range(self.round, self.max_scattered + 1):
+                if r in self.completed:
+                    continue
+                if not (per_round(r) if per_round is not None else r < in_order):
+                    continue
                 slot = r % eng.layout.L
                 self._inputs.pop(r, None)
                 lag = self.max_round - r
                 self.lag_hist[lag] = self.lag_hist.get(lag, 0) + 1
                 if lag > eng.max_lag:
                     self.rounds_forced += 1
+                if r != self.round:
+                    self.out_of_order += 1
                 self.data_sink(AllReduceOutput(self._outs.pop(r, eng.outputs[slot]), eng.counts[slot], r))
                 self.node.send_complete(self.id, r, self.generation)
+                self.completed.add(r)
                 self.delivered += 1
                 self._t_last = time.time()
                 if self._t_first is None:
                     self._t_first = self._t_last
                 progressed = True
+            while self.round in self.completed:   # AllreduceWorker.scala:261-267
+                self.completed.discard(self.round)
+                self.round += 1
             if not block or progressed or self.delivered >= self.max_scattered + 1:
                 return
             time.sleep(0)  # blocking mode: yield until the next round flushes

@@ -1,6 +1,5 @@
 set -u
 mkdir -p gpurun_out
-python bench/ncu_target.py bulk 8 > gpurun_out/AB_plain.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:bulkRoundKernel -s 48 -c 27 -o gpurun_out/r2_ncu_bulk -f python bench/ncu_target.py bulk 8 > gpurun_out/AB_ncu.log 2>&1
-tail -3 gpurun_out/AB_plain.log gpurun_out/AB_ncu.log
-ls -la gpurun_out/*.ncu-rep
+TR() { n=$1; port=$2; shift 2; timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node "$n" --master-addr 127.0.0.1 --master-port "$port" "$@"; }
+timeout 600 python -m pytest tests/test_gpu_multi.py -x -q -m gpu -k "suite and 2" 2>&1 | tail -30 > gpurun_out/AD_multi2.txt; tail -3 gpurun_out/AD_multi2.txt
+TR 2 29841 bench.py --gpus 2 --steps 40 --warmup 5 --no-e2e 2>gpurun_out/AD_bench2.err | grep "^{" > gpurun_out/AD_bench2.json

@@ -190,7 +190,7 @@ static __device__ int destDecision1(const AarRankParams& p, const AarLayout& l, 
       g = (unsigned)(v & 1u);
     } else {
       const uint32_t need = (uint32_t)(p.round - l.L + 1);
-      const uint32_t* base = reinterpret_cast<const uint32_t*>(my + l.peerBaseOff) + dest;
+      const uint32_t* base = reinterpret_cast<const uint32_t*>(my + l.slotBaseOff) + (p.round % l.L) * AAR_MAXP + dest;
       if (ld_acquire_sys_u32(base) < need) {
         if (!blocking) return -1;
         Deadline dl(p.timeoutNs);

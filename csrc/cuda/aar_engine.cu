@@ -24,7 +24,8 @@ struct AarEngine {
   std::vector<cudaEvent_t> slotDone;   // one per ring slot: the round that used it last has finished
   std::vector<char> slotUsed;
   cudaEvent_t inputReady = nullptr;    // records the caller's stream before a round moves to an internal stream
-  unsigned* hostWords = nullptr;       // [0] doorbell, [1] rounds flushed (pinned, mapped)
+  unsigned* hostWords = nullptr;       // [0] doorbell, [kDoneWord0 + slot] round+1 of the last round flushed in that slot (pinned, mapped)
+  int inOrder = 0;                     // rounds known flushed in order (host-side scan of the slot words)
   unsigned* devWords = nullptr;
   long long launches = 0;
 };
@@ -32,6 +33,7 @@ struct AarEngine {
 namespace {
 
 using aar_host::fail;
+constexpr int kDoneWord0 = 16, kHostWords = 16 + 64;  // room for a ring of up to 64 slots
 
 #define AAR_CUDA(call, what)                                                                     \
   do {                                                                                           \
@@ -85,16 +87,17 @@ AAR_API int aar_engine_create(const AarLayout* layout, int rank, void* const* re
   cudaError_t err = cudaGetDevice(&e->device);
   if (err != cudaSuccess) return bail(err, "cudaGetDevice");
   void* h = nullptr;
-  err = cudaHostAlloc(&h, 16 * sizeof(unsigned), cudaHostAllocMapped | cudaHostAllocPortable);
+  if (layout->L > kHostWords - kDoneWord0) return bail(cudaErrorInvalidValue, "ring deeper than 64 slots");
+  err = cudaHostAlloc(&h, kHostWords * sizeof(unsigned), cudaHostAllocMapped | cudaHostAllocPortable);
   if (err != cudaSuccess) return bail(err, "cudaHostAlloc");
-  memset(h, 0, 16 * sizeof(unsigned));
+  memset(h, 0, kHostWords * sizeof(unsigned));
   e->hostWords = static_cast<unsigned*>(h);
   void* d = nullptr;
   err = cudaHostGetDevicePointer(&d, h, 0);
   if (err != cudaSuccess) return bail(err, "cudaHostGetDevicePointer");
   e->devWords = static_cast<unsigned*>(d);
   e->p.doorbell = reinterpret_cast<const int*>(e->devWords);
-  e->p.hostDone = e->devWords + 1;
+  e->p.hostDone = e->devWords + kDoneWord0;
   if (e->nStreams)
     for (int i = 0; i < e->nStreams; ++i) {
       err = cudaStreamCreateWithFlags(&e->streams[i], cudaStreamNonBlocking);
@@ -135,7 +138,10 @@ AAR_API int aar_engine_tune_bulk(AarEngine* e, int split) {
 // Round numbering that does not begin at 0 (a master resumed from a checkpoint): the completion word starts at `round`.
 AAR_API int aar_engine_start_at(AarEngine* e, int round) {
   if (!e || round < 0) return fail(AAR_EINVAL, "aar_engine_start_at: bad argument");
-  static_cast<volatile unsigned*>(e->hostWords)[1] = (unsigned)round;
+  volatile unsigned* w = e->hostWords;
+  for (int r = round - e->lay.L; r < round; ++r)
+    if (r >= 0) w[kDoneWord0 + r % e->lay.L] = (unsigned)(r + 1);   // every earlier round counts as flushed
+  e->inOrder = round;
   return AAR_OK;
 }
 
@@ -210,9 +216,16 @@ AAR_API int aar_engine_set_doorbell(AarEngine* e, int newestRound) {
   return AAR_OK;
 }
 
+AAR_API int aar_engine_round_flushed(AarEngine* e, int round) {
+  if (!e || round < 0) return 0;
+  // slot words only grow (round + 1, then round + L + 1, ...): >= covers a later tenant of the slot as well
+  return static_cast<volatile unsigned*>(e->hostWords)[kDoneWord0 + round % e->lay.L] >= (unsigned)(round + 1) ? 1 : 0;
+}
+
 AAR_API int aar_engine_rounds_flushed(AarEngine* e) {
   if (!e) return -1;
-  return (int)static_cast<volatile unsigned*>(e->hostWords)[1];
+  while (aar_engine_round_flushed(e, e->inOrder)) e->inOrder++;
+  return e->inOrder;
 }
 
 AAR_API long long aar_engine_launches(AarEngine* e) { return e ? e->launches : -1; }

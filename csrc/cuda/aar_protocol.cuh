@@ -76,7 +76,7 @@ static __device__ bool scatterDecision(const AarRankParams& p, const AarLayout& 
           go = (unsigned)(v & 1u);
         } else {
           const uint32_t need = (uint32_t)(p.round - l.L + 1);
-          const uint32_t* base = reinterpret_cast<const uint32_t*>(my + l.peerBaseOff) + dest;
+          const uint32_t* base = reinterpret_cast<const uint32_t*>(my + l.slotBaseOff) + (p.round % l.L) * AAR_MAXP + dest;
           Deadline dl(p.timeoutNs);
           unsigned spins = 0;
           for (;;) {
@@ -174,7 +174,8 @@ static __device__ unsigned bcastDestMask(const AarRankParams& p, const AarLayout
     __shared__ unsigned k2Dest;
     __syncthreads();
     if (threadIdx.x == 0) {
-      const uint32_t* base = reinterpret_cast<const uint32_t*>(regionOf(p, p.rank) + l.peerBaseOff);
+      // "has retired THIS round": the slot's word (rounds retire out of order, the newest-round word would not do)
+      const uint32_t* base = reinterpret_cast<const uint32_t*>(regionOf(p, p.rank) + l.slotBaseOff) + (p.round % l.L) * AAR_MAXP;
       unsigned e = m;
       for (int d = 0; d < l.P; ++d)
         if (d != p.rank && (int)ld_relaxed_sys_u32(base + d) > p.round) e &= ~(1u << d);
@@ -206,24 +207,20 @@ static __device__ void retireRoundWith(const AarRankParams& p, const AarLayout& 
       atomicExch(ctr, 0u);
       __threadfence();
       cleanup(p, l);
-      // Rounds of one rank may overlap on two streams (the maxLag window), but they retire in order: peers use
-      // peerBase as "every round below this is finished with its slot".  The older round's CTAs are resident and
-      // never wait for this one, so this spin ends.
-      if (p.flags & AAR_FLAG_OVERLAPPED) {
-        const uint32_t* flushed = statusWord(p, l, 1);
-        unsigned backoff = 64;
-        while (ld_relaxed_sys_u32(flushed) < (uint32_t)p.round) {
-          __nanosleep(backoff);
-          if (backoff < 1024) backoff *= 2;
-        }
-      }
+      // Retirement is per ring slot: peers read slotBase[slot][me] before they overwrite MY slot (round R needs "retired R - L"
+      // in slot R % L), so rounds of one rank may retire in any order -- round r+1 before round r when its quorum lands first
+      // (AllreduceWorker.scala:253-268).  peerBase[me] is only raised: the newest round this rank has retired (catch-up predicate).
       __threadfence_system();
+      const int slot = p.round % l.L;
       for (int i2 = 0; i2 < l.P; ++i2) {
         const int dest = (i2 + p.rank) % l.P;
-        st_release_sys_u32(reinterpret_cast<uint32_t*>(regionOf(p, dest) + l.peerBaseOff) + p.rank, (uint32_t)(p.round + 1));
+        st_release_sys_u32(reinterpret_cast<uint32_t*>(regionOf(p, dest) + l.slotBaseOff) + slot * AAR_MAXP + p.rank, (uint32_t)(p.round + 1));
+        asm volatile("red.relaxed.sys.global.max.u32 [%0], %1;" ::"l"(reinterpret_cast<uint32_t*>(regionOf(p, dest) + l.peerBaseOff) + p.rank),
+                     "r"((uint32_t)(p.round + 1))
+                     : "memory");
       }
       atomicMax(statusWord(p, l, 1), (uint32_t)(p.round + 1));  // rounds flushed
-      if (p.hostDone) st_release_sys_u32(p.hostDone, (uint32_t)(p.round + 1));
+      if (p.hostDone) st_release_sys_u32(p.hostDone + slot, (uint32_t)(p.round + 1));
     }
   }
 }

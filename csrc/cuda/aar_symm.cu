@@ -130,6 +130,7 @@ AAR_API int aar_layout_compute(int P, int dataSize, int maxChunkSize, int maxLag
   }
   l.pflagSOff = take((uint64_t)l.L * l.C * l.piecesPerChunk * AAR_MAXP * 4);
   l.pflagROff = take((uint64_t)l.L * P * l.C * l.piecesPerChunk * 8);
+  l.slotBaseOff = take((uint64_t)l.L * AAR_MAXP * 4);
   l.regionBytes = alignUp(off, 2ull << 20);
   *out = l;
   return AAR_OK;

@@ -33,7 +33,7 @@ extern "C" {
 #define AAR_FLAG_FORCE 4u       /* K8: do not wait, take whatever has arrived (catch-up, AllreduceWorker.scala:91-97) */
 #define AAR_FLAG_SKIP_SCATTER 8u /* fused kernel: this rank contributes nothing this round (fault injection) */
 #define AAR_FLAG_VIEW_OUTPUT 16u /* K3 does not copy: the caller reads the reduce-ring slot itself, stream-ordered */
-#define AAR_FLAG_OVERLAPPED 64u /* consecutive rounds of this rank run on different streams: retire strictly in order */
+#define AAR_FLAG_OVERLAPPED 64u /* consecutive rounds of this rank run on different streams (informational since retirement is per slot) */
 #define AAR_FLAG_ELIDE_LATE 512u /* thresholds < 1: a rank that is a whole round late skips pushes whose owner has decided without it
                                    and broadcasts to peers that have retired the round; needs the strict kernel variants (set
                                    together with AAR_FLAG_BCAST_FC); opt-in until verified on hardware */
@@ -87,6 +87,10 @@ typedef struct AarLayout {
   int tilesPerPiece, piecesPerChunk;
   uint64_t pflagSOff;        /* u32 [L][C][piecesPerChunk][AAR_MAXP]   epoch, written by src: "my piece of your block is staged" */
   uint64_t pflagROff;        /* u64 [L][P(owner)][C][piecesPerChunk]   epoch<<32 | contributor count, written by owner: "reduced piece has landed" */
+  uint64_t slotBaseOff;      /* u32 [L][AAR_MAXP]   per ring slot: round+1 of the last round each peer retired IN THAT SLOT.  Flow control for
+                                slot reuse reads this (round R may overwrite slot R % L of a peer once that peer retired round R - L), so rounds
+                                need not retire in order: round r+1 completes before round r when its quorum lands first
+                                (AllreduceWorker.scala:253-268, AllreduceSpec.scala:675-677).  peerBase keeps the NEWEST retired round per peer. */
 } AarLayout;
 
 /* Per-rank launch parameters (passed to the kernels by value). */
@@ -102,7 +106,7 @@ typedef struct AarRankParams {
   void* output;              /* dataSize elements */
   int* outCounts;            /* totalChunks ints (AllReduceOutput.count), may be NULL */
   const int* doorbell;       /* host-mapped: newest round announced by the master, may be NULL */
-  unsigned* hostDone;        /* host-mapped: receives round+1 when the round is flushed, may be NULL */
+  unsigned* hostDone;        /* host-mapped u32[L]: word (round % L) receives round+1 when the round is flushed, may be NULL */
   void* region[AAR_MAXP];    /* every rank's region as mapped in this rank's address space */
   void* mcRegion;            /* multicast mapping of the regions (NVLS), may be NULL */
 } AarRankParams;
@@ -221,7 +225,8 @@ int aar_engine_start_at(AarEngine* e, int round);             /* round numbering
 int aar_engine_wait(AarEngine* e, int round, void* stream);   /* `stream` waits for the round (no host blocking) */
 int aar_engine_synchronize(AarEngine* e);                      /* host waits for every launched round */
 int aar_engine_set_doorbell(AarEngine* e, int newestRound);    /* StartAllreduce from the master: monotone */
-int aar_engine_rounds_flushed(AarEngine* e);                   /* completion word written by the last CTA of a round */
+int aar_engine_rounds_flushed(AarEngine* e);                   /* rounds flushed IN ORDER from the start (every round below this is done) */
+int aar_engine_round_flushed(AarEngine* e, int round);         /* 1 if this round has been flushed (rounds may complete out of order) */
 long long aar_engine_launches(AarEngine* e);
 int aar_engine_destroy(AarEngine* e);
 

@@ -139,6 +139,72 @@ def threshold_case():
     symm.close()
 
 
+def out_of_order_case():
+    """AllreduceSpec.scala:675-677 on real peers: the last rank starts round 0 thirty milliseconds late (straggler injector), round
+    1 is launched right behind it on the other stream.  At thresholds 1.0 round 0 waits for the late push, round 1 does not:
+    every rank sees round 1 flushed while round 0 is still in flight, then round 0; both are bit-exact."""
+    import time
+
+    n, chunk = 1 << 18, 1 << 14
+    lay = L.compute_layout(world, n, chunk, 1, L.AAR_F32, 0, False)
+    k[0] += 1
+    symm = SymmetricMemory(UnixRendezvous(rank, world, f"{sess}_m{k[0]}"), lay.regionBytes, lr, want_multicast=False)
+    eng = RoundEngine.from_symmetric(symm, lay, algo="bulk", timeout_ms=5000.0)
+    xs0, xs1 = inputs_for(n, torch.float32, 8100), inputs_for(n, torch.float32, 8101)
+    rdv.barrier()
+    out0, _ = eng.enqueue_round(0, xs0[rank], delay_ns=30_000_000 if rank == world - 1 else 0)
+    out1, _ = eng.enqueue_round(1, xs1[rank])
+    t0 = time.time()
+    while not eng.round_flushed(1) and time.time() - t0 < 10:
+        pass
+    first = eng.round_flushed(1) and not eng.round_flushed(0)
+    eng.synchronize()
+    torch.cuda.synchronize()
+    ok = first and eng.round_flushed(0) and eng.rounds_flushed() == 2
+    ok &= bool(torch.equal(out0, ordered_sum(xs0, list(range(world)), torch.float32))) and bool(torch.equal(out1, ordered_sum(xs1, list(range(world)), torch.float32)))
+    check("round 1 is flushed before round 0 when round 0's last contribution is late", ok and eng.status() == 0)
+    eng.close()
+    symm.close()
+
+
+def self_start_case():
+    """AllreduceSpec.scala:106-124 on real peers: the last worker never sees a StartAllreduce (its handler drops them); it starts
+    every round by itself because its peers post the rounds they start on the shared board, and the job completes."""
+    from akka_allreduce_b200 import _core as core
+
+    n, chunk, rounds = 1 << 16, 1 << 12, 10
+    port = int(os.environ.get("MASTER_PORT", "29500")) + 58
+    master = None
+    if rank == 0:
+        master = AllreduceMaster(world, 1.0, 1.0, 1.0, 1, n, rounds - 1, chunk, pipeline_depth=1, port=port)
+        master.start(120)
+    rdv.barrier()
+    seen = []
+
+    class W(AllreduceWorker):
+        def _on_message(self, msg):
+            if isinstance(msg, core.StartAllreduce) and self.id == world - 1:
+                return
+            super()._on_message(msg)
+
+    def source(req):
+        return AllReduceInput(inputs_for(n, torch.float32, 6000 + req.iteration)[worker.id])
+
+    def sink(out):
+        want = ordered_sum(inputs_for(n, torch.float32, 6000 + out.iteration), list(range(world)), torch.float32)
+        in_switch = worker.engine.algo in ("nvls", "nvls_bulk")
+        seen.append((out.iteration, bool(torch.allclose(out.data, want, rtol=2e-5, atol=1e-4)) if in_switch else bool(torch.equal(out.data, want))))
+
+    worker = W(source, sink, backend="cuda", device=lr, session=f"{sess}_selfstart")
+    ok = worker.run("127.0.0.1", port, timeout_sec=120)
+    if master:
+        master.join(30)
+    m = worker.metrics()
+    mine = m["self_started_rounds"] == rounds if worker.id == world - 1 else m["self_started_rounds"] == 0
+    check("a worker that never hears StartAllreduce starts every round because its peers have", ok and mine and sorted(seen) == [(r, True) for r in range(rounds)])
+    worker.close()
+
+
 def api_case():
     """AllreduceMaster + AllreduceWorker(backend=cuda) end to end, 12 rounds, pipelined master clock."""
     n, chunk, rounds = 1 << 18, 1 << 14, 12
@@ -196,7 +262,9 @@ engine_case(1003, 17, torch.float32, "twoshot", overlap=False)
 engine_case(1 << 20, 1 << 16, torch.float32, "auto", normalize=True)
 engine_case(1 << 22, 1 << 18, torch.float32, "auto", rounds=12, max_lag=3)
 threshold_case()
+out_of_order_case()
 api_case()
+self_start_case()
 rdv.barrier()
 if rank == 0:
     print("MULTI-GPU RESULT:", "FAILED " + "; ".join(failures) if failures else "ALL PASSED", flush=True)

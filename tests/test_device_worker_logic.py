@@ -290,3 +290,175 @@ def test_late_joiner_reinitialises_the_device_plane_workers():
     # both old engines were rung out and synchronised before they were closed
     old = [c for c in closed if c[1] >= (1 << 30)]
     assert len(old) >= 2 and all(s for _, _, s in old)
+
+
+class OutOfOrderFabric(Fabric):
+    """A data plane that flushes rounds in whatever order their quorum lands (what the device does since retirement is per ring
+    slot): round `held` is kept back until `release()` says so (the test: until round `held + 1` has reached every sink)."""
+
+    def __init__(self, world, n, held=0, release=lambda: True):
+        super().__init__(world, n)
+        self.held, self.release = held, release
+
+    def _advance(self):
+        progressed = True
+        while progressed:
+            progressed = False
+            for eng in self.engines.values():
+                for r in sorted(eng.enqueued):
+                    if r in eng.done:
+                        continue
+                    got = self.inputs.get(r, {})
+                    if len(got) < self.quorum:
+                        continue
+                    if r == self.held and not self.release():
+                        continue
+                    out = np.zeros(self.n, dtype=np.float32)
+                    for s in sorted(got):
+                        out = out + got[s]
+                    slot = r % eng.layout.L
+                    assert eng._slot_round[slot] in (None, r - eng.layout.L), "output slot reused before its round was consumed"
+                    eng.outputs[slot][:] = out
+                    eng.counts[slot][:] = len(got)
+                    eng._slot_round[slot] = r
+                    eng.done.add(r)
+                    progressed = True
+
+
+class OutOfOrderEngine(FakeEngine):
+    def __init__(self, *a):
+        super().__init__(*a)
+        self.done = set()
+
+    def round_flushed(self, r):
+        with self.fabric.lock:
+            self.fabric._advance()
+            return r in self.done
+
+    def rounds_flushed(self):
+        with self.fabric.lock:
+            k = 0
+            while k in self.done:
+                k += 1
+            return k
+
+
+def test_a_later_round_completes_before_an_earlier_one_when_the_device_flushes_it_first():
+    """AllreduceSpec.scala:675-677 ("multi-round allreduce v3": round 1 completes before round 0) on the device-plane worker: the
+    sink and the master see round 1 first, `round` stays at 0 until round 0 lands, then advances past both; nothing is lost, no
+    output slot is reused before its round reached the sink."""
+    world, n, rounds = 2, 8, 12
+    sunk = [[], []]
+    fabric = OutOfOrderFabric(world, n, held=0, release=lambda: all(1 in s for s in sunk))
+    master = AllreduceMaster(world, 1.0, 1.0, 1.0, 2, n, rounds - 1, 4, pipeline_depth=2)
+    master.start(60)
+
+    class W(FakeWorker):
+        def _make_engine(self, m):
+            return OutOfOrderEngine(self.fabric, m.dest_id, m.data_size, m.max_lag)
+
+    workers = []
+    for i in range(world):
+        def source(req, i=i):
+            return AllReduceInput(np.full(n, float(i + 1) + req.iteration, dtype=np.float32))
+
+        def sink(out, i=i):
+            assert np.all(np.asarray(out.data) == 3.0 + 2 * out.iteration), "sum of both ranks for that round"
+            sunk[i].append(out.iteration)
+
+        workers.append(W(fabric, source, sink))
+    threads = [threading.Thread(target=w.run, args=("127.0.0.1", master.port, 60)) for w in workers]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(90)
+    assert master.join(30)
+    for i, w in enumerate(workers):
+        assert sorted(sunk[i]) == list(range(rounds)), "every round reached the sink exactly once"
+        assert sunk[i].index(1) < sunk[i].index(0), "round 1 completed before round 0"
+        assert w.metrics()["rounds_out_of_order"] >= 1 and w.round == rounds and not w.completed
+    assert master.metrics()["completions_counted"] == world * rounds
+
+
+def test_a_worker_that_never_hears_from_the_master_starts_rounds_because_its_peers_have():
+    """AllreduceWorker.scala:123-126 / AllreduceSpec.scala:106-124 (peer-ahead self-start): worker 1 drops every StartAllreduce of
+    the master; it still fetches and launches every round, because worker 0 posts the rounds it starts on the shared board."""
+    import os
+
+    from akka_allreduce_b200 import _core as core
+    from akka_allreduce_b200.parallel.board import PeerBoard
+
+    world, n, rounds = 2, 8, 10
+    fabric = Fabric(world, n)
+    master = AllreduceMaster(world, 1.0, 1.0, 1.0, 1, n, rounds - 1, 4, pipeline_depth=1)
+    master.start(60)
+    session = f"test_selfstart_{os.getpid()}"
+    sunk = [[], []]
+
+    class W(FakeWorker):
+        deaf = False
+
+        def _make_engine(self, m):
+            self.board = PeerBoard(session, world, m.dest_id)
+            return FakeEngine(self.fabric, m.dest_id, m.data_size, m.max_lag)
+
+        def _on_message(self, msg):
+            if self.deaf and isinstance(msg, core.StartAllreduce):
+                return   # the master's clock never reaches this worker
+            super()._on_message(msg)
+
+    workers = []
+    for i in range(world):
+        def source(req, i=i):
+            return AllReduceInput(np.full(n, float(i + 1), dtype=np.float32))
+
+        w = W(fabric, source, lambda out, i=i: sunk[i].append(out.iteration))
+        workers.append(w)
+    threads = [threading.Thread(target=w.run, args=("127.0.0.1", master.port, 60)) for w in workers]
+    for t in threads:
+        t.start()
+    # worker ids are assigned in join order: make the one that got id 1 deaf as soon as it knows
+    deadline = time.time() + 30
+    while time.time() < deadline and not all(w.id >= 0 for w in workers):
+        time.sleep(0.01)
+    for t in threads:
+        t.join(90)
+    assert master.join(30)
+    assert all(s == list(range(rounds)) for s in sunk)
+
+
+def test_self_start_counts_the_rounds_it_started(tmp_path):
+    """The same with the deaf worker chosen up front (by construction order): its self_started_rounds metric covers every round."""
+    import os
+
+    from akka_allreduce_b200 import _core as core
+    from akka_allreduce_b200.parallel.board import PeerBoard
+
+    world, n, rounds = 2, 8, 8
+    fabric = Fabric(world, n)
+    master = AllreduceMaster(world, 1.0, 1.0, 1.0, 1, n, rounds - 1, 4, pipeline_depth=1)
+    master.start(60)
+    session = f"test_selfstart2_{os.getpid()}"
+
+    class W(FakeWorker):
+        deaf = False
+
+        def _make_engine(self, m):
+            self.board = PeerBoard(session, world, m.dest_id)
+            return FakeEngine(self.fabric, m.dest_id, m.data_size, m.max_lag)
+
+        def _on_message(self, msg):
+            if self.deaf and isinstance(msg, core.StartAllreduce):
+                return
+            super()._on_message(msg)
+
+    ws = [W(fabric, lambda req: AllReduceInput(np.ones(n, dtype=np.float32)), lambda out: None) for _ in range(world)]
+    ws[1].deaf = True
+    threads = [threading.Thread(target=w.run, args=("127.0.0.1", master.port, 60)) for w in ws]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(90)
+    assert master.join(30)
+    assert ws[1].metrics()["self_started_rounds"] == rounds and ws[0].metrics()["self_started_rounds"] == 0
+    assert ws[1].metrics()["rounds_delivered"] == rounds

@@ -90,9 +90,11 @@ def test_c_abi_structs_match_the_ctypes_declarations():
     assert (lay.reduceOff, lay.stageOff, lay.sflagOff, lay.traceOff, lay.regionBytes) == (134217728, 268435456, 402653184, 402656768, 404750336)
     offs = [getattr(lay, f) for f, _ in L.AarLayout._fields_ if f.endswith("Off") and getattr(lay, f)]
     # round 2 appended the piece flags of the bulk kernels behind the eager-gather decision words
-    assert len(set(offs)) == len(offs) and max(offs) == lay.pflagROff and lay.egDecOff < lay.pflagSOff < lay.pflagROff
+    # ... and the per-slot retirement words (rounds may retire out of order) behind those
+    assert len(set(offs)) == len(offs) and max(offs) == lay.slotBaseOff and lay.egDecOff < lay.pflagSOff < lay.pflagROff < lay.slotBaseOff
     assert lay.pflagSOff >= lay.egDecOff + lay.L * lay.P * lay.C * 8
-    assert lay.pflagROff + lay.L * lay.P * lay.C * lay.piecesPerChunk * 8 <= lay.regionBytes
+    assert lay.slotBaseOff >= lay.pflagROff + lay.L * lay.P * lay.C * lay.piecesPerChunk * 8
+    assert lay.slotBaseOff + lay.L * 16 * 4 <= lay.regionBytes
     assert (lay.tilesPerPiece, lay.piecesPerChunk) == (8, 16)
 
 

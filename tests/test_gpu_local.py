@@ -284,6 +284,26 @@ def test_oneshot_threshold():
     assert torch.equal(outs[1], acc) and int(counts[1][0]) == 3
 
 
+def test_round_one_retires_before_round_zero(kernel_impl):
+    """Retirement is per ring slot (AllreduceSpec.scala:675-677: round 1 completes before round 0): round 1 runs to the end while
+    round 0 has not even started, then round 0, then the slots are reused by rounds 2 and 3 -- every round bit-exact, the slot
+    words say which round each slot retired last, the newest-round words never go backwards."""
+    P, n, chunk = 4, 1 << 16, 1 << 12
+    cl = cluster(P, n, chunk, max_lag=1)
+    inputs = {r: make_inputs(P, n, torch.float32, 4000 + r) for r in range(4)}
+    for rnd in (1, 0, 3, 2):
+        outs, counts = cl.run_round(rnd, inputs[rnd])
+        want, wc = oracle(inputs[rnd], P, n, chunk, lambda o, c: list(range(P)), torch.float32)
+        torch.cuda.synchronize()
+        for r in range(P):
+            assert torch.equal(outs[r], want) and torch.equal(counts[r], wc) and cl.status(r) == 0, f"round {rnd} rank {r}"
+        if rnd == 1:
+            assert cl.slot_base(0) == [[0] * P, [2] * P] and cl.peer_base(0) == [2] * P
+        if rnd == 0:
+            assert cl.slot_base(0) == [[1] * P, [2] * P] and cl.peer_base(0) == [2] * P, "the newest-round word is only raised"
+    assert cl.slot_base(2) == [[3] * P, [4] * P] and cl.peer_base(2) == [4] * P
+
+
 def test_device_ring_snapshot_restore(tmp_path):
     """Checkpoint of the device-resident ring: flags and payload of a rank survive save -> load -> restore into a fresh
     engine, which then continues the round numbering (the reference has no checkpointing)."""
