@@ -137,7 +137,10 @@ class RoundEngine:
         self._native = None
         with torch.cuda.device(self.device):
             self._streams = [torch.cuda.Stream(device=self.device) for _ in range(self.inflight)] if self.overlap else []
-            self._events = [torch.cuda.Event() for _ in range(layout.L)]
+            # one event per round in a ring of L + streams entries (see aar_engine.cu: what a later round or a consumer waits for)
+            self._ring = layout.L + max(1, self.inflight if self.overlap else 1)
+            self._events = [torch.cuda.Event() for _ in range(self._ring)]
+            self._event_round = [-1] * self._ring
             if os.environ.get("AAR_NATIVE_ENGINE", "1") not in ("", "0") and not self._nvtx:
                 regs = (C.c_void_p * layout.P)(*[region_ptrs[j] for j in range(layout.P)])
                 h = C.c_void_p(0)
@@ -278,7 +281,18 @@ class RoundEngine:
             stream = self._streams[rnd % self.inflight]
             stream.wait_stream(cur)          # x was produced on the caller's stream
             p.flags |= L.FLAG_OVERLAPPED
+            # every round <= rnd - L of this rank must be done before this one starts (retirement is per ring slot: nothing else
+            # keeps one stream from running ahead of the other, and the catch-up predicate relies on the window)
+            for k in range(1, self.inflight):
+                q = rnd - self.layout.L
+                while q >= 0 and q % self.inflight != (rnd + k) % self.inflight:
+                    q -= 1
+                if q >= 0 and self._event_round[q % self._ring] == q:
+                    stream.wait_event(self._events[q % self._ring])
         run_stream = stream or cur
+        q = rnd - self.layout.L           # the output / count buffers of this slot belong to round rnd - L until it is done
+        if q >= 0 and self._event_round[q % self._ring] == q:
+            run_stream.wait_event(self._events[q % self._ring])
         s = C.c_void_p(run_stream.cuda_stream)
         if self._nvtx:
             torch.cuda.nvtx.range_push(f"aar.round{rnd}.{self.algo}.slot{slot}")
@@ -308,7 +322,8 @@ class RoundEngine:
             L.check(self.lib.aar_launch_nvls(self._pref, self._lay, 7 | (self.nvls_reduce_ctas << 8) | (self.nvls_stage_ctas << 16), self.grid, s), "aar_launch_nvls")
         else:
             raise ValueError(f"unknown algo {self.algo}")
-        self._events[slot].record(run_stream)
+        self._events[rnd % self._ring].record(run_stream)
+        self._event_round[rnd % self._ring] = rnd
         if self._nvtx:
             torch.cuda.nvtx.range_pop()
         self.launches += 1
@@ -326,7 +341,7 @@ class RoundEngine:
         if self.algo not in ("nvls", "nvls_bulk") or not lay.stageOff:
             return None
         if rnd >= lay.L:
-            (stream or torch.cuda.current_stream(self.device)).wait_event(self._events[rnd % lay.L])
+            self.wait_round(rnd - lay.L, stream)
         V = 16 // lay.elemSize
         padded = (lay.dataSize + V - 1) // V * V
         off = lay.stageOff + (rnd % lay.L) * padded * lay.elemSize
@@ -338,15 +353,17 @@ class RoundEngine:
             st = stream or torch.cuda.current_stream(self.device)
             L.check(self.lib.aar_engine_wait(self._native, rnd, C.c_void_p(st.cuda_stream)), "aar_engine_wait")
             return
-        (stream or torch.cuda.current_stream(self.device)).wait_event(self._events[rnd % self.layout.L])
+        if self._event_round[rnd % self._ring] >= rnd:   # == rnd: its event; > rnd: a later round launched behind its completion
+            (stream or torch.cuda.current_stream(self.device)).wait_event(self._events[rnd % self._ring])
 
     def synchronize(self) -> None:
         """Host waits until every launched round of this rank has finished."""
         if self._native is not None:
             L.check(self.lib.aar_engine_synchronize(self._native), "aar_engine_synchronize")
             return
-        for ev in self._events:
-            ev.synchronize()
+        for ev, r in zip(self._events, self._event_round):
+            if r >= 0:
+                ev.synchronize()
 
     def wait_all(self, stream: torch.cuda.Stream | None = None) -> None:
         st = stream or torch.cuda.current_stream(self.device)
@@ -355,8 +372,9 @@ class RoundEngine:
                 if r >= 0:
                     L.check(self.lib.aar_engine_wait(self._native, r, C.c_void_p(st.cuda_stream)), "aar_engine_wait")
             return
-        for ev in self._events:
-            st.wait_event(ev)
+        for ev, r in zip(self._events, self._event_round):
+            if r >= 0:
+                st.wait_event(ev)
 
     def allreduce(self, x: torch.Tensor, rnd: int | None = None) -> torch.Tensor:
         """Convenience: one round, result tensor (stream-ordered)."""

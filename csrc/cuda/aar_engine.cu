@@ -21,8 +21,13 @@ struct AarEngine {
   int nStreams = 0;   // internal streams the rounds rotate over (0: rounds run on the caller's stream)
   int device = 0;
   cudaStream_t streams[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-  std::vector<cudaEvent_t> slotDone;   // one per ring slot: the round that used it last has finished
-  std::vector<char> slotUsed;
+  // One event per round in a ring of L + streams entries: what a later round, a consumer or synchronize() waits for.
+  // Round R is launched behind (a) the caller's stream, (b) round R - L (same output slot) and (c) EVERY round <= R - L of this
+  // rank: retirement is per ring slot, so nothing else keeps one stream from running ahead of the other, and a peer that sees
+  // round R retired must be able to conclude that no rank is still in a round <= R - L (the catch-up predicate relies on it).
+  std::vector<cudaEvent_t> slotDone;
+  std::vector<int> slotRound;          // round whose completion the event holds, -1 = none
+  int newest = -1;
   cudaEvent_t inputReady = nullptr;    // records the caller's stream before a round moves to an internal stream
   unsigned* hostWords = nullptr;       // [0] doorbell, [kDoneWord0 + slot] round+1 of the last round flushed in that slot (pinned, mapped)
   int inOrder = 0;                     // rounds known flushed in order (host-side scan of the slot words)
@@ -103,9 +108,10 @@ AAR_API int aar_engine_create(const AarLayout* layout, int rank, void* const* re
       err = cudaStreamCreateWithFlags(&e->streams[i], cudaStreamNonBlocking);
       if (err != cudaSuccess) return bail(err, "cudaStreamCreateWithFlags");
     }
-  e->slotDone.assign((size_t)layout->L, nullptr);
-  e->slotUsed.assign((size_t)layout->L, 0);
-  for (int s = 0; s < layout->L; ++s) {
+  const int ring = layout->L + (e->nStreams > 1 ? e->nStreams : 1);
+  e->slotDone.assign((size_t)ring, nullptr);
+  e->slotRound.assign((size_t)ring, -1);
+  for (int s = 0; s < ring; ++s) {
     err = cudaEventCreateWithFlags(&e->slotDone[(size_t)s], cudaEventDisableTiming);
     if (err != cudaSuccess) return bail(err, "cudaEventCreateWithFlags");
   }
@@ -150,7 +156,7 @@ AAR_API int aar_engine_enqueue_ex(AarEngine* e, int round, const void* input, vo
   const char* what = "aar_engine_enqueue";
   if (!e || !input || !output) return fail(AAR_EINVAL, "%s: null argument", what);
   if (round < 0) return fail(AAR_EINVAL, "%s: round %d", what, round);
-  const int slot = round % e->lay.L;
+  const int ring = (int)e->slotDone.size();
   cudaStream_t caller = static_cast<cudaStream_t>(callerStream);
   cudaStream_t run = caller;
   AarRankParams p = e->p;  // by value: the launchers copy it into the kernel parameters before they return
@@ -164,6 +170,19 @@ AAR_API int aar_engine_enqueue_ex(AarEngine* e, int round, const void* input, vo
     AAR_CUDA(cudaEventRecord(e->inputReady, caller), "cudaEventRecord(input)");   // the input was produced on the caller's stream
     AAR_CUDA(cudaStreamWaitEvent(run, e->inputReady, 0), "cudaStreamWaitEvent(input)");
     p.flags |= AAR_FLAG_OVERLAPPED;
+    // every round <= R - L of this rank must be done: one wait per other stream, on that stream's newest such round (the
+    // round's own stream is in order already)
+    for (int s = 1; s < e->nStreams; ++s) {
+      int q = round - e->lay.L;
+      while (q >= 0 && q % e->nStreams != (round + s) % e->nStreams) --q;
+      if (q >= 0 && e->slotRound[(size_t)(q % ring)] == q)
+        AAR_CUDA(cudaStreamWaitEvent(run, e->slotDone[(size_t)(q % ring)], 0), "cudaStreamWaitEvent(window)");
+    }
+  }
+  {  // the output / count buffers of this slot belong to round R - L until it is done
+    const int q = round - e->lay.L;
+    if (q >= 0 && e->slotRound[(size_t)(q % ring)] == q)
+      AAR_CUDA(cudaStreamWaitEvent(run, e->slotDone[(size_t)(q % ring)], 0), "cudaStreamWaitEvent(slot)");
   }
   int rc;
   if (delayNs) {  // straggler injection: this rank's round starts late
@@ -188,24 +207,26 @@ AAR_API int aar_engine_enqueue_ex(AarEngine* e, int round, const void* input, vo
       break;
   }
   if (rc) return rc;
-  AAR_CUDA(cudaEventRecord(e->slotDone[(size_t)slot], run), "cudaEventRecord(slot)");
-  e->slotUsed[(size_t)slot] = 1;
+  AAR_CUDA(cudaEventRecord(e->slotDone[(size_t)(round % ring)], run), "cudaEventRecord(round)");
+  e->slotRound[(size_t)(round % ring)] = round;
+  if (round > e->newest) e->newest = round;
   e->launches++;
   return AAR_OK;
 }
 
 AAR_API int aar_engine_wait(AarEngine* e, int round, void* stream) {
   if (!e || round < 0) return fail(AAR_EINVAL, "aar_engine_wait: bad argument");
-  const size_t slot = (size_t)(round % e->lay.L);
-  if (!e->slotUsed[slot]) return AAR_OK;  // nothing was launched into this slot yet
-  AAR_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), e->slotDone[slot], 0), "cudaStreamWaitEvent(slot)");
+  const size_t at = (size_t)(round % (int)e->slotDone.size());
+  if (e->slotRound[at] < round) return AAR_OK;  // not launched (yet)
+  // == round: that round's event.  > round: the entry was reused by a later round, which was launched behind this one's completion
+  AAR_CUDA(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), e->slotDone[at], 0), "cudaStreamWaitEvent(round)");
   return AAR_OK;
 }
 
 AAR_API int aar_engine_synchronize(AarEngine* e) {
   if (!e) return fail(AAR_EINVAL, "aar_engine_synchronize: null engine");
   for (size_t s = 0; s < e->slotDone.size(); ++s)
-    if (e->slotUsed[s]) AAR_CUDA(cudaEventSynchronize(e->slotDone[s]), "cudaEventSynchronize");
+    if (e->slotRound[s] >= 0) AAR_CUDA(cudaEventSynchronize(e->slotDone[s]), "cudaEventSynchronize");
   return AAR_OK;
 }
 
@@ -236,7 +257,7 @@ AAR_API int aar_engine_destroy(AarEngine* e) {
   if (!e) return AAR_OK;
   static_cast<volatile unsigned*>(e->hostWords)[0] = 1u << 30;
   for (size_t s = 0; s < e->slotDone.size(); ++s)
-    if (e->slotUsed[s]) cudaEventSynchronize(e->slotDone[s]);
+    if (e->slotRound[s] >= 0) cudaEventSynchronize(e->slotDone[s]);
   destroyParts(e);
   delete e;
   return AAR_OK;

@@ -79,7 +79,9 @@ struct Region {
   std::vector<std::atomic<uint32_t>> osflag;          // [L][P]
   std::vector<std::atomic<uint32_t>> sflag;           // [L][C][P]
   std::vector<std::atomic<uint64_t>> rflag;           // [L][P][C]
-  std::vector<std::atomic<uint32_t>> peerBase;        // [P]
+  std::vector<std::atomic<uint32_t>> peerBase;        // [P]     newest round each peer has retired (+1): catch-up predicate only
+  std::vector<std::atomic<uint32_t>> slotBase;        // [L][P]  per ring slot: round + 1 of the last round each peer retired there (flow control)
+  std::vector<std::atomic<uint32_t>> slotFlushed;     // [L]     this rank's completion word per slot (what the host polls)
   std::vector<std::atomic<uint32_t>> k1Ctr;           // [L][P][C]
   std::vector<std::atomic<uint64_t>> k1Dec;           // [L][P]   epoch << 32 | go
   std::vector<std::atomic<uint64_t>> egDec;           // [L][P*C] epoch << 32 | (count + 1), 0 = abandoned   (eager gather)
@@ -95,7 +97,7 @@ struct Region {
   explicit Region(const Config& c)
       : scatter((size_t)c.L * c.P * c.blockLen()), reduce((size_t)c.L * c.P * c.blockLen()), stage((size_t)c.L * c.dataSize()),
         oneshot(c.oneshot ? (size_t)c.L * c.P * c.dataSize() : 0), osflag((size_t)c.L * c.P), sflag((size_t)c.L * c.C * c.P),
-        rflag((size_t)c.L * c.P * c.C), peerBase(c.P), k1Ctr((size_t)c.L * c.P * c.C), k1Dec((size_t)c.L * c.P),
+        rflag((size_t)c.L * c.P * c.C), peerBase(c.P), slotBase((size_t)c.L * c.P), slotFlushed(c.L), k1Ctr((size_t)c.L * c.P * c.C), k1Dec((size_t)c.L * c.P),
         egDec((size_t)c.L * c.P * c.C), k2Dec((size_t)c.L * c.C), k2Ctr((size_t)c.L * c.C),
         k3Dec(c.L), k3Ctr(c.L), counts((size_t)c.L * c.P * c.C), consumed(c.L), output(c.L, std::vector<float>(c.dataSize())),
         outCounts(c.L, std::vector<int>(c.P * c.C)) {
@@ -139,7 +141,7 @@ bool scatterDecision(World& w, int rank, int round, int dest) {
   if ((v >> 32) == epoch) return v & 1;
   uint64_t go = 1;
   int spins = 0;
-  while ((int)my.peerBase[dest].load(std::memory_order_acquire) < round - c.L + 1) {
+  while ((int)my.slotBase[(size_t)(round % c.L) * c.P + dest].load(std::memory_order_acquire) < round - c.L + 1) {
     if ((++spins & 63) == 0 && (forced(w, rank, round) || spins > c.spinBudget)) {
       go = 0;  // the peer fell out of the window: its copy of this contribution is dropped
       w.drops++;
@@ -266,7 +268,7 @@ void phaseReduce(World& w, int rank, int round, int cta, int nctas, std::mt19937
   // Late-work elision: a destination that has already retired this round will never gather this chunk
   if (c.elide && cta < (long)c.C * c.S)
     for (int d = 0; d < c.P; ++d)
-      if (d != rank && (int)my.peerBase[d].load(std::memory_order_acquire) > round && (destMask >> d & 1)) {
+      if (d != rank && (int)my.slotBase[(size_t)(round % c.L) * c.P + d].load(std::memory_order_acquire) > round && (destMask >> d & 1)) {
         destMask &= ~(1u << d);
         w.elidedBcasts++;
       }
@@ -491,16 +493,25 @@ void verifyOneshot(World& w, int rank, int round) {
   }
 }
 
-// K6: last CTA of the kernel retires the slot; with two rounds in flight retirement stays in order
+// K6: last CTA of the kernel retires the slot.  Retirement is per ring slot (peers' flow control reads slotBase[slot][me]), so
+// with two rounds in flight round r+1 may retire before round r; peerBase[me] is only raised
 void retire(World& w, int rank, int round, int nctas) {
   const Config& c = w.cfg;
   Region& my = *w.region[rank];
   std::atomic<uint32_t>& ctr = my.k3Ctr[round % c.L];
   if (ctr.fetch_add(1, std::memory_order_acq_rel) + 1 == (uint32_t)nctas) {
     ctr.store(0, std::memory_order_relaxed);
-    while ((int)my.flushed.load(std::memory_order_acquire) < round) std::this_thread::yield();
-    for (int i = 0; i < c.P; ++i) w.region[(i + rank) % c.P]->peerBase[rank].store((uint32_t)round + 1, std::memory_order_release);
-    my.flushed.store((uint32_t)round + 1, std::memory_order_release);
+    for (int i = 0; i < c.P; ++i) {
+      Region& peer = *w.region[(i + rank) % c.P];
+      peer.slotBase[(size_t)(round % c.L) * c.P + rank].store((uint32_t)round + 1, std::memory_order_release);
+      uint32_t cur = peer.peerBase[rank].load(std::memory_order_relaxed);
+      while (cur < (uint32_t)round + 1 && !peer.peerBase[rank].compare_exchange_weak(cur, (uint32_t)round + 1, std::memory_order_relaxed)) {
+      }
+    }
+    my.slotFlushed[round % c.L].store((uint32_t)round + 1, std::memory_order_release);
+    uint32_t f = my.flushed.load(std::memory_order_relaxed);
+    while (f < (uint32_t)round + 1 && !my.flushed.compare_exchange_weak(f, (uint32_t)round + 1, std::memory_order_release)) {
+    }
   }
 }
 
@@ -572,6 +583,11 @@ int main(int argc, char** argv) {
             // the worker launches round R only after the sink has consumed round R - L (same output / count buffers)
             if (round >= cf.L)
               while (w.region[rank]->consumed[round % cf.L].load(std::memory_order_acquire) != round - cf.L) std::this_thread::yield();
+            // ... and only after EVERY round up to R - L of this rank has been flushed (the engine makes round R's stream wait for
+            // them): with per-slot retirement nothing else keeps one stream from running arbitrarily far ahead of the other, and
+            // a peer that sees round R retired must be able to conclude that nobody is still in a round <= R - L
+            for (int q = round - cf.L; q > round - 2 * cf.L && q >= 0; --q)
+              while ((int)w.region[rank]->slotFlushed[q % cf.L].load(std::memory_order_acquire) < q + 1) std::this_thread::yield();
             if (rank == (round % cf.P) && (rng() % 3 == 0)) std::this_thread::sleep_for(std::chrono::microseconds(300));  // straggler
             if (cf.lagger && rank == 0 && cta == 0) std::this_thread::sleep_for(std::chrono::microseconds(1500 + rng() % 2000));
             if (cf.oneshot) {
@@ -585,7 +601,7 @@ int main(int argc, char** argv) {
             b->wait();  // kernel boundary: the stream's next kernel starts when every CTA of this one is done
             if (cta == 0) {
               // host side: wait for the completion word, then consume this round's output slot before it is reused
-              while ((int)w.region[rank]->flushed.load(std::memory_order_acquire) < round + 1) std::this_thread::yield();
+              while ((int)w.region[rank]->slotFlushed[round % cf.L].load(std::memory_order_acquire) < round + 1) std::this_thread::yield();
               if (cf.oneshot) verifyOneshot(w, rank, round);
               else verifyRound(w, rank, round);
               w.region[rank]->consumed[round % cf.L].store(round, std::memory_order_release);
