@@ -39,7 +39,24 @@ class UnixRendezvous:
             while len(by_rank) < world - 1:
                 c, _ = srv.accept()
                 c.settimeout(timeout)
-                (r,) = struct.unpack("i", self._recvn(c, 4))
+                # The abstract socket namespace has no file permissions, and whoever completes this rendezvous receives the
+                # file descriptors of this job's device memory: only a process of the same user (or root) may take part, and
+                # only with a rank that exists and has not been claimed.
+                try:
+                    _pid, uid, _gid = struct.unpack("3i", c.getsockopt(socket.SOL_SOCKET, socket.SO_PEERCRED, struct.calcsize("3i")))
+                except OSError:
+                    uid = None
+                if uid is None or uid not in (os.getuid(), 0):
+                    c.close()
+                    continue
+                try:
+                    (r,) = struct.unpack("i", self._recvn(c, 4))
+                except (ConnectionError, socket.timeout, OSError):
+                    c.close()
+                    continue
+                if not (1 <= r < world) or r in by_rank:
+                    c.close()   # out-of-range or duplicate rank: not one of ours
+                    continue
                 by_rank[r] = c
             self.conns = [by_rank[r] for r in range(1, world)]
             srv.close()

@@ -5,6 +5,7 @@
 // ReduceBlock never exist as messages (they are NVLink stores + release flags); they are
 // materialised only by the CPU engine, which doubles as oracle and timed CPU baseline.
 #pragma once
+#include <stdexcept>
 #include <cstdint>
 #include <map>
 #include <string>
@@ -12,6 +13,15 @@
 #include <vector>
 
 namespace aar {
+
+// A well-formed frame whose CONTENT violates the protocol and that came from a peer: ids or sizes outside the geometry, a round
+// absurdly far ahead.  Its own type so that a transport can drop the offending link instead of letting one bogus frame end the
+// process; errors that are this worker's own (the data source returning the wrong size, AllreduceWorker.scala:174-176) stay
+// ordinary exceptions and propagate.
+struct ProtocolError : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+
 
 // Opaque address of an actor inside a transport (index into its routing table).
 using Address = int64_t;

@@ -734,6 +734,9 @@ int WorkerNode::poll(int timeoutMs) {
       } catch (const WireError& e) {
         AAR_WARN("worker: protocol error on a peer link: %s", e.what());
         alive = false;
+      } catch (const ProtocolError& e) {  // well-formed frame, impossible content: that peer's link goes, this worker stays
+        AAR_WARN("worker: peer sent an impossible message, dropping its link: %s", e.what());
+        alive = false;
       }
       if (!alive) deadIn.push_back(k);
     }

@@ -114,9 +114,18 @@ void Worker::onStart(const StartAllreduce& m) {
   for (auto it = completed_.begin(); it != completed_.end();) it = (*it < round_) ? completed_.erase(it) : std::next(it);
 }
 
+// How far ahead of this worker's newest round a peer's block may be: the master is never more than maxLag + 1 rounds ahead of a
+// quorum, so a peer cannot legitimately be further ahead than a few windows.
+static constexpr long long kMaxPeerAhead = 1 << 16;
+
 // AllreduceWorker.scala:106-127
 void Worker::onScatter(const ScatterBlock& s) {
-  if (s.destId != id_) throw std::runtime_error("ScatterBlock delivered to the wrong worker");
+  // Everything a peer controls is checked BEFORE the frame can make this worker do anything (the self-start below fetches and
+  // scatters every round up to s.round): a bogus frame costs its sender the link, not this worker hours of catch-up.
+  if (s.destId != id_) throw ProtocolError("ScatterBlock delivered to the wrong worker");
+  if (s.srcId < 0 || s.srcId >= geo_.P || s.chunkId < 0 || s.chunkId >= geo_.numChunks(id_)) throw ProtocolError("ScatterBlock: bad srcId/chunkId");
+  if ((int)s.value.size() > geo_.chunkLen(id_, s.chunkId)) throw ProtocolError("ScatterBlock: chunk larger than its slot");
+  if (s.round < 0 || (long long)s.round - maxRound_ > kMaxPeerAhead) throw ProtocolError("ScatterBlock: round " + std::to_string(s.round) + " is out of range");
   metrics_.scatterReceived++;
   if (s.round < round_ || completed_.count(s.round)) {
     metrics_.staleDrops++;
@@ -130,9 +139,6 @@ void Worker::onScatter(const ScatterBlock& s) {
       return;
     }
   }
-  if (s.srcId < 0 || s.srcId >= geo_.P || s.chunkId < 0 || s.chunkId >= geo_.numChunks(id_))
-    throw std::runtime_error("ScatterBlock: bad srcId/chunkId");
-  if ((int)s.value.size() > geo_.chunkLen(id_, s.chunkId)) throw std::runtime_error("ScatterBlock: chunk larger than its slot");
   bool fresh = scatterBuf_.store(s.round, s.srcId, s.chunkId, s.value.data(), (int)s.value.size());
   if (!fresh) {
     metrics_.duplicateDrops++;
@@ -148,9 +154,11 @@ void Worker::onScatter(const ScatterBlock& s) {
 // AllreduceWorker.scala:129-150
 void Worker::onReduce(const ReduceBlock& r) {
   if ((int)r.value.size() > geo_.maxChunkSize)
-    throw std::runtime_error("Reduced block of size " + std::to_string(r.value.size()) + " is larger than maxChunkSize " +
-                             std::to_string(geo_.maxChunkSize));
-  if (r.destId != id_) throw std::runtime_error("ReduceBlock delivered to the wrong worker");
+    throw ProtocolError("Reduced block of size " + std::to_string(r.value.size()) + " is larger than maxChunkSize " + std::to_string(geo_.maxChunkSize));
+  if (r.destId != id_) throw ProtocolError("ReduceBlock delivered to the wrong worker");
+  if (r.srcId < 0 || r.srcId >= geo_.P || r.chunkId < 0 || r.chunkId >= geo_.numChunks(r.srcId)) throw ProtocolError("ReduceBlock: bad srcId/chunkId");
+  if ((int)r.value.size() > geo_.chunkLen(r.srcId, r.chunkId)) throw ProtocolError("ReduceBlock: chunk larger than its slot");
+  if (r.round < 0 || (long long)r.round - maxRound_ > kMaxPeerAhead) throw ProtocolError("ReduceBlock: round " + std::to_string(r.round) + " is out of range");
   metrics_.reduceReceived++;
   if (r.round < round_ || completed_.count(r.round)) {
     metrics_.staleDrops++;
@@ -164,9 +172,6 @@ void Worker::onReduce(const ReduceBlock& r) {
       return;
     }
   }
-  if (r.srcId < 0 || r.srcId >= geo_.P || r.chunkId < 0 || r.chunkId >= geo_.numChunks(r.srcId))
-    throw std::runtime_error("ReduceBlock: bad srcId/chunkId");
-  if ((int)r.value.size() > geo_.chunkLen(r.srcId, r.chunkId)) throw std::runtime_error("ReduceBlock: chunk larger than its slot");
   bool fresh = reduceBuf_.store(r.round, r.srcId, r.chunkId, r.value.data(), (int)r.value.size(), r.count);
   if (!fresh) {
     metrics_.duplicateDrops++;

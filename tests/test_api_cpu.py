@@ -125,3 +125,46 @@ def test_log_level_applies_to_both_runtimes():
     log.set_level("ERROR")
     assert log.get_logger().level == 40
     log.set_level("WARNING")
+
+
+def test_rendezvous_turns_away_out_of_range_and_duplicate_ranks():
+    """The rendezvous hands out the fds of the job's device memory: a connection that claims a rank outside 1..world-1, or one
+    that is already taken, is closed and the rendezvous completes with the real peers."""
+    import os
+    import socket
+    import struct
+    import threading
+
+    from akka_allreduce_b200.parallel.symmetric import UnixRendezvous
+
+    session = f"test_rdv_{os.getpid()}"
+    box = {}
+    t = threading.Thread(target=lambda: box.setdefault("r0", UnixRendezvous(0, 2, session, timeout=30)))
+    t.start()
+    addr = "\0aar_rdv_" + session
+    import time
+
+    for bogus in (7, 0, -3):
+        for _ in range(200):
+            s = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            try:
+                s.connect(addr)
+                break
+            except (FileNotFoundError, ConnectionRefusedError):
+                s.close()
+                time.sleep(0.01)
+        s.sendall(struct.pack("i", bogus))
+        s.settimeout(5)
+        assert s.recv(1) == b"", "the rendezvous must close a connection with an impossible rank"
+        s.close()
+    r1 = UnixRendezvous(1, 2, session, timeout=30)
+    t.join(30)
+    assert not t.is_alive()
+    got = {}
+    t2 = threading.Thread(target=lambda: got.setdefault("a", box["r0"].all_gather_bytes(b"zero")))
+    t2.start()
+    assert r1.all_gather_bytes(b"one!") == [b"zero", b"one!"]
+    t2.join(10)
+    assert got["a"] == [b"zero", b"one!"]
+    r1.close()
+    box["r0"].close()

@@ -395,3 +395,30 @@ def test_reduce_block_larger_than_chunk_raises():
     h.start(0)
     with pytest.raises(Exception, match="larger than"):
         h.reduce([1, 2, 3], 1, 0, 0, 0, 2)
+
+
+def test_impossible_peer_frames_are_rejected_before_they_can_make_the_worker_do_anything():
+    """A well-formed frame with impossible content (ids or sizes outside the geometry, a round absurdly far ahead) raises a
+    protocol error BEFORE the peer-ahead self-start can run: the data source is not asked for a single round, nothing is sent.
+    (The TCP transport drops the link that delivered it and keeps serving; csrc/core/tcp_transport.cpp.)"""
+    import pytest
+
+    fetched = []
+
+    def source(it):
+        fetched.append(it)
+        return np.zeros(8, dtype=np.float32)
+
+    h = Harness(source)
+    h.init(4, 1, 1.0, 1.0, 1, 8, 2)
+    for bad in (lambda: h.scatter([1, 2], 0, 1, 99, 5),            # chunk id outside my block
+                lambda: h.scatter([1, 2, 3], 0, 1, 0, 5),          # payload larger than the chunk's slot
+                lambda: h.scatter([1, 2], 9, 1, 0, 5),             # source id outside the cluster
+                lambda: h.scatter([1, 2], 0, 1, 0, 1 << 28),       # a round that would mean hours of catch-up
+                lambda: h.reduce([1, 2], 0, 1, 7, 5, 4),
+                lambda: h.reduce([1, 2], 0, 3, 0, 5, 4)):          # not addressed to me
+        with pytest.raises(RuntimeError):
+            bad()
+    assert fetched == [] and not h.outbox, "a rejected frame must not have started any round"
+    h.scatter([1, 2], 0, 1, 0, 3)                                   # a legitimate peer-ahead block still self-starts
+    assert fetched == [0, 1, 2, 3]
