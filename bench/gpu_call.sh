@@ -1,7 +1,6 @@
 set -u
 mkdir -p gpurun_out
-TR() { n=$1; port=$2; shift 2; timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node "$n" --master-addr 127.0.0.1 --master-port "$port" "$@"; }
-timeout 600 python -m pytest tests/test_gpu_multi.py -x -q -m gpu -k "suite and 2" 2>&1 | tail -30 > gpurun_out/AE_multi2.txt; tail -3 gpurun_out/AE_multi2.txt
-TR 2 29841 bench.py --gpus 2 --steps 40 --warmup 5 --no-e2e 2>gpurun_out/AE_bench2.err | grep "^{" > gpurun_out/AE_bench2.json
-AAR_NATIVE_ENGINE=0 TR 2 29842 bench.py --gpus 2 --steps 40 --warmup 5 --no-e2e --no-nccl 2>gpurun_out/AE_bench2_py.err | grep "^{" > gpurun_out/AE_bench2_py.json
-AAR_NATIVE_ENGINE=0 timeout 300 python -m pytest tests/test_gpu_local.py -x -q -m gpu -k "snapshot or strict or start_at or retires" 2>&1 | tail -3
+TR() { n=$1; port=$2; shift 2; timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node "$n" --master-addr 127.0.0.1 --master-port "$port" "$@"; }
+nvidia-smi nvlink -gt d -i 0 2>&1 | head -8 > gpurun_out/AF_nvlink_raw.txt
+TR 2 29861 bench/nvlink_bytes.py --algo bulk 2>&1 | grep "^\[" > gpurun_out/AF_nvlink_bulk2.json
+TR 2 29862 bench/nvlink_bytes.py --algo nvls_bulk 2>&1 | grep "^\[" > gpurun_out/AF_nvlink_nvls2.json
