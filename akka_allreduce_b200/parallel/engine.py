@@ -24,7 +24,8 @@ ONESHOT_MAX_BYTES = int(os.environ.get("AAR_ONESHOT_MAX_BYTES", 256 * 1024))
 
 
 _DONE_WORD0 = 16   # host-mapped words: [0] doorbell, [_DONE_WORD0 + slot] completion per ring slot
-_ALGO_CODE = {"twoshot": 0, "pipelined": 1, "oneshot": 2, "nvls": 3, "bulk": 4, "nvls_bulk": 5}
+_ALGO_CODE = {"twoshot": 0, "pipelined": 1, "oneshot": 2, "nvls": 3, "bulk": 4, "nvls_bulk": 5, "nvls_onehop": 6}
+_IN_SWITCH = ("nvls", "nvls_bulk", "nvls_onehop")
 _TABLE = None
 
 
@@ -126,7 +127,7 @@ class RoundEngine:
             # thresholds 1.0 every round waits for the late rank and deeper overlap buys nothing.
             max_inflight = 4 if not self.full_thresholds else 2
         self.inflight = max(2, min(int(max_inflight), layout.L, 8)) if self.overlap else 1
-        if self.inflight > 2 and grid == 0:
+        if (self.inflight > 2 or (self.algo == "nvls_onehop" and self.overlap)) and grid == 0:
             # every round in flight must be able to hold ALL its CTAs at once: a kernel that waits for peers while it occupies the
             # SMs an earlier round of this rank still needs is a resource deadlock (seen at 4 in flight with full-size grids)
             sms = C.c_int(0)
@@ -185,9 +186,9 @@ class RoundEngine:
                     continue
                 if name == "oneshot" and not lay.oneshotOff:
                     continue
-                if (name == "nvls_bulk" and not nvls_ok) or (name == "nvls" and not (nvls_ok and not normalize)):
+                if (name in ("nvls_bulk", "nvls_onehop") and not nvls_ok) or (name == "nvls" and not (nvls_ok and not normalize)):
                     continue
-                if name in ("bulk", "nvls_bulk") and not bulk_ok:
+                if name in ("bulk", "nvls_bulk", "nvls_onehop") and not bulk_ok:
                     continue
                 if name == "bulk":
                     self.bulk_split = int(split)
@@ -202,9 +203,9 @@ class RoundEngine:
             return "bulk" if bulk_ok else "pipelined"
         if algo == "oneshot" and not lay.oneshotOff:
             raise ValueError("algo=oneshot needs a layout with one-shot buffers")
-        if algo in ("nvls", "nvls_bulk") and not (self.mc_ptr and lay.stageOff):
+        if algo in _IN_SWITCH and not (self.mc_ptr and lay.stageOff):
             raise ValueError(f"algo={algo} needs a multicast mapping and the staging area")
-        if algo in ("bulk", "nvls_bulk") and not bulk_ok:
+        if algo in ("bulk", "nvls_bulk", "nvls_onehop") and not bulk_ok:
             raise ValueError(f"algo={algo} needs blocks and chunks that are multiples of 16 bytes")
         if algo not in _ALGO_CODE:
             raise ValueError(f"unknown algo {algo}")
@@ -247,7 +248,7 @@ class RoundEngine:
             # the one-shot kernel has no barrier between its push and its reduce: a CTA may store output tile t while another
             # CTA of this rank has not pushed that part of the input to a slower peer yet
             raise ValueError("in-place rounds (out aliasing the input) are not supported by the one-shot kernel")
-        if self.algo in ("bulk", "nvls_bulk") and x.data_ptr() % 16:
+        if self.algo in ("bulk", "nvls_bulk", "nvls_onehop") and x.data_ptr() % 16:
             # the bulk copy engine needs 16-byte aligned addresses: bounce an oddly offset view through an aligned buffer
             b = self._bounce.get(slot)
             if b is None:
@@ -257,7 +258,7 @@ class RoundEngine:
         if self._native is not None:
             if stream is not None:
                 raise NotImplementedError("the native engine picks its own stream (AAR_NATIVE_ENGINE=0 for explicit streams)")
-            tuning = (self.split, self.nvls_reduce_ctas | (self.nvls_stage_ctas << 8), self.nvls_bulk_split if self.algo == "nvls_bulk" else self.bulk_split)
+            tuning = (self.split, self.nvls_reduce_ctas | (self.nvls_stage_ctas << 8), self.nvls_bulk_split if self.algo in ("nvls_bulk", "nvls_onehop") else self.bulk_split)
             if tuning != self._native_tuning:   # knobs changed since the last round (benchmarks sweep them)
                 L.check(self.lib.aar_engine_tune(self._native, tuning[0], tuning[1]), "aar_engine_tune")
                 L.check(self.lib.aar_engine_tune_bulk(self._native, tuning[2]), "aar_engine_tune_bulk")
@@ -304,8 +305,8 @@ class RoundEngine:
             L.check(self.lib.aar_launch_round_pipelined(self._pref, self._lay, self.grid, self.split, s), "aar_launch_round_pipelined")
         elif self.algo == "oneshot":
             L.check(self.lib.aar_launch_oneshot(self._pref, self._lay, 2, self.grid, s), "aar_launch_oneshot")
-        elif self.algo in ("bulk", "nvls_bulk"):
-            which = 1 if self.algo == "nvls_bulk" else 0
+        elif self.algo in ("bulk", "nvls_bulk", "nvls_onehop"):
+            which = {"bulk": 0, "nvls_bulk": 1, "nvls_onehop": 2}[self.algo]
             if self.lib.aar_bulk_supported(self._pref, self._lay, which):
                 L.check(self.lib.aar_launch_round_bulk(self._pref, self._lay, which, 7, self.grid, self.nvls_bulk_split if which else self.bulk_split, s),
                         "aar_launch_round_bulk")
@@ -338,7 +339,7 @@ class RoundEngine:
         The slot was last read by the peers' reduce of round rnd - L; every owner had finished that before this rank's round
         rnd - L could retire, so ordering after that round's event is enough: `stream` (default: current) is made to wait."""
         lay = self.layout
-        if self.algo not in ("nvls", "nvls_bulk") or not lay.stageOff:
+        if self.algo not in _IN_SWITCH or not lay.stageOff:
             return None
         if rnd >= lay.L:
             self.wait_round(rnd - lay.L, stream)

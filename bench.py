@@ -217,7 +217,7 @@ def main():
             got = eng._region_view(lay.reduceOff + ((rnd - 1) % lay.L) * lay.P * lay.blkStride * lay.elemSize, a.data_size * lay.elemSize, dtype)
         else:
             got = out
-        in_switch = eng.algo in ("nvls", "nvls_bulk")
+        in_switch = eng.algo in ("nvls", "nvls_bulk", "nvls_onehop")
         if in_switch:
             ok = bool(torch.allclose(got.float(), want.float(), rtol=2e-5 if dtype == torch.float32 else 2e-2, atol=1e-4))
         else:

@@ -48,7 +48,7 @@ for _ in range(a.rounds):
 eng.wait_all(); torch.cuda.synchronize(); rdv.barrier()
 c1 = counters()
 nbytes = a.n * 4
-model = nbytes * (1 + 1 / world) if eng.algo in ("nvls", "nvls_bulk") else 2 * nbytes * (world - 1) / world
+model = nbytes * (1 + 1 / world) if eng.algo in ("nvls", "nvls_bulk", "nvls_onehop") else 2 * nbytes * (world - 1) / world
 res = {"rank": rank, "world": world, "algo": eng.algo, "bytes": nbytes, "rounds": a.rounds, "model_bytes_per_round_per_direction": model}
 if c0 and c1:
     res["tx_bytes_per_round"] = (c1[0] - c0[0]) * 1024 / a.rounds

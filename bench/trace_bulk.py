@@ -9,7 +9,7 @@ from akka_allreduce_b200.parallel.engine import RoundEngine
 from akka_allreduce_b200.parallel.symmetric import SymmetricMemory, UnixRendezvous
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--n", type=int, default=16 << 20)
+ap.add_argument("--elems", dest="n", type=int, default=16 << 20)
 ap.add_argument("--chunk", type=int, default=1 << 20)
 ap.add_argument("--algo", default="bulk")
 ap.add_argument("--split", default="0:0")
@@ -40,6 +40,20 @@ tr = symm.tensor(rank, lay.traceOff, L.TRACE_CTAS * L.TRACE_MARKS * 8, torch.int
 n = int((tr[:, 0] != 0).sum())
 tr = tr[:n]
 t0 = float(tr[:, 0].min())
+if a.algo == "nvls_onehop":   # stage CTAs first, then reduce CTAs: print every mark over all CTAs and stop
+    out = {"world": world, "algo": eng.algo, "ctas": n}
+    for k, nm in {0: "entry", 1: "stage done", 2: "all flags seen", 3: "reduce done", 5: "exit"}.items():
+        col = tr[:, k]
+        col = col[col > 0]
+        if len(col):
+            col = (col - t0) / 1e3
+            out[nm] = [len(col), round(float(col.min()), 1), round(float(col.median()), 1), round(float(col.max()), 1)]
+    res = rdv.all_gather_bytes(json.dumps(out).encode())
+    if rank == 0:
+        for b in res:
+            print(b.decode())
+    rdv.barrier()
+    sys.exit(0)
 split = eng.nvls_bulk_split if a.algo == "nvls_bulk" else eng.bulk_split
 # the library's default split when 0 (keep in sync with aar_launch_round_bulk)
 if split == 0:

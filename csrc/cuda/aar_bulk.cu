@@ -856,13 +856,160 @@ __global__ void __launch_bounds__(kThreads, 1) bulkRoundKernel(const AarRankPara
   traceMark(p, l, 5);
 }
 
+// ------------------------------------------------------------------------------------------------ in-switch, one hop
+// For small and medium messages the two-hop in-switch round (reduce my block, multicast it, everybody gathers) is three
+// dependent steps of a few microseconds each.  One hop less: every rank stages its vector, tells EVERY rank when all of it is
+// staged (one flag per source), and then reduces the WHOLE vector through the switch (multimem.ld_reduce) straight into its own
+// output -- no multimem.st, no reduce ring, no gather.  The switch pulls each GPU's vector P times instead of once, so this only
+// pays while P x bytes over the link is cheaper than a hop (the selector table decides; measured crossover in profiles/).
+//   CTAs [0, nA)   stage my input (bulk copies), the last piece's publisher tells every rank
+//   the rest       wait for all P flags, in-switch reduce of my share of the pieces into the output
+template <typename T>
+struct StageAllRole {
+  static constexpr bool kPublishes = true;
+  const AarRankParams& p;
+  const AarLayout& l;
+  int nctas, slot, pieceElems, total, idx;
+  uint32_t epoch;
+  char* stage;
+  bool inPlace, go;
+
+  __device__ StageAllRole(const AarRankParams& p_, const AarLayout& l_, int cta, int nctas_, bool go_) : p(p_), l(l_), nctas(nctas_), go(go_) {
+    slot = p.round % l.L;
+    epoch = (uint32_t)(p.round + 1);
+    pieceElems = l.tilesPerPiece * l.tileElems;
+    total = (l.dataSize + pieceElems - 1) / pieceElems;
+    idx = cta;
+    stage = regionOf(p, p.rank) + l.stageOff + (long long)slot * paddedData(l) * (long long)sizeof(T);
+    inPlace = reinterpret_cast<const char*>(p.input) == stage;
+  }
+  __device__ int nextUnit(CopyUnit& u, bool) {
+    if (!go || idx >= total) return 0;
+    const long long off = (long long)idx * pieceElems;
+    const int n = (int)min((long long)pieceElems, (long long)l.dataSize - off);
+    u.src = reinterpret_cast<const char*>(reinterpret_cast<const T*>(p.input) + off);
+    u.dst = stage + off * (long long)sizeof(T);
+    u.bytes = inPlace ? 0u : (uint32_t)n * (uint32_t)sizeof(T);
+    u.a = u.b = u.c = 0;
+    idx += nctas;
+    return 1;
+  }
+  // after the publishing thread's fence: count the piece; whoever counts the last one tells every rank
+  __device__ void complete(uint32_t, uint32_t, uint32_t) {
+    unsigned* ctr = reinterpret_cast<unsigned*>(regionOf(p, p.rank) + l.k1CtrOff) + (long long)slot * l.P * l.C;
+    unsigned old;
+    asm volatile("atom.acq_rel.gpu.global.add.u32 %0, [%1], 1;" : "=r"(old) : "l"(ctr) : "memory");
+    if (old + 1 == (unsigned)total) {
+      atomicExch(ctr, 0u);
+      for (int i2 = 0; i2 < l.P; ++i2) {
+        const int dest = (i2 + p.rank) % l.P;
+        st_release_sys_u32(reinterpret_cast<uint32_t*>(regionOf(p, dest) + l.oneshotFlagOff) + slot * AAR_MAXP + p.rank, epoch);
+      }
+    }
+  }
+};
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads, 1) nvlsOneHopKernel(const AarRankParams p, const AarLayout l, int nA) {
+  extern __shared__ __align__(1024) unsigned char dsm[];
+  __shared__ BulkShared bs;
+  const int nctas = gridDim.x, b = blockIdx.x;
+  const int slot = p.round % l.L;
+  const uint32_t epoch = (uint32_t)(p.round + 1);
+  const int P = l.P;
+  traceMark(p, l, 0);
+  if (b < nA) {
+    bulkInit(bs, dsm);
+    if (threadIdx.x == 0 || threadIdx.x == 32) {
+      // Every rank reads my whole staging slot: it may be rewritten once ALL of them have retired the slot's previous tenant
+      // (both threads take the same decide-once decisions).
+      bool go = true;
+      unsigned known = 0, goMask = 0;
+      for (int d = 0; d < P; ++d) go = destDecision1(p, l, d, known, goMask, true) && go;
+      StageAllRole<T> role(p, l, b, nA, go);
+      if (threadIdx.x == 32) doneDrain(bs.done, role);
+      else runCopyRole(p, l, role, bs, dsm);
+    }
+    if (threadIdx.x == 0) traceMark(p, l, 1);
+  } else {
+    const int cta = b - nA, n = nctas - nA;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const uint32_t* flags = reinterpret_cast<const uint32_t*>(regionOf(p, p.rank) + l.oneshotFlagOff) + slot * AAR_MAXP;
+      Deadline dl(p.timeoutNs);
+      unsigned spins = 0, backoff = 32;
+      int ok = 0;
+      for (;;) {
+        int have = 0;
+        for (int j = 0; j < P; ++j) have += ld_relaxed_sys_u32(flags + j) == epoch ? 1 : 0;
+        if (have == P) {
+          ok = 1;
+          break;
+        }
+        if ((p.flags & AAR_FLAG_FORCE) || ((++spins & 31u) == 0)) {
+          if (forcedByHost(p, l)) break;
+          if (dl.expired()) {
+            atomicOr(statusWord(p, l, 0), AAR_ST_TIMEOUT_REDUCE);
+            break;
+          }
+        }
+        __nanosleep(backoff);
+        if (backoff < 256) backoff *= 2;
+      }
+      for (int j = 0; j < P && ok; ++j) (void)ld_acquire_sys_u32(flags + j);
+      bs.bcast[0] = ok;
+      traceMark(p, l, 2);
+    }
+    __syncthreads();
+    const int ok = bs.bcast[0];
+    constexpr int V = Elem<T>::kPerVec;
+    const float divisor = ((p.flags & AAR_FLAG_NORMALIZE) && P > 1) ? (float)P : 1.f;
+    const char* mcStage = reinterpret_cast<const char*>(p.mcRegion) + l.stageOff + (long long)slot * paddedData(l) * (long long)sizeof(T);
+    char* out = reinterpret_cast<char*>(p.output);
+    const int nvTotal = l.dataSize / V;
+    if (cta == 0 && p.outCounts)
+      for (int i = threadIdx.x; i < l.totalChunks; i += kThreads) p.outCounts[i] = ok ? P : 0;
+    // 8 x 16-byte switch loads in flight per thread; a rank that gave up (forced round, timeout) flushes zeros with count 0
+    constexpr int U = 8;
+    for (long long base = (long long)cta * kThreads * U + threadIdx.x; base < nvTotal; base += (long long)n * kThreads * U) {
+      uint4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = base + (long long)u * kThreads;
+        if (i < nvTotal) {
+          if (!ok) v[u] = make_uint4(0, 0, 0, 0);
+          else if (sizeof(T) == 4) v[u] = multimem_ld_reduce_f32x4(mcStage + (size_t)i * 16);
+          else v[u] = multimem_ld_reduce_bf16x8(mcStage + (size_t)i * 16);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = base + (long long)u * kThreads;
+        if (i < nvTotal) {
+          if (ok && divisor != 1.f) {
+            float f[V];
+            Elem<T>::unpack(v[u], f);
+#pragma unroll
+            for (int k = 0; k < V; ++k) f[k] = f[k] / divisor;
+            v[u] = Elem<T>::pack(f);
+          }
+          st_stream(out + (size_t)i * 16, v[u]);
+        }
+      }
+    }
+    if (threadIdx.x == 0) traceMark(p, l, 3);
+  }
+  retireRound(p, l, nctas);
+  traceMark(p, l, 5);
+}
+
 // ------------------------------------------------------------------------------------------------ host side
 struct KernelInfo {
   bool ready = false;
   int maxGrid = 0;
 };
 std::mutex g_mutex;
-KernelInfo g_info[64][4];  // [device][kernel]
+KernelInfo g_info[64][6];  // [device][kernel]
 
 template <typename K>
 int prepare(K kernel, int which, int* maxGrid) {
@@ -892,8 +1039,9 @@ int supported(const AarRankParams* p, const AarLayout* lay, int algo, const char
   else if (reinterpret_cast<uintptr_t>(p->input) % 16) *why = "the input must be 16-byte aligned";
   else if (!(p->flags & AAR_FLAG_VIEW_OUTPUT) && reinterpret_cast<uintptr_t>(p->output) % 16) *why = "the output must be 16-byte aligned";
   else if (lay->tileElems * lay->elemSize != kCopyTile) *why = "layout tile size differs from the copy tile";
-  else if (algo == 1) {
-    if (!p->mcRegion || lay->stageOff == 0) *why = "the in-switch path needs a multicast mapping and the staging area";
+  else if (algo == 1 || algo == 2) {
+    if (algo == 2 && lay->oneshotFlagOff == 0) *why = "layout without the one-shot flag words";
+    else if (!p->mcRegion || lay->stageOff == 0) *why = "the in-switch path needs a multicast mapping and the staging area";
     else if (p->minRequired != lay->P || p->minChunksRequired != lay->totalChunks || (p->flags & (AAR_FLAG_SKIP_SCATTER | AAR_FLAG_EXACT_QUORUM)))
       *why = "the switch sums every bound GPU, so thresholds must be 1.0 (use the P2P path otherwise)";
   }
@@ -912,7 +1060,36 @@ AAR_API int aar_launch_round_bulk(const AarRankParams* p, const AarLayout* lay, 
   const char* what = "aar_launch_round_bulk";
   if (!p || !lay) return aar_host::fail(AAR_EINVAL, "%s: null params", what);
   if (p->rank < 0 || p->rank >= lay->P || lay->P > AAR_MAXP) return aar_host::fail(AAR_EINVAL, "%s: bad rank %d for P=%d", what, p->rank, lay->P);
-  if (algo != 0 && algo != 1) return aar_host::fail(AAR_EINVAL, "%s: algo must be 0 (P2P) or 1 (NVLS)", what);
+  if (algo < 0 || algo > 2) return aar_host::fail(AAR_EINVAL, "%s: algo must be 0 (P2P), 1 (NVLS) or 2 (NVLS, one hop)", what);
+  if (algo == 2) {
+    if (phases != 7) return aar_host::fail(AAR_EINVAL, "%s: the one-hop in-switch round is one launch (phases = 7)", what);
+    if (lay->dtype != AAR_F32 && lay->dtype != AAR_BF16) return aar_host::fail(AAR_EINVAL, "%s: unknown dtype %d", what, lay->dtype);
+    const char* why2 = nullptr;
+    if (!supported(p, lay, algo, &why2)) return aar_host::fail(AAR_EUNSUPPORTED, "%s: %s", what, why2);
+    const bool bf = lay->dtype == AAR_BF16;
+    int maxGrid2 = 0;
+    int rc2 = bf ? prepare(nvlsOneHopKernel<__nv_bfloat16>, 5, &maxGrid2) : prepare(nvlsOneHopKernel<float>, 4, &maxGrid2);
+    if (rc2) return rc2;
+    int g2 = grid > 0 ? grid : maxGrid2;
+    if (g2 > maxGrid2) g2 = maxGrid2;
+    const int pieceElems = lay->tilesPerPiece * lay->tileElems;
+    const int pieces = (lay->dataSize + pieceElems - 1) / pieceElems;
+    int nA2 = split & 0xffff;
+    if (nA2 <= 0) nA2 = g2 / 4;
+    if (nA2 > pieces) nA2 = pieces;
+    if (nA2 < 1) nA2 = 1;
+    const long long vecs = (long long)lay->dataSize * lay->elemSize / 16;
+    long long nB2 = (vecs + (long long)kThreads * 8 - 1) / ((long long)kThreads * 8);   // one pass of 8 vectors per thread
+    if (nB2 < 1) nB2 = 1;
+    if (nB2 > g2 - nA2) nB2 = g2 - nA2;
+    if (nB2 < 1) return aar_host::fail(AAR_EINVAL, "%s: no CTA left for the reduce", what);
+    const int grid2 = nA2 + (int)nB2;
+    if (bf) nvlsOneHopKernel<__nv_bfloat16><<<grid2, kThreads, kBulkDynSmem, (cudaStream_t)stream>>>(*p, *lay, nA2);
+    else nvlsOneHopKernel<float><<<grid2, kThreads, kBulkDynSmem, (cudaStream_t)stream>>>(*p, *lay, nA2);
+    cudaError_t e2 = cudaGetLastError();
+    if (e2 != cudaSuccess) return aar_host::fail(AAR_ECUDA, "%s: launch failed: %s", what, cudaGetErrorString(e2));
+    return AAR_OK;
+  }
   if (phases != 7 && phases != 1 && phases != 2 && phases != 4) return aar_host::fail(AAR_EINVAL, "%s: phases must be 7, 1, 2 or 4", what);
   if (lay->dtype != AAR_F32 && lay->dtype != AAR_BF16) return aar_host::fail(AAR_EINVAL, "%s: unknown dtype %d", what, lay->dtype);
   const char* why = nullptr;

@@ -62,9 +62,9 @@ AAR_API int aar_engine_create(const AarLayout* layout, int rank, void* const* re
   const char* what = "aar_engine_create";
   if (!layout || !regions || !out) return fail(AAR_EINVAL, "%s: null argument", what);
   if (rank < 0 || rank >= layout->P || layout->P > AAR_MAXP) return fail(AAR_EINVAL, "%s: bad rank %d for P=%d", what, rank, layout->P);
-  if (algo < 0 || algo > 5) return fail(AAR_EINVAL, "%s: algo %d (0 two-shot, 1 pipelined, 2 one-shot, 3 NVLS, 4 bulk P2P, 5 bulk NVLS)", what, algo);
+  if (algo < 0 || algo > 6) return fail(AAR_EINVAL, "%s: algo %d (0 two-shot, 1 pipelined, 2 one-shot, 3 NVLS, 4 bulk P2P, 5 bulk NVLS, 6 bulk NVLS one hop)", what, algo);
   if (algo == 2 && !layout->oneshotOff) return fail(AAR_EINVAL, "%s: the layout has no one-shot buffers", what);
-  if ((algo == 3 || algo == 5) && !(mcRegion && layout->stageOff)) return fail(AAR_EINVAL, "%s: NVLS needs a multicast mapping and the staging area", what);
+  if ((algo == 3 || algo == 5 || algo == 6) && !(mcRegion && layout->stageOff)) return fail(AAR_EINVAL, "%s: NVLS needs a multicast mapping and the staging area", what);
   AarEngine* e = new AarEngine();
   e->lay = *layout;
   memset(&e->p, 0, sizeof e->p);
@@ -203,7 +203,7 @@ AAR_API int aar_engine_enqueue_ex(AarEngine* e, int round, const void* input, vo
       rc = aar_launch_nvls(&p, &e->lay, 7 | (e->nvlsReduce << 8) | (e->nvlsStage << 16), e->grid, run);
       break;
     default:
-      rc = aar_launch_round_bulk(&p, &e->lay, e->algo == 5 ? 1 : 0, 7, e->grid, e->bulkSplit, run);
+      rc = aar_launch_round_bulk(&p, &e->lay, e->algo == 6 ? 2 : (e->algo == 5 ? 1 : 0), 7, e->grid, e->bulkSplit, run);
       break;
   }
   if (rc) return rc;

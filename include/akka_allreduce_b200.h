@@ -137,7 +137,8 @@ int aar_launch_round_pipelined(const AarRankParams* p, const AarLayout* lay, int
  * ring driven by one thread per CTA, every completion is a bulk-group wait (no store-queue drain), roles sweep the block
  * chunk by chunk so push, reduce and gather of one round overlap.  Same flags, decisions and thresholds as the kernels above
  * (a rank may use either for any round); slot flow control for the broadcast and one eager-gather decision per chunk are
- * always on.  algo 0 = two-shot P2P, 1 = NVLS (thresholds must be 1.0; piece-granular flags, every rank must use it).
+ * always on.  algo 0 = two-shot P2P, 1 = NVLS (thresholds must be 1.0; piece-granular flags, every rank must use it),
+ * 2 = NVLS in one hop (small / medium messages: every rank reduces the whole vector through the switch into its own output).
  * phases: 7 = one launch, CTAs specialised by role (split = nA | nB << 16: push/stage CTAs, reduce CTAs; 0 = heuristic);
  * 1 / 2 / 4 = one phase with the whole grid (single-device emulation).  Needs 16-byte aligned geometry and pointers
  * (AAR_EUNSUPPORTED otherwise: use the kernels above). */

@@ -75,7 +75,7 @@ def engine_case(n, chunk, dtype, algo, rounds=5, th=1.0, normalize=False, overla
         eng.wait_round(r)
         torch.cuda.synchronize()
         want = ordered_sum(xs, list(range(world)), dtype, normalize)
-        if eng.algo in ("nvls", "nvls_bulk"):  # the switch does not promise peer-index order: equal up to fp32 reassociation
+        if eng.algo in ("nvls", "nvls_bulk", "nvls_onehop"):  # the switch does not promise peer-index order: equal up to fp32 reassociation
             good &= bool(torch.allclose(out.float(), want.float(), rtol=2e-5 if dtype == torch.float32 else 2e-2, atol=1e-4))
             # ... but every rank must hold the SAME bits (one multimem.st lands everywhere), and the same inputs must give the
             # same bits again (round r + rounds below repeats round r's inputs)
@@ -192,7 +192,7 @@ def self_start_case():
 
     def sink(out):
         want = ordered_sum(inputs_for(n, torch.float32, 6000 + out.iteration), list(range(world)), torch.float32)
-        in_switch = worker.engine.algo in ("nvls", "nvls_bulk")
+        in_switch = worker.engine.algo in ("nvls", "nvls_bulk", "nvls_onehop")
         seen.append((out.iteration, bool(torch.allclose(out.data, want, rtol=2e-5, atol=1e-4)) if in_switch else bool(torch.equal(out.data, want))))
 
     worker = W(source, sink, backend="cuda", device=lr, session=f"{sess}_selfstart")
@@ -223,7 +223,7 @@ def api_case():
     def sink(out):
         xs = inputs_for(n, torch.float32, 5000 + out.iteration)
         want = ordered_sum(xs, list(range(world)), torch.float32)
-        in_switch = worker.engine.algo in ("nvls", "nvls_bulk")   # the switch does not promise peer-index order
+        in_switch = worker.engine.algo in ("nvls", "nvls_bulk", "nvls_onehop")   # the switch does not promise peer-index order
         ok = bool(torch.allclose(out.data, want, rtol=2e-5, atol=1e-4)) if in_switch else bool(torch.equal(out.data, want))
         good[0] &= ok and int(out.count.min()) == world
         seen.append(out.iteration)
@@ -252,6 +252,8 @@ for dtype in (torch.float32, torch.bfloat16):
     engine_case(1 << 22, 1 << 18, dtype, "bulk", rounds=8, overlap=False)
     engine_case(1 << 22, 1 << 18, dtype, "nvls_bulk", rounds=6)
     engine_case(1 << 18, 1 << 18, dtype, "nvls_bulk")
+    engine_case(1 << 18, 1 << 18, dtype, "nvls_onehop", rounds=6)
+    engine_case(1 << 20, 1 << 16, dtype, "nvls_onehop", rounds=4, normalize=True)
 engine_case((1 << 20) + 8, 40000, torch.float32, "pipelined")      # unaligned blocks and chunks: scalar path
 engine_case((1 << 20) + 8, 40000, torch.float32, "bulk")           # ... which the bulk engine hands to the register kernels
 engine_case(1 << 24, 1 << 20, torch.float32, "bulk", rounds=6, max_lag=1)   # the headline geometry
