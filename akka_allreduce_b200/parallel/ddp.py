@@ -76,7 +76,8 @@ class ThresholdDDP:
                  max_lag: int = 1, th_reduce: float = 1.0, th_complete: float = 1.0, session: str = "ddp", algo: str = "auto",
                  sink: Callable[[int, AllReduceOutput], None] | None = None, comm_ctas: int = 0, engine_factory=None):
         """comm_ctas: SM budget of the gradient allreduce (CTAs per launch, one CTA occupies one SM); 0 = all SMs.  A bucket's
-        round runs while backward is still producing the next bucket, so every SM it holds is taken from the GEMMs.
+        round runs while backward is still producing the next bucket, so every SM it holds is taken from the GEMMs; the last
+        bucket (ready when backward ends) always gets all SMs.
         engine_factory(bucket_index, numel, chunk) -> engine: replaces the data plane (the hook / bucket bookkeeping is then
         testable without a GPU, tests/test_models_ddp_cpu.py); `device` may then be a torch.device such as cpu."""
         self.module, self.rank, self.world = module, rank, world
@@ -94,7 +95,10 @@ class ThresholdDDP:
         self.buckets: list[GradientBucket] = []
         ordered = list(reversed(params))
         code = L.AAR_F32 if dtype == torch.float32 else L.AAR_BF16
-        for i, (idx, n) in enumerate(plan_buckets([p.numel() for p in ordered], per_bucket, world * 64)):
+        plan = plan_buckets([p.numel() for p in ordered], per_bucket, world * 64)
+        for i, (idx, n) in enumerate(plan):
+            # the last bucket becomes ready when backward ends: nothing is left to share the SMs with, its round is the exposed tail
+            grid = 0 if i == len(plan) - 1 else comm_ctas
             g = [ordered[k] for k in idx]
             b = GradientBucket(i, n, dtype, self.device)
             off = 0
@@ -110,9 +114,9 @@ class ThresholdDDP:
                 lay = L.compute_layout(world, n, chunk, max_lag, code, 0, True)
                 b.symm = SymmetricMemory(UnixRendezvous(rank, world, f"{session}_b{i}"), lay.regionBytes, device, want_multicast=True)
                 b.engine = RoundEngine.from_symmetric(b.symm, lay, th_reduce=th_reduce, th_complete=th_complete, normalize=True, algo=algo,
-                                                      grid=comm_ctas)
+                                                      grid=grid)
             else:
-                b.engine = RoundEngine.single_process(n, chunk, max_lag, dtype=dtype, device=device, normalize=True, grid=comm_ctas)
+                b.engine = RoundEngine.single_process(n, chunk, max_lag, dtype=dtype, device=device, normalize=True, grid=grid)
             from ..worker import AllreduceWorker
 
             b.worker = AllreduceWorker.local(b.data_source, b.data_sink, b.engine, worker_id=rank)
@@ -143,7 +147,9 @@ class ThresholdDDP:
     def _launch(self, b: GradientBucket):
         # in place: every element range is pushed (read) before the chunk that overwrites it can have been reduced
         b.launched_step = self.step
-        b.worker.start_allreduce(self.step)   # -> data_source -> kernels -> (stream-ordered) data_sink
+        # -> data_source -> kernels.  The sink is NOT reached here: delivering makes the current stream -- the one backward is
+        # running on -- wait for the round, which would serialise every bucket's round with the rest of backward.  finish() joins.
+        b.worker.start_allreduce(self.step, deliver=False)
 
     def finish(self) -> None:
         """Call after backward(): the current stream waits for every bucket's round, sinks have been invoked, hooks re-armed."""
@@ -154,6 +160,8 @@ class ThresholdDDP:
                                    "backward() under ddp.no_sync() for all but the last micro-batch.")
             if b.launched_step < self.step:   # a parameter without gradient this step, or no_sync(): launch what we have
                 self._launch(b)
+        for b in self.buckets:
+            b.worker.deliver()                # the current stream waits for the bucket's round; data_sink runs
             if self.user_sink and b.last_out is not None:
                 self.user_sink(b.index, b.last_out)
         self.step += 1

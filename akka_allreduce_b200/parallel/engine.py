@@ -137,7 +137,8 @@ class RoundEngine:
         # (csrc/cuda/aar_engine.cu); AAR_NATIVE_ENGINE=0 keeps the Python choreography (NVTX ranges, explicit streams).
         self._native = None
         with torch.cuda.device(self.device):
-            self._streams = [torch.cuda.Stream(device=self.device) for _ in range(self.inflight)] if self.overlap else []
+            prio = 0 if os.environ.get("AAR_STREAM_PRIORITY", "high") in ("default", "0") else -1   # as csrc/cuda/aar_engine.cu
+            self._streams = [torch.cuda.Stream(device=self.device, priority=prio) for _ in range(self.inflight)] if self.overlap else []
             # one event per round in a ring of L + streams entries (see aar_engine.cu: what a later round or a consumer waits for)
             self._ring = layout.L + max(1, self.inflight if self.overlap else 1)
             self._events = [torch.cuda.Event() for _ in range(self._ring)]

@@ -183,9 +183,16 @@ class AllreduceWorker:
         w.max_round = w.max_scattered = -1
         return w
 
-    def start_allreduce(self, rnd: int) -> None:
-        """Local mode: StartAllreduce(rnd) from the caller's clock."""
+    def start_allreduce(self, rnd: int, *, deliver: bool = True) -> None:
+        """Local mode: StartAllreduce(rnd) from the caller's clock.  deliver=False only launches: the caller's stream is NOT made
+        to wait for the round here, so whatever it enqueues next (the rest of a backward pass) runs beside the round; the
+        caller joins later with deliver()."""
         self._on_start(rnd)
+        if deliver:
+            self.deliver()
+
+    def deliver(self) -> None:
+        """Local mode: hand every launched round to the sink (stream-ordered: the current stream waits for each of them)."""
         if self.stream_ordered:
             self._deliver_stream_ordered()
         else:

@@ -17,7 +17,7 @@ from akka_allreduce_b200.parallel.ddp import ThresholdDDP  # noqa: E402
 from akka_allreduce_b200.parallel.symmetric import UnixRendezvous  # noqa: E402
 
 ap = argparse.ArgumentParser()
-ap.add_argument("--impl", default="both", choices=["aar", "nccl", "both"])
+ap.add_argument("--impl", default="both", choices=["aar", "nccl", "none", "both"])
 ap.add_argument("--batch", type=int, default=8)
 ap.add_argument("--seq", type=int, default=1024)
 ap.add_argument("--steps", type=int, default=10)
@@ -26,6 +26,7 @@ ap.add_argument("--bucket-mb", type=float, default=32.0)
 ap.add_argument("--layers", type=int, default=12)
 ap.add_argument("--comm-ctas", type=int, default=0, help="SM budget of the gradient allreduce kernels (0 = all SMs)")
 ap.add_argument("--algo", default="auto")
+ap.add_argument("--configs", default="", help="several framework arms in one process: algo:ctas:priority,... e.g. bulk:0:high,pipelined:32:default")
 a = ap.parse_args()
 rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 lr = int(os.environ.get("LOCAL_RANK", rank))
@@ -54,12 +55,16 @@ def data(step):
 res = {"world": world, "batch_per_gpu": a.batch, "seq": a.seq, "layers": a.layers, "bucket_mb": a.bucket_mb}
 
 
-def run(impl):
+def run(impl, key=None, algo=None, ctas=None, prio=None):
+    key = key or impl
     model = build()
     opt = torch.optim.AdamW(model.parameters(), lr=1e-4, fused=True)
     ddp = None
     if impl == "aar":
-        ddp = ThresholdDDP(model, rank, world, lr, bucket_mb=a.bucket_mb, session=sess + "_" + impl, comm_ctas=a.comm_ctas, algo=a.algo)
+        if prio:
+            os.environ["AAR_STREAM_PRIORITY"] = prio
+        ddp = ThresholdDDP(model, rank, world, lr, bucket_mb=a.bucket_mb, session=sess + "_" + key.replace(":", "_"),
+                           comm_ctas=a.comm_ctas if ctas is None else ctas, algo=algo or a.algo)
         buckets = ddp.buckets
     else:
         import torch.distributed as dist
@@ -72,6 +77,8 @@ def run(impl):
         works = []
 
         def launch(b):
+            if impl == "none":        # no gradient exchange at all: the compute-only floor of the step (not a training run)
+                return
             comm.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(comm):
                 dist.all_reduce(b.buffer)
@@ -104,16 +111,29 @@ def run(impl):
         losses.append(float(loss))
     ms = gmax(sum(times) / len(times))
     toks = world * a.batch * a.seq / (ms * 1e-3)
-    res[impl] = {"ms_per_step": round(ms, 3), "tokens_per_sec": round(toks, 1), "loss_first": round(losses[0], 4), "loss_last": round(losses[-1], 4),
+    res[key] = {"ms_per_step": round(ms, 3), "tokens_per_sec": round(toks, 1), "loss_first": round(losses[0], 4), "loss_last": round(losses[-1], 4),
                  "buckets": len(ddp.buckets), "bucket_elems": ddp.buckets[0].buffer.numel(),
-                 "algo": ddp.buckets[0].engine.algo if impl == "aar" else "nccl", "params": model.num_params()}
+                 "algo": ddp.buckets[0].engine.algo if impl == "aar" else impl, "params": model.num_params()}
     ddp.close()
     del model, opt
     torch.cuda.empty_cache()
 
 
-for impl in (["aar", "nccl"] if a.impl == "both" else [a.impl]):
-    run(impl)
+if a.configs:
+    for cfg in a.configs.split(","):
+        f = cfg.split(":")
+        algo, ctas, prio = f[0], (f[1] if len(f) > 1 else "0"), (f[2] if len(f) > 2 else "high")
+        run("aar", key=cfg, algo=algo, ctas=int(ctas), prio=prio)
+    run("nccl")
+    run("none")
+    for cfg in a.configs.split(","):
+        res[cfg]["vs_nccl"] = round(res["nccl"]["ms_per_step"] / res[cfg]["ms_per_step"], 3)
+    floor = res["none"]["ms_per_step"]
+    for k in list(a.configs.split(",")) + ["nccl"]:
+        res[k]["exposed_comm_ms"] = round(res[k]["ms_per_step"] - floor, 3)
+else:
+    for impl in (["aar", "nccl"] if a.impl == "both" else [a.impl]):
+        run(impl)
 if "aar" in res and "nccl" in res:
     res["aar_vs_nccl"] = round(res["nccl"]["ms_per_step"] / res["aar"]["ms_per_step"], 3)
 if rank == 0:

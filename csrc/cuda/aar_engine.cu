@@ -6,6 +6,7 @@
 // The default enqueue path of parallel/engine.py (AAR_NATIVE_ENGINE=0 switches back to the Python choreography).
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <vector>
@@ -103,11 +104,20 @@ AAR_API int aar_engine_create(const AarLayout* layout, int rank, void* const* re
   e->devWords = static_cast<unsigned*>(d);
   e->p.doorbell = reinterpret_cast<const int*>(e->devWords);
   e->p.hostDone = e->devWords + kDoneWord0;
-  if (e->nStreams)
+  if (e->nStreams) {
+    // The round streams get the device's greatest priority unless AAR_STREAM_PRIORITY=default: a bulk CTA needs a whole SM's
+    // shared memory, so when the caller's own kernels (a backward pass) keep every SM busy, a round only starts promptly if
+    // its CTAs are placed ahead of the caller's pending ones.
+    int least = 0, greatest = 0;
+    err = cudaDeviceGetStreamPriorityRange(&least, &greatest);
+    if (err != cudaSuccess) return bail(err, "cudaDeviceGetStreamPriorityRange");
+    const char* pe = getenv("AAR_STREAM_PRIORITY");
+    const bool plain = pe && (!strcmp(pe, "default") || !strcmp(pe, "0"));
     for (int i = 0; i < e->nStreams; ++i) {
-      err = cudaStreamCreateWithFlags(&e->streams[i], cudaStreamNonBlocking);
-      if (err != cudaSuccess) return bail(err, "cudaStreamCreateWithFlags");
+      err = cudaStreamCreateWithPriority(&e->streams[i], cudaStreamNonBlocking, plain ? 0 : greatest);
+      if (err != cudaSuccess) return bail(err, "cudaStreamCreateWithPriority");
     }
+  }
   const int ring = layout->L + (e->nStreams > 1 ? e->nStreams : 1);
   e->slotDone.assign((size_t)ring, nullptr);
   e->slotRound.assign((size_t)ring, -1);

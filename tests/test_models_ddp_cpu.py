@@ -119,6 +119,9 @@ def test_threshold_ddp_bookkeeping_with_a_fake_data_plane():
         loss.backward()
         launched_in_backward = [e for e in log if e[0] == "enqueue"]
         assert launched_in_backward and all(r == step for _, _, r in launched_in_backward)
+        # backward's stream must not have been made to wait for any round yet: that would serialise the round with the rest
+        # of backward (measured on B200: the whole gradient allreduce time added to the step).  finish() is the join.
+        assert not [e for e in log if e[0] == "wait"], "a hook made the stream wait for its bucket's round"
         ddp.finish()
         enq = [i for k, i, _ in log if k == "enqueue"]
         assert sorted(enq) == list(range(len(ddp.buckets))), "every bucket exactly once per step (the one holding `unused` from finish())"
