@@ -225,11 +225,16 @@ __device__ __forceinline__ void reduceSpan(const AarRankParams& p, const AarLayo
     if (kFC) {
       if (P <= 2) reduceSpanVec<T, kBcast, 2, 2, true>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor, destMask);
       else if (P <= 4) reduceSpanVec<T, kBcast, 4, 2, true>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor, destMask);
-      else reduceSpanVec<T, kBcast, 8, 1, true>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor, destMask);
+      else reduceSpanVec<T, kBcast, 4, 1, true>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor, destMask);
+    } else if (!kBcast) {
+      // one-shot (small, latency-bound messages): four loads in flight per thread keep the loop free of spills
+      if (P <= 2) reduceSpanVec<T, kBcast, 2, 2>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
+      else if (P <= 4) reduceSpanVec<T, kBcast, 4, 2>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
+      else reduceSpanVec<T, kBcast, 4, 1>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
     } else {
       if (P <= 2) reduceSpanVec<T, kBcast, 2, 2>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
       else if (P <= 4) reduceSpanVec<T, kBcast, 4, 2>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
-      else reduceSpanVec<T, kBcast, 8, 1>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
+      else reduceSpanVec<T, kBcast, 4, 1>(p, l, rows, rowStride, outElemOff, localOut, nv, mask, divisor);
     }
   }
   for (int i = nv * V + threadIdx.x; i < n; i += kThreads) {
@@ -285,12 +290,12 @@ __device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int
   const bool vecOk = geomVecOk<T>(l);
   const SegPlan plan(l, myChunks, nctas, kNvls ? 1 : unitsPerCta);
   const int S = plan.segs, segElems = plan.segElems(l);
-  const long long total = (long long)myChunks * S;
+  const int total = myChunks * S;   // <= chunks x tiles of one block: far below 2^31
   unsigned destMask = 0xffffffffu;
   if (kFC && !kNvls && cta < total) destMask = bcastDestMask(p, l, sm);
-  for (long long idx = cta; idx < total; idx += nctas) {
-    const int s = (int)(idx % S);
-    const int c = (int)(idx / S);
+  for (int idx = cta; idx < total; idx += nctas) {
+    const int s = idx % S;
+    const int c = idx / S;
     const int clen = chunkLen(l, p.rank, c);
     const int off = s * segElems;
     if (off >= clen) continue;
@@ -336,7 +341,7 @@ __device__ void phaseReduceBcast(const AarRankParams& p, const AarLayout& l, int
       __threadfence_system();
       unsigned* ctr = reinterpret_cast<unsigned*>(my + l.k2CtrOff) + (long long)slot * C + c;
       const unsigned old = atomicAdd(ctr, 1u);
-      if (old + 1 == plan.liveSegs(l, clen)) {  // last segment of this "ReduceBlock": tell every peer, count included
+      if (old + 1 == (unsigned)((clen + segElems - 1) / segElems)) {  // last live segment of this "ReduceBlock": tell every peer, count included
         atomicExch(ctr, 0u);
         __threadfence_system();
         const uint64_t word = (epoch << 32) | (uint64_t)count;
