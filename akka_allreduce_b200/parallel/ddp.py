@@ -74,10 +74,12 @@ class GradientBucket:
 class ThresholdDDP:
     def __init__(self, module: torch.nn.Module, rank: int, world: int, device: int, *, bucket_mb: float = 32.0, max_chunk: int = 1 << 20,
                  max_lag: int = 1, th_reduce: float = 1.0, th_complete: float = 1.0, session: str = "ddp", algo: str = "auto",
-                 sink: Callable[[int, AllReduceOutput], None] | None = None, comm_ctas: int = 0, engine_factory=None):
+                 sink: Callable[[int, AllReduceOutput], None] | None = None, comm_ctas: int = 0, comm_split: tuple[int, int] | None = None,
+                 engine_factory=None):
         """comm_ctas: SM budget of the gradient allreduce (CTAs per launch, one CTA occupies one SM); 0 = all SMs.  A bucket's
         round runs while backward is still producing the next bucket, so every SM it holds is taken from the GEMMs; the last
-        bucket (ready when backward ends) always gets all SMs.
+        bucket (ready when backward ends) always gets all SMs.  comm_split = (push CTAs, reduce CTAs) of a budgeted round on the
+        bulk kernels, the rest gathers (the library's default split is tuned for a full grid).
         engine_factory(bucket_index, numel, chunk) -> engine: replaces the data plane (the hook / bucket bookkeeping is then
         testable without a GPU, tests/test_models_ddp_cpu.py); `device` may then be a torch.device such as cpu."""
         self.module, self.rank, self.world = module, rank, world
@@ -117,6 +119,8 @@ class ThresholdDDP:
                                                       grid=grid)
             else:
                 b.engine = RoundEngine.single_process(n, chunk, max_lag, dtype=dtype, device=device, normalize=True, grid=grid)
+            if comm_split and grid and hasattr(b.engine, "bulk_split"):
+                b.engine.bulk_split = int(comm_split[0]) | (int(comm_split[1]) << 16)
             from ..worker import AllreduceWorker
 
             b.worker = AllreduceWorker.local(b.data_source, b.data_sink, b.engine, worker_id=rank)

@@ -26,7 +26,7 @@ ap.add_argument("--bucket-mb", type=float, default=32.0)
 ap.add_argument("--layers", type=int, default=12)
 ap.add_argument("--comm-ctas", type=int, default=0, help="SM budget of the gradient allreduce kernels (0 = all SMs)")
 ap.add_argument("--algo", default="auto")
-ap.add_argument("--configs", default="", help="several framework arms in one process: algo:ctas:priority,... e.g. bulk:0:high,pipelined:32:default")
+ap.add_argument("--configs", default="", help="several framework arms in one process: algo:ctas[:priority[:pushCTAs:reduceCTAs]],... e.g. bulk:0:high,bulk:16:high:4:7")
 a = ap.parse_args()
 rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 lr = int(os.environ.get("LOCAL_RANK", rank))
@@ -55,7 +55,7 @@ def data(step):
 res = {"world": world, "batch_per_gpu": a.batch, "seq": a.seq, "layers": a.layers, "bucket_mb": a.bucket_mb}
 
 
-def run(impl, key=None, algo=None, ctas=None, prio=None):
+def run(impl, key=None, algo=None, ctas=None, prio=None, split=None):
     key = key or impl
     model = build()
     opt = torch.optim.AdamW(model.parameters(), lr=1e-4, fused=True)
@@ -64,7 +64,7 @@ def run(impl, key=None, algo=None, ctas=None, prio=None):
         if prio:
             os.environ["AAR_STREAM_PRIORITY"] = prio
         ddp = ThresholdDDP(model, rank, world, lr, bucket_mb=a.bucket_mb, session=sess + "_" + key.replace(":", "_"),
-                           comm_ctas=a.comm_ctas if ctas is None else ctas, algo=algo or a.algo)
+                           comm_ctas=a.comm_ctas if ctas is None else ctas, algo=algo or a.algo, comm_split=split)
         buckets = ddp.buckets
     else:
         import torch.distributed as dist
@@ -123,7 +123,8 @@ if a.configs:
     for cfg in a.configs.split(","):
         f = cfg.split(":")
         algo, ctas, prio = f[0], (f[1] if len(f) > 1 else "0"), (f[2] if len(f) > 2 else "high")
-        run("aar", key=cfg, algo=algo, ctas=int(ctas), prio=prio)
+        split = (int(f[3]), int(f[4])) if len(f) > 4 else None     # algo:ctas:priority:pushCTAs:reduceCTAs
+        run("aar", key=cfg, algo=algo, ctas=int(ctas), prio=prio or "high", split=split)
     run("nccl")
     run("none")
     for cfg in a.configs.split(","):
