@@ -235,11 +235,9 @@ class RoundEngine:
             self._in_order += 1
         return self._in_order
 
-    def enqueue_round(self, rnd: int, x: torch.Tensor, *, stream: torch.cuda.Stream | None = None, force: bool = False,
-                      skip_scatter: bool = False, out: torch.Tensor | None = None, delay_ns: int = 0):
-        """Launch round `rnd` with input `x`; returns (output, counts) tensors that are valid after `wait_round(rnd)` (or once
-        the explicit `stream` reaches the end of the round) and are reused maxLag+1 rounds later.  `x` must stay alive
-        and unmodified until then."""
+    def prepare_round(self, rnd: int, x: torch.Tensor, out: torch.Tensor | None = None):
+        """Everything enqueue_round does before the launch: validate the input, pick the output, bounce an unaligned view,
+        forward changed tuning knobs.  Returns (x, output) -- the tensors the launch will read and write."""
         if x.dtype != self.dtype or x.numel() != self.data_size or not x.is_contiguous() or x.device != self.device:
             raise ValueError(f"input must be a contiguous {self.dtype} tensor of {self.data_size} elements on {self.device} "
                              f"(AllreduceWorker.scala:174-176 rejects a size that differs from initialisation)")
@@ -257,20 +255,51 @@ class RoundEngine:
             b.copy_(x)
             x = b
         if self._native is not None:
-            if stream is not None:
-                raise NotImplementedError("the native engine picks its own stream (AAR_NATIVE_ENGINE=0 for explicit streams)")
             tuning = (self.split, self.nvls_reduce_ctas | (self.nvls_stage_ctas << 8), self.nvls_bulk_split if self.algo in ("nvls_bulk", "nvls_onehop") else self.bulk_split)
             if tuning != self._native_tuning:   # knobs changed since the last round (benchmarks sweep them)
                 L.check(self.lib.aar_engine_tune(self._native, tuning[0], tuning[1]), "aar_engine_tune")
                 L.check(self.lib.aar_engine_tune_bulk(self._native, tuning[2]), "aar_engine_tune_bulk")
                 self._native_tuning = tuning
+        return x, output
+
+    def note_launched(self, rnd: int) -> None:
+        """Bookkeeping after a launch (also called by the C++ round loop's source adapter, which launches through the C entry
+        point itself)."""
+        self._slot_round[rnd % self.layout.L] = rnd
+        self.launches += 1
+        self.rounds_enqueued = max(self.rounds_enqueued, rnd + 1)
+
+    def native_plane(self):
+        """The data plane as the C++ round loop wants it (csrc/core/device_loop.h): engine handle + the addresses of the four C
+        entry points.  None on the Python launch path."""
+        if self._native is None:
+            return None
+        from .. import _core as core
+
+        def addr(fn):
+            return C.cast(fn, C.c_void_p).value
+
+        handle = self._native.value if hasattr(self._native, "value") else int(self._native)
+        return core.DevicePlane(engine=handle, enqueue=addr(self.lib.aar_engine_enqueue_ex), doorbell=addr(self.lib.aar_engine_set_doorbell),
+                                flushed=addr(self.lib.aar_engine_round_flushed), synchronize=addr(self.lib.aar_engine_synchronize),
+                                slots=self.layout.L, max_lag=self.max_lag, data_size=self.data_size,
+                                extra_flags=self.base_flags & ~self._native_flags)
+
+    def enqueue_round(self, rnd: int, x: torch.Tensor, *, stream: torch.cuda.Stream | None = None, force: bool = False,
+                      skip_scatter: bool = False, out: torch.Tensor | None = None, delay_ns: int = 0):
+        """Launch round `rnd` with input `x`; returns (output, counts) tensors that are valid after `wait_round(rnd)` (or once
+        the explicit `stream` reaches the end of the round) and are reused maxLag+1 rounds later.  `x` must stay alive
+        and unmodified until then."""
+        x, output = self.prepare_round(rnd, x, out)
+        slot = rnd % self.layout.L
+        if self._native is not None:
+            if stream is not None:
+                raise NotImplementedError("the native engine picks its own stream (AAR_NATIVE_ENGINE=0 for explicit streams)")
             extra = (L.FLAG_FORCE if force else 0) | (L.FLAG_SKIP_SCATTER if skip_scatter else 0) | (self.base_flags & ~self._native_flags)
             L.check(self.lib.aar_engine_enqueue_ex(self._native, rnd, C.c_void_p(x.data_ptr()), C.c_void_p(output.data_ptr()),
                                                    C.c_void_p(self.counts[slot].data_ptr()), extra,
                                                    C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream), int(delay_ns)), "aar_engine_enqueue")
-            self._slot_round[slot] = rnd
-            self.launches += 1
-            self.rounds_enqueued = max(self.rounds_enqueued, rnd + 1)
+            self.note_launched(rnd)
             return output, self.counts[slot]
         p = self.params
         p.round = rnd

@@ -28,6 +28,7 @@ CORE_SOURCES = [
     "core/checkpoint.cpp",
     "core/local_cluster.cpp",
     "core/tcp_transport.cpp",
+    "core/device_loop.cpp",
 ]
 CUDA_SOURCES = ["cuda/aar_kernels.cu", "cuda/aar_bulk.cu", "cuda/aar_symm.cu", "cuda/aar_bench.cu", "cuda/aar_engine.cu"]
 CUDA_ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]

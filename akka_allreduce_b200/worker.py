@@ -20,6 +20,7 @@ backend="cuda" : control messages (InitWorkers / StartAllreduce / CompleteAllred
 """
 from __future__ import annotations
 
+import os
 import time
 from typing import Callable
 
@@ -33,7 +34,8 @@ class AllreduceWorker:
     def __init__(self, data_source: DataSource, data_sink: DataSink, backend: str = "cuda", *, device: int | None = None,
                  dtype: str = "fp32", algo: str = "auto", normalize: bool = False, exact_quorum: bool = False,
                  spin_timeout_ms: float = 0.0, grid: int = 0, session: str | None = None, want_multicast: bool = True,
-                 zero_copy_input: bool = False, on_init: Callable[["AllreduceWorker"], None] | None = None):
+                 zero_copy_input: bool = False, on_init: Callable[["AllreduceWorker"], None] | None = None,
+                 native_loop: bool | None = None):
         if backend not in ("cpu", "cuda"):
             raise ValueError("backend must be 'cpu' or 'cuda'")
         self.data_source, self.data_sink, self.backend = data_source, data_sink, backend
@@ -41,6 +43,12 @@ class AllreduceWorker:
         self.normalize, self.exact_quorum, self.spin_timeout_ms, self.grid = normalize, exact_quorum, spin_timeout_ms, grid
         self.session, self.want_multicast, self.on_init = session, want_multicast, on_init
         self.zero_copy_input = zero_copy_input
+        # the round loop in C++ (csrc/core/device_loop.cpp): Python is called for the source, the sink and InitWorkers only
+        self.native_loop = (os.environ.get("AAR_NATIVE_LOOP", "0") not in ("", "0")) if native_loop is None else bool(native_loop)
+        self._loop = None
+        self._loop_error = None
+        self._direct = False
+        self._plane_callbacks = None   # ctypes thunks of a Python data plane (tests): must outlive the plane
         self.node: core.WorkerNode | None = None
         self.id = -1
         self.generation = 0
@@ -83,6 +91,9 @@ class AllreduceWorker:
 
             self._cpu_worker = core.Worker(src, snk, self.node)
             self.node.attach(self._cpu_worker)
+        elif self.native_loop:
+            self._loop = core.DeviceLoop(self._loop_source, self._loop_sink, self.node)
+            self._loop.set_init(self._loop_init)
         else:
             self.node.set_handler(self._on_message)
         return self
@@ -94,6 +105,18 @@ class AllreduceWorker:
         if self.backend == "cpu":
             ok = self.node.run(timeout_sec)
             self.id = self._cpu_worker.id
+            self.master_lost = ok and not self.node.shutdown_by_master
+            return ok
+        if self._loop is not None:
+            self._loop_error = None
+            try:
+                ok = self._loop.run(self.node, timeout_sec)   # poll -> peer-ahead -> deliver, without the interpreter lock
+            except RuntimeError:
+                if self._loop_error is not None:   # a Python data plane failed inside a C thunk: surface its own exception
+                    raise self._loop_error
+                raise
+            finally:
+                self._sync_from_loop()
             self.master_lost = ok and not self.node.shutdown_by_master
             return ok
         deadline = time.time() + timeout_sec
@@ -109,6 +132,13 @@ class AllreduceWorker:
 
     def step(self, timeout_ms: int = 0) -> None:
         """One iteration of the event loop (for callers that own the loop)."""
+        if self._loop is not None:
+            self.node.set_handler(self._loop.receive)
+            self.node.poll(timeout_ms)
+            self._loop.peer_ahead()
+            self._loop.deliver_flushed()
+            self._sync_from_loop()
+            return
         self.node.poll(timeout_ms)
         if self.backend == "cuda":
             self._peer_ahead()
@@ -130,6 +160,8 @@ class AllreduceWorker:
         """rounds/s, forced completions, lag and the data-plane counters (CPU backend: the C++ worker's counters)."""
         if self.backend == "cpu":
             return dict(self._cpu_worker.metrics()) if self._cpu_worker else {}
+        if self._loop is not None:
+            self._sync_from_loop()
         m = {"id": self.id, "generation": self.generation, "rounds_delivered": self.delivered, "rounds_forced": self.rounds_forced,
              "max_round": self.max_round, "max_scattered": self.max_scattered, "lag": self.max_round - self.delivered + 1,
              "rounds_out_of_order": self.out_of_order, "self_started_rounds": self.self_starts}
@@ -145,6 +177,8 @@ class AllreduceWorker:
         return m
 
     def close(self) -> None:
+        if self._loop is not None:
+            self._loop.clear_plane()   # the handle below is about to be destroyed
         if self.engine is not None:
             # Kernels of this incarnation may still be waiting for peers that are being re-initialised themselves (a late joiner
             # makes the master re-init everyone).  Their region, doorbell and completion words are about to be unmapped: ring the
@@ -165,6 +199,108 @@ class AllreduceWorker:
         if self.board is not None:
             self.board.close(unlink=self.id == 0)
             self.board = None
+
+    # ------------------------------------------------------------------ C++ round loop: what it calls back
+    def _loop_init(self, m) -> None:
+        """InitWorkers under the C++ loop: build the data plane as always, then hand the loop its handle."""
+        self._loop.clear_plane()
+        self._on_init(m)
+        eng = self.engine
+        plane = eng.native_plane() if hasattr(eng, "native_plane") else None
+        self._direct = plane is not None   # launches go C++ -> aar_engine_enqueue_ex; otherwise through the thunks below
+        if plane is None:
+            plane = self._python_plane(eng)
+        self._loop.set_plane(plane, self.id, self.generation, m.master, self.start_round)
+        if self.board is not None:
+            self._loop.set_board(self.board.post, self.board.newest)
+
+    def _python_plane(self, eng):
+        """A data plane that only exists in Python (the launch path with AAR_NATIVE_ENGINE=0, fake engines in tests), wrapped in C
+        thunks so the same loop drives it."""
+        import ctypes as C
+
+        ENQ = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint, C.c_void_p, C.c_ulonglong)
+        I2 = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int)
+        I1 = C.CFUNCTYPE(C.c_int, C.c_void_p)
+        per_round = getattr(eng, "round_flushed", None)
+
+        def enqueue(_e, rnd, _i, _o, _c, _f, _s, _d):
+            x, out = self._inputs[rnd], self._outs.get(rnd)
+            try:
+                eng.enqueue_round(rnd, x, out=out) if out is not None else eng.enqueue_round(rnd, x)
+            except Exception as exc:   # a C caller cannot unwind a Python exception: report it as a failed launch
+                self._loop_error = exc
+                return 1
+            return 0
+
+        def doorbell(_e, newest):
+            eng.set_doorbell(newest)
+            return 0
+
+        scan = {"last": -1, "in_order": 0}
+
+        def flushed(_e, rnd):
+            if per_round is not None:
+                return int(per_round(rnd))
+            # a data plane that only reports an in-order count completes in order: one snapshot per ascending scan of the loop
+            if scan["last"] < 0 or rnd <= scan["last"]:
+                scan["in_order"] = eng.rounds_flushed()
+            scan["last"] = rnd
+            return int(rnd < scan["in_order"])
+
+        def synchronize(_e):
+            eng.synchronize()
+            return 0
+
+        self._plane_callbacks = (ENQ(enqueue), I2(doorbell), I2(flushed), I1(synchronize))
+        a = [C.cast(f, C.c_void_p).value for f in self._plane_callbacks]
+        return core.DevicePlane(engine=1, enqueue=a[0], doorbell=a[1], flushed=a[2], synchronize=a[3], slots=eng.layout.L,
+                                max_lag=eng.max_lag, data_size=eng.data_size)
+
+    def _loop_source(self, rnd: int):
+        """source(round) for the C++ loop: the caller's data_source plus everything that needs the tensors (size check, output
+        choice, alignment bounce); returns raw pointers."""
+        eng = self.engine
+        req = AllReduceInputRequest(rnd)
+        if self.zero_copy_input and hasattr(eng, "stage_input"):
+            req.buffer = eng.stage_input(rnd)
+        inp = self.data_source(req)
+        x = inp.data
+        n = x.numel() if hasattr(x, "numel") else len(x)
+        out = getattr(inp, "out", None)
+        if n != eng.data_size:   # the loop raises the reference's message (AllreduceWorker.scala:174-176)
+            return (0, 0, 0, 0, n)
+        if self._direct:
+            import torch
+
+            x, output = eng.prepare_round(rnd, x, out)
+            eng.note_launched(rnd)
+            slot = rnd % eng.layout.L
+            ptrs = (x.data_ptr(), output.data_ptr(), eng.counts[slot].data_ptr(), torch.cuda.current_stream(eng.device).cuda_stream, n)
+        else:
+            ptrs = (0, 0, 0, 0, n)
+        self._inputs[rnd] = x
+        if out is not None:
+            self._outs[rnd] = out
+        return ptrs
+
+    def _loop_sink(self, rnd: int, slot: int) -> None:
+        eng = self.engine
+        self._inputs.pop(rnd, None)
+        self.data_sink(AllReduceOutput(self._outs.pop(rnd, eng.outputs[slot]), eng.counts[slot], rnd))
+        self._t_last = time.time()
+        if self._t_first is None:
+            self._t_first = self._t_last
+
+    def _sync_from_loop(self) -> None:
+        """Mirror the loop's state into the attributes metrics() and the tests read."""
+        lp = self._loop
+        st = lp.stats()
+        self.round, self.max_round, self.max_scattered = lp.round, lp.max_round, lp.max_scattered
+        self.completed = set(lp.completed)
+        self.delivered = self.start_round + st["rounds_delivered"]
+        self.out_of_order, self.self_starts, self.rounds_forced = st["rounds_out_of_order"], st["self_started_rounds"], st["rounds_forced"]
+        self.lag_hist = dict(st["lag_hist"])
 
     # ------------------------------------------------------------------ masterless mode
     @classmethod
@@ -324,7 +460,7 @@ class AllreduceWorker:
             progressed = False
             in_order = eng.rounds_flushed() if per_round is None else None
             for r in range(self.round, self.max_scattered + 1):
-                if r in self.completed:
+                if r < self.round or r in self.completed:   # self.round moves inside this loop
                     continue
                 if not (per_round(r) if per_round is not None else r < in_order):
                     continue
@@ -344,9 +480,9 @@ class AllreduceWorker:
                 if self._t_first is None:
                     self._t_first = self._t_last
                 progressed = True
-            while self.round in self.completed:   # AllreduceWorker.scala:261-267
-                self.completed.discard(self.round)
-                self.round += 1
+                while self.round in self.completed:   # AllreduceWorker.scala:261-267: past every already-completed round
+                    self.completed.discard(self.round)
+                    self.round += 1
             if not block or progressed or self.delivered >= self.max_scattered + 1:
                 return
             time.sleep(0)  # blocking mode: yield until the next round flushes

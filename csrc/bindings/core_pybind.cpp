@@ -7,6 +7,7 @@
 #include "../core/checkpoint.h"
 #include "../core/config.h"
 #include "../core/data_buffer.h"
+#include "../core/device_loop.h"
 #include "../core/geometry.h"
 #include "../core/local_cluster.h"
 #include "../core/logging.h"
@@ -210,6 +211,100 @@ PYBIND11_MODULE(_core, m) {
       .def("metrics", [](const Worker& w) { return w.metrics().asMap(); })
       .def("contributor_histogram", [](const Worker& w) {
         return std::vector<int64_t>(w.metrics().contributorHist.begin(), w.metrics().contributorHist.end());
+      });
+
+  // ---- device-plane round loop (csrc/core/device_loop.h): Python is the caller's source and sink, nothing else per round
+  py::class_<DevicePlane>(m, "DevicePlane")
+      .def(py::init([](uintptr_t engine, uintptr_t enqueue, uintptr_t doorbell, uintptr_t flushed, uintptr_t synchronize, int slots, int maxLag,
+                       long long dataSize, unsigned extraFlags) {
+             DevicePlane p;
+             p.engine = reinterpret_cast<void*>(engine);
+             p.enqueue = reinterpret_cast<DevicePlane::EnqueueFn>(enqueue);
+             p.doorbell = reinterpret_cast<DevicePlane::DoorbellFn>(doorbell);
+             p.flushed = reinterpret_cast<DevicePlane::FlushedFn>(flushed);
+             p.synchronize = reinterpret_cast<DevicePlane::SyncFn>(synchronize);
+             p.slots = slots;
+             p.maxLag = maxLag;
+             p.dataSize = dataSize;
+             p.extraFlags = extraFlags;
+             return p;
+           }),
+           py::arg("engine"), py::arg("enqueue"), py::arg("doorbell"), py::arg("flushed"), py::arg("synchronize") = 0, py::arg("slots") = 2,
+           py::arg("max_lag") = 1, py::arg("data_size") = 0, py::arg("extra_flags") = 0u)
+      .def_readonly("slots", &DevicePlane::slots)
+      .def_readonly("max_lag", &DevicePlane::maxLag)
+      .def_readonly("data_size", &DevicePlane::dataSize);
+
+  py::class_<DeviceLoop>(m, "DeviceLoop")
+      .def(py::init([](py::object source, py::object sink, WorkerPort* port) {
+             // source(round) -> (input ptr, output ptr, counts ptr, stream, numel) ; sink(round, slot)
+             return std::make_unique<DeviceLoop>(
+                 [source](int round) {
+                   py::gil_scoped_acquire gil;
+                   py::tuple t = source(round).cast<py::tuple>();
+                   RoundBuffers b;
+                   b.input = t[0].cast<uintptr_t>();
+                   b.output = t[1].cast<uintptr_t>();
+                   b.counts = t[2].cast<uintptr_t>();
+                   b.stream = t[3].cast<uintptr_t>();
+                   b.numel = t[4].cast<long long>();
+                   return b;
+                 },
+                 [sink](int round, int slot) {
+                   py::gil_scoped_acquire gil;
+                   sink(round, slot);
+                 },
+                 port);
+           }),
+           py::arg("source"), py::arg("sink"), py::arg("port"), py::keep_alive<1, 4>())
+      .def("set_init",
+           [](DeviceLoop& l, py::object fn) {
+             l.setInit([fn](const InitWorkers& msg) {
+               py::gil_scoped_acquire gil;
+               fn(msg);
+             });
+           })
+      .def("set_board",
+           [](DeviceLoop& l, py::object post, py::object newest) {
+             l.setBoard(
+                 [post](int r) {
+                   py::gil_scoped_acquire gil;
+                   post(r);
+                 },
+                 [newest]() {
+                   py::gil_scoped_acquire gil;
+                   return newest().cast<int>();
+                 });
+           })
+      .def("set_plane", &DeviceLoop::setPlane, py::arg("plane"), py::arg("id"), py::arg("generation") = 0, py::arg("master") = kNoAddress,
+           py::arg("start_round") = 0)
+      .def("clear_plane", &DeviceLoop::clearPlane)
+      .def("receive", [](DeviceLoop& l, const Message& msg) { l.receive(msg); }, py::call_guard<py::gil_scoped_release>())
+      .def("on_start", &DeviceLoop::onStart, py::arg("round"), py::call_guard<py::gil_scoped_release>())
+      .def("peer_ahead", &DeviceLoop::peerAhead, py::call_guard<py::gil_scoped_release>())
+      .def("deliver_flushed", &DeviceLoop::deliverFlushed, py::arg("block") = false, py::call_guard<py::gil_scoped_release>())
+      .def("drain", &DeviceLoop::drain, py::call_guard<py::gil_scoped_release>())
+      .def("run", &DeviceLoop::run, py::arg("node"), py::arg("timeout_sec") = 3600.0, py::call_guard<py::gil_scoped_release>())
+      .def_property_readonly("busy", &DeviceLoop::busy)
+      .def_property_readonly("id", &DeviceLoop::id)
+      .def_property_readonly("generation", &DeviceLoop::generation)
+      .def_property_readonly("round", &DeviceLoop::round)
+      .def_property_readonly("max_round", &DeviceLoop::maxRound)
+      .def_property_readonly("max_scattered", &DeviceLoop::maxScattered)
+      .def_property_readonly("start_round", &DeviceLoop::startRound)
+      .def_property_readonly("completed", [](const DeviceLoop& l) { return std::vector<int>(l.completed().begin(), l.completed().end()); })
+      .def("stats", [](const DeviceLoop& l) {
+        const DeviceLoopStats& s = l.stats();
+        py::dict d;
+        d["rounds_delivered"] = s.delivered;
+        d["rounds_out_of_order"] = s.outOfOrder;
+        d["self_started_rounds"] = s.selfStarts;
+        d["rounds_forced"] = s.forced;
+        d["rounds_launched"] = s.launched;
+        py::dict h;
+        for (auto& kv : s.lagHist) h[py::int_(kv.first)] = kv.second;
+        d["lag_hist"] = h;
+        return d;
       });
 
   py::class_<MasterConfig>(m, "MasterConfig")

@@ -205,10 +205,11 @@ def self_start_case():
     worker.close()
 
 
-def api_case():
-    """AllreduceMaster + AllreduceWorker(backend=cuda) end to end, 12 rounds, pipelined master clock."""
+def api_case(native_loop=False):
+    """AllreduceMaster + AllreduceWorker(backend=cuda) end to end, 12 rounds, pipelined master clock.  native_loop: the round loop
+    in C++ (csrc/core/device_loop.cpp) launching through aar_engine_enqueue_ex directly; Python is the source and the sink only."""
     n, chunk, rounds = 1 << 18, 1 << 14, 12
-    port = int(os.environ.get("MASTER_PORT", "29500")) + 57
+    port = int(os.environ.get("MASTER_PORT", "29500")) + (59 if native_loop else 57)
     master = None
     if rank == 0:
         master = AllreduceMaster(world, 1.0, 1.0, 1.0, 1, n, rounds - 1, chunk, pipeline_depth=1, port=port)
@@ -228,17 +229,21 @@ def api_case():
         good[0] &= ok and int(out.count.min()) == world
         seen.append(out.iteration)
 
-    worker = AllreduceWorker(source, sink, backend="cuda", device=lr, session=f"{sess}_api")
+    worker = AllreduceWorker(source, sink, backend="cuda", device=lr, session=f"{sess}_api{int(native_loop)}", native_loop=native_loop)
     ok = worker.run("127.0.0.1", port, timeout_sec=120)
     if master:
         master.join(30)
-    check("public API: master + cuda workers, rounds in order, sums exact", ok and good[0] and seen == list(range(rounds)))
+    m = worker.metrics()
+    what = "public API, round loop in C++" if native_loop else "public API"
+    check(f"{what}: master + cuda workers, every round once, sums exact",
+          ok and good[0] and sorted(seen) == list(range(rounds)) and m["rounds_delivered"] == rounds and (not native_loop or worker._direct))
     worker.close()
 
 
 only = os.environ.get("AAR_MULTI_ONLY", "")
 if only == "api":   # quick check of the public API path alone
     api_case()
+    api_case(native_loop=True)
     rdv.barrier()
     if rank == 0:
         print("MULTI-GPU RESULT:", "FAILED " + "; ".join(failures) if failures else "ALL PASSED", flush=True)
@@ -266,6 +271,7 @@ engine_case(1 << 22, 1 << 18, torch.float32, "auto", rounds=12, max_lag=3)
 threshold_case()
 out_of_order_case()
 api_case()
+api_case(native_loop=True)
 self_start_case()
 rdv.barrier()
 if rank == 0:
