@@ -27,7 +27,10 @@ class PeerBoard:
             self.mm = mmap.mmap(fd, size)
         finally:
             os.close(fd)
-        self.post(initial)
+        # A fresh incarnation: whatever an earlier job with the same session name left in this worker's word is stale (a stale
+        # word ahead of the master's clock would make every peer self-start rounds nobody asked for).  Callers create the board
+        # before the barrier that precedes the first launch, so every word has been reset before anybody reads one.
+        struct.pack_into("<q", self.mm, 8 * self.rank, initial + 1)
 
     def post(self, newest_round: int) -> None:
         """This worker has started every round up to `newest_round` (monotone)."""

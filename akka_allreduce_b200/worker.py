@@ -44,7 +44,8 @@ class AllreduceWorker:
         self.session, self.want_multicast, self.on_init = session, want_multicast, on_init
         self.zero_copy_input = zero_copy_input
         # the round loop in C++ (csrc/core/device_loop.cpp): Python is called for the source, the sink and InitWorkers only
-        self.native_loop = (os.environ.get("AAR_NATIVE_LOOP", "0") not in ("", "0")) if native_loop is None else bool(native_loop)
+        self.native_loop = (os.environ.get("AAR_NATIVE_LOOP", "1") not in ("", "0")) if native_loop is None else bool(native_loop)
+        self.drop_start = False     # fault injection: the master's StartAllreduce never reaches this worker (tests of the self-start)
         self._loop = None
         self._loop_error = None
         self._direct = False
@@ -205,6 +206,7 @@ class AllreduceWorker:
         """InitWorkers under the C++ loop: build the data plane as always, then hand the loop its handle."""
         self._loop.clear_plane()
         self._on_init(m)
+        self._loop.set_drop_start(bool(self.drop_start))   # after the caller's on_init hook, which may decide it from the id
         eng = self.engine
         plane = eng.native_plane() if hasattr(eng, "native_plane") else None
         self._direct = plane is not None   # launches go C++ -> aar_engine_enqueue_ex; otherwise through the thunks below
@@ -351,7 +353,7 @@ class AllreduceWorker:
         if isinstance(msg, core.InitWorkers):
             self._on_init(msg)
         elif isinstance(msg, core.StartAllreduce):
-            if msg.generation in (0, self.generation):
+            if not self.drop_start and msg.generation in (0, self.generation):
                 self._on_start(msg.round)
 
     def _on_init(self, m) -> None:

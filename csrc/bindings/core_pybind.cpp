@@ -279,6 +279,7 @@ PYBIND11_MODULE(_core, m) {
       .def("set_plane", &DeviceLoop::setPlane, py::arg("plane"), py::arg("id"), py::arg("generation") = 0, py::arg("master") = kNoAddress,
            py::arg("start_round") = 0)
       .def("clear_plane", &DeviceLoop::clearPlane)
+      .def("set_drop_start", &DeviceLoop::setDropStart, py::arg("drop"))
       .def("receive", [](DeviceLoop& l, const Message& msg) { l.receive(msg); }, py::call_guard<py::gil_scoped_release>())
       .def("on_start", &DeviceLoop::onStart, py::arg("round"), py::call_guard<py::gil_scoped_release>())
       .def("peer_ahead", &DeviceLoop::peerAhead, py::call_guard<py::gil_scoped_release>())

@@ -28,7 +28,7 @@ void DeviceLoop::receive(const Message& msg) {
   if (auto* init = std::get_if<InitWorkers>(&msg)) {
     if (init_) init_(*init);
   } else if (auto* start = std::get_if<StartAllreduce>(&msg)) {
-    if (start->generation == 0 || start->generation == generation_) onStart(start->round);
+    if (!dropStart_ && (start->generation == 0 || start->generation == generation_)) onStart(start->round);
   }
   // ScatterBlock / ReduceBlock never travel on the control channel of the device plane: they are NVLink stores
 }

@@ -67,6 +67,8 @@ class DeviceLoop {
   // (Re)initialisation: wipes all round state (AllreduceWorker.scala:44 "clear round info to start over").
   void setPlane(const DevicePlane& plane, int id, int generation, Address master, int startRound);
   void clearPlane() { plane_ = DevicePlane(); }
+  // Fault injection: a worker the master's StartAllreduce never reaches (it must then start its rounds because its peers have).
+  void setDropStart(bool drop) { dropStart_ = drop; }
 
   void receive(const Message& msg);   // InitWorkers -> init callback; StartAllreduce -> onStart; everything else is not ours
   void onStart(int round);            // AllreduceWorker.scala:84-104
@@ -95,6 +97,7 @@ class DeviceLoop {
   WorkerPort* port_;
   DevicePlane plane_;
   Address master_ = kNoAddress;
+  bool dropStart_ = false;
   int id_ = -1, generation_ = 0, startRound_ = 0;
   int round_ = 0;           // oldest round that has not reached the sink (the reference's `round`)
   int maxRound_ = -1, maxScattered_ = -1;

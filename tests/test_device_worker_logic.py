@@ -380,7 +380,8 @@ def test_a_later_round_completes_before_an_earlier_one_when_the_device_flushes_i
     assert master.metrics()["completions_counted"] == world * rounds
 
 
-def test_a_worker_that_never_hears_from_the_master_starts_rounds_because_its_peers_have():
+@pytest.mark.parametrize("native_loop", [False, True])
+def test_a_worker_that_never_hears_from_the_master_starts_rounds_because_its_peers_have(native_loop):
     """AllreduceWorker.scala:123-126 / AllreduceSpec.scala:106-124 (peer-ahead self-start): worker 1 drops every StartAllreduce of
     the master; it still fetches and launches every round, because worker 0 posts the rounds it starts on the shared board."""
     import os
@@ -392,27 +393,21 @@ def test_a_worker_that_never_hears_from_the_master_starts_rounds_because_its_pee
     fabric = Fabric(world, n)
     master = AllreduceMaster(world, 1.0, 1.0, 1.0, 1, n, rounds - 1, 4, pipeline_depth=1)
     master.start(60)
-    session = f"test_selfstart_{os.getpid()}"
+    session = f"test_selfstart_{os.getpid()}_{int(native_loop)}"
     sunk = [[], []]
 
     class W(FakeWorker):
-        deaf = False
-
         def _make_engine(self, m):
             self.board = PeerBoard(session, world, m.dest_id)
             return FakeEngine(self.fabric, m.dest_id, m.data_size, m.max_lag)
-
-        def _on_message(self, msg):
-            if self.deaf and isinstance(msg, core.StartAllreduce):
-                return   # the master's clock never reaches this worker
-            super()._on_message(msg)
 
     workers = []
     for i in range(world):
         def source(req, i=i):
             return AllReduceInput(np.full(n, float(i + 1), dtype=np.float32))
 
-        w = W(fabric, source, lambda out, i=i: sunk[i].append(out.iteration))
+        w = W(fabric, source, lambda out, i=i: sunk[i].append(out.iteration), native_loop=native_loop)
+        w.drop_start = i == 1   # the master's clock never reaches this worker
         workers.append(w)
     threads = [threading.Thread(target=w.run, args=("127.0.0.1", master.port, 60)) for w in workers]
     for t in threads:
@@ -427,7 +422,8 @@ def test_a_worker_that_never_hears_from_the_master_starts_rounds_because_its_pee
     assert all(s == list(range(rounds)) for s in sunk)
 
 
-def test_self_start_counts_the_rounds_it_started(tmp_path):
+@pytest.mark.parametrize("native_loop", [False, True])
+def test_self_start_counts_the_rounds_it_started(tmp_path, native_loop):
     """The same with the deaf worker chosen up front (by construction order): its self_started_rounds metric covers every round."""
     import os
 
@@ -438,22 +434,15 @@ def test_self_start_counts_the_rounds_it_started(tmp_path):
     fabric = Fabric(world, n)
     master = AllreduceMaster(world, 1.0, 1.0, 1.0, 1, n, rounds - 1, 4, pipeline_depth=1)
     master.start(60)
-    session = f"test_selfstart2_{os.getpid()}"
+    session = f"test_selfstart2_{os.getpid()}_{int(native_loop)}"
 
     class W(FakeWorker):
-        deaf = False
-
         def _make_engine(self, m):
             self.board = PeerBoard(session, world, m.dest_id)
             return FakeEngine(self.fabric, m.dest_id, m.data_size, m.max_lag)
 
-        def _on_message(self, msg):
-            if self.deaf and isinstance(msg, core.StartAllreduce):
-                return
-            super()._on_message(msg)
-
-    ws = [W(fabric, lambda req: AllReduceInput(np.ones(n, dtype=np.float32)), lambda out: None) for _ in range(world)]
-    ws[1].deaf = True
+    ws = [W(fabric, lambda req: AllReduceInput(np.ones(n, dtype=np.float32)), lambda out: None, native_loop=native_loop) for _ in range(world)]
+    ws[1].drop_start = True
     threads = [threading.Thread(target=w.run, args=("127.0.0.1", master.port, 60)) for w in ws]
     for t in threads:
         t.start()
@@ -462,3 +451,24 @@ def test_self_start_counts_the_rounds_it_started(tmp_path):
     assert master.join(30)
     assert ws[1].metrics()["self_started_rounds"] == rounds and ws[0].metrics()["self_started_rounds"] == 0
     assert ws[1].metrics()["rounds_delivered"] == rounds
+
+
+def test_peer_board_is_monotone_and_a_new_incarnation_resets_its_own_word(tmp_path):
+    from akka_allreduce_b200.parallel.board import PeerBoard
+
+    a = PeerBoard("board_unit", 2, 0, directory=str(tmp_path))
+    b = PeerBoard("board_unit", 2, 1, directory=str(tmp_path))
+    assert a.newest() == -1
+    a.post(4)
+    a.post(2)                      # never goes back
+    assert b.newest() == 4
+    b.post(6)
+    assert a.newest() == 6
+    a.close()
+    b.close()
+    # the same session name again (a job restarted on the same port): both words start over, nothing stale is read
+    a2 = PeerBoard("board_unit", 2, 0, directory=str(tmp_path))
+    b2 = PeerBoard("board_unit", 2, 1, initial=9, directory=str(tmp_path))   # a resumed master: rounds below 10 count as started
+    assert a2.newest() == 9
+    a2.close()
+    b2.close(unlink=True)
