@@ -1,9 +1,8 @@
 #!/bin/bash
 # scratch: the command list of the current gpurun call
 mkdir -p gpurun_out
-TR() { n=$1; port=$2; shift 2; timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $port "$@"; }
-for rep in 1 2; do
-for prio in default high; do
-  AAR_STREAM_PRIORITY=$prio TR 4 2999$rep bench.py --gpus 4 --steps 30 --warmup 5 --no-e2e --no-nccl 2>/dev/null | grep "^{" | python -c "
-import json,sys; d=json.loads(sys.stdin.read()); print('$prio', d['ms_per_step'], d['algo'])"
-done; done
+timeout 300 python bench.py 2> gpurun_out/AT_bench1.err | grep "^{" > gpurun_out/AT_bench1.json; python -c "
+import json; d=json.load(open('gpurun_out/AT_bench1.json')); print(d['ms_per_step'], d['clocks'], d['verified'], d['e2e']['vs_h2d_floor'])"
+tail -3 gpurun_out/AT_bench1.err
+timeout 600 python -m pytest tests -x -q -m gpu > gpurun_out/AT_gpu_suite.txt 2>&1; echo "pytest rc=$?"; tail -2 gpurun_out/AT_gpu_suite.txt
+timeout 200 python -c "import __graft_entry__ as g; g.smoke(); print('SMOKE OK')" 2>&1 | tail -1
