@@ -23,6 +23,7 @@ TARGETS = {
     "fuzz_checkpoint": ("fuzz_checkpoint.cpp", ["worker.cpp", "master.cpp", "checkpoint.cpp"]),
     "fuzz_cluster": ("fuzz_cluster.cpp", ["worker.cpp", "master.cpp", "local_cluster.cpp"]),
     "asan_cluster": ("tsan_cluster.cpp", CORE),
+    "asan_device_loop": ("tsan_device_loop.cpp", CORE + ["device_loop.cpp"]),
 }
 
 
@@ -98,3 +99,12 @@ def test_tcp_cluster_is_clean_under_asan_ubsan(exes):
     r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=280)
     assert "runtime error" not in r.stderr and "AddressSanitizer" not in r.stderr, r.stderr[-3000:]
     assert r.returncode == 0 and "finished=1 flushed=180 bad=0" in r.stdout, (r.stdout + r.stderr)[-2000:]
+
+
+def test_device_round_loop_is_clean_under_asan_ubsan(exes):
+    """csrc/core/device_loop.cpp end to end in C++ (master + 3 workers over TCP, fake device plane with its own threads,
+    out-of-order flushes, one rank that never hears StartAllreduce)."""
+    exe = exes["asan_device_loop"]
+    r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=280)
+    assert "runtime error" not in r.stderr and "AddressSanitizer" not in r.stderr, r.stderr[-3000:]
+    assert r.returncode == 0 and "finished=1 sunk=240 duplicates=0 bad=0" in r.stdout, (r.stdout + r.stderr)[-2000:]
