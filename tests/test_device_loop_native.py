@@ -248,3 +248,52 @@ def test_worker_on_the_native_loop_delivers_out_of_order():
         assert sorted(lg.sunk) == list(range(rounds))
         assert lg.sunk.index(1) < lg.sunk.index(0), lg.sunk
         assert w.metrics()["rounds_out_of_order"] >= 1
+
+
+# ---------------------------------------------------------------------------------------------- properties
+def test_random_schedules_keep_the_loop_invariants():
+    """Random interleavings of StartAllreduce, board updates, device flushes and deliveries (hypothesis): every round is fetched
+    once and in order, launched once, sunk once and only after the device flushed it, never relaunched into a ring slot whose
+    previous round has not reached the sink, CompleteAllreduce follows every sink, and `round` is the oldest round not yet sunk."""
+    from hypothesis import given, settings
+    from hypothesis import strategies as st
+
+    ops = st.lists(st.tuples(st.sampled_from(["start", "board", "flush", "deliver"]), st.integers(0, 40)), min_size=1, max_size=60)
+
+    @settings(max_examples=150, deadline=None)
+    @given(slots=st.integers(1, 4), polls=st.integers(1, 3), start_round=st.integers(0, 5), ops=ops)
+    def run(slots, polls, start_round, ops):
+        fp = FakePlane(slots=slots, max_lag=slots - 1, flush_after_polls=polls)
+        loop, rec = make_loop(fp, start_round=start_round)
+        board = SimpleNamespace(newest=start_round - 1)
+        loop.set_board(lambda r: None, lambda: board.newest)
+        top = start_round - 1
+        for op, v in ops:
+            if op == "start":
+                top = max(top, min(start_round + v, top + 6))     # the master's clock moves at most a few rounds at a time
+                loop.on_start(top)
+            elif op == "board":
+                board.newest = max(board.newest, min(start_round + v, top + 3))
+                loop.peer_ahead()
+                top = max(top, board.newest)
+            elif op == "flush" and fp.enqueued:
+                fp.flushed.add(fp.enqueued[v % len(fp.enqueued)])
+            else:
+                loop.deliver_flushed()
+        # invariants
+        launched = list(range(start_round, loop.max_scattered + 1))
+        assert rec.fetched == launched and fp.enqueued == launched
+        sunk = [r for r, _ in rec.sunk]
+        assert len(sunk) == len(set(sunk)) and all(r in fp.flushed for r in sunk)
+        assert all(slot == r % slots for r, slot in rec.sunk)
+        for r in launched:
+            if r - slots >= start_round:
+                assert fp.events.index(("sink", r - slots)) < fp.events.index(("enq", r))
+        assert [m.round for _, m in rec.sent] == sunk
+        not_sunk = [r for r in launched if r not in sunk]
+        assert loop.round == (min(not_sunk) if not_sunk else loop.max_scattered + 1)
+        assert loop.completed == sorted(r for r in sunk if r > loop.round)
+        assert loop.max_round == top and loop.max_scattered == top
+        assert loop.stats()["rounds_delivered"] == len(sunk)
+
+    run()
