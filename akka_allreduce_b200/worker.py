@@ -296,10 +296,9 @@ class AllreduceWorker:
 
     def _sync_from_loop(self) -> None:
         """Mirror the loop's state into the attributes metrics() and the tests read."""
-        lp = self._loop
-        st = lp.stats()
-        self.round, self.max_round, self.max_scattered = lp.round, lp.max_round, lp.max_scattered
-        self.completed = set(lp.completed)
+        st = self._loop.stats()   # one consistent snapshot (metrics() may be called from another thread while the loop runs)
+        self.round, self.max_round, self.max_scattered = st["round"], st["max_round"], st["max_scattered"]
+        self.completed = set(st["completed"])
         self.delivered = self.start_round + st["rounds_delivered"]
         self.out_of_order, self.self_starts, self.rounds_forced = st["rounds_out_of_order"], st["self_started_rounds"], st["rounds_forced"]
         self.lag_hist = dict(st["lag_hist"])

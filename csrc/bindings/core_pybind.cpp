@@ -293,10 +293,19 @@ PYBIND11_MODULE(_core, m) {
       .def_property_readonly("max_round", &DeviceLoop::maxRound)
       .def_property_readonly("max_scattered", &DeviceLoop::maxScattered)
       .def_property_readonly("start_round", &DeviceLoop::startRound)
-      .def_property_readonly("completed", [](const DeviceLoop& l) { return std::vector<int>(l.completed().begin(), l.completed().end()); })
+      .def_property_readonly("completed",
+                             [](const DeviceLoop& l) {
+                               const std::set<int> c = l.completed();
+                               return std::vector<int>(c.begin(), c.end());
+                             })
       .def("stats", [](const DeviceLoop& l) {
-        const DeviceLoopStats& s = l.stats();
+        const DeviceLoop::Snapshot snap = l.snapshot();   // one consistent view, safe while the loop runs in another thread
+        const DeviceLoopStats& s = snap.stats;
         py::dict d;
+        d["round"] = snap.round;
+        d["max_round"] = snap.maxRound;
+        d["max_scattered"] = snap.maxScattered;
+        d["completed"] = std::vector<int>(snap.completed.begin(), snap.completed.end());
         d["rounds_delivered"] = s.delivered;
         d["rounds_out_of_order"] = s.outOfOrder;
         d["self_started_rounds"] = s.selfStarts;

@@ -13,6 +13,7 @@ namespace aar {
 
 void DeviceLoop::setPlane(const DevicePlane& plane, int id, int generation, Address master, int startRound) {
   if (!plane.valid() || plane.slots < 1) throw std::invalid_argument("DeviceLoop: incomplete data plane");
+  std::lock_guard<std::mutex> g(mu_);
   plane_ = plane;
   id_ = id;
   generation_ = generation;
@@ -35,7 +36,10 @@ void DeviceLoop::receive(const Message& msg) {
 
 void DeviceLoop::onStart(int round) {
   if (!plane_.valid()) return;   // before InitWorkers: nothing to start (the master re-sends after initialisation)
-  if (round > maxRound_) maxRound_ = round;
+  if (round > maxRound_) {
+    std::lock_guard<std::mutex> g(mu_);
+    maxRound_ = round;
+  }
   plane_.doorbell(plane_.engine, maxRound_);   // kernels more than maxLag behind stop waiting: the catch-up loop without a host round-trip
   if (boardPost_) boardPost_(maxRound_);
   const int L = plane_.slots;
@@ -50,6 +54,7 @@ void DeviceLoop::onStart(int round) {
     const int rc = plane_.enqueue(plane_.engine, r, reinterpret_cast<const void*>(b.input), reinterpret_cast<void*>(b.output),
                                   reinterpret_cast<int*>(b.counts), plane_.extraFlags, reinterpret_cast<void*>(b.stream), 0ull);
     if (rc != 0) throw std::runtime_error("DeviceLoop: enqueue of round " + std::to_string(r) + " failed with code " + std::to_string(rc));
+    std::lock_guard<std::mutex> g(mu_);
     ++stats_.launched;
     maxScattered_ = r;
   }
@@ -59,7 +64,10 @@ bool DeviceLoop::peerAhead() {
   if (!boardNewest_ || !plane_.valid()) return false;
   const int newest = boardNewest_();
   if (newest <= maxRound_) return false;
-  stats_.selfStarts += newest - maxRound_;
+  {
+    std::lock_guard<std::mutex> g(mu_);
+    stats_.selfStarts += newest - maxRound_;
+  }
   onStart(newest);
   return true;
 }
@@ -72,15 +80,16 @@ int DeviceLoop::deliverFlushed(bool block) {
     for (int r = round_; r <= maxScattered_; ++r) {
       if (r < round_ || completed_.count(r)) continue;   // round_ moves inside this loop
       if (!plane_.flushed(plane_.engine, r)) continue;
+      sink_(r, r % plane_.slots);
+      if (port_) port_->send(master_, CompleteAllreduce{id_, r, generation_});
+      ++progressed;
+      std::lock_guard<std::mutex> g(mu_);
       const int lag = maxRound_ - r;
       ++stats_.lagHist[lag];
       if (lag > plane_.maxLag) ++stats_.forced;
       if (r != round_) ++stats_.outOfOrder;
-      sink_(r, r % plane_.slots);
-      if (port_) port_->send(master_, CompleteAllreduce{id_, r, generation_});
       completed_.insert(r);
       ++stats_.delivered;
-      ++progressed;
       while (completed_.count(round_)) {   // AllreduceWorker.scala:261-267: past every already-completed round
         completed_.erase(round_);
         ++round_;

@@ -11,6 +11,7 @@
 #include <cstdint>
 #include <functional>
 #include <map>
+#include <mutex>
 #include <set>
 
 #include "messages.h"
@@ -75,18 +76,28 @@ class DeviceLoop {
   bool peerAhead();                   // AllreduceWorker.scala:123-126 through the board; true if rounds were started
   int deliverFlushed(bool block);     // AllreduceWorker.scala:253-268; returns rounds delivered
   void drain();                       // job over: ring the doorbell far ahead, wait for the device, deliver what flushed
-  bool busy() const { return plane_.valid() && stats_.delivered + startRound_ < (long long)maxScattered_ + 1; }
+  bool busy() const { return plane_.valid() && stats_.delivered + startRound_ < (long long)maxScattered_ + 1; }   // loop thread only
   // Serve until the master says Shutdown / its link closes (true) or the timeout expires (false).
   bool run(WorkerNode& node, double timeoutSec);
 
-  int id() const { return id_; }
-  int generation() const { return generation_; }
-  int round() const { return round_; }
-  int maxRound() const { return maxRound_; }
-  int maxScattered() const { return maxScattered_; }
-  int startRound() const { return startRound_; }
-  const std::set<int>& completed() const { return completed_; }
-  const DeviceLoopStats& stats() const { return stats_; }
+  // Observers: safe from any thread while the loop runs (a metrics endpoint reads them from its own thread).
+  struct Snapshot {
+    int id, generation, round, maxRound, maxScattered, startRound;
+    std::set<int> completed;
+    DeviceLoopStats stats;
+  };
+  Snapshot snapshot() const {
+    std::lock_guard<std::mutex> g(mu_);
+    return Snapshot{id_, generation_, round_, maxRound_, maxScattered_, startRound_, completed_, stats_};
+  }
+  int id() const { return snapshot().id; }
+  int generation() const { return snapshot().generation; }
+  int round() const { return snapshot().round; }
+  int maxRound() const { return snapshot().maxRound; }
+  int maxScattered() const { return snapshot().maxScattered; }
+  int startRound() const { return snapshot().startRound; }
+  std::set<int> completed() const { return snapshot().completed; }
+  DeviceLoopStats stats() const { return snapshot().stats; }
 
  private:
   Source source_;
@@ -103,6 +114,7 @@ class DeviceLoop {
   int maxRound_ = -1, maxScattered_ = -1;
   std::set<int> completed_;  // rounds >= round_ that have reached the sink (the reference's `completed`)
   DeviceLoopStats stats_;
+  mutable std::mutex mu_;    // guards the round state and the counters against observers; never held across a callback
 };
 
 }  // namespace aar

@@ -2,7 +2,8 @@
 // one master and three workers over real TCP sockets; each worker's data plane is a C function table over an in-process
 // "fabric" whose completion words are written by a separate device thread per rank (as the GPU writes host-mapped words),
 // in an order that lets later rounds flush before earlier ones.  One worker never hears StartAllreduce (drop-start fault
-// injection) and must follow its peers through the board.  Built with -fsanitize=thread / address,undefined by
+// injection) and must follow its peers through the board; an observer thread per worker reads the loop's state while it runs
+// (what a metrics endpoint does).  Built with -fsanitize=thread / address,undefined by
 // tests/test_tsan.py and tests/test_sanitizers.py.
 #include <algorithm>
 #include <atomic>
@@ -158,7 +159,20 @@ int main() {
                       });
         if (!device.joinable()) device = std::thread(deviceThread, &plane);
       });
+      // a metrics endpoint reading the loop's state from its own thread while the loop runs
+      std::atomic<bool> watching{true};
+      std::atomic<long> observed{0};
+      std::thread observer([&] {
+        while (watching.load()) {
+          const DeviceLoop::Snapshot s = loop.snapshot();
+          if (s.round > s.maxScattered + 1 || (long long)s.completed.size() > kSlots) ++bad;
+          observed += s.stats.delivered >= 0;
+          std::this_thread::sleep_for(std::chrono::microseconds(20));
+        }
+      });
       loop.run(node, 60.0);
+      watching.store(false);
+      observer.join();
       plane.stop.store(true);
       if (device.joinable()) device.join();
       outOfOrder += loop.stats().outOfOrder;
