@@ -213,8 +213,10 @@ class AllreduceWorker:
         if plane is None:
             plane = self._python_plane(eng)
         self._loop.set_plane(plane, self.id, self.generation, m.master, self.start_round)
-        if self.board is not None:
+        if self.board is not None and len(m.workers) > 1:   # nobody to be ahead of in a world of one
             self._loop.set_board(self.board.post, self.board.newest)
+        else:
+            self._loop.clear_board()
 
     def _python_plane(self, eng):
         """A data plane that only exists in Python (the launch path with AAR_NATIVE_ENGINE=0, fake engines in tests), wrapped in C

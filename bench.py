@@ -385,6 +385,7 @@ def run_e2e(a, rank, world, local_rank, dtype, nbytes, rdv, max_over_ranks, glob
     host_counts = None
     host_head = torch.empty(1024, dtype=dtype).pin_memory()
     copy_stream = torch.cuda.Stream(device=dev)
+    read_stream = torch.cuda.Stream(device=dev)
     marks = {}
     bytes_in = nbytes
     state = {"d2h": 0}
@@ -400,9 +401,13 @@ def run_e2e(a, rank, world, local_rank, dtype, nbytes, rdv, max_over_ranks, glob
         nonlocal host_counts
         if host_counts is None:
             host_counts = torch.empty(out.count.numel(), dtype=torch.int32).pin_memory()
-        host_counts.copy_(out.count, non_blocking=True)
-        host_head.copy_(out.data[:1024], non_blocking=True)
-        torch.cuda.current_stream(dev).synchronize()
+        # The worker calls the sink after the host has SEEN the round flushed (completion word written by the round's last CTA
+        # behind a system fence), so the result may be read on any stream.  A stream of its own: on the current stream the
+        # read-back would queue behind the NEXT round's host -> device copy, which the source has already enqueued there.
+        with torch.cuda.stream(read_stream):
+            host_counts.copy_(out.count, non_blocking=True)
+            host_head.copy_(out.data[:1024], non_blocking=True)
+        read_stream.synchronize()
         state["d2h"] = host_counts.numel() * 4 + host_head.numel() * host_head.element_size()
         if int(host_counts.min()) != N:
             raise RuntimeError(f"round {out.iteration}: contributor counts {host_counts.tolist()} != {N}")
@@ -470,8 +475,8 @@ def run_e2e(a, rank, world, local_rank, dtype, nbytes, rdv, max_over_ranks, glob
     return {"value": N * nbytes / (ms * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": ms, "rounds_per_sec": 1e3 / ms,
             "h2d_bytes_per_step": bytes_in, "d2h_bytes_per_step": state["d2h"],
             "path": "AllreduceMaster(pipeline_depth=maxLag) + AllreduceWorker(backend=cuda); source: pinned host -> device copy of the whole "
-                    "input per round; sink: contributor counts + a 1024-element slice read back per round (the reduced vector itself stays on "
-                    "the device, where the next consumer is)", "algo": info.get("algo", a.algo),
+                    "input per round (copy stream); sink: contributor counts + a 1024-element slice read back per round on a stream of its own, "
+                    "synchronised every round (the reduced vector itself stays on the device, where the next consumer is)", "algo": info.get("algo", a.algo),
             "rounds_in_flight": info.get("rounds_in_flight", 1),
             "h2d_floor_ms_per_step": floor_ms, "vs_h2d_floor": ms / floor_ms if floor_ms else None,
             "nccl_same_source_sink_ms_per_step": nccl_ms, "vs_nccl": (nccl_ms / ms) if nccl_ms else None}

@@ -276,6 +276,7 @@ PYBIND11_MODULE(_core, m) {
                    return newest().cast<int>();
                  });
            })
+      .def("clear_board", [](DeviceLoop& l) { l.setBoard(nullptr, nullptr); })
       .def("set_plane", &DeviceLoop::setPlane, py::arg("plane"), py::arg("id"), py::arg("generation") = 0, py::arg("master") = kNoAddress,
            py::arg("start_round") = 0)
       .def("clear_plane", &DeviceLoop::clearPlane)

@@ -11,6 +11,16 @@
 
 namespace aar {
 
+namespace {
+inline void cpuRelax() {
+#if defined(__x86_64__) || defined(__i386__)
+  __builtin_ia32_pause();
+#elif defined(__aarch64__)
+  asm volatile("yield");
+#endif
+}
+}  // namespace
+
 void DeviceLoop::setPlane(const DevicePlane& plane, int id, int generation, Address master, int startRound) {
   if (!plane.valid() || plane.slots < 1) throw std::invalid_argument("DeviceLoop: incomplete data plane");
   std::lock_guard<std::mutex> g(mu_);
@@ -116,14 +126,20 @@ bool DeviceLoop::run(WorkerNode& node, double timeoutSec) {
   node.setHandler([this](const Message& m) { receive(m); });
   unsigned idle = 0;
   while (!node.shutdownRequested() && Clock::now() < deadline) {
-    // Nothing in flight: sleep in poll() until the master (or a heartbeat deadline) wakes us.  Rounds in flight: look at the
-    // socket without blocking and at the completion words; after a while without progress, stop burning the core.
+    // Nothing in flight: sleep in poll() until the master (or a heartbeat deadline) wakes us.  Rounds in flight: watch the
+    // completion words closely for a short while (small rounds finish within microseconds), then back off -- the socket and the
+    // board are looked at every eighth pass, with a pause of about two microseconds between passes -- so that a long round does
+    // not cost a core hammering system calls.
     const bool inFlight = busy();
-    const int handled = node.poll(inFlight ? 0 : 1);
-    const bool started = peerAhead();
+    const bool lookAround = !inFlight || idle < 64 || (idle & 7u) == 0;
+    const int handled = lookAround ? node.poll(inFlight ? 0 : 1) : 0;
+    const bool started = lookAround && peerAhead();
     const int delivered = deliverFlushed(false);
-    if (handled || started || delivered) idle = 0;
-    else if (inFlight && ++idle > 2000) sched_yield();
+    if (handled || started || delivered) {
+      idle = 0;
+    } else if (inFlight && ++idle >= 64) {
+      for (int i = 0; i < 48; ++i) cpuRelax();
+    }
   }
   drain();
   return node.shutdownRequested();
