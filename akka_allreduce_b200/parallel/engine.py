@@ -45,6 +45,33 @@ def selector_table() -> dict:
     return _TABLE
 
 
+def pick_algo(P: int, elem_size: int, nbytes: int, *, bulk_ok: bool, nvls_ok: bool, oneshot_ok: bool, normalize: bool = False,
+              table: dict | None = None) -> tuple[str, int]:
+    """`algo="auto"` as a pure function: (kernel family, role split) for a message of `nbytes` at world size P.  First row of the
+    measured table that covers the size AND whose kernel this layout / these thresholds can run; without a usable row, small
+    messages take the one-hop kernel and the rest the bulk engine kernels.  bulk_ok: 16-byte aligned geometry; nvls_ok: multicast
+    mapping + staging + full thresholds + no exact-quorum policy (the switch sums every bound GPU); oneshot_ok: the layout has
+    one-shot buffers."""
+    if P == 1:
+        return ("bulk" if bulk_ok else "twoshot"), 0
+    rows = (selector_table() if table is None else table).get(str(P), {}).get("fp32" if elem_size == 4 else "bf16", [])
+    for max_bytes, name, split in rows:
+        if nbytes > max_bytes:
+            continue
+        if name == "oneshot" and not oneshot_ok:
+            continue
+        if (name in ("nvls_bulk", "nvls_onehop") and not nvls_ok) or (name == "nvls" and not (nvls_ok and not normalize)):
+            continue
+        if name in ("bulk", "nvls_bulk", "nvls_onehop") and not bulk_ok:
+            continue
+        return name, int(split)
+    if oneshot_ok and nbytes <= ONESHOT_MAX_BYTES:
+        return "oneshot", 0
+    if nvls_ok and P >= 8:
+        return "nvls_bulk", 0
+    return ("bulk" if bulk_ok else "pipelined"), 0
+
+
 class RoundEngine:
     def __init__(self, rank: int, region_ptrs: Sequence[int], layout: L.AarLayout, *, th_reduce: float = 1.0, th_complete: float = 1.0,
                  normalize: bool = False, exact_quorum: bool = False, timeout_ms: float = 0.0, device: int = 0, grid: int = 0,
@@ -179,29 +206,13 @@ class RoundEngine:
         bulk_ok = self._bulk_geometry()
         nvls_ok = bool(self.mc_ptr and lay.stageOff and bulk_ok and self.full_thresholds and not exact_quorum)   # normalisation: sum / P in registers
         if algo == "auto":
-            if lay.P == 1:
-                return "bulk" if bulk_ok else "twoshot"
-            rows = selector_table().get(str(lay.P), {}).get("fp32" if lay.elemSize == 4 else "bf16", [])
-            for max_bytes, name, split in rows:
-                if nbytes > max_bytes:
-                    continue
-                if name == "oneshot" and not lay.oneshotOff:
-                    continue
-                if (name in ("nvls_bulk", "nvls_onehop") and not nvls_ok) or (name == "nvls" and not (nvls_ok and not normalize)):
-                    continue
-                if name in ("bulk", "nvls_bulk", "nvls_onehop") and not bulk_ok:
-                    continue
-                if name == "bulk":
-                    self.bulk_split = int(split)
-                elif name == "nvls_bulk":
-                    self.nvls_bulk_split = int(split)
-                return name
-            # no table row: small messages take the one-hop kernel, the rest the bulk engine kernels
-            if lay.oneshotOff and nbytes <= ONESHOT_MAX_BYTES:
-                return "oneshot"
-            if nvls_ok and lay.P >= 8:
-                return "nvls_bulk"
-            return "bulk" if bulk_ok else "pipelined"
+            name, split = pick_algo(lay.P, lay.elemSize, nbytes, bulk_ok=bulk_ok, nvls_ok=nvls_ok, oneshot_ok=bool(lay.oneshotOff),
+                                    normalize=normalize)
+            if name == "bulk":
+                self.bulk_split = split
+            elif name == "nvls_bulk":
+                self.nvls_bulk_split = split
+            return name
         if algo == "oneshot" and not lay.oneshotOff:
             raise ValueError("algo=oneshot needs a layout with one-shot buffers")
         if algo in _IN_SWITCH and not (self.mc_ptr and lay.stageOff):
