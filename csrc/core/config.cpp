@@ -391,8 +391,9 @@ AllreduceSettings AllreduceSettings::fromConfig(const Config& c) {
   if (s.quorumPolicy != "all-arrived" && s.quorumPolicy != "exact")
     throw std::runtime_error("config: allreduce.quorum-policy must be all-arrived or exact");
   bool algoOk = false;
-  for (const char* a : {"auto", "oneshot", "twoshot", "pipelined", "nvls"}) algoOk = algoOk || s.algo == a;
-  if (!algoOk) throw std::runtime_error("config: allreduce.algo must be one of auto, oneshot, twoshot, pipelined, nvls");
+  for (const char* a : {"auto", "bulk", "nvls_bulk", "nvls_onehop", "oneshot", "twoshot", "pipelined", "nvls"}) algoOk = algoOk || s.algo == a;
+  if (!algoOk)
+    throw std::runtime_error("config: allreduce.algo must be one of auto, bulk, nvls_bulk, nvls_onehop, oneshot, twoshot, pipelined, nvls");
   for (float th : {m.thAllreduce, m.thReduce, m.thComplete})
     if (!(th > 0.f && th <= 1.f)) throw std::runtime_error("config: thresholds must be in (0, 1]");
   if (s.dtype != "fp32" && s.dtype != "bf16") throw std::runtime_error("config: allreduce.dtype must be fp32 or bf16");

@@ -130,3 +130,14 @@ def test_settings_reject_out_of_range_and_unknown_values():
             settings(body)
     s = settings("start-round = 7\n algo = pipelined\n quorum-policy = exact\n data-size = 0")
     assert s.master.start_round == 7 and s.algo == "pipelined" and s.quorum_policy == "exact" and s.master.data_size == 0
+
+
+def test_every_kernel_family_the_engine_knows_is_accepted_by_the_config():
+    """allreduce.algo is handed to RoundEngine(algo=...): the config must accept exactly the names the engine does."""
+    from akka_allreduce_b200.parallel.engine import _ALGO_CODE
+
+    for name in ["auto", *sorted(_ALGO_CODE)]:
+        s = core.AllreduceSettings.from_config(core.Config.parse_string("allreduce { algo = " + name + " }"))
+        assert s.algo == name
+    with pytest.raises(Exception, match="nvls_onehop"):
+        core.AllreduceSettings.from_config(core.Config.parse_string("allreduce { algo = ring }"))
