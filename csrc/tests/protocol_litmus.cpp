@@ -64,6 +64,7 @@ struct Config {
   bool eagerDecision = true;       // eager gather: one decision per (round, chunk) shared by all CTAs (proposed fix)
   int nvls = 0;                    // 1 = NVLS path as shipped (staging slots without flow control, the switch sums every rank),
                                    // 2 = strict NVLS (staging obeys the slot flow control, incomplete decisions are not published)
+                                   // 3 = in-switch round in one hop (nvlsOneHopKernel), normal mode only
   bool oneshot = false;            // K5: every rank pushes its whole vector to every peer and sums the arrived set locally
   bool elide = false;              // a rank that is a whole round late skips work nobody will read (AAR_FLAG_ELIDE_LATE)
   int spinBudget = 1 << 30;        // stand-in for the %globaltimer deadline of a wait (default: timeoutNs = 0, unbounded)
@@ -493,6 +494,70 @@ void verifyOneshot(World& w, int rank, int round) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------- in-switch round in one hop
+// nvlsOneHopKernel (csrc/cuda/aar_bulk.cu): stage CTAs copy the input into this rank's staging slot once EVERY rank has retired the
+// slot's previous tenant (all of them read it), the CTA that finishes the last tile flags every rank; the other CTAs wait for all
+// P flags and sum the P staging slots (the switch's reads of peer memory) straight into the output.  Normal mode only: the
+// kernel's give-up decision is per CTA, so a forced round is outside what this model checks (docs/PROTOCOL.md).
+void phaseOneHop(World& w, int rank, int round, int cta, int nctas, std::mt19937& rng) {
+  const Config& c = w.cfg;
+  const int slot = round % c.L;
+  const uint32_t epoch = (uint32_t)round + 1;
+  Region& my = *w.region[rank];
+  const int tile = c.chunkLen / c.S, Tn = c.dataSize() / tile;
+  const int nA = std::max(1, nctas / 2);
+  if (cta < nA) {
+    bool go = true;
+    for (int d = 0; d < c.P; ++d) go = scatterDecision(w, rank, round, d) && go;
+    if (!go) return;
+    for (int t = cta; t < Tn; t += nA) {
+      jitter(rng);
+      float* dst = my.stage.data() + (size_t)slot * c.dataSize() + (size_t)t * tile;
+      for (int k = 0; k < tile; ++k) dst[k] = w.input[round][rank][(size_t)t * tile + k];
+      std::atomic<uint32_t>& ctr = my.k1Ctr[(size_t)slot * c.P * c.C];
+      if (ctr.fetch_add(1, std::memory_order_acq_rel) + 1 == (uint32_t)Tn) {
+        ctr.store(0, std::memory_order_relaxed);
+        for (int i = 0; i < c.P; ++i) w.region[(i + rank) % c.P]->osflag[(size_t)slot * c.P + rank].store(epoch, std::memory_order_release);
+      }
+    }
+    return;
+  }
+  int spins = 0;
+  for (;;) {
+    int have = 0;
+    for (int src = 0; src < c.P; ++src) have += my.osflag[(size_t)slot * c.P + src].load(std::memory_order_acquire) == epoch;
+    if (have == c.P) break;
+    if ((++spins & 31) == 0 && spins > c.spinBudget) {
+      w.failures++;   // normal mode: nobody may give up
+      return;
+    }
+    std::this_thread::yield();
+  }
+  if (cta == nA)
+    for (int i = 0; i < c.P * c.C; ++i) my.outCounts[slot][i] = c.P;
+  for (int t = cta - nA; t < Tn; t += nctas - nA) {
+    jitter(rng);
+    for (int k = 0; k < tile; ++k) {
+      const size_t e = (size_t)t * tile + k;
+      float acc = 0.f;
+      for (int src = 0; src < c.P; ++src) acc += w.region[src]->stage[(size_t)slot * c.dataSize() + e];   // multimem.ld_reduce
+      my.output[slot][e] = acc;
+    }
+  }
+}
+
+void verifyOneHop(World& w, int rank, int round) {
+  const Config& c = w.cfg;
+  const int slot = round % c.L;
+  Region& my = *w.region[rank];
+  if (my.outCounts[slot][0] != c.P) w.failures++;
+  for (int e = 0; e < c.dataSize(); ++e) {
+    float want = 0.f;
+    for (int src = 0; src < c.P; ++src) want += w.input[round][src][e];
+    if (my.output[slot][e] != want) w.failures++;
+  }
+}
+
 // K6: last CTA of the kernel retires the slot.  Retirement is per ring slot (peers' flow control reads slotBase[slot][me]), so
 // with two rounds in flight round r+1 may retire before round r; peerBase[me] is only raised
 void retire(World& w, int rank, int round, int nctas) {
@@ -590,7 +655,9 @@ int main(int argc, char** argv) {
               while ((int)w.region[rank]->slotFlushed[q % cf.L].load(std::memory_order_acquire) < q + 1) std::this_thread::yield();
             if (rank == (round % cf.P) && (rng() % 3 == 0)) std::this_thread::sleep_for(std::chrono::microseconds(300));  // straggler
             if (cf.lagger && rank == 0 && cta == 0) std::this_thread::sleep_for(std::chrono::microseconds(1500 + rng() % 2000));
-            if (cf.oneshot) {
+            if (cf.nvls == 3) {
+              phaseOneHop(w, rank, round, cta, cf.G, rng);
+            } else if (cf.oneshot) {
               phaseOneshot(w, rank, round, cta, cf.G, rng);
             } else {
               phaseScatter(w, rank, round, cta, cf.G, rng);
@@ -602,7 +669,8 @@ int main(int argc, char** argv) {
             if (cta == 0) {
               // host side: wait for the completion word, then consume this round's output slot before it is reused
               while ((int)w.region[rank]->slotFlushed[round % cf.L].load(std::memory_order_acquire) < round + 1) std::this_thread::yield();
-              if (cf.oneshot) verifyOneshot(w, rank, round);
+              if (cf.nvls == 3) verifyOneHop(w, rank, round);
+              else if (cf.oneshot) verifyOneshot(w, rank, round);
               else verifyRound(w, rank, round);
               w.region[rank]->consumed[round % cf.L].store(round, std::memory_order_release);
             }

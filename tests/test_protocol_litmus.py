@@ -129,3 +129,19 @@ def test_oneshot_path_as_shipped_is_race_free_also_in_degraded_mode(litmus, cfg)
     r = run(litmus, *cfg)
     assert "WARNING: ThreadSanitizer" not in r.stderr, r.stderr[-3000:]
     assert r.returncode == 0 and "failures=0" in r.stdout, r.stdout + r.stderr[-1000:]
+
+
+# seed, P, rounds, threshold %, maxLag, overlap, CTAs, fc, lagger, eagerDecision, spinBudget, elide, nvls (3 = one hop)
+ONE_HOP = [(1, 4, 14, 100, 1, 1, 4, 0, 0, 0, 1 << 30, 0, 3), (2, 2, 16, 100, 1, 1, 4, 0, 0, 0, 1 << 30, 0, 3),
+           (3, 3, 12, 100, 2, 1, 5, 0, 0, 0, 1 << 30, 0, 3), (4, 5, 10, 100, 1, 0, 4, 0, 0, 0, 1 << 30, 0, 3),
+           (5, 4, 12, 100, 3, 1, 6, 0, 0, 0, 1 << 30, 0, 3)]
+
+
+@pytest.mark.parametrize("cfg", ONE_HOP)
+def test_one_hop_in_switch_round_is_race_free_in_normal_mode(litmus, cfg):
+    """nvlsOneHopKernel: every rank reads every rank's staging slot, so a slot may only be restaged once ALL ranks retired its
+    previous tenant; one flag per source after the last staged tile; whole-vector sum into the local output.  Two rounds in
+    flight, rotating stragglers.  (A forced round is outside the model: the kernel's give-up is decided per CTA.)"""
+    r = run(litmus, *cfg)
+    assert "WARNING: ThreadSanitizer" not in r.stderr, r.stderr[-3000:]
+    assert r.returncode == 0 and "failures=0" in r.stdout, r.stdout + r.stderr[-1000:]
