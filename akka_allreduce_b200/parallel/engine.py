@@ -121,6 +121,9 @@ class RoundEngine:
         if self.algo == "bulk" and layout.P > 1 and os.environ.get("AAR_SELF_DIRECT", "1") not in ("", "0"):
             p.flags |= L.FLAG_SELF_DIRECT
         p.timeoutNs = int(timeout_ms * 1e6)
+        if self.algo == "nvls_onehop" and (timeout_ms > 0 or not self.full_thresholds):
+            # its give-up is decided per CTA, not once per round (docs/PROTOCOL.md): no setting in which a round can be forced
+            raise ValueError("algo=nvls_onehop is offered for thresholds 1.0 without a spin timeout only")
         dev_addr = C.cast(dev, C.c_void_p).value
         p.doorbell = dev_addr            # word 0: newest round announced by the master
         p.hostDone = dev_addr + 4 * _DONE_WORD0   # one word per ring slot: round + 1 of the last round flushed in that slot
