@@ -121,9 +121,11 @@ class RoundEngine:
         if self.algo == "bulk" and layout.P > 1 and os.environ.get("AAR_SELF_DIRECT", "1") not in ("", "0"):
             p.flags |= L.FLAG_SELF_DIRECT
         p.timeoutNs = int(timeout_ms * 1e6)
-        if self.algo == "nvls_onehop" and (timeout_ms > 0 or not self.full_thresholds):
-            # its give-up is decided per CTA, not once per round (docs/PROTOCOL.md): no setting in which a round can be forced
-            raise ValueError("algo=nvls_onehop is offered for thresholds 1.0 without a spin timeout only")
+        if self.algo == "nvls_onehop" and not self.full_thresholds:
+            # in-switch (every rank is summed), and its give-up is decided per CTA, not once per round (docs/PROTOCOL.md): only
+            # where no round is ever forced in normal operation.  A spin timeout stays allowed as a liveness guard -- a round that
+            # runs into it sets the status bits, so its output is flagged whatever it contains.
+            raise ValueError("algo=nvls_onehop is offered for thresholds 1.0 only")
         dev_addr = C.cast(dev, C.c_void_p).value
         p.doorbell = dev_addr            # word 0: newest round announced by the master
         p.hostDone = dev_addr + 4 * _DONE_WORD0   # one word per ring slot: round + 1 of the last round flushed in that slot
